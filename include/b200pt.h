@@ -1,0 +1,152 @@
+/* b200pt — C-ABI of the B200-native path tracer (libb200pt.so).
+ *
+ * This is the drop-in boundary for the reference's render hot path.  The reference has no FFI layer;
+ * its boundary is the C++ class `SampleRenderer` (HelloPathtracing_sv4_vmv23/SimplePathtracer.h:45-188).
+ * Every entry point below names the reference member / call site it replaces.  The C++ class in
+ * include/ref_api/SimplePathtracer.h forwards 1:1 to these functions; Python binds them with ctypes.
+ *
+ * Conventions: plain pointers and sizes only (no torch / STL types); every function returns 0 on
+ * success and -1 on failure, with the message retrievable through b200pt_last_error() (thread-local).
+ * One context per GPU, externally synchronised (the reference is single-threaded).
+ * There is NO CPU fallback: creating a context without a usable CUDA device fails.
+ */
+#ifndef B200PT_H
+#define B200PT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+struct LaunchParams;               /* include/ref_api/LaunchParams.h — 312-byte reference layout */
+struct Material;                   /* include/ref_api/Material.h     — 104-byte reference layout */
+typedef struct b200pt_ctx b200pt_ctx;
+
+/* ---- render configuration: the reference's compile-time switches as run-time fields --------------
+ * (SURVEY.md §5 "config / flag system").  Presets reproduce each variant's literals. */
+enum { B200PT_SCHEDULE_AS_GIVEN = 0,   /* one launch, every LaunchParams field as the caller set it      */
+       B200PT_SCHEDULE_UNIFORM  = 1,   /* FOV_OFF branch, sv4/SimplePathtracer.cpp:85-131                */
+       B200PT_SCHEDULE_FOVEATED = 2 }; /* 3-pass sv4 schedule, sv4/SimplePathtracer.cpp:132-216          */
+enum { B200PT_SHADOW_ANY_HIT = 0,      /* orig: TERMINATE_ON_FIRST_HIT, orig/deviceProgram.cu:198        */
+       B200PT_SHADOW_CULL_BACK = 1 };  /* sv3/sv4: CULL_BACK_FACING_TRIANGLES, sv4/deviceProgram.cu:240  */
+enum { B200PT_DISPLAY_SRGB = 0,        /* make_color(accum), orig/deviceProgram.cu:467                   */
+       B200PT_DISPLAY_REINHARD = 1 };  /* make_color(reinhard(accum*exposure, 1)), sv4/deviceProgram.cu:557-568 */
+enum { B200PT_ACCUM_LERP = 0,          /* running mean lerp(prev, clamp(cur,0,10), 1/(n+1)), sv4/deviceProgram.cu:545-553 */
+       B200PT_ACCUM_SUM  = 1 };        /* multi-GPU sample split: accum_buffer holds the SUM of clamped passes
+                                          (associative across ranks); finish with b200pt_resolve_sum()   */
+
+typedef struct b200pt_config {
+    int   schedule;           /* B200PT_SCHEDULE_*                                                       */
+    int   max_depth;          /* loop breaks when depth >= max_depth: 4 (sv3/sv4), 8 (orig), 3 (sv/sv2)  */
+    float tmin, tmax;         /* 0.01 / 1e16 (sv3/sv4), 0.001 / 1e16 (orig)                              */
+    int   shadow_mode;        /* B200PT_SHADOW_*                                                         */
+    int   display;            /* B200PT_DISPLAY_*                                                        */
+    float exposure;           /* 4 = 2^2 (sv4), 8 = 2^3 (sv3); ignored for DISPLAY_SRGB                  */
+    int   uniform_spl;        /* SCHEDULE_UNIFORM: samples_per_launch written by render(); 0 = keep caller's */
+    int   accumulate;         /* SCHEDULE_UNIFORM: 0 = force subframe_index 0 (sv4 FOV_OFF), 1 = progressive (sv3/orig) */
+    int   inner_radius, outer_radius;   /* SCHEDULE_FOVEATED ring radii, 157 / 515                       */
+    int   launch_w, launch_h; /* SCHEDULE_AS_GIVEN launch dimensions; 0 = frame.size                     */
+    int   write_aovs;         /* 1 = also write normal/color/albedo buffers (orig/deviceProgram.cu:472-474) */
+    int   increment_subframe; /* 1 = render() does subframe_index++ (sv3/sv4); 0 = caller does (orig)    */
+    int   accum_mode;         /* B200PT_ACCUM_*                                                          */
+    int   russian_roulette;   /* 0 = off (reference behaviour). Opt-in estimator extension; breaks RNG parity */
+    int   tile_rank, tile_count; /* multi-GPU tile split: this context renders launch rows whose 32-row band
+                                    index % tile_count == tile_rank; tile_count <= 1 = whole frame        */
+    int   profile;            /* 1 = record per-stage CUDA-event timings + traversal counters            */
+    int   reserved[4];
+} b200pt_config;
+
+/* Fill *cfg with a named preset: "orig", "sv3_uniform", "sv4_uniform", "sv4_fov". */
+int b200pt_config_preset(b200pt_config* cfg, const char* name);
+
+/* ---- lifetime: replaces SampleRenderer ctor plumbing (sv4/SimplePathtracer.cpp:42-75, 313-343) ---- */
+b200pt_ctx* b200pt_create(int device);            /* NULL on failure (see b200pt_last_error)            */
+void        b200pt_destroy(b200pt_ctx* ctx);
+const char* b200pt_last_error(void);
+
+/* ---- scene upload: replaces the per-mesh uploads + build inputs of buildAccel()
+ *      (sv4/SimplePathtracer.cpp:603-664), createTextures() (:749-800) and the SBT records (:574-595). */
+int b200pt_add_texture(b200pt_ctx* ctx, const uint32_t* rgba8, int width, int height);   /* returns textureID >= 0, or -1 */
+int b200pt_add_mesh(b200pt_ctx* ctx,
+                    const float* vertex_xyz, size_t n_vertices,
+                    const float* normal_xyz,            /* may be NULL (never read by the path)          */
+                    const float* texcoord_uv,           /* may be NULL                                   */
+                    const uint32_t* index_xyz, size_t n_triangles,
+                    const struct Material* material,
+                    int diffuse_texture_id);            /* -1 = none; returns meshID >= 0, or -1         */
+/* LBVH build: Morton codes -> radix sort -> Karras hierarchy -> refit -> SAH leaf collapse + treelet
+ * refinement -> 32-byte nodes + 48-byte Woop triangles.  Replaces optixAccelBuild/optixAccelCompact
+ * (sv4/SimplePathtracer.cpp:670-737).  *handle_out receives the value for LaunchParams.traversable. */
+int b200pt_build_accel(b200pt_ctx* ctx, uint64_t* handle_out);
+
+/* ---- frame state: SampleRenderer::resize / setProbe (sv4/SimplePathtracer.cpp:231-277, 295-311) ---- */
+int b200pt_resize(b200pt_ctx* ctx, int width, int height, struct LaunchParams* params /* buffers + size written */);
+int b200pt_set_probe(b200pt_ctx* ctx, int width, int height, const float* data_rgba,
+                     const float* pdfX, const float* cdfX, const float* pdfY, const float* cdfY,
+                     const float* offset_xyz, struct LaunchParams* params /* probe pointers written */);
+
+/* ---- the hot path: SampleRenderer::render() (sv4/SimplePathtracer.cpp:77-217) ---------------------
+ * Reads the caller's live LaunchParams (camera, frame.c, subframe_index, ...), runs the wavefront
+ * integrator for the configured schedule, writes accum/frame buffers, updates *params exactly as the
+ * reference's render() leaves its public `launchParams`, and blocks until the GPU is idle. */
+int b200pt_render(b200pt_ctx* ctx, struct LaunchParams* params, const b200pt_config* cfg);
+/* Same, without the trailing device synchronisation (for back-to-back timing on ctx's stream). */
+int b200pt_render_async(b200pt_ctx* ctx, struct LaunchParams* params, const b200pt_config* cfg);
+int b200pt_synchronize(b200pt_ctx* ctx);
+
+/* SampleRenderer::downloadPixels (sv4/SimplePathtracer.cpp:279-283): W*H RGBA8, R in the low byte. */
+int b200pt_download_pixels(b200pt_ctx* ctx, uint32_t* host_rgba8);
+int b200pt_download_accum(b200pt_ctx* ctx, float* host_rgba_f32);                /* W*H float4             */
+int b200pt_download_aov(b200pt_ctx* ctx, int which /*0 normal,1 albedo,2 color*/, float* host_rgba_f32);
+/* Device pointers of the internal buffers (for NCCL reduce/gather by the multi-GPU driver). */
+int b200pt_device_buffers(b200pt_ctx* ctx, void** accum_f4, void** frame_rgba8, void** stream);
+/* ACCUM_SUM epilogue on rank 0: accum = sum / n_passes, then the display transform into frame_buffer. */
+int b200pt_resolve_sum(b200pt_ctx* ctx, const struct LaunchParams* params, const b200pt_config* cfg, int n_passes);
+int b200pt_clear_accum(b200pt_ctx* ctx);
+
+/* computeFinalPixelColors (sv4/toneMap.cu:41-70, toneMap.h:4): sqrt-gamma float4 -> RGBA8, device pointers. */
+int b200pt_tonemap_sqrt(int width, int height, const void* d_float4_in, void* d_rgba8_out, void* stream);
+/* Host-buffer convenience around the same kernel (H2D + kernel + D2H). */
+int b200pt_tonemap_sqrt_host(b200pt_ctx* ctx, int width, int height, const float* h_float4_in, uint32_t* h_rgba8_out);
+
+/* ---- parity hooks (tests only; none of these is on the timed path) ---------------------------------*/
+/* Primary-ray closest hit for every launch index (jitter of sample 0, i.e. exactly the first radiance
+ * optixTrace of sv4/deviceProgram.cu:481): mesh = build-input index, prim = index within that mesh. */
+int b200pt_trace_primary(b200pt_ctx* ctx, const struct LaunchParams* params, const b200pt_config* cfg,
+                         int32_t* prim, int32_t* mesh, float* t, float* u, float* v);
+/* Arbitrary rays: o/d are n*3 floats.  any_hit != 0 -> occlusion query with cfg->shadow_mode (result in prim: 1/0). */
+int b200pt_trace_rays(b200pt_ctx* ctx, const float* origin_xyz, const float* dir_xyz, size_t n,
+                      float tmin, float tmax, int any_hit, int shadow_mode,
+                      int32_t* prim, int32_t* mesh, float* t, float* u, float* v);
+/* Integer BVH-build stages, bit-exact against a host reference: 63-bit Morton code (21 bits/axis) per
+ * global triangle (input order) and the stable radix-sort permutation.  scene_bounds = 6 floats (lo xyz, hi xyz). */
+int b200pt_debug_morton(b200pt_ctx* ctx, uint64_t* codes, uint32_t* sorted_order, float* scene_bounds);
+typedef struct b200pt_bvh_info {
+    uint64_t n_triangles, n_nodes, n_leaves;
+    uint32_t max_leaf_size, max_depth;
+    float    sah_cost;           /* SAH cost of the final tree (Ct = 1, Ci = 1.2) */
+    float    sah_cost_lbvh;      /* before refinement */
+    float    build_ms;
+    uint64_t node_bytes, tri_bytes;
+} b200pt_bvh_info;
+int b200pt_bvh_info_get(b200pt_ctx* ctx, b200pt_bvh_info* out);
+/* Copies of the flattened BVH for structural validation in tests (32-byte nodes). */
+int b200pt_download_bvh(b200pt_ctx* ctx, void* nodes32, size_t max_nodes, uint32_t* tri_global_id, size_t max_tris);
+
+typedef struct b200pt_counters {      /* last render()                                                  */
+    uint64_t samples;                 /* camera paths started                                           */
+    uint64_t radiance_rays, shadow_rays;
+    uint64_t nodes_fetched, tris_fetched;      /* 32-byte node records / 48-byte Woop triangles (profile=1) */
+    uint64_t nodes_fetched_shadow, tris_fetched_shadow;
+    float    ms_total, ms_raygen, ms_trace_closest, ms_trace_any, ms_shade, ms_accumulate;   /* profile=1 */
+    uint32_t kernel_launches;         /* kernels launched by the last render()                          */
+    uint32_t n_trace_closest_launches, n_trace_any_launches;
+} b200pt_counters;
+int b200pt_get_counters(b200pt_ctx* ctx, b200pt_counters* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200PT_H */

@@ -1,0 +1,191 @@
+"""Python mirror of the reference's host renderer class, forwarding 1:1 to the C-ABI (include/b200pt.h).
+
+reference: class SampleRenderer, HelloPathtracing_sv4_vmv23/SimplePathtracer.h:45-188 and
+SimplePathtracer.cpp:42-75 (ctor), :77-217 (render), :231-277 (resize), :279-283 (downloadPixels),
+:285-292 (setCamera), :295-311 (setProbe).  `launchParams` is a public, live LaunchParams that callers poke
+directly (main.cpp:310-320,392) and that every render() re-reads.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from .structs import BvhInfo, Config, Counters, LaunchParams, float3, preset
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def host_params(width, height, camera=None, samples_per_launch=1, subframe_index=0):
+    """A LaunchParams filled the way resize()+setCamera() would, without device buffers (CPU-side tools)."""
+    p = LaunchParams()
+    p.frame.size.x, p.frame.size.y = int(width), int(height)
+    p.frame.subframe_index = subframe_index
+    p.frame.factor.x = p.frame.factor.y = p.frame.factor.z = 1
+    p.frame.fillSize = 1
+    p.frame.r_inner, p.frame.r_outer = 0.0, 1e9
+    p.samples_per_launch = samples_per_launch
+    if camera is not None:
+        set_camera(p, camera)
+    return p
+
+
+def set_camera(p, camera):
+    """SimplePathtracer.cpp:285-292 — aspect is overridden by the frame size."""
+    camera.setAspectRatio(np.float32(p.frame.size.x) / np.float32(p.frame.size.y))
+    U, V, W = camera.UVWFrame()
+    p.camera.U, p.camera.V, p.camera.W = float3(*U), float3(*V), float3(*W)
+    p.camera.eye = float3(*camera.eye)
+
+
+class SampleRenderer:
+    def __init__(self, model, device=0, config="sv4_fov"):
+        """ctor: uploads every mesh/texture and builds the acceleration structure (LBVH) on the GPU."""
+        self._L = _lib.lib()
+        self.model = model                     # borrowed, like the reference (SimplePathtracer.h:173)
+        self.config = preset(config) if isinstance(config, str) else config
+        self.launchParams = LaunchParams()
+        self._h = self._L.b200pt_create(int(device))
+        if not self._h:
+            raise _lib.B200ptError(self._L.b200pt_last_error().decode())
+        self._h = C.c_void_p(self._h)
+        for tex in model.textures:
+            px = np.ascontiguousarray(tex.pixel, np.uint32)
+            if self._L.b200pt_add_texture(self._h, _ptr(px), int(tex.resolution[0]), int(tex.resolution[1])) < 0:
+                _lib.check(-1)
+        for mesh in model.meshes:
+            v = np.ascontiguousarray(mesh.vertex, np.float32)
+            idx = np.ascontiguousarray(mesh.index, np.uint32)
+            n = np.ascontiguousarray(mesh.normal, np.float32) if len(mesh.normal) else None
+            tc = np.ascontiguousarray(mesh.texcoord, np.float32) if len(mesh.texcoord) else None
+            if self._L.b200pt_add_mesh(self._h, _ptr(v), len(v), _ptr(n), _ptr(tc), _ptr(idx), len(idx),
+                                       C.byref(mesh.material), int(mesh.diffuseTextureID)) < 0:
+                _lib.check(-1)
+        handle = C.c_uint64(0)
+        _lib.check(self._L.b200pt_build_accel(self._h, C.byref(handle)))
+        self.launchParams.traversable = handle.value
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.b200pt_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- reference interface ---------------------------------------------------------------------
+    def render(self, config=None, sync=True):
+        if self.launchParams.frame.size.x == 0:
+            return
+        cfg = config or self.config
+        fn = self._L.b200pt_render if sync else self._L.b200pt_render_async
+        _lib.check(fn(self._h, C.byref(self.launchParams), C.byref(cfg)))
+
+    def synchronize(self):
+        _lib.check(self._L.b200pt_synchronize(self._h))
+
+    def resize(self, newSize):
+        w, h = int(newSize[0]), int(newSize[1])
+        if w == 0 or h == 0:
+            return
+        _lib.check(self._L.b200pt_resize(self._h, w, h, C.byref(self.launchParams)))
+
+    def downloadPixels(self, h_pixels=None):
+        w, h = self.launchParams.frame.size.x, self.launchParams.frame.size.y
+        if h_pixels is None:
+            h_pixels = np.empty((h, w), np.uint32)
+        _lib.check(self._L.b200pt_download_pixels(self._h, _ptr(h_pixels)))
+        return h_pixels
+
+    def setCamera(self, camera):
+        self.lastSetCamera = camera
+        set_camera(self.launchParams, camera)
+
+    def setProbe(self, probe):
+        if not probe.valid:
+            raise RuntimeError("Probe Data is not valid")          # Probe.h:104-105
+        off = np.asarray(probe.offset, np.float32)
+        _lib.check(self._L.b200pt_set_probe(self._h, probe.width, probe.height, _ptr(probe.data), _ptr(probe.pdfX),
+                                            _ptr(probe.cdfX), _ptr(probe.pdfY), _ptr(probe.cdfY), _ptr(off),
+                                            C.byref(self.launchParams)))
+
+    # ---- extras behind the same C-ABI -----------------------------------------------------------
+    def downloadAccum(self):
+        w, h = self.launchParams.frame.size.x, self.launchParams.frame.size.y
+        out = np.empty((h, w, 4), np.float32)
+        _lib.check(self._L.b200pt_download_accum(self._h, _ptr(out)))
+        return out
+
+    def downloadAOV(self, which):
+        w, h = self.launchParams.frame.size.x, self.launchParams.frame.size.y
+        out = np.empty((h, w, 4), np.float32)
+        _lib.check(self._L.b200pt_download_aov(self._h, {"normal": 0, "albedo": 1, "color": 2}[which], _ptr(out)))
+        return out
+
+    def clearAccum(self):
+        _lib.check(self._L.b200pt_clear_accum(self._h))
+
+    def resolveSum(self, n_passes, config=None):
+        cfg = config or self.config
+        _lib.check(self._L.b200pt_resolve_sum(self._h, C.byref(self.launchParams), C.byref(cfg), int(n_passes)))
+
+    def deviceBuffers(self):
+        a, f, s = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        _lib.check(self._L.b200pt_device_buffers(self._h, C.byref(a), C.byref(f), C.byref(s)))
+        return a.value, f.value, s.value
+
+    def counters(self):
+        c = Counters()
+        _lib.check(self._L.b200pt_get_counters(self._h, C.byref(c)))
+        return c
+
+    def bvhInfo(self):
+        b = BvhInfo()
+        _lib.check(self._L.b200pt_bvh_info_get(self._h, C.byref(b)))
+        return b
+
+    def tracePrimary(self, config=None):
+        cfg = config or self.config
+        lw = cfg.launch_w or self.launchParams.frame.size.x
+        lh = cfg.launch_h or self.launchParams.frame.size.y
+        n = lw * lh
+        prim, mesh = np.empty(n, np.int32), np.empty(n, np.int32)
+        t, u, v = (np.empty(n, np.float32) for _ in range(3))
+        _lib.check(self._L.b200pt_trace_primary(self._h, C.byref(self.launchParams), C.byref(cfg), _ptr(prim), _ptr(mesh),
+                                                _ptr(t), _ptr(u), _ptr(v)))
+        return prim, mesh, t, u, v
+
+    def traceRays(self, org, dirs, tmin, tmax, any_hit=False, shadow_mode=0):
+        org, dirs = np.ascontiguousarray(org, np.float32), np.ascontiguousarray(dirs, np.float32)
+        n = len(org)
+        prim, mesh = np.zeros(n, np.int32), np.zeros(n, np.int32)
+        t, u, v = (np.zeros(n, np.float32) for _ in range(3))
+        _lib.check(self._L.b200pt_trace_rays(self._h, _ptr(org), _ptr(dirs), n, tmin, tmax, int(any_hit), int(shadow_mode),
+                                             _ptr(prim), _ptr(mesh), _ptr(t), _ptr(u), _ptr(v)))
+        return prim, mesh, t, u, v
+
+    def debugMorton(self):
+        n = self.model.num_triangles()
+        codes, order, bounds = np.empty(n, np.uint64), np.empty(n, np.uint32), np.empty(6, np.float32)
+        _lib.check(self._L.b200pt_debug_morton(self._h, _ptr(codes), _ptr(order), _ptr(bounds)))
+        return codes, order, bounds
+
+    def downloadBvh(self):
+        info = self.bvhInfo()
+        nodes = np.empty((int(info.n_nodes), 8), np.float32)
+        tri_ids = np.empty(int(info.n_triangles), np.uint32)
+        _lib.check(self._L.b200pt_download_bvh(self._h, _ptr(nodes), len(nodes), _ptr(tri_ids), len(tri_ids)))
+        return nodes, tri_ids
+
+
+def computeFinalPixelColors(renderer, rgba_f32):
+    """toneMap.cu:41-70 through the host-buffer convenience entry point."""
+    rgba = np.ascontiguousarray(rgba_f32, np.float32)
+    h, w = rgba.shape[:2]
+    out = np.empty((h, w), np.uint32)
+    _lib.check(renderer._L.b200pt_tonemap_sqrt_host(renderer._h, w, h, _ptr(rgba), _ptr(out)))
+    return out
