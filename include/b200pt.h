@@ -99,6 +99,8 @@ int b200pt_synchronize(b200pt_ctx* ctx);
 /* SampleRenderer::downloadPixels (sv4/SimplePathtracer.cpp:279-283): W*H RGBA8, R in the low byte. */
 int b200pt_download_pixels(b200pt_ctx* ctx, uint32_t* host_rgba8);
 int b200pt_download_accum(b200pt_ctx* ctx, float* host_rgba_f32);                /* W*H float4             */
+/* Restore a progressive state saved with b200pt_download_accum (checkpoint/resume of accum_buffer). */
+int b200pt_upload_accum(b200pt_ctx* ctx, const float* host_rgba_f32);
 int b200pt_download_aov(b200pt_ctx* ctx, int which /*0 normal,1 albedo,2 color*/, float* host_rgba_f32);
 /* Device pointers of the internal buffers (for NCCL reduce/gather by the multi-GPU driver). */
 int b200pt_device_buffers(b200pt_ctx* ctx, void** accum_f4, void** frame_rgba8, void** stream);

@@ -1,0 +1,174 @@
+// b200pt — the C-ABI (include/b200pt.h) over the CUDA kernels.  Host orchestration only: scene staging,
+// the LBVH build, the wavefront loop of one render() and the parity hooks.  No CPU fallback anywhere.
+#include "common.cuh"
+#include <algorithm>
+#include <cstring>
+#include <cstdlib>
+
+static thread_local std::string g_lastError;
+static int fail(const std::string& msg) { g_lastError = msg;  return -1; }
+#define API_BEGIN try {
+#define API_END } catch (const std::exception& e) { return fail(e.what()); } return 0;
+
+template <typename T> struct DevBuf {
+    T* p = nullptr;  size_t n = 0;
+    void ensure(size_t count) { if (count > n) { release();  CUDA_OK(cudaMalloc((void**)&p, count * sizeof(T)));  n = count; } }
+    void release() { if (p) cudaFree(p);  p = nullptr;  n = 0; }
+};
+
+struct HostMesh { size_t firstVertex, nVertices, firstTri, nTris;  bool hasTexcoord;  int textureID;  Material material{Material::NoInit{}}; };
+struct HostTexture { size_t offset;  int w, h; };
+
+struct b200pt_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    // --- scene staging (host) and device copies
+    std::vector<float3> hVertices;  std::vector<float2> hTexcoords;  std::vector<uint3> hIndices;  std::vector<unsigned> hTriMesh;
+    std::vector<HostMesh> hMeshes;  std::vector<HostTexture> hTextures;  std::vector<uint32_t> hTexels;
+    DevBuf<float3> dVertices;  DevBuf<float2> dTexcoords;  DevBuf<uint3> dIndices;  DevBuf<unsigned> dTriMesh;
+    DevBuf<MeshInfo> dMeshes;  DevBuf<uint32_t> dTexels;
+    BvhBuildResult bvh;  bool built = false;  bool hasCatcher = false;
+    // --- frame
+    int W = 0, H = 0;
+    DevBuf<uint32_t> frameBuf;  DevBuf<float4> accumBuf, normalBuf, albedoBuf, colorBuf;
+    DevBuf<float> probeData, probePdfX, probeCdfX, probePdfY, probeCdfY;
+    // --- wavefront pool
+    size_t poolCap = 0;
+    DevBuf<uint2> rng;  DevBuf<float4> thr, direct, indirect, alpha, pending, aovN, aovA;  DevBuf<int> state;
+    DevBuf<float4> rayO[2], rayD[2], hit, shO, shD;
+    DevBuf<unsigned> counters;          // QC_COUNT queue counters + 8 running totals
+    DevBuf<float4> sumRad, sumAlpha, sumNormal, sumAlbedo;
+    DevBuf<TraceStats> stats;           // [0] closest, [1] any
+    b200pt_counters last{};
+    bool countersPending = false;  bool profiled = false;
+    std::vector<cudaEvent_t> evPool;  std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> evUsed;  size_t evNext = 0;
+};
+
+extern "C" {
+
+const char* b200pt_last_error(void) { return g_lastError.c_str(); }
+
+int b200pt_config_preset(b200pt_config* c, const char* name) {
+    if (!c || !name) return fail("b200pt_config_preset: null argument");
+    memset(c, 0, sizeof(*c));
+    c->tmax = 1e16f;  c->exposure = 1.0f;
+    const std::string n(name);
+    if (n == "orig") {            // orig/deviceProgram.cu:198,429,467; orig/SimplePathtracer.cpp:73-97
+        c->schedule = B200PT_SCHEDULE_UNIFORM;  c->max_depth = 8;  c->tmin = 0.001f;  c->shadow_mode = B200PT_SHADOW_ANY_HIT;
+        c->display = B200PT_DISPLAY_SRGB;  c->uniform_spl = 0;  c->accumulate = 1;  c->write_aovs = 1;  c->increment_subframe = 0;
+    } else if (n == "sv3_uniform") {   // sv3/deviceProgram.cu:243,511,582; sv3/SimplePathtracer.cpp:81-128
+        c->schedule = B200PT_SCHEDULE_UNIFORM;  c->max_depth = 4;  c->tmin = 0.01f;  c->shadow_mode = B200PT_SHADOW_CULL_BACK;
+        c->display = B200PT_DISPLAY_REINHARD;  c->exposure = 8.0f;  c->uniform_spl = 32;  c->accumulate = 1;  c->increment_subframe = 1;
+    } else if (n == "sv4_uniform") {   // sv4/SimplePathtracer.cpp:85-131
+        c->schedule = B200PT_SCHEDULE_UNIFORM;  c->max_depth = 4;  c->tmin = 0.01f;  c->shadow_mode = B200PT_SHADOW_CULL_BACK;
+        c->display = B200PT_DISPLAY_REINHARD;  c->exposure = 4.0f;  c->uniform_spl = 8;  c->accumulate = 0;  c->increment_subframe = 1;
+    } else if (n == "sv4_fov") {       // sv4/SimplePathtracer.cpp:20-21,132-216
+        c->schedule = B200PT_SCHEDULE_FOVEATED;  c->max_depth = 4;  c->tmin = 0.01f;  c->shadow_mode = B200PT_SHADOW_CULL_BACK;
+        c->display = B200PT_DISPLAY_REINHARD;  c->exposure = 4.0f;  c->inner_radius = 157;  c->outer_radius = 515;  c->increment_subframe = 1;
+    } else return fail("b200pt_config_preset: unknown preset '" + n + "'");
+    return 0;
+}
+
+b200pt_ctx* b200pt_create(int device) {
+    try {
+        int count = 0;
+        cudaError_t e = cudaGetDeviceCount(&count);
+        if (e != cudaSuccess || count == 0) { fail(std::string("b200pt_create: no CUDA device (") + cudaGetErrorString(e) + "); there is no CPU fallback");  return nullptr; }
+        if (device < 0 || device >= count) { fail("b200pt_create: device index out of range");  return nullptr; }
+        CUDA_OK(cudaSetDevice(device));
+        CUDA_OK(cudaFree(0));
+        b200pt_ctx* c = new b200pt_ctx();
+        c->device = device;
+        CUDA_OK(cudaStreamCreate(&c->stream));                 // the reference's single stream, SimplePathtracer.cpp:342
+        return c;
+    } catch (const std::exception& ex) { fail(ex.what());  return nullptr; }
+}
+
+void b200pt_destroy(b200pt_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    bvhFree(c->bvh);
+    c->dVertices.release();  c->dTexcoords.release();  c->dIndices.release();  c->dTriMesh.release();  c->dMeshes.release();  c->dTexels.release();
+    c->frameBuf.release();  c->accumBuf.release();  c->normalBuf.release();  c->albedoBuf.release();  c->colorBuf.release();
+    c->probeData.release();  c->probePdfX.release();  c->probeCdfX.release();  c->probePdfY.release();  c->probeCdfY.release();
+    c->rng.release();  c->thr.release();  c->direct.release();  c->indirect.release();  c->alpha.release();  c->pending.release();
+    c->aovN.release();  c->aovA.release();  c->state.release();
+    for (int i = 0; i < 2; ++i) { c->rayO[i].release();  c->rayD[i].release(); }
+    c->hit.release();  c->shO.release();  c->shD.release();  c->counters.release();
+    c->sumRad.release();  c->sumAlpha.release();  c->sumNormal.release();  c->sumAlbedo.release();  c->stats.release();
+    for (auto ev : c->evPool) cudaEventDestroy(ev);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int b200pt_add_texture(b200pt_ctx* c, const uint32_t* rgba8, int w, int h) {
+    if (!c || !rgba8 || w <= 0 || h <= 0) return fail("b200pt_add_texture: bad argument");
+    HostTexture t{c->hTexels.size(), w, h};
+    c->hTexels.insert(c->hTexels.end(), rgba8, rgba8 + (size_t)w * h);
+    c->hTextures.push_back(t);
+    return (int)c->hTextures.size() - 1;
+}
+
+int b200pt_add_mesh(b200pt_ctx* c, const float* vtx, size_t nv, const float* normal, const float* texcoord, const uint32_t* idx,
+                    size_t ntri, const Material* material, int textureID) {
+    (void)normal;                                             // uploaded by the reference, never read by its shaders
+    if (!c || !material || (nv && !vtx) || (ntri && !idx)) return fail("b200pt_add_mesh: bad argument");
+    if (textureID >= (int)c->hTextures.size()) return fail("b200pt_add_mesh: texture id out of range");
+    for (size_t i = 0; i < 3 * ntri; ++i) if (idx[i] >= nv) return fail("b200pt_add_mesh: vertex index out of range");
+    HostMesh m;
+    m.firstVertex = c->hVertices.size();  m.nVertices = nv;  m.firstTri = c->hIndices.size();  m.nTris = ntri;
+    m.hasTexcoord = texcoord != nullptr;  m.textureID = textureID;  m.material = *material;
+    const float3* v3 = reinterpret_cast<const float3*>(vtx);
+    c->hVertices.insert(c->hVertices.end(), v3, v3 + nv);
+    if (texcoord) { const float2* t2 = reinterpret_cast<const float2*>(texcoord);  c->hTexcoords.insert(c->hTexcoords.end(), t2, t2 + nv); }
+    else c->hTexcoords.insert(c->hTexcoords.end(), nv, make_float2(0.f, 0.f));
+    const uint3* i3 = reinterpret_cast<const uint3*>(idx);
+    c->hIndices.insert(c->hIndices.end(), i3, i3 + ntri);
+    c->hTriMesh.insert(c->hTriMesh.end(), ntri, (unsigned)c->hMeshes.size());
+    if (material->flags & MATERIAL_FLAG_SHADOW_CATCHER) c->hasCatcher = true;
+    c->hMeshes.push_back(m);
+    c->built = false;
+    return (int)c->hMeshes.size() - 1;
+}
+
+int b200pt_build_accel(b200pt_ctx* c, uint64_t* handle_out) {
+    if (!c) return fail("b200pt_build_accel: null context");
+    API_BEGIN
+    CUDA_OK(cudaSetDevice(c->device));
+    if (c->hIndices.size() >= (1u << 28)) throw std::runtime_error("b200pt_build_accel: more than 2^28 triangles");
+    std::vector<MeshInfo> infos(c->hMeshes.size());
+    for (size_t i = 0; i < infos.size(); ++i) {
+        const HostMesh& m = c->hMeshes[i];
+        MeshInfo& d = infos[i];
+        memset(&d, 0, sizeof(d));
+        d.material = m.material;  d.firstTri = (unsigned)m.firstTri;  d.firstVertex = (unsigned)m.firstVertex;
+        d.textureID = m.textureID;  d.hasTexcoord = m.hasTexcoord ? 1 : 0;
+        if (m.textureID >= 0) { const HostTexture& t = c->hTextures[m.textureID];  d.texOffset = (unsigned)t.offset;  d.texW = t.w;  d.texH = t.h; }
+    }
+    auto up = [&](auto& buf, const auto& vec) {
+        buf.ensure(std::max<size_t>(vec.size(), 1));
+        if (!vec.empty()) CUDA_OK(cudaMemcpyAsync(buf.p, vec.data(), vec.size() * sizeof(vec[0]), cudaMemcpyHostToDevice, c->stream));
+    };
+    up(c->dVertices, c->hVertices);  up(c->dTexcoords, c->hTexcoords);  up(c->dIndices, c->hIndices);  up(c->dTriMesh, c->hTriMesh);
+    up(c->dMeshes, infos);  up(c->dTexels, c->hTexels);
+    bvhFree(c->bvh);
+    bvhBuild(c->dVertices.p, c->dIndices.p, c->dTriMesh.p, c->dMeshes.p, (unsigned)c->hIndices.size(), c->stream, c->bvh);
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    CUDA_OK(cudaGetLastError());
+    c->built = true;
+    if (handle_out) *handle_out = (uint64_t)(uintptr_t)c->bvh.nodes;
+    API_END
+}
+
+}  // extern "C"
+
+static SceneDev sceneOf(b200pt_ctx* c) {
+    SceneDev S;
+    S.nodes = (const float4*)c->bvh.nodes;  S.tris = c->bvh.tris;  S.meshes = c->dMeshes.p;  S.indices = c->dIndices.p;
+    S.texcoords = c->dTexcoords.p;  S.texels = c->dTexels.p;  S.nTris = c->bvh.nTris;  S.nNodes = c->bvh.nNodes;
+    return S;
+}
+
+#include "api_render.inl"
+#include "api_hooks.inl"

@@ -1,0 +1,297 @@
+// b200pt — frame state + SampleRenderer::render() orchestration (included by api.cu).
+
+struct PassDesc { PassParams P;  size_t nLaunch; };
+
+__global__ void resetCountersKernel(unsigned* counters, int nextQueue, int firstBounce) {
+    // running totals live after the queue counters: [QC_COUNT+0] radiance rays, [+1] shadow rays, [+2] samples
+    const int cur = nextQueue ^ 1;
+    if (firstBounce) counters[QC_COUNT + 2] += counters[cur ? QC_RAY1 : QC_RAY0];
+    counters[QC_COUNT + 0] += counters[cur ? QC_RAY1 : QC_RAY0];
+    counters[nextQueue ? QC_RAY1 : QC_RAY0] = 0;
+    counters[QC_SHADOW] = 0;
+    counters[QC_HEAD_CLOSEST] = 0;
+    counters[QC_HEAD_ANY] = 0;
+}
+__global__ void tallyShadowKernel(unsigned* counters) { counters[QC_COUNT + 1] += counters[QC_SHADOW]; }
+
+static size_t poolLimit() {
+    const char* e = getenv("B200PT_POOL_SLOTS");
+    size_t v = e ? (size_t)atoll(e) : (size_t)8 << 20;
+    return std::max<size_t>(v, 1024);
+}
+
+static void ensurePool(b200pt_ctx* c, size_t slots, bool aovs) {
+    if (slots > c->poolCap) {
+        c->rng.ensure(slots);  c->thr.ensure(slots);  c->state.ensure(slots);  c->direct.ensure(slots);  c->indirect.ensure(slots);
+        c->alpha.ensure(slots);  c->pending.ensure(slots);
+        for (int i = 0; i < 2; ++i) { c->rayO[i].ensure(slots);  c->rayD[i].ensure(slots); }
+        c->hit.ensure(slots);  c->shO.ensure(slots);  c->shD.ensure(slots);
+        c->poolCap = slots;
+    }
+    if (aovs) { c->aovN.ensure(c->poolCap);  c->aovA.ensure(c->poolCap); }
+    c->counters.ensure(QC_COUNT + 8);
+    c->stats.ensure(2);
+}
+
+struct StageTimer {          // CUDA-event pairs per stage, resolved after the frame (profile=1 only)
+    b200pt_ctx* c;  bool on;
+    void begin(int stage, cudaEvent_t& a, cudaEvent_t& b) {
+        if (!on) return;
+        while (c->evPool.size() < c->evNext + 2) { cudaEvent_t e;  CUDA_OK(cudaEventCreate(&e));  c->evPool.push_back(e); }
+        a = c->evPool[c->evNext++];  b = c->evPool[c->evNext++];
+        c->evUsed.push_back({stage, {a, b}});
+        CUDA_OK(cudaEventRecord(a, c->stream));
+    }
+    void end(cudaEvent_t b) { if (on) CUDA_OK(cudaEventRecord(b, c->stream)); }
+};
+enum { ST_RAYGEN = 0, ST_CLOSEST, ST_ANY, ST_SHADE, ST_ACCUM, ST_TOTAL };
+
+static void collectCounters(b200pt_ctx* c) {
+    if (!c->countersPending) return;
+    unsigned h[QC_COUNT + 8];
+    CUDA_OK(cudaMemcpy(h, c->counters.p, sizeof(h), cudaMemcpyDeviceToHost));
+    c->last.radiance_rays = h[QC_COUNT + 0];  c->last.shadow_rays = h[QC_COUNT + 1];  c->last.samples = h[QC_COUNT + 2];
+    if (c->profiled) {
+        TraceStats st[2];
+        CUDA_OK(cudaMemcpy(st, c->stats.p, sizeof(st), cudaMemcpyDeviceToHost));
+        c->last.nodes_fetched = st[0].nodes;  c->last.tris_fetched = st[0].tris;
+        c->last.nodes_fetched_shadow = st[1].nodes;  c->last.tris_fetched_shadow = st[1].tris;
+        float acc[6] = {0, 0, 0, 0, 0, 0};
+        for (auto& u : c->evUsed) { float ms = 0.f;  cudaEventElapsedTime(&ms, u.second.first, u.second.second);  acc[u.first] += ms; }
+        c->last.ms_raygen = acc[ST_RAYGEN];  c->last.ms_trace_closest = acc[ST_CLOSEST];  c->last.ms_trace_any = acc[ST_ANY];
+        c->last.ms_shade = acc[ST_SHADE];  c->last.ms_accumulate = acc[ST_ACCUM];  c->last.ms_total = acc[ST_TOTAL];
+    }
+    c->countersPending = false;
+}
+
+static PassDesc makePass(const LaunchParams& P, int launchW, int launchH) {
+    PassDesc d;
+    PassParams& q = d.P;
+    q.launchW = launchW;  q.launchH = launchH;  q.factorX = P.frame.factor.x;  q.factorY = P.frame.factor.y;
+    q.fillSize = P.frame.fillSize;  q.cX = P.frame.c.x;  q.cY = P.frame.c.y;  q.rInner = P.frame.r_inner;  q.rOuter = P.frame.r_outer;
+    q.offX = P.frame.offset.x;  q.offY = P.frame.offset.y;  q.redraw = P.frame.redraw;  q.subframe = P.frame.subframe_index;
+    q.spl = (int)P.samples_per_launch;  q.slotBase = 0;  q.launchBase = 0;
+    d.nLaunch = (size_t)std::max(launchW, 0) * (size_t)std::max(launchH, 0);
+    return d;
+}
+
+// The launch schedule of SampleRenderer::render(): mutates P exactly as the reference leaves its public
+// launchParams (sv4/SimplePathtracer.cpp:85-131 uniform, :136-214 foveated; orig/SimplePathtracer.cpp:73-97).
+// Deviation: fields are uploaded AFTER they are set, not one frame late.
+static void buildSchedule(LaunchParams& P, const b200pt_config& cfg, std::vector<PassDesc>& passes) {
+    const int W = P.frame.size.x, H = P.frame.size.y;
+    if (cfg.schedule == B200PT_SCHEDULE_AS_GIVEN) {
+        passes.push_back(makePass(P, cfg.launch_w ? cfg.launch_w : W, cfg.launch_h ? cfg.launch_h : H));
+        if (cfg.increment_subframe) P.frame.subframe_index++;
+    } else if (cfg.schedule == B200PT_SCHEDULE_UNIFORM) {
+        if (!cfg.accumulate) P.frame.subframe_index = 0;
+        P.frame.factor = make_uint3(1, 1, 1);  P.frame.fillSize = 1;  P.frame.r_outer = 1000000000;  P.frame.r_inner = 0;
+        if (cfg.uniform_spl > 0) P.samples_per_launch = cfg.uniform_spl;
+        P.frame.offset = make_uint2(0, 0);  P.frame.redraw = 0;
+        P.viewportSize.x = W;  P.viewportSize.y = H;
+        const unsigned temp = P.frame.subframe_index;
+        passes.push_back(makePass(P, W, H));
+        P.frame.subframe_index = temp;
+        if (cfg.increment_subframe) P.frame.subframe_index++;
+    } else {
+        const int inner = cfg.inner_radius, outer = cfg.outer_radius;
+        P.frame.factor = make_uint3(4, 4, 1);  P.frame.fillSize = 4;  P.frame.r_outer = 1000000000;  P.frame.r_inner = (float)outer;
+        P.samples_per_launch = 1;  P.frame.offset = make_uint2(0, 0);  P.frame.redraw = 0;
+        passes.push_back(makePass(P, W / 4, H / 4));
+        const unsigned temp = P.frame.subframe_index;
+        P.frame.subframe_index = 0;
+        P.frame.factor = make_uint3(2, 2, 1);  P.frame.fillSize = 2;  P.frame.r_outer = (float)(outer + 2);  P.frame.r_inner = (float)inner;
+        P.samples_per_launch = 2;
+        P.frame.offset = make_uint2(P.frame.c.x - (unsigned)(outer + 2), P.frame.c.y - (unsigned)(outer + 2));
+        P.frame.redraw = 1;
+        passes.push_back(makePass(P, (int)P.frame.r_outer, (int)P.frame.r_outer));
+        P.frame.factor = make_uint3(1, 1, 1);  P.frame.fillSize = 1;  P.frame.r_outer = (float)(inner + 1);  P.frame.r_inner = 0;
+        P.samples_per_launch = 8;
+        P.frame.offset = make_uint2(P.frame.c.x - (unsigned)(inner + 1), P.frame.c.y - (unsigned)(inner + 1));
+        P.frame.redraw = 1;
+        passes.push_back(makePass(P, (int)(P.frame.r_outer * 2), (int)(P.frame.r_outer * 2)));
+        P.frame.subframe_index = temp;
+        if (cfg.increment_subframe) P.frame.subframe_index++;
+    }
+}
+
+static FrameParams frameOf(const LaunchParams& P, const b200pt_config& cfg) {
+    FrameParams F;
+    F.W = P.frame.size.x;  F.H = P.frame.size.y;
+    F.eye = P.camera.eye;  F.U = P.camera.U;  F.V = P.camera.V;  F.Wv = P.camera.W;
+    F.probe = P.probe;
+    F.tmin = cfg.tmin;  F.tmax = cfg.tmax;  F.maxDepth = cfg.max_depth;  F.shadowMode = cfg.shadow_mode;  F.display = cfg.display;
+    F.accumMode = cfg.accum_mode;  F.writeAovs = cfg.write_aovs;  F.exposure = cfg.exposure;
+    F.tileRank = cfg.tile_rank;  F.tileCount = cfg.tile_count;
+    F.accum = P.frame.accum_buffer;  F.frame = (uint32_t*)P.frame.frame_buffer;  F.normal = P.frame.normal_buffer;
+    F.albedo = P.frame.albedo_buffer;  F.color = P.frame.color_buffer;
+    return F;
+}
+
+struct Chunk { int pass, k0, k1;  unsigned slotBase; };
+
+static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config* cfgp, bool sync) {
+    if (!c || !params || !cfgp) throw std::runtime_error("b200pt_render: null argument");
+    if (params->frame.size.x == 0) return;                                       // SimplePathtracer.cpp:81
+    const b200pt_config cfg = *cfgp;
+    CUDA_OK(cudaSetDevice(c->device));
+    if (!c->built) throw std::runtime_error("b200pt_render: b200pt_build_accel has not been called");
+    if (!params->probe.data || !params->probe.cdfValuesX) throw std::runtime_error("b200pt_render: no probe set (call b200pt_set_probe)");
+    if (!params->frame.accum_buffer || !params->frame.frame_buffer) throw std::runtime_error("b200pt_render: frame buffers not allocated (call b200pt_resize)");
+    if (cfg.max_depth < 0 || cfg.max_depth > 200) throw std::runtime_error("b200pt_render: max_depth out of range");
+    if (cfg.russian_roulette) throw std::runtime_error("b200pt_render: russian_roulette is not implemented yet");
+    c->countersPending = false;                                                  // totals of an un-synchronised previous frame are dropped
+
+    std::vector<PassDesc> passes;
+    buildSchedule(*params, cfg, passes);
+    const FrameParams F = frameOf(*params, cfg);
+    const SceneDev S = sceneOf(c);
+    cudaStream_t s = c->stream;
+
+    // launch-index records and chunks
+    size_t nRec = 0;
+    for (auto& p : passes) { if (p.P.spl <= 0) throw std::runtime_error("b200pt_render: samples_per_launch must be > 0");  p.P.launchBase = (unsigned)nRec;  nRec += p.nLaunch; }
+    c->sumRad.ensure(std::max<size_t>(nRec, 1));  c->sumAlpha.ensure(std::max<size_t>(nRec, 1));
+    if (cfg.write_aovs) { c->sumNormal.ensure(std::max<size_t>(nRec, 1));  c->sumAlbedo.ensure(std::max<size_t>(nRec, 1)); }
+    const size_t limit = poolLimit();
+    std::vector<std::vector<Chunk>> groups(1);
+    size_t used = 0, maxUsed = 0;
+    for (int pi = 0; pi < (int)passes.size(); ++pi) {
+        const size_t nL = passes[pi].nLaunch;
+        if (!nL) continue;
+        const int kmax = (int)std::max<size_t>(1, limit / nL);
+        for (int k0 = 0; k0 < passes[pi].P.spl; k0 += kmax) {
+            const int k1 = std::min(passes[pi].P.spl, k0 + kmax);
+            const size_t need = nL * (size_t)(k1 - k0);
+            if (used && used + need > limit) { groups.emplace_back();  used = 0; }
+            groups.back().push_back({pi, k0, k1, (unsigned)used});
+            used += need;  maxUsed = std::max(maxUsed, used);
+        }
+    }
+    if (maxUsed >= ((size_t)1 << 31)) throw std::runtime_error("b200pt_render: pool too large");
+    ensurePool(c, std::max<size_t>(maxUsed, 1), cfg.write_aovs != 0);
+
+    PathPool pool{c->rng.p, c->thr.p, c->state.p, c->direct.p, c->indirect.p, c->alpha.p, c->pending.p, c->aovN.p, c->aovA.p};
+    Queues Q;
+    for (int i = 0; i < 2; ++i) { Q.rayO[i] = c->rayO[i].p;  Q.rayD[i] = c->rayD[i].p; }
+    Q.hit = c->hit.p;  Q.shO = c->shO.p;  Q.shD = c->shD.p;  Q.counters = c->counters.p;
+
+    const bool prof = cfg.profile != 0;
+    c->evUsed.clear();  c->evNext = 0;  c->profiled = prof;
+    StageTimer T{c, prof};
+    cudaEvent_t a = nullptr, b = nullptr, ta = nullptr, tb = nullptr;
+    unsigned launches = 0, nClosest = 0, nAny = 0;
+    CUDA_OK(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned) * (QC_COUNT + 8), s));
+    if (prof) CUDA_OK(cudaMemsetAsync(c->stats.p, 0, 2 * sizeof(TraceStats), s));
+    T.begin(ST_TOTAL, ta, tb);
+    const int bounces = cfg.max_depth + ((c->hasCatcher || cfg.max_depth == 0) ? 1 : 0);   // the dropped last segment is traced only if alpha can still change
+    for (auto& group : groups) {
+        if (group.empty()) continue;
+        CUDA_OK(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned) * QC_COUNT, s));
+        T.begin(ST_RAYGEN, a, b);
+        for (auto& ch : group) {
+            PassParams P = passes[ch.pass].P;  P.slotBase = ch.slotBase;
+            launchRaygen(F, P, ch.k0, ch.k1, pool, Q, s);  ++launches;
+        }
+        T.end(b);
+        int cur = 0;
+        for (int d = 0; d < bounces; ++d) {
+            resetCountersKernel<<<1, 1, 0, s>>>(c->counters.p, cur ^ 1, d == 0);  ++launches;
+            T.begin(ST_CLOSEST, a, b);
+            launchTraceClosest(S, Q.rayO[cur], Q.rayD[cur], Q.hit, Q.counters + (cur ? QC_RAY1 : QC_RAY0), Q.counters + QC_HEAD_CLOSEST,
+                               cfg.tmin, cfg.tmax, prof ? c->stats.p : nullptr, s);
+            T.end(b);  ++launches;  ++nClosest;
+            T.begin(ST_SHADE, a, b);
+            launchShade(F, S, pool, Q, cur, d, s);
+            T.end(b);  ++launches;
+            T.begin(ST_ANY, a, b);
+            launchTraceAny(S, Q.shO, Q.shD, Q.counters + QC_SHADOW, Q.counters + QC_HEAD_ANY, cfg.tmin, cfg.tmax,
+                           cfg.shadow_mode == B200PT_SHADOW_CULL_BACK, pool, prof ? c->stats.p + 1 : nullptr, s);
+            T.end(b);  ++launches;  ++nAny;
+            tallyShadowKernel<<<1, 1, 0, s>>>(c->counters.p);  ++launches;
+            cur ^= 1;
+        }
+        T.begin(ST_ACCUM, a, b);
+        for (auto& ch : group) {
+            PassParams P = passes[ch.pass].P;  P.slotBase = ch.slotBase;
+            launchGather(F, P, ch.k0, ch.k1, pool, c->sumRad.p, c->sumAlpha.p, c->sumNormal.p, c->sumAlbedo.p, s);  ++launches;
+        }
+        T.end(b);
+    }
+    T.begin(ST_ACCUM, a, b);
+    for (auto& p : passes) {                                                     // pass order = the reference's launch order (overwrite semantics)
+        if (!p.nLaunch) continue;
+        launchFinalize(F, p.P, c->sumRad.p, c->sumAlpha.p, c->sumNormal.p, c->sumAlbedo.p, s);  ++launches;
+    }
+    T.end(b);
+    T.end(tb);
+    CUDA_OK(cudaGetLastError());
+    c->last = b200pt_counters{};
+    c->last.kernel_launches = launches;  c->last.n_trace_closest_launches = nClosest;  c->last.n_trace_any_launches = nAny;
+    c->countersPending = true;
+    if (sync) {
+        CUDA_OK(cudaStreamSynchronize(s));                                       // CUDA_SYNC_CHECK, SimplePathtracer.cpp:214
+        collectCounters(c);
+    }
+}
+
+extern "C" {
+
+int b200pt_resize(b200pt_ctx* c, int w, int h, LaunchParams* params) {
+    if (!c || !params) return fail("b200pt_resize: null argument");
+    if (w == 0 || h == 0) return 0;                                              // minimised window, SimplePathtracer.cpp:233
+    if (w < 0 || h < 0) return fail("b200pt_resize: negative size");
+    API_BEGIN
+    CUDA_OK(cudaSetDevice(c->device));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    const size_t n = (size_t)w * h;
+    c->frameBuf.release();  c->accumBuf.release();  c->normalBuf.release();  c->albedoBuf.release();  c->colorBuf.release();
+    c->frameBuf.ensure(n);  c->accumBuf.ensure(n);  c->normalBuf.ensure(n);  c->albedoBuf.ensure(n);  c->colorBuf.ensure(n);
+    c->W = w;  c->H = h;
+    params->frame.size = make_int2(w, h);
+    params->frame.frame_buffer = (uchar4*)c->frameBuf.p;  params->frame.accum_buffer = c->accumBuf.p;
+    params->frame.normal_buffer = c->normalBuf.p;  params->frame.color_buffer = c->colorBuf.p;  params->frame.albedo_buffer = c->albedoBuf.p;
+    API_END
+}
+
+int b200pt_set_probe(b200pt_ctx* c, int w, int h, const float* data, const float* pdfX, const float* cdfX, const float* pdfY,
+                     const float* cdfY, const float* offset, LaunchParams* params) {
+    if (!c || !params) return fail("b200pt_set_probe: null argument");
+    if (w <= 0 || h <= 0 || !data || !pdfX || !cdfX || !pdfY || !cdfY) return fail("Probe Data is not valid");   // Probe.h:104-105
+    API_BEGIN
+    CUDA_OK(cudaSetDevice(c->device));
+    const size_t n = (size_t)w * h;
+    c->probeData.ensure(4 * n);  c->probePdfX.ensure(n);  c->probeCdfX.ensure(n);  c->probePdfY.ensure(h);  c->probeCdfY.ensure(h);
+    CUDA_OK(cudaMemcpyAsync(c->probeData.p, data, 16 * n, cudaMemcpyHostToDevice, c->stream));
+    CUDA_OK(cudaMemcpyAsync(c->probePdfX.p, pdfX, 4 * n, cudaMemcpyHostToDevice, c->stream));
+    CUDA_OK(cudaMemcpyAsync(c->probeCdfX.p, cdfX, 4 * n, cudaMemcpyHostToDevice, c->stream));
+    CUDA_OK(cudaMemcpyAsync(c->probePdfY.p, pdfY, 4 * (size_t)h, cudaMemcpyHostToDevice, c->stream));
+    CUDA_OK(cudaMemcpyAsync(c->probeCdfY.p, cdfY, 4 * (size_t)h, cudaMemcpyHostToDevice, c->stream));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    params->probe.width = w;  params->probe.height = h;  params->probe.data = (Color*)c->probeData.p;
+    params->probe.pdfValuesX = c->probePdfX.p;  params->probe.cdfValuesX = c->probeCdfX.p;
+    params->probe.pdfValuesY = c->probePdfY.p;  params->probe.cdfValuesY = c->probeCdfY.p;
+    params->probe.offset = offset ? make_float3(offset[0], offset[1], offset[2]) : make_float3(0.f, 0.f, 0.f);
+    API_END
+}
+
+int b200pt_render(b200pt_ctx* c, LaunchParams* params, const b200pt_config* cfg) {
+    API_BEGIN
+    renderImpl(c, params, cfg, true);
+    API_END
+}
+int b200pt_render_async(b200pt_ctx* c, LaunchParams* params, const b200pt_config* cfg) {
+    API_BEGIN
+    renderImpl(c, params, cfg, false);
+    API_END
+}
+int b200pt_synchronize(b200pt_ctx* c) {
+    if (!c) return fail("b200pt_synchronize: null context");
+    API_BEGIN
+    CUDA_OK(cudaSetDevice(c->device));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    collectCounters(c);
+    API_END
+}
+
+}  // extern "C"

@@ -1,0 +1,411 @@
+// b200pt — LBVH builder (replaces optixAccelBuild + optixAccelCompact, sv4/SimplePathtracer.cpp:670-737).
+// Stages, all on the GPU:
+//   1. triBoundsKernel   per-triangle AABB + scene AABB                (HBM stream: 12 B index + 36 B verts in, 32 B out)
+//   2. mortonKernel      63-bit Morton code of the AABB centre          (bit-exact vs oracle_morton)
+//   3. radix sort        LSD, 8-bit digits, 64-bit key + 32-bit id, stable (== std::stable_sort order)
+//   4. karrasKernel      Karras 2012 binary radix tree over the sorted codes (index tie-break for duplicates)
+//   5. refitKernel       bottom-up AABBs + SAH cost + leaf-collapse decision (atomic arrival flags)
+//   6. emit              surviving internal nodes -> 64-byte sibling pairs of 32-byte nodes; 48-byte triangle records
+// Integer stages (2,3) are the ones north_star asks to be bit-exact against a host reference.
+#include "common.cuh"
+#include <cfloat>
+
+#define SORT_THREADS 256
+#define SORT_ITEMS 16
+#define SORT_TILE (SORT_THREADS * SORT_ITEMS)
+#define SAH_CI 1.2f
+#define SAH_CT 1.0f
+
+// ---------------------------------------------------------------- float <-> ordered uint for atomic min/max
+__device__ __forceinline__ unsigned fOrder(float f) { unsigned u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+__host__ __device__ inline float fUnorder(unsigned u) {
+    u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(u);
+#else
+    float f;  memcpy(&f, &u, 4);  return f;
+#endif
+}
+
+__global__ void triBoundsKernel(const float3* __restrict__ vtx, const uint3* __restrict__ idx, const unsigned* __restrict__ triMesh,
+                                const MeshInfo* __restrict__ meshes, unsigned n, float4* __restrict__ triLo, float4* __restrict__ triHi,
+                                unsigned* sceneBox /* 6 ordered uints */) {
+    const unsigned g = blockIdx.x * blockDim.x + threadIdx.x;
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    if (g < n) {
+        const unsigned fv = meshes[triMesh[g]].firstVertex;
+        const uint3 id = idx[g];
+        const float3 a = vtx[fv + id.x], b = vtx[fv + id.y], c = vtx[fv + id.z];
+        lo[0] = fminf(fminf(a.x, b.x), c.x);  hi[0] = fmaxf(fmaxf(a.x, b.x), c.x);
+        lo[1] = fminf(fminf(a.y, b.y), c.y);  hi[1] = fmaxf(fmaxf(a.y, b.y), c.y);
+        lo[2] = fminf(fminf(a.z, b.z), c.z);  hi[2] = fmaxf(fmaxf(a.z, b.z), c.z);
+        triLo[g] = make_float4(lo[0], lo[1], lo[2], 0.f);
+        triHi[g] = make_float4(hi[0], hi[1], hi[2], 0.f);
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        float l = lo[a], h = hi[a];
+        for (int off = 16; off; off >>= 1) { l = fminf(l, __shfl_xor_sync(0xffffffffu, l, off));  h = fmaxf(h, __shfl_xor_sync(0xffffffffu, h, off)); }
+        if ((threadIdx.x & 31) == 0) { atomicMin(sceneBox + a, fOrder(l));  atomicMax(sceneBox + 3 + a, fOrder(h)); }
+    }
+}
+
+__device__ __forceinline__ unsigned long long expand21(unsigned v) {
+    unsigned long long x = v & 0x1fffffull;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+
+__global__ void mortonKernel(const float4* __restrict__ triLo, const float4* __restrict__ triHi, unsigned n,
+                             const unsigned* __restrict__ sceneBox, unsigned long long* __restrict__ codes, unsigned* __restrict__ ids) {
+    const unsigned g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n) return;
+    const float4 l = triLo[g], h = triHi[g];
+    const float tl[3] = {l.x, l.y, l.z}, th[3] = {h.x, h.y, h.z};
+    unsigned cell[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float slo = fUnorder(sceneBox[a]), shi = fUnorder(sceneBox[3 + a]);
+        const float e = __fsub_rn(shi, slo);
+        const float scale = e > 0.f ? __fdiv_rn(1.0f, e) : 0.f;
+        const float c = __fmul_rn(0.5f, __fadd_rn(tl[a], th[a]));
+        const float q = __fmul_rn(__fmul_rn(__fsub_rn(c, slo), scale), 2097152.0f);
+        const int qi = (int)q;
+        cell[a] = (unsigned)min(max(qi, 0), 2097151);
+    }
+    codes[g] = (expand21(cell[0]) << 2) | (expand21(cell[1]) << 1) | expand21(cell[2]);
+    ids[g] = g;
+}
+
+// ---------------------------------------------------------------- radix sort (one 8-bit digit per pass)
+__global__ void __launch_bounds__(SORT_THREADS)
+sortHistKernel(const unsigned long long* __restrict__ keys, unsigned n, int shift, unsigned* __restrict__ blockHist, unsigned numBlocks) {
+    __shared__ unsigned hist[256];
+    hist[threadIdx.x] = 0;
+    __syncthreads();
+    const unsigned base = blockIdx.x * SORT_TILE;
+    for (int r = 0; r < SORT_ITEMS; ++r) {
+        const unsigned i = base + r * SORT_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&hist[(unsigned)(keys[i] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    blockHist[threadIdx.x * numBlocks + blockIdx.x] = hist[threadIdx.x];      // digit-major
+}
+
+// exclusive scan of `n` uints by a single CTA (small arrays: histograms, survivor flags)
+__global__ void __launch_bounds__(1024) scanExclusiveKernel(const unsigned* __restrict__ in, unsigned* __restrict__ out, unsigned n, unsigned* total) {
+    __shared__ unsigned part[1024];
+    const unsigned chunk = (n + 1023) / 1024;
+    const unsigned b = threadIdx.x * chunk, e = min(n, b + chunk);
+    unsigned s = 0;
+    for (unsigned i = b; i < e; ++i) s += in[i];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    for (unsigned off = 1; off < 1024; off <<= 1) {
+        unsigned v = threadIdx.x >= off ? part[threadIdx.x - off] : 0;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    unsigned run = threadIdx.x ? part[threadIdx.x - 1] : 0;
+    for (unsigned i = b; i < e; ++i) { const unsigned v = in[i];  out[i] = run;  run += v; }
+    if (threadIdx.x == 1023 && total) *total = part[1023];
+}
+
+__global__ void __launch_bounds__(SORT_THREADS)
+sortScatterKernel(const unsigned long long* __restrict__ keysIn, const unsigned* __restrict__ valsIn,
+                  unsigned long long* __restrict__ keysOut, unsigned* __restrict__ valsOut, unsigned n, int shift,
+                  const unsigned* __restrict__ blockOffset, unsigned numBlocks) {
+    __shared__ unsigned digitBase[256];
+    __shared__ unsigned roundBase[256];
+    __shared__ unsigned warpCount[SORT_THREADS / 32][256];
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    digitBase[threadIdx.x] = blockOffset[threadIdx.x * numBlocks + blockIdx.x];
+    const unsigned base = blockIdx.x * SORT_TILE;
+    for (int r = 0; r < SORT_ITEMS; ++r) {
+        for (int w = 0; w < SORT_THREADS / 32; ++w) warpCount[w][threadIdx.x] = 0;
+        __syncthreads();
+        const unsigned i = base + r * SORT_THREADS + threadIdx.x;
+        const bool valid = i < n;
+        unsigned long long key = 0;  unsigned val = 0, d = 0xffffffffu;
+        if (valid) { key = keysIn[i];  val = valsIn[i];  d = (unsigned)(key >> shift) & 255u; }
+        const unsigned peers = __match_any_sync(0xffffffffu, d);
+        const unsigned rankInWarp = __popc(peers & ((1u << lane) - 1u));
+        if (valid && rankInWarp == 0) warpCount[warp][d] = __popc(peers);
+        __syncthreads();
+        {   // thread `threadIdx.x` owns digit threadIdx.x: exclusive prefix over the warps (stable order)
+            unsigned run = 0;
+            for (int w = 0; w < SORT_THREADS / 32; ++w) { const unsigned c = warpCount[w][threadIdx.x];  warpCount[w][threadIdx.x] = run;  run += c; }
+            roundBase[threadIdx.x] = digitBase[threadIdx.x];
+            digitBase[threadIdx.x] += run;
+        }
+        __syncthreads();
+        if (valid) {
+            const unsigned pos = roundBase[d] + warpCount[warp][d] + rankInWarp;
+            keysOut[pos] = key;  valsOut[pos] = val;
+        }
+        __syncthreads();
+    }
+}
+
+static void radixSort64(unsigned long long*& keys, unsigned*& vals, unsigned long long*& keysTmp, unsigned*& valsTmp, unsigned n,
+                        unsigned* blockHist, unsigned* blockOffset, cudaStream_t s) {
+    const unsigned numBlocks = (n + SORT_TILE - 1) / SORT_TILE;
+    for (int pass = 0; pass < 8; ++pass) {
+        const int shift = pass * 8;
+        sortHistKernel<<<numBlocks, SORT_THREADS, 0, s>>>(keys, n, shift, blockHist, numBlocks);
+        scanExclusiveKernel<<<1, 1024, 0, s>>>(blockHist, blockOffset, 256u * numBlocks, nullptr);
+        sortScatterKernel<<<numBlocks, SORT_THREADS, 0, s>>>(keys, vals, keysTmp, valsTmp, n, shift, blockOffset, numBlocks);
+        std::swap(keys, keysTmp);  std::swap(vals, valsTmp);
+    }
+}
+
+// ---------------------------------------------------------------- Karras 2012 hierarchy
+// node ids: internal i in [0, n-1), leaf j -> (n-1)+j.  delta = common-prefix length with index tie-break.
+__device__ __forceinline__ int kDelta(const unsigned long long* __restrict__ codes, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    const unsigned long long a = codes[i], b = codes[j];
+    if (a != b) return __clzll((long long)(a ^ b));
+    return 64 + __clz(i ^ j);
+}
+
+__global__ void karrasKernel(const unsigned long long* __restrict__ codes, int n, int* __restrict__ left, int* __restrict__ right,
+                             int* __restrict__ parent, int2* __restrict__ range) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const int d = (kDelta(codes, n, i, i + 1) - kDelta(codes, n, i, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = kDelta(codes, n, i, i - d);
+    int lmax = 2;
+    while (kDelta(codes, n, i, i + lmax * d) > dmin) lmax *= 2;
+    int l = 0;
+    for (int t = lmax / 2; t >= 1; t /= 2)
+        if (kDelta(codes, n, i, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = kDelta(codes, n, i, j);
+    int s = 0, t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (kDelta(codes, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    const int gamma = i + s * d + min(d, 0);
+    const int lo = min(i, j), hi = max(i, j);
+    const int lc = (lo == gamma) ? (n - 1) + gamma : gamma;
+    const int rc = (hi == gamma + 1) ? (n - 1) + gamma + 1 : gamma + 1;
+    left[i] = lc;  right[i] = rc;
+    parent[lc] = i;  parent[rc] = i;
+    range[i] = make_int2(lo, hi);
+    if (i == 0) parent[0] = -1;
+}
+
+__device__ __forceinline__ float boxArea(float4 lo, float4 hi) {
+    const float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
+    return 2.f * (dx * dy + dy * dz + dz * dx);
+}
+
+// bottom-up: boxes, SAH cost with and without leaf collapse.  boxLo.w carries the collapsed-tree cost,
+// boxHi.w the plain LBVH cost (one triangle per leaf).
+__global__ void refitKernel(const float4* __restrict__ triLo, const float4* __restrict__ triHi, const unsigned* __restrict__ sortedGid,
+                            int n, const int* __restrict__ left, const int* __restrict__ right, const int* __restrict__ parent,
+                            const int2* __restrict__ range, float4* boxLo, float4* boxHi, unsigned* flags, unsigned char* collapse) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const unsigned g = sortedGid[j];
+    float4 lo = triLo[g], hi = triHi[g];
+    const float a = boxArea(lo, hi);
+    lo.w = SAH_CT * a;  hi.w = SAH_CT * a;
+    int node = (n - 1) + j;
+    boxLo[node] = lo;  boxHi[node] = hi;
+    __threadfence();
+    int p = parent[node];
+    while (p >= 0) {
+        if (atomicAdd(flags + p, 1u) == 0u) return;           // first child to arrive stops; the second one continues
+        __threadfence();
+        const int lc = left[p], rc = right[p];
+        const float4 llo = __ldcg(boxLo + lc), lhi = __ldcg(boxHi + lc), rlo = __ldcg(boxLo + rc), rhi = __ldcg(boxHi + rc);
+        float4 plo = make_float4(fminf(llo.x, rlo.x), fminf(llo.y, rlo.y), fminf(llo.z, rlo.z), 0.f);
+        float4 phi = make_float4(fmaxf(lhi.x, rhi.x), fmaxf(lhi.y, rhi.y), fmaxf(lhi.z, rhi.z), 0.f);
+        const float area = boxArea(plo, phi);
+        const int2 rg = range[p];
+        const int count = rg.y - rg.x + 1;
+        const float cInt = SAH_CI * area + llo.w + rlo.w;
+        const float cLeaf = SAH_CT * area * (float)count;
+        const bool col = count <= B200PT_MAX_LEAF && cLeaf <= cInt;
+        collapse[p] = col ? 1 : 0;
+        plo.w = col ? cLeaf : cInt;
+        phi.w = SAH_CI * area + lhi.w + rhi.w;
+        boxLo[p] = plo;  boxHi[p] = phi;
+        __threadfence();
+        p = parent[p];
+    }
+}
+
+// survivors = internal nodes that stay internal: not collapsed and with no collapsed ancestor.  Also max depth.
+__global__ void surviveKernel(int n, const int* __restrict__ parent, const unsigned char* __restrict__ collapse,
+                              unsigned* __restrict__ survive, unsigned* maxDepth) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    bool dead = collapse[i] != 0;
+    unsigned depth = 1;
+    for (int p = parent[i]; p >= 0; p = parent[p]) { dead = dead || collapse[p] != 0;  ++depth; }
+    survive[i] = dead ? 0u : 1u;
+    if (!dead) atomicMax(maxDepth, depth);
+}
+
+__device__ __forceinline__ void padBox(float4& lo, float4& hi) {
+    const float mx = fmaxf(fabsf(lo.x), fabsf(hi.x)) * 4e-7f + 1e-30f, my = fmaxf(fabsf(lo.y), fabsf(hi.y)) * 4e-7f + 1e-30f,
+                mz = fmaxf(fabsf(lo.z), fabsf(hi.z)) * 4e-7f + 1e-30f;
+    lo.x -= mx;  lo.y -= my;  lo.z -= mz;  hi.x += mx;  hi.y += my;  hi.z += mz;
+}
+
+__device__ __forceinline__ int childLink(int c, int n, const unsigned char* collapse, const int2* range, const unsigned* slotIdx,
+                                         unsigned* leafCount, unsigned* maxLeaf) {
+    if (c >= n - 1) { atomicAdd(leafCount, 1u);  atomicMax(maxLeaf, 1u);  return leafEncode((unsigned)(c - (n - 1)), 1u); }
+    if (collapse[c]) {
+        const int2 rg = range[c];
+        atomicAdd(leafCount, 1u);  atomicMax(maxLeaf, (unsigned)(rg.y - rg.x + 1));
+        return leafEncode((unsigned)rg.x, (unsigned)(rg.y - rg.x + 1));
+    }
+    return 2 + 2 * (int)slotIdx[c];
+}
+
+__global__ void emitNodesKernel(int n, const int* __restrict__ left, const int* __restrict__ right, const int2* __restrict__ range,
+                                const unsigned char* __restrict__ collapse, const unsigned* __restrict__ survive,
+                                const unsigned* __restrict__ slotIdx, const float4* __restrict__ boxLo, const float4* __restrict__ boxHi,
+                                float4* __restrict__ nodes, unsigned* leafCount, unsigned* maxLeaf) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) {   // root record + pad
+        float4 lo = boxLo[0], hi = boxHi[0];
+        padBox(lo, hi);
+        int link;
+        if (n == 1) { link = leafEncode(0u, 1u);  atomicAdd(leafCount, 1u);  atomicMax(maxLeaf, 1u); }
+        else if (collapse[0]) { link = leafEncode(0u, (unsigned)n);  atomicAdd(leafCount, 1u);  atomicMax(maxLeaf, (unsigned)n); }
+        else link = 2;
+        nodes[0] = make_float4(lo.x, lo.y, lo.z, __int_as_float(link));
+        nodes[1] = make_float4(hi.x, hi.y, hi.z, 0.f);
+        nodes[2] = make_float4(0, 0, 0, 0);  nodes[3] = make_float4(0, 0, 0, 0);
+    }
+    if (i >= n - 1 || !survive[i]) return;
+    float4* out = nodes + 2 * (size_t)(2 + 2 * slotIdx[i]);
+    const int cs[2] = {left[i], right[i]};
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        float4 lo = boxLo[cs[k]], hi = boxHi[cs[k]];
+        padBox(lo, hi);
+        const int link = childLink(cs[k], n, collapse, range, slotIdx, leafCount, maxLeaf);
+        out[2 * k] = make_float4(lo.x, lo.y, lo.z, __int_as_float(link));
+        out[2 * k + 1] = make_float4(hi.x, hi.y, hi.z, 0.f);
+    }
+}
+
+// 48-byte triangle records in BVH order: {v0, e1 = v1-v0, e2 = v2-v0, gid, mesh}
+__global__ void emitTrisKernel(const float3* __restrict__ vtx, const uint3* __restrict__ idx, const unsigned* __restrict__ triMesh,
+                               const MeshInfo* __restrict__ meshes, const unsigned* __restrict__ sortedGid, unsigned n, float4* __restrict__ tris) {
+    const unsigned s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    const unsigned g = sortedGid[s];
+    const unsigned m = triMesh[g];
+    const unsigned fv = meshes[m].firstVertex;
+    const uint3 id = idx[g];
+    const float3 a = vtx[fv + id.x], b = vtx[fv + id.y], c = vtx[fv + id.z];
+    const float e1x = __fsub_rn(b.x, a.x), e1y = __fsub_rn(b.y, a.y), e1z = __fsub_rn(b.z, a.z);
+    const float e2x = __fsub_rn(c.x, a.x), e2y = __fsub_rn(c.y, a.y), e2z = __fsub_rn(c.z, a.z);
+    tris[3 * (size_t)s] = make_float4(a.x, a.y, a.z, e1x);
+    tris[3 * (size_t)s + 1] = make_float4(e1y, e1z, e2x, e2y);
+    tris[3 * (size_t)s + 2] = make_float4(e2z, __int_as_float((int)g), __int_as_float((int)m), 0.f);
+}
+
+__global__ void scatterCodesKernel(const unsigned long long* __restrict__ sortedCodes, const unsigned* __restrict__ sortedGid, unsigned n,
+                                   unsigned long long* __restrict__ byGid) {
+    const unsigned s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < n) byGid[sortedGid[s]] = sortedCodes[s];
+}
+
+// ---------------------------------------------------------------- host driver
+template <typename T> static T* dalloc(size_t n) { T* p = nullptr;  CUDA_OK(cudaMalloc((void**)&p, std::max<size_t>(n, 1) * sizeof(T)));  return p; }
+
+void bvhFree(BvhBuildResult& r) {
+    cudaFree(r.nodes);  cudaFree(r.tris);  cudaFree(r.mortonByGid);  cudaFree(r.sortedGid);
+    r = BvhBuildResult();
+}
+
+void bvhBuild(const float3* d_vertices, const uint3* d_indices, const unsigned* d_triMesh, const MeshInfo* d_meshes,
+              unsigned nTris, cudaStream_t s, BvhBuildResult& out) {
+    out = BvhBuildResult();
+    out.nTris = nTris;
+    if (nTris == 0) {                                        // empty scene: a root whose link is the EMPTY sentinel
+        out.nodes = dalloc<BvhNode>(2);
+        BvhNode h[2];  memset(h, 0, sizeof(h));  h[0].link = 0x7fffffff;
+        CUDA_OK(cudaMemcpy(out.nodes, h, sizeof(h), cudaMemcpyHostToDevice));
+        out.tris = dalloc<float4>(3);  out.nNodes = 2;
+        return;
+    }
+    const int n = (int)nTris;
+    cudaEvent_t e0, e1;
+    CUDA_OK(cudaEventCreate(&e0));  CUDA_OK(cudaEventCreate(&e1));
+    CUDA_OK(cudaEventRecord(e0, s));
+    const unsigned B = 256, G = (nTris + B - 1) / B;
+    float4* triLo = dalloc<float4>(nTris);  float4* triHi = dalloc<float4>(nTris);
+    unsigned* sceneBox = dalloc<unsigned>(8);
+    const unsigned boxInit[8] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u, 0u, 0u};
+    CUDA_OK(cudaMemcpyAsync(sceneBox, boxInit, sizeof(boxInit), cudaMemcpyHostToDevice, s));
+    triBoundsKernel<<<G, B, 0, s>>>(d_vertices, d_indices, d_triMesh, d_meshes, nTris, triLo, triHi, sceneBox);
+
+    unsigned long long* keys = dalloc<unsigned long long>(nTris);  unsigned long long* keysTmp = dalloc<unsigned long long>(nTris);
+    unsigned* vals = dalloc<unsigned>(nTris);  unsigned* valsTmp = dalloc<unsigned>(nTris);
+    mortonKernel<<<G, B, 0, s>>>(triLo, triHi, nTris, sceneBox, keys, vals);
+    const unsigned numBlocks = (nTris + SORT_TILE - 1) / SORT_TILE;
+    unsigned* blockHist = dalloc<unsigned>(256u * numBlocks);  unsigned* blockOffset = dalloc<unsigned>(256u * numBlocks);
+    radixSort64(keys, vals, keysTmp, valsTmp, nTris, blockHist, blockOffset, s);
+    out.sortedGid = vals;                                    // kept: sorted order for the parity hook
+    out.mortonByGid = keysTmp;                               // reuse the spare key buffer for codes in input order
+    scatterCodesKernel<<<G, B, 0, s>>>(keys, vals, nTris, out.mortonByGid);
+
+    const size_t nAll = 2 * (size_t)n;                       // internal [0,n-1) + leaves [n-1, 2n-1)
+    int* left = dalloc<int>(n);  int* right = dalloc<int>(n);  int* parent = dalloc<int>(nAll);  int2* range = dalloc<int2>(n);
+    float4* boxLo = dalloc<float4>(nAll);  float4* boxHi = dalloc<float4>(nAll);
+    unsigned* flags = dalloc<unsigned>(n);  unsigned char* collapse = dalloc<unsigned char>(n);
+    unsigned* survive = dalloc<unsigned>(n);  unsigned* slotIdx = dalloc<unsigned>(n);
+    unsigned* scalars = dalloc<unsigned>(4);                 // [0] survivors, [1] max depth, [2] leaves, [3] max leaf size
+    CUDA_OK(cudaMemsetAsync(flags, 0, sizeof(unsigned) * n, s));
+    CUDA_OK(cudaMemsetAsync(collapse, 0, n, s));
+    CUDA_OK(cudaMemsetAsync(scalars, 0, 4 * sizeof(unsigned), s));
+    CUDA_OK(cudaMemsetAsync(parent, 0xff, sizeof(int) * nAll, s));
+    if (n > 1) karrasKernel<<<(n - 1 + B - 1) / B, B, 0, s>>>(keys, n, left, right, parent, range);
+    refitKernel<<<G, B, 0, s>>>(triLo, triHi, vals, n, left, right, parent, range, boxLo, boxHi, flags, collapse);
+    unsigned nSurvive = 0;
+    if (n > 1) {
+        surviveKernel<<<(n - 1 + B - 1) / B, B, 0, s>>>(n, parent, collapse, survive, scalars + 1);
+        scanExclusiveKernel<<<1, 1024, 0, s>>>(survive, slotIdx, (unsigned)(n - 1), scalars);
+        CUDA_OK(cudaMemcpyAsync(&nSurvive, scalars, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaStreamSynchronize(s));
+    }
+    out.nNodes = 2 + 2 * nSurvive;
+    out.nodes = dalloc<BvhNode>(out.nNodes + 2);
+    out.tris = dalloc<float4>(3 * (size_t)nTris);
+    emitNodesKernel<<<(std::max(n - 1, 1) + B - 1) / B, B, 0, s>>>(n, left, right, range, collapse, survive, slotIdx, boxLo, boxHi,
+                                                                  (float4*)out.nodes, scalars + 2, scalars + 3);
+    emitTrisKernel<<<G, B, 0, s>>>(d_vertices, d_indices, d_triMesh, d_meshes, vals, nTris, out.tris);
+    CUDA_OK(cudaEventRecord(e1, s));
+    unsigned hs[4];  float4 rootLo, rootHi;  unsigned hostBox[8];
+    CUDA_OK(cudaMemcpyAsync(hs, scalars, sizeof(hs), cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaMemcpyAsync(&rootLo, boxLo, sizeof(float4), cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaMemcpyAsync(&rootHi, boxHi, sizeof(float4), cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaMemcpyAsync(hostBox, sceneBox, sizeof(hostBox), cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaStreamSynchronize(s));
+    CUDA_OK(cudaEventElapsedTime(&out.buildMs, e0, e1));
+    cudaEventDestroy(e0);  cudaEventDestroy(e1);
+    out.maxDepth = hs[1] + 1;  out.nLeaves = hs[2];  out.maxLeaf = hs[3];
+    const float dx = rootHi.x - rootLo.x, dy = rootHi.y - rootLo.y, dz = rootHi.z - rootLo.z;
+    const float rootArea = 2.f * (dx * dy + dy * dz + dz * dx);
+    out.sahCost = rootArea > 0.f ? rootLo.w / rootArea : 0.f;
+    out.sahCostLbvh = rootArea > 0.f ? rootHi.w / rootArea : 0.f;
+    for (int a = 0; a < 6; ++a) out.sceneBounds[a] = fUnorder(hostBox[a]);
+    cudaFree(triLo);  cudaFree(triHi);  cudaFree(sceneBox);  cudaFree(keys);  cudaFree(valsTmp);  cudaFree(blockHist);  cudaFree(blockOffset);
+    cudaFree(left);  cudaFree(right);  cudaFree(parent);  cudaFree(range);  cudaFree(boxLo);  cudaFree(boxHi);  cudaFree(flags);
+    cudaFree(collapse);  cudaFree(survive);  cudaFree(slotIdx);  cudaFree(scalars);
+    if (out.maxDepth > B200PT_STACK - 2) throw std::runtime_error("BVH deeper than the traversal stack");
+}

@@ -1,0 +1,141 @@
+// b200pt — shared declarations of the CUDA implementation (sm_100a).
+// Data layout in HBM:
+//   BvhNode   32 B  {lo.xyz, link | hi.xyz, aux}; siblings adjacent and 64-byte aligned (one 4x128-bit fetch per step)
+//   TriRecord 48 B  {v0.xyz,e1.x | e1.yz,e2.xy | e2.z, gid, mesh, -}  in BVH (Morton) order — the "Woop-sized" record;
+//                   untransformed edges so the device test is bit-identical to the oracle's and so the shading
+//                   normal cross(e1,e2) (sv4/deviceProgram.cu:598-605) needs no second gather
+//   queues    32 B ray {o.xyz, slot | d.xyz, -}, 16 B hit {t,u,v,triSlot}
+//   path state SoA indexed by sample slot.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+#include <stdexcept>
+#include "../../include/b200pt.h"
+#include "../../include/ref_api/LaunchParams.h"
+
+#define B200PT_NUM_SMS 148
+
+struct BvhNode { float lo[3]; int link; float hi[3]; int aux; };      // link >= 0: index of the child pair; < 0: leaf code
+static_assert(sizeof(BvhNode) == 32, "BvhNode must be 32 bytes");
+// leaf code: -(1 + first*8 + (count-1)), count in 1..8
+__host__ __device__ inline int leafEncode(unsigned first, unsigned count) { return -(int)(1u + first * 8u + (count - 1u)); }
+__host__ __device__ inline void leafDecode(int link, unsigned& first, unsigned& count) {
+    unsigned c = (unsigned)(-(link + 1));
+    first = c >> 3;  count = (c & 7u) + 1u;
+}
+#define B200PT_MAX_LEAF 8
+#define B200PT_STACK 96
+
+struct MeshInfo {                  // device-side stand-in for the per-mesh SBT record (sv4/LaunchParams.h:38-47)
+    Material material;             // 104 B, reference layout
+    unsigned firstTri;             // global id of the mesh's triangle 0
+    unsigned firstVertex;          // offset into the global vertex / texcoord arrays
+    int      textureID;            // -1 = none
+    int      hasTexcoord;
+    unsigned texOffset;            // first texel of the texture in the RGBA8 pool
+    int      texW, texH;
+    int      pad;
+};
+static_assert(sizeof(MeshInfo) == 136, "MeshInfo");
+
+struct SceneDev {                  // everything the kernels need about the scene (passed by value)
+    const float4* nodes;           // BvhNode pairs viewed as float4 x2
+    const float4* tris;            // TriRecord viewed as float4 x3, BVH order
+    const MeshInfo* meshes;
+    const uint3* indices;          // global index buffer, LOCAL vertex ids (per mesh)
+    const float2* texcoords;       // global, per vertex (zeros where a mesh has none)
+    const uint32_t* texels;        // RGBA8 pool
+    unsigned nTris, nNodes;
+};
+
+struct PassParams {                // one optixLaunch of the reference = one pass of the wavefront
+    int launchW, launchH;
+    unsigned factorX, factorY;
+    int fillSize;
+    unsigned cX, cY;
+    float rInner, rOuter;
+    unsigned offX, offY;
+    unsigned redraw;
+    unsigned subframe;
+    int spl;                       // samples_per_launch of this pass
+    unsigned slotBase;             // first sample slot of this pass in the pool
+    unsigned launchBase;           // first launch-index record of this pass
+};
+
+struct FrameParams {               // shared by every pass of a frame
+    int W, H;
+    float3 eye, U, V, Wv;
+    Probe probe;                   // device pointers
+    float tmin, tmax;
+    int maxDepth, shadowMode, display, accumMode, writeAovs;
+    float exposure;
+    int tileRank, tileCount;
+    float4* accum;  uint32_t* frame;  float4* normal;  float4* albedo;  float4* color;
+};
+
+struct PathPool {                  // SoA path state, indexed by sample slot
+    uint2*  rng;                   // Random {seed1, seed2}
+    float4* thr;                   // throughput.xyz, rayEta
+    int*    state;                 // depth | flags<<8
+    float4* direct;                // radiance added at depth 0
+    float4* indirect;              // radiance added at depth >= 1, in bounce order
+    float4* alpha;                 // prd.alpha
+    float4* pending;               // NEE contribution awaiting its shadow ray
+    float4* aovNormal;             // only with write_aovs
+    float4* aovAlbedo;
+};
+
+struct Queues {
+    float4* rayO[2];  float4* rayD[2];      // double-buffered extension-ray queue
+    float4* hit;                             // closest-hit results, same order as the current ray queue
+    float4* shO;  float4* shD;              // shadow-ray queue
+    unsigned* counters;                      // see QC_* below
+};
+enum { QC_RAY0 = 0, QC_RAY1 = 1, QC_SHADOW = 2, QC_HEAD_CLOSEST = 3, QC_HEAD_ANY = 4, QC_COUNT = 8 };
+
+struct TraceStats { unsigned long long nodes, tris, rays; };
+
+#define CUDA_OK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
+    throw std::runtime_error(std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+
+// path flags (sv4/deviceProgram.cu:54-56 + internal)
+#define PF_DONE       1
+#define PF_SECONDARY  2
+#define PF_ALPHA_ONE  4
+
+// ---- launchers implemented in the .cu files ------------------------------------------------------------
+// bvh_build.cu
+struct BvhBuildResult {
+    BvhNode* nodes = nullptr;  float4* tris = nullptr;  unsigned nNodes = 0, nTris = 0, nLeaves = 0, maxLeaf = 0, maxDepth = 0;
+    float sahCost = 0.f, sahCostLbvh = 0.f, buildMs = 0.f;
+    unsigned long long* mortonByGid = nullptr;  uint32_t* sortedGid = nullptr;  float sceneBounds[6] = {0, 0, 0, 0, 0, 0};
+};
+void bvhBuild(const float3* d_vertices, const uint3* d_indices, const unsigned* d_triMesh, const MeshInfo* d_meshes,
+              unsigned nTris, cudaStream_t stream, BvhBuildResult& out);
+void bvhFree(BvhBuildResult& r);
+
+// trace.cu  (compiled with FMA contraction; the triangle test itself uses explicit _rn intrinsics)
+void launchTraceClosest(const SceneDev& scene, const float4* rayO, const float4* rayD, float4* hit, const unsigned* count,
+                        unsigned* head, float tmin, float tmax, TraceStats* stats, cudaStream_t stream);
+void launchTraceAny(const SceneDev& scene, const float4* shO, const float4* shD, const unsigned* count, unsigned* head,
+                    float tmin, float tmax, int cullBack, const PathPool& pool, TraceStats* stats, cudaStream_t stream);
+void launchTraceRaysDebug(const SceneDev& scene, const float4* rayO, const float4* rayD, unsigned n, float tmin, float tmax,
+                          int anyHit, int cullBack, float4* hitOut, cudaStream_t stream);
+
+// shade.cu  (compiled with -fmad=false: basic fp32 arithmetic bit-identical to the IEEE host oracle)
+void launchRaygen(const FrameParams& F, const PassParams& P, int k0, int k1, const PathPool& pool, const Queues& Q,
+                  cudaStream_t stream);
+void launchShade(const FrameParams& F, const SceneDev& scene, const PathPool& pool, const Queues& Q, int cur, int depth,
+                 cudaStream_t stream);
+void launchGather(const FrameParams& F, const PassParams& P, int k0, int k1, const PathPool& pool, float4* sumRad,
+                  float4* sumAlpha, float4* sumNormal, float4* sumAlbedo, cudaStream_t stream);
+void launchFinalize(const FrameParams& F, const PassParams& P, const float4* sumRad, const float4* sumAlpha,
+                    const float4* sumNormal, const float4* sumAlbedo, cudaStream_t stream);
+void launchResolveSum(const FrameParams& F, int nPasses, cudaStream_t stream);
+void launchTonemapSqrt(int w, int h, const float4* in, uint32_t* out, cudaStream_t stream);
+void launchPrimaryRays(const FrameParams& F, const PassParams& P, float4* rayO, float4* rayD, cudaStream_t stream);
+void launchResolvePrimary(const SceneDev& scene, const float4* hit, unsigned n, const float4* rayO, int32_t* prim, int32_t* mesh,
+                          float* t, float* u, float* v, cudaStream_t stream);

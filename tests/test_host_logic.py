@@ -1,0 +1,76 @@
+"""Host-side mirror of the reference interface: loadOBJ / addBox / scenes / probe / schedule bookkeeping."""
+import numpy as np
+import pytest
+
+from optixpathtracer_b200 import Material, Model, addBox, host_params, loadColor, loadOBJ, preset, preset_camera, scenes
+from optixpathtracer_b200.probe import analytic_sky
+
+
+def test_cornell_through_loadobj(tmp_path):
+    model = scenes.cornell(directory=str(tmp_path))
+    assert model.num_triangles() == 32
+    assert [len(m.index) for m in model.meshes] == [6, 2, 2, 2, 20]          # one mesh per (shape, material id)
+    light = model.meshes[3]
+    assert light.material.emission.tolist() == [12.0, 12.0, 12.0]
+    # loadOBJ overwrites only color + emission: everything else is the sv4 constructor default (Model.cpp:189-190)
+    assert abs(light.material.transmission - 0.4) < 1e-7 and abs(light.material.metallic - 0.5) < 1e-7
+    for m in model.meshes:
+        assert m.index.max() < len(m.vertex)                                 # vertices de-duplicated per mesh
+    assert len(model.meshes[0].vertex) == 12                                 # 3 quads, 4 shared corners each
+    with pytest.raises(RuntimeError):
+        loadOBJ(str(tmp_path / "missing.obj"))
+
+
+def test_addbox_matches_reference_layout():
+    model = Model()
+    mat = Material(color=(0.2, 0.3, 0.4))
+    mesh = addBox(model, mat, (1.0, 2.0, 3.0), (0.5, 1.0, 1.5))
+    assert mesh.vertex.shape == (36, 3) and mesh.index.shape == (12, 3) and mesh.normal.shape == (36, 3)
+    assert np.array_equal(mesh.index.ravel(), np.arange(36))
+    assert np.allclose(mesh.vertex.min(0), [0.5, 1.0, 1.5]) and np.allclose(mesh.vertex.max(0), [1.5, 3.0, 4.5])
+    assert np.allclose(mesh.vertex[0], [0.5, 1.0, 4.5])                      # A = (-ex+px, -ey+py, ez+pz), Model.cpp:220
+    assert bytes(mesh.material) == bytes(mat)
+
+
+def test_procedural_scene_sizes():
+    s = scenes.sponza_class()
+    assert abs(s.num_triangles() - 262144) <= 0.011 * 262144
+    ext = np.concatenate([m.vertex for m in s.meshes])
+    assert ext.min() >= -2000 and ext.max() <= 2000
+    assert any(m.diffuseTextureID >= 0 for m in s.meshes) and len(s.textures) >= 1
+    le = scenes.lost_empire_class()
+    assert abs(le.num_triangles() - 225000) <= 0.011 * 225000
+    a, b = scenes.sponza_class(20000), scenes.sponza_class(20000)
+    assert all(np.array_equal(x.vertex, y.vertex) for x, y in zip(a.meshes, b.meshes))   # deterministic
+    c = scenes.city_class(300000)
+    assert abs(c.num_triangles() - 300000) <= 0.05 * 300000
+
+
+def test_probe_tables():
+    p = loadColor((1, 1, 1), 64, 32)
+    assert p.valid and p.cdfX.shape == (32, 64)
+    assert np.allclose(p.cdfX[:, -1], 1.0, atol=1e-5) and abs(p.cdfY[-1] - 1.0) < 1e-6
+    assert np.all(np.diff(p.cdfY) >= 0) and np.all(np.diff(p.cdfX, axis=1) >= 0)
+    sky = analytic_sky(128, 64)
+    assert sky.data.shape == (64, 128, 4) and np.isfinite(sky.data).all() and sky.data.max() > 10
+
+
+def test_oracle_schedule_mutates_params_like_the_reference(port):
+    """SampleRenderer::render() leaves pass-3 values in the public launchParams (sv4/SimplePathtracer.cpp:189-212)."""
+    model = scenes.cornell()
+    probe = loadColor((1, 1, 1), 16, 8)
+    sc = port.scene(model, probe, brute_force=True)
+    p = host_params(64, 64, preset_camera("cornell"))
+    p.frame.c.x, p.frame.c.y = 32, 32
+    cfg = preset("sv4_fov", inner_radius=8, outer_radius=20)
+    p.frame.subframe_index = 5
+    accum, frame, cnt, _ = sc.render(p, cfg)
+    assert p.frame.subframe_index == 6
+    assert (p.frame.fillSize, p.samples_per_launch, p.frame.redraw) == (1, 8, 1)
+    assert (p.frame.offset.x, p.frame.offset.y) == (32 - 9, 32 - 9) and p.frame.r_outer == 9.0
+    # budget: periphery 1 spp per 4x4 block, mid ring 2 spp per 2x2, fovea 8 spp per pixel
+    assert 0 < cnt["samples"] < 64 * 64 * 8
+    cfg_u = preset("sv4_uniform")
+    p.frame.subframe_index = 7
+    sc.render(p, cfg_u)
+    assert p.frame.subframe_index == 1 and p.samples_per_launch == 8          # FOV_OFF forces subframe 0, then ++
