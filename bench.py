@@ -168,3 +168,223 @@ def run_reference(a):
             "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------ the B200 arm
+def _peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        p = json.load(open(path))
+        return float(p["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (burst copy bandwidth)"
+    except Exception:
+        return 7700.0, "B200_PROFILING.md fallback (nominal HBM3e ~7.7 TB/s); MEASURED_PEAKS.json absent"
+
+
+def run_b200(a):
+    import torch
+    import torch.distributed as dist
+    from optixpathtracer_b200 import SampleRenderer
+    from optixpathtracer_b200.structs import ACCUM_SUM
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    model, cam, probe, cfg = build_workload(a)
+    t0 = time.time()
+    r = SampleRenderer(model, device=local, config=cfg)
+    ctor_s = time.time() - t0
+    r.resize((a.width, a.height))
+    r.setCamera(cam)
+    r.setProbe(probe)
+    info = r.bvhInfo()
+    n_px = a.width * a.height
+    _, _, stream_ptr = r.deviceBuffers()
+    stream = torch.cuda.ExternalStream(stream_ptr, device=local)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")           # > 126 MB L2
+
+    # N > 1: sample split.  The accumulation buffer is a torch tensor the caller points launchParams at (the
+    # reference's render(CUDAOutputBuffer&) does the same with frame_buffer, SimplePathtracer.cpp:219-229).
+    accum_t = None
+    if world > 1:
+        cfg.accum_mode = ACCUM_SUM
+        accum_t = torch.zeros(n_px * 4, dtype=torch.float32, device="cuda")
+        r.launchParams.frame.accum_buffer = accum_t.data_ptr()
+    cfg.profile = 1                                                              # stage events only (no counter atomics)
+
+    def frame_index(step):                                                      # rank r renders sub-frames r, r+N, ...
+        return step * world + rank
+
+    stage = dict(raygen=0.0, trace_closest=0.0, trace_any=0.0, shade=0.0, accumulate=0.0, total=0.0)
+    n_closest = n_any = launches = 0
+    rays = dict(radiance=0, shadow=0, samples=0)
+
+    def one_step(step, timed):
+        nonlocal n_closest, n_any, launches
+        with torch.cuda.stream(stream):
+            flush.fill_(step & 0xff)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        r.launchParams.frame.subframe_index = frame_index(step)
+        e0.record(stream)
+        r.render(sync=False)
+        e1.record(stream)
+        r.synchronize()
+        if timed:
+            c = r.counters()
+            for k in stage:
+                stage[k] += getattr(c, "ms_" + k)
+            n_closest += c.n_trace_closest_launches
+            n_any += c.n_trace_any_launches
+            launches += c.kernel_launches
+            rays["radiance"] += c.radiance_rays
+            rays["shadow"] += c.shadow_rays
+            rays["samples"] += c.samples
+        return e0.elapsed_time(e1)
+
+    for i in range(a.warmup):
+        one_step(i, False)
+    if world > 1:
+        accum_t.zero_()
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local) if rank == 0 else None
+    wall0 = time.time()
+    ms = 0.0
+    for i in range(a.steps):
+        ms += one_step(a.warmup + i, True)
+    reduce_ms = 0.0
+    if world > 1:                                                                # one fp32 reduce of the SUM buffer + resolve on rank 0
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            e0.record(stream)
+            dist.reduce(accum_t, dst=0, op=dist.ReduceOp.SUM)
+            if rank == 0:
+                r.resolveSum(a.steps * world)
+            e1.record(stream)
+        stream.synchronize()
+        reduce_ms = e0.elapsed_time(e1)
+        ms += reduce_ms
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    wall = time.time() - wall0
+    clocks = sampler.stop() if sampler else None
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        tot = torch.tensor([rays["samples"], rays["radiance"], rays["shadow"], launches], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        all_samples, all_rad, all_sh, all_launches = (float(x) for x in tot.tolist())
+    else:
+        all_samples, all_rad, all_sh, all_launches = rays["samples"], rays["radiance"], rays["shadow"], launches
+    value = all_samples / (ms * 1e-3) / 1e6
+    mrays = (all_rad + all_sh) / (ms * 1e-3) / 1e6
+
+    # ---- e2e: the reference-facing call sequence with HOST buffers, every step (N ranks in parallel)
+    cfg.profile = 0
+    if world > 1:
+        cfg.accum_mode = 0
+        r.resize((a.width, a.height))
+    host_px = np.empty((a.height, a.width), np.uint32)
+    for i in range(2):
+        r.setCamera(cam)
+        r.launchParams.frame.subframe_index = frame_index(i)
+        r.render()
+        r.downloadPixels(host_px)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for i in range(a.steps):
+        r.setCamera(cam)                                                        # host -> LaunchParams (312 B, re-read by every render)
+        r.launchParams.frame.subframe_index = frame_index(i)
+        r.render()                                                              # blocking, as the reference's render()
+        r.downloadPixels(host_px)                                               # D2H W*H RGBA8
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e_value = n_px * a.spl * a.steps * world / e2e_s / 1e6
+
+    # ---- roofline of the dominant kernel: algorithmic bytes from a counters replay of the same frames
+    cfg.profile = 2
+    nodes = tris = crays = 0
+    nodes_s = tris_s = srays = 0
+    replay = min(a.steps, 4)
+    for i in range(replay):
+        r.launchParams.frame.subframe_index = frame_index(a.warmup + i)
+        r.render()
+        c = r.counters()
+        nodes += c.nodes_fetched
+        tris += c.tris_fetched
+        crays += c.radiance_rays
+        nodes_s += c.nodes_fetched_shadow
+        tris_s += c.tris_fetched_shadow
+        srays += c.shadow_rays
+    cfg.profile = 0
+
+    if rank == 0:
+        peak, peak_src = _peaks()
+        bytes_closest_per_frame = (32 * nodes + 48 * tris + (32 + 16) * crays) / replay
+        bytes_any_per_frame = (32 * nodes_s + 48 * tris_s + (32 + 4) * srays) / replay
+        launches_per_frame = n_closest / a.steps
+        ms_closest_per_launch = stage["trace_closest"] / max(1, n_closest)
+        achieved = bytes_closest_per_frame / launches_per_frame / (ms_closest_per_launch * 1e-3) / 1e9
+        any_gbs = bytes_any_per_frame / (stage["trace_any"] / a.steps * 1e-3) / 1e9 if stage["trace_any"] > 0 else 0.0
+        line = {
+            "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": config_json(a, model, {"parallelism": "single GPU" if world == 1 else f"sample split over {world} GPUs (rank r renders sub-frames r, r+N, ...), one NCCL fp32 reduce of the SUM buffer + resolve on rank 0 inside the timed region",
+                                             "bvh": {"nodes": int(info.n_nodes), "leaves": int(info.n_leaves), "sah": round(float(info.sah_cost), 2),
+                                                     "sah_lbvh": round(float(info.sah_cost_lbvh), 2), "build_ms": round(float(info.build_ms), 3),
+                                                     "bytes": int(info.node_bytes + info.tri_bytes)},
+                                             "ctor_seconds": round(ctor_s, 3)}),
+            "mrays_per_s": mrays, "radiance_rays_per_sample": all_rad / max(1.0, all_samples), "shadow_rays_per_sample": all_sh / max(1.0, all_samples),
+            "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": 312, "d2h_bytes_per_step": 4 * n_px,
+                    "note": "setCamera + render() (blocking) + downloadPixels() into host memory every step; scene/BVH upload is one-off in the ctor "
+                            f"({ctor_s:.2f} s incl. LBVH build {float(info.build_ms):.2f} ms)"},
+            "gpu_launches": int(all_launches),
+            "roofline": {"bound": "hbm", "kernel": "traceClosestKernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": bytes_closest_per_frame / launches_per_frame, "launches_per_step": launches_per_frame,
+                         "avg_launch_ms": ms_closest_per_launch,
+                         "nodes_per_ray": nodes / max(1, crays), "tris_per_ray": tris / max(1, crays),
+                         "bytes_per_ray": (32 * nodes + 48 * tris) / max(1, crays) + 48,
+                         "trace_any_gbs": any_gbs},
+            "stage_ms_per_step": {k: v / a.steps for k, v in stage.items()},
+            "reduce_ms": reduce_ms, "wall_seconds_timed_region": wall, "clocks": clocks,
+        }
+        if not a.no_cpu_baseline and world == 1:
+            cb = cpu_baseline(a, model, cam, probe, cfg, a.cpu_seconds)
+            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "mrays_per_s")}
+        print(json.dumps(line), flush=True)
+    r.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+        return
+    if a.gpus > 1 and "WORLD_SIZE" not in os.environ:
+        # convenience: re-launch under torchrun exactly as the driver would
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={a.gpus}", "--master-addr", "127.0.0.1",
+               "--master-port", str(29500 + os.getpid() % 2000), os.path.abspath(__file__)] + sys.argv[1:]
+        raise SystemExit(subprocess.call(cmd))
+    run_b200(a)
+
+
+if __name__ == "__main__":
+    main()

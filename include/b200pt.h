@@ -54,7 +54,7 @@ typedef struct b200pt_config {
     int   russian_roulette;   /* 0 = off (reference behaviour). Opt-in estimator extension; breaks RNG parity */
     int   tile_rank, tile_count; /* multi-GPU tile split: this context renders launch rows whose 32-row band
                                     index % tile_count == tile_rank; tile_count <= 1 = whole frame        */
-    int   profile;            /* 1 = record per-stage CUDA-event timings + traversal counters            */
+    int   profile;            /* bit 0: per-stage CUDA-event timings; bit 1: traversal counters (slower kernels) */
     int   reserved[4];
 } b200pt_config;
 

@@ -40,7 +40,7 @@ struct b200pt_ctx {
     DevBuf<float4> sumRad, sumAlpha, sumNormal, sumAlbedo;
     DevBuf<TraceStats> stats;           // [0] closest, [1] any
     b200pt_counters last{};
-    bool countersPending = false;  bool profiled = false;
+    bool countersPending = false;  int profiled = 0;
     std::vector<cudaEvent_t> evPool;  std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> evUsed;  size_t evNext = 0;
 };
 

@@ -51,11 +51,13 @@ static void collectCounters(b200pt_ctx* c) {
     unsigned h[QC_COUNT + 8];
     CUDA_OK(cudaMemcpy(h, c->counters.p, sizeof(h), cudaMemcpyDeviceToHost));
     c->last.radiance_rays = h[QC_COUNT + 0];  c->last.shadow_rays = h[QC_COUNT + 1];  c->last.samples = h[QC_COUNT + 2];
-    if (c->profiled) {
+    if (c->profiled & 2) {
         TraceStats st[2];
         CUDA_OK(cudaMemcpy(st, c->stats.p, sizeof(st), cudaMemcpyDeviceToHost));
         c->last.nodes_fetched = st[0].nodes;  c->last.tris_fetched = st[0].tris;
         c->last.nodes_fetched_shadow = st[1].nodes;  c->last.tris_fetched_shadow = st[1].tris;
+    }
+    if (c->profiled & 1) {
         float acc[6] = {0, 0, 0, 0, 0, 0};
         for (auto& u : c->evUsed) { float ms = 0.f;  cudaEventElapsedTime(&ms, u.second.first, u.second.second);  acc[u.first] += ms; }
         c->last.ms_raygen = acc[ST_RAYGEN];  c->last.ms_trace_closest = acc[ST_CLOSEST];  c->last.ms_trace_any = acc[ST_ANY];
@@ -176,13 +178,13 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
     for (int i = 0; i < 2; ++i) { Q.rayO[i] = c->rayO[i].p;  Q.rayD[i] = c->rayD[i].p; }
     Q.hit = c->hit.p;  Q.shO = c->shO.p;  Q.shD = c->shD.p;  Q.counters = c->counters.p;
 
-    const bool prof = cfg.profile != 0;
-    c->evUsed.clear();  c->evNext = 0;  c->profiled = prof;
+    const bool prof = (cfg.profile & 1) != 0, count = (cfg.profile & 2) != 0;   // 1: stage events, 2: traversal counters
+    c->evUsed.clear();  c->evNext = 0;  c->profiled = cfg.profile & 3;
     StageTimer T{c, prof};
     cudaEvent_t a = nullptr, b = nullptr, ta = nullptr, tb = nullptr;
     unsigned launches = 0, nClosest = 0, nAny = 0;
     CUDA_OK(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned) * (QC_COUNT + 8), s));
-    if (prof) CUDA_OK(cudaMemsetAsync(c->stats.p, 0, 2 * sizeof(TraceStats), s));
+    if (count) CUDA_OK(cudaMemsetAsync(c->stats.p, 0, 2 * sizeof(TraceStats), s));
     T.begin(ST_TOTAL, ta, tb);
     const int bounces = cfg.max_depth + ((c->hasCatcher || cfg.max_depth == 0) ? 1 : 0);   // the dropped last segment is traced only if alpha can still change
     for (auto& group : groups) {
@@ -199,14 +201,14 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
             resetCountersKernel<<<1, 1, 0, s>>>(c->counters.p, cur ^ 1, d == 0);  ++launches;
             T.begin(ST_CLOSEST, a, b);
             launchTraceClosest(S, Q.rayO[cur], Q.rayD[cur], Q.hit, Q.counters + (cur ? QC_RAY1 : QC_RAY0), Q.counters + QC_HEAD_CLOSEST,
-                               cfg.tmin, cfg.tmax, prof ? c->stats.p : nullptr, s);
+                               cfg.tmin, cfg.tmax, count ? c->stats.p : nullptr, s);
             T.end(b);  ++launches;  ++nClosest;
             T.begin(ST_SHADE, a, b);
             launchShade(F, S, pool, Q, cur, d, s);
             T.end(b);  ++launches;
             T.begin(ST_ANY, a, b);
             launchTraceAny(S, Q.shO, Q.shD, Q.counters + QC_SHADOW, Q.counters + QC_HEAD_ANY, cfg.tmin, cfg.tmax,
-                           cfg.shadow_mode == B200PT_SHADOW_CULL_BACK, pool, prof ? c->stats.p + 1 : nullptr, s);
+                           cfg.shadow_mode == B200PT_SHADOW_CULL_BACK, pool, count ? c->stats.p + 1 : nullptr, s);
             T.end(b);  ++launches;  ++nAny;
             tallyShadowKernel<<<1, 1, 0, s>>>(c->counters.p);  ++launches;
             cur ^= 1;
