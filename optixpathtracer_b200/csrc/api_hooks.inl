@@ -184,7 +184,7 @@ int b200pt_download_bvh(b200pt_ctx* c, void* nodes32, size_t maxNodes, uint32_t*
     if (maxNodes < c->bvh.nNodes || maxTris < c->bvh.nTris) throw std::runtime_error("b200pt_download_bvh: buffers too small");
     CUDA_OK(cudaSetDevice(c->device));
     CUDA_OK(cudaMemcpy(nodes32, c->bvh.nodes, sizeof(BvhNode) * (size_t)c->bvh.nNodes, cudaMemcpyDeviceToHost));
-    if (c->bvh.nTris) CUDA_OK(cudaMemcpy(triGid, c->bvh.sortedGid, 4 * (size_t)c->bvh.nTris, cudaMemcpyDeviceToHost));
+    if (c->bvh.nTris) CUDA_OK(cudaMemcpy(triGid, c->bvh.finalGid, 4 * (size_t)c->bvh.nTris, cudaMemcpyDeviceToHost));
     API_END
 }
 

@@ -4,8 +4,10 @@
 //   2. mortonKernel      63-bit Morton code of the AABB centre          (bit-exact vs oracle_morton)
 //   3. radix sort        LSD, 8-bit digits, 64-bit key + 32-bit id, stable (== std::stable_sort order)
 //   4. karrasKernel      Karras 2012 binary radix tree over the sorted codes (index tie-break for duplicates)
-//   5. refitKernel       bottom-up AABBs + SAH cost + leaf-collapse decision (atomic arrival flags)
-//   6. emit              surviving internal nodes -> 64-byte sibling pairs of 32-byte nodes; 48-byte triangle records
+//   5. refitKernel       bottom-up AABBs + SAH cost of the plain LBVH (atomic arrival flags); reported, not traversed
+//   6. bvh_sah.cuh       binned-SAH treelet refinement, level by level, over the LBVH's ranges -> 64-byte sibling
+//                        pairs of 32-byte nodes (the tree the traversal kernels read)
+//   7. emitTrisKernel    48-byte triangle records in final BVH order
 // Integer stages (2,3) are the ones north_star asks to be bit-exact against a host reference.
 #include "common.cuh"
 #include <cfloat>
@@ -15,6 +17,7 @@
 #define SORT_TILE (SORT_THREADS * SORT_ITEMS)
 #define SAH_CI 1.2f
 #define SAH_CT 1.0f
+#include "bvh_sah.cuh"
 
 // ---------------------------------------------------------------- float <-> ordered uint for atomic min/max
 __device__ __forceinline__ unsigned fOrder(float f) { unsigned u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
@@ -243,62 +246,74 @@ __global__ void refitKernel(const float4* __restrict__ triLo, const float4* __re
     }
 }
 
-// survivors = internal nodes that stay internal: not collapsed and with no collapsed ancestor.  Also max depth.
-__global__ void surviveKernel(int n, const int* __restrict__ parent, const unsigned char* __restrict__ collapse,
-                              unsigned* __restrict__ survive, unsigned* maxDepth) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n - 1) return;
-    bool dead = collapse[i] != 0;
-    unsigned depth = 1;
-    for (int p = parent[i]; p >= 0; p = parent[p]) { dead = dead || collapse[p] != 0;  ++depth; }
-    survive[i] = dead ? 0u : 1u;
-    if (!dead) atomicMax(maxDepth, depth);
+// ---------------------------------------------------------------- multi-block exclusive scan (flags -> ranks)
+#define SCAN_TILE 4096
+__global__ void __launch_bounds__(1024) scanTileSumKernel(const unsigned* __restrict__ in, unsigned n, unsigned* __restrict__ tileSum) {
+    __shared__ unsigned part[32];
+    const unsigned base = blockIdx.x * SCAN_TILE + threadIdx.x * 4;
+    unsigned s = 0;
+    for (int k = 0; k < 4; ++k) if (base + k < n) s += in[base + k];
+    for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        unsigned v = part[threadIdx.x];
+        for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (threadIdx.x == 0) tileSum[blockIdx.x] = v;
+    }
+}
+__global__ void __launch_bounds__(1024) scanTileApplyKernel(const unsigned* __restrict__ in, unsigned n, const unsigned* __restrict__ tileOffset,
+                                                            unsigned* __restrict__ out) {
+    __shared__ unsigned part[32];
+    const unsigned base = blockIdx.x * SCAN_TILE + threadIdx.x * 4;
+    unsigned v[4], s = 0;
+    for (int k = 0; k < 4; ++k) { v[k] = base + k < n ? in[base + k] : 0;  s += v[k]; }
+    unsigned inc = s;
+    for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, inc, o);  if ((threadIdx.x & 31) >= o) inc += t; }
+    if ((threadIdx.x & 31) == 31) part[threadIdx.x >> 5] = inc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        unsigned w = part[threadIdx.x], winc = w;
+        for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, winc, o);  if (threadIdx.x >= o) winc += t; }
+        part[threadIdx.x] = winc - w;
+    }
+    __syncthreads();
+    unsigned run = tileOffset[blockIdx.x] + part[threadIdx.x >> 5] + inc - s;
+    for (int k = 0; k < 4; ++k) { if (base + k < n) out[base + k] = run;  run += v[k]; }
 }
 
-__device__ __forceinline__ void padBox(float4& lo, float4& hi) {
-    const float mx = fmaxf(fabsf(lo.x), fabsf(hi.x)) * 4e-7f + 1e-30f, my = fmaxf(fabsf(lo.y), fabsf(hi.y)) * 4e-7f + 1e-30f,
-                mz = fmaxf(fabsf(lo.z), fabsf(hi.z)) * 4e-7f + 1e-30f;
-    lo.x -= mx;  lo.y -= my;  lo.z -= mz;  hi.x += mx;  hi.y += my;  hi.z += mz;
+// ---------------------------------------------------------------- treelet job selection (see bvh_sah.cuh)
+// rank = exclusive prefix of the current level's item-start flags over sorted triangle positions (nullptr: level 1,
+// every triangle is an item).  A node roots a job when it holds <= JOB_T items and its parent holds more.
+__device__ __forceinline__ unsigned itemsIn(const unsigned* __restrict__ rank, int lo, int hi) { return rank ? rank[hi + 1] - rank[lo] : (unsigned)(hi - lo + 1); }
+
+__global__ void selectJobsKernel(int n, const int* __restrict__ parent, const int2* __restrict__ range, const unsigned* __restrict__ rank,
+                                 unsigned* __restrict__ flagNext, const unsigned* __restrict__ rankNext, SahJob* __restrict__ jobs) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= 2 * n - 1) return;
+    int2 rg;
+    if (v < n - 1) rg = range[v];  else rg = make_int2(v - (n - 1), v - (n - 1));
+    const unsigned cnt = itemsIn(rank, rg.x, rg.y);
+    if (cnt == 0 || cnt > JOB_T) return;
+    const int p = parent[v];
+    if (p >= 0) { const int2 pr = range[p];  if (itemsIn(rank, pr.x, pr.y) <= JOB_T) return; }
+    if (!rankNext) flagNext[rg.x] = 1u;
+    else jobs[rankNext[rg.x]] = SahJob{rank ? rank[rg.x] : (unsigned)rg.x, cnt, (unsigned)rg.x};
 }
 
-__device__ __forceinline__ int childLink(int c, int n, const unsigned char* collapse, const int2* range, const unsigned* slotIdx,
-                                         unsigned* leafCount, unsigned* maxLeaf) {
-    if (c >= n - 1) { atomicAdd(leafCount, 1u);  atomicMax(maxLeaf, 1u);  return leafEncode((unsigned)(c - (n - 1)), 1u); }
-    if (collapse[c]) {
-        const int2 rg = range[c];
-        atomicAdd(leafCount, 1u);  atomicMax(maxLeaf, (unsigned)(rg.y - rg.x + 1));
-        return leafEncode((unsigned)rg.x, (unsigned)(rg.y - rg.x + 1));
+// SAH cost of the final tree: sum over records of Ci*A (inner) or Ct*count*A (leaf), over the root area.
+__global__ void sahCostKernel(const float4* __restrict__ nodes, unsigned nRecords, double* cost) {
+    const unsigned r = blockIdx.x * blockDim.x + threadIdx.x;
+    float c = 0.f;
+    if (r < nRecords && r != 1) {
+        const float4 lo = nodes[2 * (size_t)r], hi = nodes[2 * (size_t)r + 1];
+        const int link = __float_as_int(lo.w);
+        const float a = boxArea(lo, hi);
+        if (link >= 0) c = SAH_CI * a;
+        else { unsigned first, count;  leafDecode(link, first, count);  c = SAH_CT * a * (float)count; }
     }
-    return 2 + 2 * (int)slotIdx[c];
-}
-
-__global__ void emitNodesKernel(int n, const int* __restrict__ left, const int* __restrict__ right, const int2* __restrict__ range,
-                                const unsigned char* __restrict__ collapse, const unsigned* __restrict__ survive,
-                                const unsigned* __restrict__ slotIdx, const float4* __restrict__ boxLo, const float4* __restrict__ boxHi,
-                                float4* __restrict__ nodes, unsigned* leafCount, unsigned* maxLeaf) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i == 0) {   // root record + pad
-        float4 lo = boxLo[0], hi = boxHi[0];
-        padBox(lo, hi);
-        int link;
-        if (n == 1) { link = leafEncode(0u, 1u);  atomicAdd(leafCount, 1u);  atomicMax(maxLeaf, 1u); }
-        else if (collapse[0]) { link = leafEncode(0u, (unsigned)n);  atomicAdd(leafCount, 1u);  atomicMax(maxLeaf, (unsigned)n); }
-        else link = 2;
-        nodes[0] = make_float4(lo.x, lo.y, lo.z, __int_as_float(link));
-        nodes[1] = make_float4(hi.x, hi.y, hi.z, 0.f);
-        nodes[2] = make_float4(0, 0, 0, 0);  nodes[3] = make_float4(0, 0, 0, 0);
-    }
-    if (i >= n - 1 || !survive[i]) return;
-    float4* out = nodes + 2 * (size_t)(2 + 2 * slotIdx[i]);
-    const int cs[2] = {left[i], right[i]};
-#pragma unroll
-    for (int k = 0; k < 2; ++k) {
-        float4 lo = boxLo[cs[k]], hi = boxHi[cs[k]];
-        padBox(lo, hi);
-        const int link = childLink(cs[k], n, collapse, range, slotIdx, leafCount, maxLeaf);
-        out[2 * k] = make_float4(lo.x, lo.y, lo.z, __int_as_float(link));
-        out[2 * k + 1] = make_float4(hi.x, hi.y, hi.z, 0.f);
-    }
+    for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0 && c != 0.f) atomicAdd(cost, (double)c);
 }
 
 // 48-byte triangle records in BVH order: {v0, e1 = v1-v0, e2 = v2-v0, gid, mesh}
@@ -328,7 +343,7 @@ __global__ void scatterCodesKernel(const unsigned long long* __restrict__ sorted
 template <typename T> static T* dalloc(size_t n) { T* p = nullptr;  CUDA_OK(cudaMalloc((void**)&p, std::max<size_t>(n, 1) * sizeof(T)));  return p; }
 
 void bvhFree(BvhBuildResult& r) {
-    cudaFree(r.nodes);  cudaFree(r.tris);  cudaFree(r.mortonByGid);  cudaFree(r.sortedGid);
+    cudaFree(r.nodes);  cudaFree(r.tris);  cudaFree(r.mortonByGid);  cudaFree(r.sortedGid);  cudaFree(r.finalGid);
     r = BvhBuildResult();
 }
 
@@ -368,44 +383,84 @@ void bvhBuild(const float3* d_vertices, const uint3* d_indices, const unsigned* 
     int* left = dalloc<int>(n);  int* right = dalloc<int>(n);  int* parent = dalloc<int>(nAll);  int2* range = dalloc<int2>(n);
     float4* boxLo = dalloc<float4>(nAll);  float4* boxHi = dalloc<float4>(nAll);
     unsigned* flags = dalloc<unsigned>(n);  unsigned char* collapse = dalloc<unsigned char>(n);
-    unsigned* survive = dalloc<unsigned>(n);  unsigned* slotIdx = dalloc<unsigned>(n);
-    unsigned* scalars = dalloc<unsigned>(4);                 // [0] survivors, [1] max depth, [2] leaves, [3] max leaf size
+    unsigned* scalars = dalloc<unsigned>(4);                 // [0] pairs allocated, [1] -, [2] leaves, [3] max leaf size
     CUDA_OK(cudaMemsetAsync(flags, 0, sizeof(unsigned) * n, s));
-    CUDA_OK(cudaMemsetAsync(collapse, 0, n, s));
     CUDA_OK(cudaMemsetAsync(scalars, 0, 4 * sizeof(unsigned), s));
     CUDA_OK(cudaMemsetAsync(parent, 0xff, sizeof(int) * nAll, s));
     if (n > 1) karrasKernel<<<(n - 1 + B - 1) / B, B, 0, s>>>(keys, n, left, right, parent, range);
     refitKernel<<<G, B, 0, s>>>(triLo, triHi, vals, n, left, right, parent, range, boxLo, boxHi, flags, collapse);
-    unsigned nSurvive = 0;
-    if (n > 1) {
-        surviveKernel<<<(n - 1 + B - 1) / B, B, 0, s>>>(n, parent, collapse, survive, scalars + 1);
-        scanExclusiveKernel<<<1, 1024, 0, s>>>(survive, slotIdx, (unsigned)(n - 1), scalars);
-        CUDA_OK(cudaMemcpyAsync(&nSurvive, scalars, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
-        CUDA_OK(cudaStreamSynchronize(s));
-    }
-    out.nNodes = 2 + 2 * nSurvive;
-    out.nodes = dalloc<BvhNode>(out.nNodes + 2);
+
+    // ---- binned-SAH treelet refinement, level by level (bvh_sah.cuh)
+    const size_t maxRecords = 4 + 2 * (size_t)n;
+    out.nodes = dalloc<BvhNode>(maxRecords);
     out.tris = dalloc<float4>(3 * (size_t)nTris);
-    emitNodesKernel<<<(std::max(n - 1, 1) + B - 1) / B, B, 0, s>>>(n, left, right, range, collapse, survive, slotIdx, boxLo, boxHi,
-                                                                  (float4*)out.nodes, scalars + 2, scalars + 3);
-    emitTrisKernel<<<G, B, 0, s>>>(d_vertices, d_indices, d_triMesh, d_meshes, vals, nTris, out.tris);
-    CUDA_OK(cudaEventRecord(e1, s));
-    unsigned hs[4];  float4 rootLo, rootHi;  unsigned hostBox[8];
+    out.finalGid = dalloc<unsigned>(nTris);
+    static bool attrSet = false;
+    if (!attrSet) { CUDA_OK(cudaFuncSetAttribute(sahJobKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SahShared)));  attrSet = true; }
+    const unsigned nFlag = nTris + 1, nTiles = (nFlag + SCAN_TILE - 1) / SCAN_TILE;
+    unsigned* flagNext = dalloc<unsigned>(nFlag);  unsigned* rankA = dalloc<unsigned>(nFlag);  unsigned* rankB = dalloc<unsigned>(nFlag);
+    unsigned* tileSum = dalloc<unsigned>(nTiles);  unsigned* tileOff = dalloc<unsigned>(nTiles);
+    const unsigned* rank = nullptr;                          // level 1: every triangle is an item
+    float4* itemLo = nullptr;  float4* itemHi = nullptr;  int* itemLink = nullptr;  int* itemDepth = nullptr;
+    unsigned levels = 0, depthHost = 0;
+    const unsigned GV = (unsigned)((nAll + B - 1) / B);
+    while (true) {
+        unsigned* rankNext = (rank == rankA) ? rankB : rankA;
+        CUDA_OK(cudaMemsetAsync(flagNext, 0, sizeof(unsigned) * nFlag, s));
+        selectJobsKernel<<<GV, B, 0, s>>>(n, parent, range, rank, flagNext, nullptr, nullptr);
+        scanTileSumKernel<<<nTiles, 1024, 0, s>>>(flagNext, nFlag, tileSum);
+        scanExclusiveKernel<<<1, 1024, 0, s>>>(tileSum, tileOff, nTiles, nullptr);
+        scanTileApplyKernel<<<nTiles, 1024, 0, s>>>(flagNext, nFlag, tileOff, rankNext);
+        unsigned nJobs = 0;
+        CUDA_OK(cudaMemcpyAsync(&nJobs, rankNext + nTris, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaStreamSynchronize(s));
+        if (nJobs == 0) throw std::runtime_error("bvhBuild: treelet selection found no job");
+        SahJob* jobs = dalloc<SahJob>(nJobs);
+        selectJobsKernel<<<GV, B, 0, s>>>(n, parent, range, rank, flagNext, rankNext, jobs);
+        float4* nextLo = dalloc<float4>(nJobs);  float4* nextHi = dalloc<float4>(nJobs);  int* nextLink = dalloc<int>(nJobs);  int* nextDepth = dalloc<int>(nJobs);
+        SahLevelIn in{itemLo, itemHi, itemLink, itemDepth, triLo, triHi, vals, levels == 0 ? 1 : 0};
+        SahLevelOut lo{nextLo, nextHi, nextLink, nextDepth, out.finalGid, (float4*)out.nodes, scalars + 0, scalars + 2};
+        const bool last = nJobs == 1;
+        sahJobKernel<<<nJobs, JOB_THREADS, sizeof(SahShared), s>>>(jobs, in, lo, last ? 1 : 0);
+        ++levels;
+        if (last) CUDA_OK(cudaMemcpyAsync(&depthHost, nextDepth, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaStreamSynchronize(s));
+        CUDA_OK(cudaGetLastError());
+        cudaFree(jobs);  cudaFree(itemLo);  cudaFree(itemHi);  cudaFree(itemLink);  cudaFree(itemDepth);
+        itemLo = nextLo;  itemHi = nextHi;  itemLink = nextLink;  itemDepth = nextDepth;  rank = rankNext;
+        if (last) break;
+        if (levels > 80) throw std::runtime_error("bvhBuild: treelet refinement did not converge");
+    }
+    cudaFree(itemLo);  cudaFree(itemHi);  cudaFree(itemLink);  cudaFree(itemDepth);
+    emitTrisKernel<<<G, B, 0, s>>>(d_vertices, d_indices, d_triMesh, d_meshes, out.finalGid, nTris, out.tris);
+    unsigned hs[4];
     CUDA_OK(cudaMemcpyAsync(hs, scalars, sizeof(hs), cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaStreamSynchronize(s));
+    out.nNodes = 2 + 2 * hs[0];
+    double* costDev = dalloc<double>(1);
+    CUDA_OK(cudaMemsetAsync(costDev, 0, sizeof(double), s));
+    sahCostKernel<<<(out.nNodes + B - 1) / B, B, 0, s>>>((const float4*)out.nodes, out.nNodes, costDev);
+    CUDA_OK(cudaEventRecord(e1, s));
+    float4 rootLo, rootHi, finalRoot[2];  unsigned hostBox[8];  double costHost = 0.0;
     CUDA_OK(cudaMemcpyAsync(&rootLo, boxLo, sizeof(float4), cudaMemcpyDeviceToHost, s));
     CUDA_OK(cudaMemcpyAsync(&rootHi, boxHi, sizeof(float4), cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaMemcpyAsync(finalRoot, out.nodes, 2 * sizeof(float4), cudaMemcpyDeviceToHost, s));
     CUDA_OK(cudaMemcpyAsync(hostBox, sceneBox, sizeof(hostBox), cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaMemcpyAsync(&costHost, costDev, sizeof(double), cudaMemcpyDeviceToHost, s));
     CUDA_OK(cudaStreamSynchronize(s));
     CUDA_OK(cudaEventElapsedTime(&out.buildMs, e0, e1));
     cudaEventDestroy(e0);  cudaEventDestroy(e1);
-    out.maxDepth = hs[1] + 1;  out.nLeaves = hs[2];  out.maxLeaf = hs[3];
+    out.maxDepth = depthHost + 1;  out.nLeaves = hs[2];  out.maxLeaf = hs[3];  out.refineLevels = levels;
     const float dx = rootHi.x - rootLo.x, dy = rootHi.y - rootLo.y, dz = rootHi.z - rootLo.z;
     const float rootArea = 2.f * (dx * dy + dy * dz + dz * dx);
-    out.sahCost = rootArea > 0.f ? rootLo.w / rootArea : 0.f;
+    const float fx = finalRoot[1].x - finalRoot[0].x, fy = finalRoot[1].y - finalRoot[0].y, fz = finalRoot[1].z - finalRoot[0].z;
+    const float finalArea = 2.f * (fx * fy + fy * fz + fz * fx);
+    out.sahCost = finalArea > 0.f ? (float)(costHost / finalArea) : 0.f;
     out.sahCostLbvh = rootArea > 0.f ? rootHi.w / rootArea : 0.f;
     for (int a = 0; a < 6; ++a) out.sceneBounds[a] = fUnorder(hostBox[a]);
     cudaFree(triLo);  cudaFree(triHi);  cudaFree(sceneBox);  cudaFree(keys);  cudaFree(valsTmp);  cudaFree(blockHist);  cudaFree(blockOffset);
     cudaFree(left);  cudaFree(right);  cudaFree(parent);  cudaFree(range);  cudaFree(boxLo);  cudaFree(boxHi);  cudaFree(flags);
-    cudaFree(collapse);  cudaFree(survive);  cudaFree(slotIdx);  cudaFree(scalars);
+    cudaFree(collapse);  cudaFree(scalars);  cudaFree(flagNext);  cudaFree(rankA);  cudaFree(rankB);  cudaFree(tileSum);  cudaFree(tileOff);
+    cudaFree(costDev);
     if (out.maxDepth > B200PT_STACK - 2) throw std::runtime_error("BVH deeper than the traversal stack");
 }

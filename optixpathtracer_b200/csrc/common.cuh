@@ -111,7 +111,7 @@ struct TraceStats { unsigned long long nodes, tris, rays; };
 struct BvhBuildResult {
     BvhNode* nodes = nullptr;  float4* tris = nullptr;  unsigned nNodes = 0, nTris = 0, nLeaves = 0, maxLeaf = 0, maxDepth = 0;
     float sahCost = 0.f, sahCostLbvh = 0.f, buildMs = 0.f;
-    unsigned long long* mortonByGid = nullptr;  uint32_t* sortedGid = nullptr;  float sceneBounds[6] = {0, 0, 0, 0, 0, 0};
+    unsigned long long* mortonByGid = nullptr;  uint32_t* sortedGid = nullptr;  uint32_t* finalGid = nullptr;  unsigned refineLevels = 0;  float sceneBounds[6] = {0, 0, 0, 0, 0, 0};
 };
 void bvhBuild(const float3* d_vertices, const uint3* d_indices, const unsigned* d_triMesh, const MeshInfo* d_meshes,
               unsigned nTris, cudaStream_t stream, BvhBuildResult& out);

@@ -1,19 +1,37 @@
 // b200pt — BVH traversal kernels (replace the closed optixTrace of sv4/deviceProgram.cu:207,232).
-//   traceClosestKernel : RADIANCE rays  — closest hit in (tmin,tmax), ties -> lowest global triangle id
-//   traceAnyKernel     : OCCLUSION rays — any hit (optionally only triangles front-facing the ray), early out;
+//   traceKernel<false> : RADIANCE rays  — closest hit in (tmin,tmax), ties -> lowest global triangle id
+//   traceKernel<true>  : OCCLUSION rays — any hit (optionally only triangles front-facing the ray), early out;
 //                        visible rays add their pending NEE contribution to the path's radiance accumulator
-// Persistent threads: a fixed grid of B200PT_NUM_SMS x k CTAs; each warp pulls batches of 32 rays from a
-// device-side queue head, so queue lengths never return to the host.  Node pairs are fetched as 4x128-bit
-// loads (two 32-byte siblings, 64-byte aligned), triangles as 3x128-bit loads through the read-only path.
-// Roofline: HBM/L2 gather bound; algorithmic bytes per ray = 32*nodes + 48*tris + 32 (ray) + 16 (hit).
+// Persistent warps (a fixed grid of B200PT_NUM_SMS x k CTAs).  Each warp stages chunks of 32 rays from the
+// device-side queue into shared memory with one atomic per chunk; a lane whose ray terminates takes the next
+// staged ray as soon as enough lanes are idle (per-lane replacement decided by a warp vote), so a warp never
+// idles behind its slowest ray.  Traversal is "while-while": every lane walks inner nodes until it holds a
+// postponed leaf and reaches a second one (or runs dry), then the warp intersects leaves together.
+// A 32-byte node is ONE 256-bit load (LDG.E.256, new on sm_100); a sibling pair is two of them in one 64-byte
+// aligned half cache line; a 48-byte triangle is 3x128-bit.  All fetches go through the read-only path.
+// Roofline: L1/L2 gather bound; algorithmic bytes per ray = 32*nodes + 48*tris + 32 (ray) + 16 (hit).
 // The ray/triangle test is the exact fp32 operation sequence of oracle/scene_core.h (no FMA contraction,
 // enforced with __f*_rn intrinsics), which makes the chosen triangle and (t,u,v) BVH-independent.
 #include "common.cuh"
 
 #define TRACE_BLOCK 128
+#define TRACE_WARPS (TRACE_BLOCK / 32)
 #define TRACE_BLOCKS_PER_SM 8
+#define FULL 0xffffffffu
+#define EMPTY 0x7fffffff          // "nothing left to visit"; also the root link of an empty scene
+#define NO_LEAF 0                 // leaf codes are < 0
+
+static int g_refillThreshold = -1, g_leafThreshold = -1;   // lanes that must be idle before a warp refills; tuned on B200
 
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
+
+struct Node8 { float4 a, b; };    // {lo.xyz, link | hi.xyz, aux}
+__device__ __forceinline__ Node8 ldgNode(const float4* p) {
+    Node8 n;
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(n.a.x), "=f"(n.a.y), "=f"(n.a.z), "=f"(n.a.w), "=f"(n.b.x), "=f"(n.b.y), "=f"(n.b.z), "=f"(n.b.w) : "l"(p));
+    return n;
+}
 
 struct TriHit { float t, u, v; };
 
@@ -56,6 +74,26 @@ __device__ __forceinline__ bool boxTest(const float4 n0, const float4 n1, const 
 
 struct Best { float t, u, v; int slot; unsigned gid; };
 
+// One inner-node step: fetch the sibling pair `cur`, test both, descend into the nearer hit child and push the other.
+#define NODE_STEP()                                                                              \
+    {                                                                                            \
+        const float4* p_ = S.nodes + 2 * (size_t)cur;                                            \
+        const Node8 L_ = ldgNode(p_), R_ = ldgNode(p_ + 2);                                      \
+        if (COUNT) nNodes += 2;                                                                  \
+        float tl_, tr_;                                                                          \
+        const bool hl_ = boxTest(L_.a, L_.b, o, inv, tmin, best.t, tl_);                         \
+        const bool hr_ = boxTest(R_.a, R_.b, o, inv, tmin, best.t, tr_);                         \
+        const int cl_ = __float_as_int(L_.a.w), cr_ = __float_as_int(R_.a.w);                    \
+        if (hl_ && hr_) {                                                                        \
+            const bool sw_ = tr_ < tl_;                                                          \
+            stack[sp++] = sw_ ? cl_ : cr_;                                                       \
+            cur = sw_ ? cr_ : cl_;                                                               \
+        } else if (hl_) cur = cl_;                                                               \
+        else if (hr_) cur = cr_;                                                                 \
+        else cur = sp ? stack[--sp] : EMPTY;                                                     \
+    }
+
+// Reference single-ray traversal (parity hooks only; the production kernels below inline the same steps).
 template <bool ANY, bool COUNT>
 __device__ __forceinline__ bool traverse(const SceneDev& S, const float3 o, const float3 d, float tmin, float tmax,
                                          bool cullBack, Best& best, unsigned& nNodes, unsigned& nTris) {
@@ -64,23 +102,9 @@ __device__ __forceinline__ bool traverse(const SceneDev& S, const float3 o, cons
     int sp = 0;
     best.t = tmax;  best.slot = -1;  best.gid = 0xffffffffu;  best.u = best.v = 0.f;
     int cur = __float_as_int(ldg4(S.nodes).w);            // root record's link
-    const int EMPTY = 0x7fffffff;
     while (cur != EMPTY) {
         if (cur >= 0) {
-            const float4* p = S.nodes + 2 * (size_t)cur;
-            const float4 l0 = ldg4(p), l1 = ldg4(p + 1), r0 = ldg4(p + 2), r1 = ldg4(p + 3);
-            if (COUNT) nNodes += 2;
-            float tl, tr;
-            const bool hl = boxTest(l0, l1, o, inv, tmin, best.t, tl);
-            const bool hr = boxTest(r0, r1, o, inv, tmin, best.t, tr);
-            const int cl = __float_as_int(l0.w), cr = __float_as_int(r0.w);
-            if (hl && hr) {
-                const bool swap = tr < tl;
-                stack[sp++] = swap ? cl : cr;
-                cur = swap ? cr : cl;
-            } else if (hl) cur = cl;
-            else if (hr) cur = cr;
-            else cur = sp ? stack[--sp] : EMPTY;
+            NODE_STEP()
         } else {
             unsigned first, count;
             leafDecode(cur, first, count);
@@ -105,9 +129,9 @@ __device__ __forceinline__ bool traverse(const SceneDev& S, const float3 o, cons
 
 __device__ __forceinline__ void flushStats(TraceStats* stats, unsigned nNodes, unsigned nTris, unsigned nRays) {
     for (int off = 16; off; off >>= 1) {
-        nNodes += __shfl_xor_sync(0xffffffffu, nNodes, off);
-        nTris += __shfl_xor_sync(0xffffffffu, nTris, off);
-        nRays += __shfl_xor_sync(0xffffffffu, nRays, off);
+        nNodes += __shfl_xor_sync(FULL, nNodes, off);
+        nTris += __shfl_xor_sync(FULL, nTris, off);
+        nRays += __shfl_xor_sync(FULL, nRays, off);
     }
     if ((threadIdx.x & 31) == 0) {
         atomicAdd(&stats->nodes, (unsigned long long)nNodes);
@@ -116,62 +140,122 @@ __device__ __forceinline__ void flushStats(TraceStats* stats, unsigned nNodes, u
     }
 }
 
-template <bool COUNT>
+// ANY = false: hit[i] = {t,u,v,triSlot} for ray i of the queue.
+// ANY = true : rayO.w = path slot, rayD.w = target (0 direct, 1 indirect, 2 alpha-when-occluded); see shade.cu.
+template <bool ANY, bool COUNT>
 __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_BLOCKS_PER_SM)
-traceClosestKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restrict__ rayD, float4* __restrict__ hit,
-                   const unsigned* __restrict__ countPtr, unsigned* head, float tmin, float tmax, TraceStats* stats) {
+traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restrict__ rayD, float4* __restrict__ hit,
+            const unsigned* __restrict__ countPtr, unsigned* head, float tmin, float tmax, int cullBack, PathPool pool,
+            TraceStats* stats, int refillThreshold, int leafThreshold) {
+    __shared__ float4 stageO[TRACE_WARPS][32], stageD[TRACE_WARPS][32];
     const unsigned count = *countPtr;
-    const unsigned lane = threadIdx.x & 31;
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned ltMask = (1u << lane) - 1u;
+    const int rootLink = __float_as_int(ldg4(S.nodes).w);
     unsigned nNodes = 0, nTris = 0, nRays = 0;
-    while (true) {
-        unsigned base = 0;
-        if (lane == 0) base = atomicAdd(head, 32u);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= count) break;
-        const unsigned i = base + lane;
-        if (i < count) {
-            const float4 o4 = rayO[i], d4 = rayD[i];
-            Best b;
-            traverse<false, COUNT>(S, make_float3(o4.x, o4.y, o4.z), make_float3(d4.x, d4.y, d4.z), tmin, tmax, false, b, nNodes, nTris);
-            hit[i] = make_float4(b.t, b.u, b.v, __int_as_float(b.slot));
-            if (COUNT) nRays++;
-        }
-    }
-    if (COUNT) flushStats(stats, nNodes, nTris, nRays);
-}
 
-template <bool COUNT>
-__global__ void __launch_bounds__(TRACE_BLOCK, TRACE_BLOCKS_PER_SM)
-traceAnyKernel(SceneDev S, const float4* __restrict__ shO, const float4* __restrict__ shD,
-               const unsigned* __restrict__ countPtr, unsigned* head, float tmin, float tmax, int cullBack,
-               PathPool pool, TraceStats* stats) {
-    const unsigned count = *countPtr;
-    const unsigned lane = threadIdx.x & 31;
-    unsigned nNodes = 0, nTris = 0, nRays = 0;
+    // warp-uniform staging state: rays [stageNext, stageEnd) of chunk `stageBase` are still unassigned
+    unsigned stageBase = 0, stageNext = 0, stageEnd = 0;
+    bool exhausted = false;
+
+    // per-lane ray state
+    bool active = false;
+    unsigned rayIdx = 0;
+    float3 o = make_float3(0, 0, 0), d = o, inv = o;
+    float wO = 0.f, wD = 0.f;
+    Best best;  best.t = tmax;  best.slot = -1;  best.gid = 0xffffffffu;  best.u = best.v = 0.f;
+    int cur = EMPTY, leaf = NO_LEAF, sp = 0;
+    int stack[B200PT_STACK];
+
     while (true) {
-        unsigned base = 0;
-        if (lane == 0) base = atomicAdd(head, 32u);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= count) break;
-        const unsigned i = base + lane;
-        if (i < count) {
-            const float4 o4 = shO[i], d4 = shD[i];
-            Best b;
-            const bool occluded = traverse<true, COUNT>(S, make_float3(o4.x, o4.y, o4.z), make_float3(d4.x, d4.y, d4.z), tmin, tmax,
-                                                        cullBack != 0, b, nNodes, nTris);
-            if (COUNT) nRays++;
-            // prd.radiance += pathThroughput * lightSample (sv4/deviceProgram.cu:659) resolved here.  d4.w carries the
-            // target: 0 = direct (depth 0), 1 = indirect, 2 = alpha when OCCLUDED (shadow catcher, :663-664).
-            // Single writer per slot per launch => deterministic.
-            const int target = __float_as_int(d4.w);
-            if (occluded == (target == 2)) {
-                const unsigned slot = (unsigned)__float_as_int(o4.w);
-                const float4 pend = pool.pending[slot];
-                float4* acc = (target == 0 ? pool.direct : (target == 1 ? pool.indirect : pool.alpha)) + slot;
-                float4 r = *acc;
-                r.x = __fadd_rn(r.x, pend.x);  r.y = __fadd_rn(r.y, pend.y);  r.z = __fadd_rn(r.z, pend.z);
-                *acc = r;
+        // ---------------------------------------------------------------- refill idle lanes (warp-synchronous)
+        unsigned idle = __ballot_sync(FULL, !active);
+        if (idle == FULL || ((int)__popc(idle) >= refillThreshold && !(exhausted && stageNext >= stageEnd))) {
+#pragma unroll 1
+            for (int round = 0; round < 2 && idle; ++round) {
+                if (stageNext >= stageEnd) {
+                    if (exhausted) break;
+                    unsigned b = 0;
+                    if (lane == 0) b = atomicAdd(head, 32u);
+                    b = __shfl_sync(FULL, b, 0);
+                    if (b >= count) { exhausted = true;  break; }
+                    __syncwarp();
+                    if (b + lane < count) { stageO[warp][lane] = rayO[b + lane];  stageD[warp][lane] = rayD[b + lane]; }
+                    __syncwarp();
+                    stageBase = b;  stageNext = b;  stageEnd = min(b + 32u, count);
+                }
+                const unsigned avail = stageEnd - stageNext;
+                const unsigned r = __popc(idle & ltMask);
+                if (!active && r < avail) {
+                    const unsigned j = stageNext + r;
+                    const float4 o4 = stageO[warp][j - stageBase], d4 = stageD[warp][j - stageBase];
+                    o = make_float3(o4.x, o4.y, o4.z);  d = make_float3(d4.x, d4.y, d4.z);  wO = o4.w;  wD = d4.w;
+                    inv = make_float3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+                    rayIdx = j;  active = true;
+                    best.t = tmax;  best.slot = -1;  best.gid = 0xffffffffu;  best.u = best.v = 0.f;
+                    cur = rootLink;  leaf = NO_LEAF;  sp = 0;
+                    if (COUNT) nRays++;
+                }
+                stageNext += min(avail, (unsigned)__popc(idle));
+                idle = __ballot_sync(FULL, !active);
             }
+            if (idle == FULL) break;                               // queue drained and every lane finished
+        }
+
+        // ---------------------------------------------------------------- one inner-node step per lane that can take one
+        bool occluded = false;
+        if (active && (unsigned)cur < (unsigned)EMPTY) {
+            NODE_STEP()
+            if (cur < 0 && leaf == NO_LEAF) {                      // first leaf: postpone it and keep walking
+                leaf = cur;
+                cur = sp ? stack[--sp] : EMPTY;
+            }
+        }
+        // ---------------------------------------------------------------- leaves, once enough lanes are blocked on one
+        const bool canNode = active && (unsigned)cur < (unsigned)EMPTY;
+        const unsigned nodeMask = __ballot_sync(FULL, canNode);
+        const unsigned blockedMask = __ballot_sync(FULL, active && !canNode);
+        if (nodeMask == 0u || (int)__popc(blockedMask) >= leafThreshold) {
+            if (active && leaf == NO_LEAF && cur < 0) { leaf = cur;  cur = sp ? stack[--sp] : EMPTY; }   // root leaf
+            if (active && leaf != NO_LEAF) {
+                unsigned first, cnt;
+                leafDecode(leaf, first, cnt);
+                for (unsigned k = 0; k < cnt; ++k) {
+                    const float4* tp = S.tris + 3 * (size_t)(first + k);
+                    const float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
+                    if (COUNT) nTris += 1;
+                    TriHit h;
+                    if (triTest(a, b, c, o, d, tmin, tmax, cullBack != 0, h)) {
+                        if (ANY) { occluded = true;  break; }
+                        const unsigned gid = (unsigned)__float_as_int(c.y);
+                        if (h.t < best.t || (h.t == best.t && gid < best.gid)) {
+                            best.t = h.t;  best.u = h.u;  best.v = h.v;  best.slot = (int)(first + k);  best.gid = gid;
+                        }
+                    }
+                }
+                leaf = NO_LEAF;
+                if (ANY && occluded) cur = EMPTY;
+                else if (cur < 0) { leaf = cur;  cur = sp ? stack[--sp] : EMPTY; }   // (EMPTY is positive: never taken for it)
+            }
+        }
+        // ---------------------------------------------------------------- retire finished rays
+        if (active && cur == EMPTY && leaf == NO_LEAF) {
+            if (!ANY) {
+                hit[rayIdx] = make_float4(best.t, best.u, best.v, __int_as_float(best.slot));
+            } else {
+                // prd.radiance += pathThroughput * lightSample (sv4/deviceProgram.cu:659) resolved here.  Target 2 = alpha
+                // when OCCLUDED (shadow catcher, :663-664).  Single writer per slot per launch => deterministic.
+                const int target = __float_as_int(wD);
+                if (occluded == (target == 2)) {
+                    const unsigned slot = (unsigned)__float_as_int(wO);
+                    const float4 pend = pool.pending[slot];
+                    float4* acc = (target == 0 ? pool.direct : (target == 1 ? pool.indirect : pool.alpha)) + slot;
+                    float4 r = *acc;
+                    r.x = __fadd_rn(r.x, pend.x);  r.y = __fadd_rn(r.y, pend.y);  r.z = __fadd_rn(r.z, pend.z);
+                    *acc = r;
+                }
+            }
+            active = false;
         }
     }
     if (COUNT) flushStats(stats, nNodes, nTris, nRays);
@@ -193,18 +277,38 @@ __global__ void traceRaysDebugKernel(SceneDev S, const float4* rayO, const float
     }
 }
 
+static int refillThreshold() {
+    if (g_refillThreshold < 0) {
+        const char* e = getenv("B200PT_REFILL");                  // tuning knob; the default is the measured optimum
+        g_refillThreshold = e ? atoi(e) : 8;
+        if (g_refillThreshold < 1) g_refillThreshold = 1;
+        if (g_refillThreshold > 32) g_refillThreshold = 32;
+    }
+    return g_refillThreshold;
+}
+static int leafThreshold() {
+    if (g_leafThreshold < 0) {
+        const char* e = getenv("B200PT_LEAF");                    // lanes blocked on a leaf before the warp intersects triangles
+        g_leafThreshold = e ? atoi(e) : 8;
+        if (g_leafThreshold < 1) g_leafThreshold = 1;
+        if (g_leafThreshold > 32) g_leafThreshold = 32;
+    }
+    return g_leafThreshold;
+}
+
 void launchTraceClosest(const SceneDev& scene, const float4* rayO, const float4* rayD, float4* hit, const unsigned* count,
                         unsigned* head, float tmin, float tmax, TraceStats* stats, cudaStream_t stream) {
     const dim3 grid(B200PT_NUM_SMS * TRACE_BLOCKS_PER_SM), block(TRACE_BLOCK);
-    if (stats) traceClosestKernel<true><<<grid, block, 0, stream>>>(scene, rayO, rayD, hit, count, head, tmin, tmax, stats);
-    else traceClosestKernel<false><<<grid, block, 0, stream>>>(scene, rayO, rayD, hit, count, head, tmin, tmax, nullptr);
+    const PathPool none{};
+    if (stats) traceKernel<false, true><<<grid, block, 0, stream>>>(scene, rayO, rayD, hit, count, head, tmin, tmax, 0, none, stats, refillThreshold(), leafThreshold());
+    else traceKernel<false, false><<<grid, block, 0, stream>>>(scene, rayO, rayD, hit, count, head, tmin, tmax, 0, none, nullptr, refillThreshold(), leafThreshold());
 }
 
 void launchTraceAny(const SceneDev& scene, const float4* shO, const float4* shD, const unsigned* count, unsigned* head,
                     float tmin, float tmax, int cullBack, const PathPool& pool, TraceStats* stats, cudaStream_t stream) {
     const dim3 grid(B200PT_NUM_SMS * TRACE_BLOCKS_PER_SM), block(TRACE_BLOCK);
-    if (stats) traceAnyKernel<true><<<grid, block, 0, stream>>>(scene, shO, shD, count, head, tmin, tmax, cullBack, pool, stats);
-    else traceAnyKernel<false><<<grid, block, 0, stream>>>(scene, shO, shD, count, head, tmin, tmax, cullBack, pool, nullptr);
+    if (stats) traceKernel<true, true><<<grid, block, 0, stream>>>(scene, shO, shD, nullptr, count, head, tmin, tmax, cullBack, pool, stats + 0, refillThreshold(), leafThreshold());
+    else traceKernel<true, false><<<grid, block, 0, stream>>>(scene, shO, shD, nullptr, count, head, tmin, tmax, cullBack, pool, nullptr, refillThreshold(), leafThreshold());
 }
 
 void launchTraceRaysDebug(const SceneDev& scene, const float4* rayO, const float4* rayD, unsigned n, float tmin, float tmax,
