@@ -2,17 +2,21 @@
 
 struct PassDesc { PassParams P;  size_t nLaunch; };
 
-__global__ void resetCountersKernel(unsigned* counters, int nextQueue, int firstBounce) {
-    // running totals live after the queue counters: [QC_COUNT+0] radiance rays, [+1] shadow rays, [+2] samples
-    const int cur = nextQueue ^ 1;
-    if (firstBounce) counters[QC_COUNT + 2] += counters[cur ? QC_RAY1 : QC_RAY0];
-    counters[QC_COUNT + 0] += counters[cur ? QC_RAY1 : QC_RAY0];
-    counters[nextQueue ? QC_RAY1 : QC_RAY0] = 0;
-    counters[QC_SHADOW] = 0;
-    counters[QC_HEAD_CLOSEST] = 0;
-    counters[QC_HEAD_ANY] = 0;
+// Folds the per-launch queue counters of one group into the frame totals {radiance rays, shadow rays, samples}
+// and clears them for the next group (one tiny launch per group instead of two per bounce).
+__global__ void tallyCountersKernel(unsigned* counters, int nLaunches, unsigned* totals) {
+    unsigned rays = 0, shadows = 0;
+    for (int d = threadIdx.x; d < nLaunches; d += 32) {
+        if (d < nLaunches - 1) rays += counters[QC_STRIDE * d + QC_RAYS];      // the last launch traces shadow rays only
+        shadows += counters[QC_STRIDE * d + QC_SHADOWS];
+    }
+    for (int o = 16; o; o >>= 1) { rays += __shfl_xor_sync(0xffffffffu, rays, o);  shadows += __shfl_xor_sync(0xffffffffu, shadows, o); }
+    __syncwarp();
+    const unsigned samples = counters[QC_RAYS];
+    __syncwarp();
+    if (threadIdx.x == 0) { totals[0] += rays;  totals[1] += shadows;  totals[2] += samples; }
+    for (int i = threadIdx.x; i < QC_STRIDE * nLaunches; i += 32) counters[i] = 0;
 }
-__global__ void tallyShadowKernel(unsigned* counters) { counters[QC_COUNT + 1] += counters[QC_SHADOW]; }
 
 static size_t poolLimit() {
     const char* e = getenv("B200PT_POOL_SLOTS");
@@ -29,7 +33,7 @@ static void ensurePool(b200pt_ctx* c, size_t slots, bool aovs) {
         c->poolCap = slots;
     }
     if (aovs) { c->aovN.ensure(c->poolCap);  c->aovA.ensure(c->poolCap); }
-    c->counters.ensure(QC_COUNT + 8);
+    c->counters.ensure(QC_STRIDE * QC_MAX_LAUNCHES + 8);                     // per-launch queue counters, then 8 frame totals
     c->stats.ensure(2);
 }
 
@@ -44,13 +48,13 @@ struct StageTimer {          // CUDA-event pairs per stage, resolved after the f
     }
     void end(cudaEvent_t b) { if (on) CUDA_OK(cudaEventRecord(b, c->stream)); }
 };
-enum { ST_RAYGEN = 0, ST_CLOSEST, ST_ANY, ST_SHADE, ST_ACCUM, ST_TOTAL };
+enum { ST_RAYGEN = 0, ST_TRACE, ST_TRACE_TAIL, ST_SHADE, ST_ACCUM, ST_TOTAL };
 
 static void collectCounters(b200pt_ctx* c) {
     if (!c->countersPending) return;
-    unsigned h[QC_COUNT + 8];
-    CUDA_OK(cudaMemcpy(h, c->counters.p, sizeof(h), cudaMemcpyDeviceToHost));
-    c->last.radiance_rays = h[QC_COUNT + 0];  c->last.shadow_rays = h[QC_COUNT + 1];  c->last.samples = h[QC_COUNT + 2];
+    unsigned h[8];
+    CUDA_OK(cudaMemcpy(h, c->counters.p + QC_STRIDE * QC_MAX_LAUNCHES, sizeof(h), cudaMemcpyDeviceToHost));
+    c->last.radiance_rays = h[0];  c->last.shadow_rays = h[1];  c->last.samples = h[2];
     if (c->profiled & 2) {
         TraceStats st[2];
         CUDA_OK(cudaMemcpy(st, c->stats.p, sizeof(st), cudaMemcpyDeviceToHost));
@@ -60,7 +64,7 @@ static void collectCounters(b200pt_ctx* c) {
     if (c->profiled & 1) {
         float acc[6] = {0, 0, 0, 0, 0, 0};
         for (auto& u : c->evUsed) { float ms = 0.f;  cudaEventElapsedTime(&ms, u.second.first, u.second.second);  acc[u.first] += ms; }
-        c->last.ms_raygen = acc[ST_RAYGEN];  c->last.ms_trace_closest = acc[ST_CLOSEST];  c->last.ms_trace_any = acc[ST_ANY];
+        c->last.ms_raygen = acc[ST_RAYGEN];  c->last.ms_trace_closest = acc[ST_TRACE];  c->last.ms_trace_any = acc[ST_TRACE_TAIL];
         c->last.ms_shade = acc[ST_SHADE];  c->last.ms_accumulate = acc[ST_ACCUM];  c->last.ms_total = acc[ST_TOTAL];
     }
     c->countersPending = false;
@@ -140,7 +144,7 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
     if (!c->built) throw std::runtime_error("b200pt_render: b200pt_build_accel has not been called");
     if (!params->probe.data || !params->probe.cdfValuesX) throw std::runtime_error("b200pt_render: no probe set (call b200pt_set_probe)");
     if (!params->frame.accum_buffer || !params->frame.frame_buffer) throw std::runtime_error("b200pt_render: frame buffers not allocated (call b200pt_resize)");
-    if (cfg.max_depth < 0 || cfg.max_depth > 200) throw std::runtime_error("b200pt_render: max_depth out of range");
+    if (cfg.max_depth < 0 || cfg.max_depth > QC_MAX_LAUNCHES - 8) throw std::runtime_error("b200pt_render: max_depth out of range");
     if (cfg.russian_roulette) throw std::runtime_error("b200pt_render: russian_roulette is not implemented yet");
     c->countersPending = false;                                                  // totals of an un-synchronised previous frame are dropped
 
@@ -183,13 +187,14 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
     StageTimer T{c, prof};
     cudaEvent_t a = nullptr, b = nullptr, ta = nullptr, tb = nullptr;
     unsigned launches = 0, nClosest = 0, nAny = 0;
-    CUDA_OK(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned) * (QC_COUNT + 8), s));
+    unsigned* totals = c->counters.p + QC_STRIDE * QC_MAX_LAUNCHES;
+    CUDA_OK(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned) * (QC_STRIDE * QC_MAX_LAUNCHES + 8), s));
     if (count) CUDA_OK(cudaMemsetAsync(c->stats.p, 0, 2 * sizeof(TraceStats), s));
     T.begin(ST_TOTAL, ta, tb);
     const int bounces = cfg.max_depth + ((c->hasCatcher || cfg.max_depth == 0) ? 1 : 0);   // the dropped last segment is traced only if alpha can still change
+    const int cullBack = cfg.shadow_mode == B200PT_SHADOW_CULL_BACK;
     for (auto& group : groups) {
         if (group.empty()) continue;
-        CUDA_OK(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned) * QC_COUNT, s));
         T.begin(ST_RAYGEN, a, b);
         for (auto& ch : group) {
             PassParams P = passes[ch.pass].P;  P.slotBase = ch.slotBase;
@@ -197,22 +202,20 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
         }
         T.end(b);
         int cur = 0;
-        for (int d = 0; d < bounces; ++d) {
-            resetCountersKernel<<<1, 1, 0, s>>>(c->counters.p, cur ^ 1, d == 0);  ++launches;
-            T.begin(ST_CLOSEST, a, b);
-            launchTraceClosest(S, Q.rayO[cur], Q.rayD[cur], Q.hit, Q.counters + (cur ? QC_RAY1 : QC_RAY0), Q.counters + QC_HEAD_CLOSEST,
-                               cfg.tmin, cfg.tmax, count ? c->stats.p : nullptr, s);
+        // trace launch d: extension rays of bounce d + the shadow rays shade pass d-1 emitted; launch `bounces` only shadows
+        for (int d = 0; d <= bounces; ++d) {
+            unsigned* ctr = Q.counters + QC_STRIDE * d;
+            T.begin(d < bounces ? ST_TRACE : ST_TRACE_TAIL, a, b);
+            launchTrace(S, Q.rayO[cur], Q.rayD[cur], Q.hit, ctr + (d < bounces ? QC_RAYS : 3 /* always 0 */), Q.shO, Q.shD, ctr + QC_SHADOWS, ctr + QC_HEAD, cfg.tmin, cfg.tmax,
+                        cullBack, pool, count ? c->stats.p : nullptr, s);
             T.end(b);  ++launches;  ++nClosest;
+            if (d == bounces) break;
             T.begin(ST_SHADE, a, b);
             launchShade(F, S, pool, Q, cur, d, s);
             T.end(b);  ++launches;
-            T.begin(ST_ANY, a, b);
-            launchTraceAny(S, Q.shO, Q.shD, Q.counters + QC_SHADOW, Q.counters + QC_HEAD_ANY, cfg.tmin, cfg.tmax,
-                           cfg.shadow_mode == B200PT_SHADOW_CULL_BACK, pool, count ? c->stats.p + 1 : nullptr, s);
-            T.end(b);  ++launches;  ++nAny;
-            tallyShadowKernel<<<1, 1, 0, s>>>(c->counters.p);  ++launches;
             cur ^= 1;
         }
+        tallyCountersKernel<<<1, 32, 0, s>>>(Q.counters, bounces + 1, totals);  ++launches;
         T.begin(ST_ACCUM, a, b);
         for (auto& ch : group) {
             PassParams P = passes[ch.pass].P;  P.slotBase = ch.slotBase;

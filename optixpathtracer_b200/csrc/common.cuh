@@ -92,9 +92,10 @@ struct Queues {
     float4* rayO[2];  float4* rayD[2];      // double-buffered extension-ray queue
     float4* hit;                             // closest-hit results, same order as the current ray queue
     float4* shO;  float4* shD;              // shadow-ray queue
-    unsigned* counters;                      // see QC_* below
+    unsigned* counters;                      // per trace launch d: counters[QC_STRIDE*d + QC_*]
 };
-enum { QC_RAY0 = 0, QC_RAY1 = 1, QC_SHADOW = 2, QC_HEAD_CLOSEST = 3, QC_HEAD_ANY = 4, QC_COUNT = 8 };
+// trace launch d of a frame handles the extension rays of bounce d and the shadow rays emitted by shade pass d-1
+enum { QC_RAYS = 0, QC_SHADOWS = 1, QC_HEAD = 2, QC_STRIDE = 4, QC_MAX_LAUNCHES = 208 };
 
 struct TraceStats { unsigned long long nodes, tris, rays; };
 
@@ -118,10 +119,9 @@ void bvhBuild(const float3* d_vertices, const uint3* d_indices, const unsigned* 
 void bvhFree(BvhBuildResult& r);
 
 // trace.cu  (compiled with FMA contraction; the triangle test itself uses explicit _rn intrinsics)
-void launchTraceClosest(const SceneDev& scene, const float4* rayO, const float4* rayD, float4* hit, const unsigned* count,
-                        unsigned* head, float tmin, float tmax, TraceStats* stats, cudaStream_t stream);
-void launchTraceAny(const SceneDev& scene, const float4* shO, const float4* shD, const unsigned* count, unsigned* head,
-                    float tmin, float tmax, int cullBack, const PathPool& pool, TraceStats* stats, cudaStream_t stream);
+void launchTrace(const SceneDev& scene, const float4* rayO, const float4* rayD, float4* hit, const unsigned* countC,
+                 const float4* shO, const float4* shD, const unsigned* countS, unsigned* head, float tmin, float tmax, int cullBack,
+                 const PathPool& pool, TraceStats* stats /* [0] closest, [1] any; nullptr = no counting */, cudaStream_t stream);
 void launchTraceRaysDebug(const SceneDev& scene, const float4* rayO, const float4* rayD, unsigned n, float tmin, float tmax,
                           int anyHit, int cullBack, float4* hitOut, cudaStream_t stream);
 

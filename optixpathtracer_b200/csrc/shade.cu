@@ -80,7 +80,7 @@ raygenKernel(FrameParams F, PassParams P, int k0, int k1, PathPool pool, Queues 
                 want = true;
             }
         }
-        enqueueRay(want, o4, d4, Q.rayO[0], Q.rayD[0], Q.counters + QC_RAY0);
+        enqueueRay(want, o4, d4, Q.rayO[0], Q.rayD[0], Q.counters + QC_RAYS);
     }
 }
 
@@ -106,10 +106,11 @@ DEV float3 sampleTexture(const SceneDev& S, const MeshInfo* M, float s, float t)
 }
 
 __global__ void __launch_bounds__(SHADE_BLOCK)
-shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int depthHint) {
-    const unsigned count = Q.counters[cur ? QC_RAY1 : QC_RAY0];
+shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int launch) {
+    const unsigned count = Q.counters[QC_STRIDE * launch + QC_RAYS];
     const int nxt = cur ^ 1;
-    unsigned* nextCounter = Q.counters + (nxt ? QC_RAY1 : QC_RAY0);
+    unsigned* nextCounter = Q.counters + QC_STRIDE * (launch + 1) + QC_RAYS;
+    unsigned* shadowCounter = Q.counters + QC_STRIDE * (launch + 1) + QC_SHADOWS;
     const unsigned stride = gridDim.x * blockDim.x;
     for (unsigned base = blockIdx.x * blockDim.x; base < count; base += stride) {
         const unsigned i = base + threadIdx.x;
@@ -221,9 +222,8 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int dep
             pool.state[slot] = (depth & 0xff) | (flags << 8);
         }
         enqueueRay(wantRay, ro, rd, Q.rayO[nxt], Q.rayD[nxt], nextCounter);
-        enqueueRay(wantShadow, so, sd, Q.shO, Q.shD, Q.counters + QC_SHADOW);
+        enqueueRay(wantShadow, so, sd, Q.shO, Q.shD, shadowCounter);
     }
-    (void)depthHint;
 }
 
 // Per-launch-index sums over the samples of one chunk, in sample order (result += direct+indirect, :516-517).

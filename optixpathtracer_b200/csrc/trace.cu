@@ -1,12 +1,14 @@
 // b200pt — BVH traversal kernels (replace the closed optixTrace of sv4/deviceProgram.cu:207,232).
-//   traceKernel<false> : RADIANCE rays  — closest hit in (tmin,tmax), ties -> lowest global triangle id
-//   traceKernel<true>  : OCCLUSION rays — any hit (optionally only triangles front-facing the ray), early out;
-//                        visible rays add their pending NEE contribution to the path's radiance accumulator
+//   RADIANCE rays  — closest hit in (tmin,tmax), ties -> lowest global triangle id
+//   OCCLUSION rays — any hit (optionally only triangles front-facing the ray), early out;
+//                    visible rays add their pending NEE contribution to the path's radiance accumulator
+// Both kinds are traced by the same launch of traceKernel (one launch per bounce).
 // Persistent warps (a fixed grid of B200PT_NUM_SMS x k CTAs).  Each warp stages chunks of 32 rays from the
-// device-side queue into shared memory with one atomic per chunk; a lane whose ray terminates takes the next
-// staged ray as soon as enough lanes are idle (per-lane replacement decided by a warp vote), so a warp never
-// idles behind its slowest ray.  Traversal is "while-while": every lane walks inner nodes until it holds a
-// postponed leaf and reaches a second one (or runs dry), then the warp intersects leaves together.
+// device-side queues into shared memory (one ticket atomic per chunk, cp.async, double-buffered and prefetched);
+// a lane whose ray terminates takes the next staged ray as soon as enough lanes are idle (per-lane replacement
+// decided by a warp vote), so a warp never idles behind its slowest ray.  Every loop iteration each lane takes
+// ONE inner-node step if it can; a lane that reaches a leaf postpones it and keeps walking; once enough lanes
+// are blocked on a second leaf (warp vote) the warp intersects all pending leaves together.
 // A 32-byte node is ONE 256-bit load (LDG.E.256, new on sm_100); a sibling pair is two of them in one 64-byte
 // aligned half cache line; a 48-byte triangle is 3x128-bit.  All fetches go through the read-only path.
 // Roofline: L1/L2 gather bound; algorithmic bytes per ray = 32*nodes + 48*tris + 32 (ray) + 16 (hit).
@@ -140,26 +142,41 @@ __device__ __forceinline__ void flushStats(TraceStats* stats, unsigned nNodes, u
     }
 }
 
-// ANY = false: hit[i] = {t,u,v,triSlot} for ray i of the queue.
-// ANY = true : rayO.w = path slot, rayD.w = target (0 direct, 1 indirect, 2 alpha-when-occluded); see shade.cu.
-template <bool ANY, bool COUNT>
+// cp.async (LDGSTS): 16 bytes global -> shared without a register round trip; completion via wait_all.
+__device__ __forceinline__ void cpAsync16(void* smemDst, const void* gmemSrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smemDst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" :: "r"(d), "l"(gmemSrc) : "memory");
+}
+__device__ __forceinline__ void cpAsyncCommit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cpAsyncWaitAll() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// One launch traces BOTH queues of a bounce: the extension rays (closest hit -> hit[i] = {t,u,v,triSlot}) and the
+// shadow rays the previous shade pass emitted (any hit; rayO.w = path slot, rayD.w = target: 0 direct, 1 indirect,
+// 2 alpha-when-occluded, see shade.cu).  Work is handed out in chunks of 32 rays by one ticket counter; chunk ids
+// below ceil(countC/32) are extension rays, the rest shadow rays, so the short any-hit rays fill the tail of the
+// long closest-hit ones.  The next chunk is prefetched (ticket atomic, then cp.async into the spare stage buffer)
+// while the warp is still traversing the current one.
+template <bool COUNT>
 __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_BLOCKS_PER_SM)
 traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restrict__ rayD, float4* __restrict__ hit,
-            const unsigned* __restrict__ countPtr, unsigned* head, float tmin, float tmax, int cullBack, PathPool pool,
+            const unsigned* __restrict__ countCPtr, const float4* __restrict__ shO, const float4* __restrict__ shD,
+            const unsigned* __restrict__ countSPtr, unsigned* head, float tmin, float tmax, int cullBack, PathPool pool,
             TraceStats* stats, int refillThreshold, int leafThreshold) {
-    __shared__ float4 stageO[TRACE_WARPS][32], stageD[TRACE_WARPS][32];
-    const unsigned count = *countPtr;
+    __shared__ float4 stageO[TRACE_WARPS][2][32], stageD[TRACE_WARPS][2][32];
+    const unsigned countC = *countCPtr, countS = *countSPtr;
+    const unsigned chunksC = (countC + 31u) >> 5, chunksTotal = chunksC + ((countS + 31u) >> 5);
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned ltMask = (1u << lane) - 1u;
     const int rootLink = __float_as_int(ldg4(S.nodes).w);
-    unsigned nNodes = 0, nTris = 0, nRays = 0;
+    unsigned nNodes[2] = {0, 0}, nTris[2] = {0, 0}, nRays[2] = {0, 0}, myNodes = 0, myTris = 0;
 
-    // warp-uniform staging state: rays [stageNext, stageEnd) of chunk `stageBase` are still unassigned
-    unsigned stageBase = 0, stageNext = 0, stageEnd = 0;
-    bool exhausted = false;
+    // warp-uniform staging state: rays [stageNext, stageEnd) of the current chunk are still unassigned
+    unsigned stageNext = 0, stageEnd = 0, stageFirst = 0;  int stageAny = 0, buf = 0;
+    // prefetch state: 0 idle, 1 ticket in flight, 2 chunk landing in buffer buf^1, 3 queue exhausted
+    int pf = 0;  unsigned ticket = 0, pfFirst = 0, pfEnd = 0;  int pfAny = 0, pfAge = 0;
 
     // per-lane ray state
-    bool active = false;
+    bool active = false, isAny = false;
     unsigned rayIdx = 0;
     float3 o = make_float3(0, 0, 0), d = o, inv = o;
     float wO = 0.f, wD = 0.f;
@@ -168,44 +185,88 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
     int stack[B200PT_STACK];
 
     while (true) {
+        // ---------------------------------------------------------------- prefetch the next chunk (warp-uniform)
+        if (pf == 0 && stageEnd - stageNext <= 8u) {
+            if (lane == 0) ticket = atomicAdd(head, 1u);          // not read until a later iteration: no stall here
+            pf = 1;  pfAge = 0;
+        } else if (pf == 1 && ++pfAge >= 3) {
+            const unsigned c = __shfl_sync(FULL, ticket, 0);
+            if (c >= chunksTotal) pf = 3;
+            else {
+                pfAny = c >= chunksC;
+                const unsigned first = (pfAny ? c - chunksC : c) << 5, cnt = pfAny ? countS : countC;
+                pfFirst = first;  pfEnd = min(first + 32u, cnt);
+                if (first + lane < pfEnd) {
+                    cpAsync16(&stageO[warp][buf ^ 1][lane], (pfAny ? shO : rayO) + first + lane);
+                    cpAsync16(&stageD[warp][buf ^ 1][lane], (pfAny ? shD : rayD) + first + lane);
+                }
+                cpAsyncCommit();
+                pf = 2;
+            }
+        }
         // ---------------------------------------------------------------- refill idle lanes (warp-synchronous)
         unsigned idle = __ballot_sync(FULL, !active);
-        if (idle == FULL || ((int)__popc(idle) >= refillThreshold && !(exhausted && stageNext >= stageEnd))) {
+        if (idle == FULL || ((int)__popc(idle) >= refillThreshold && !(pf == 3 && stageNext >= stageEnd))) {
 #pragma unroll 1
             for (int round = 0; round < 2 && idle; ++round) {
-                if (stageNext >= stageEnd) {
-                    if (exhausted) break;
-                    unsigned b = 0;
-                    if (lane == 0) b = atomicAdd(head, 32u);
-                    b = __shfl_sync(FULL, b, 0);
-                    if (b >= count) { exhausted = true;  break; }
+                if (stageNext >= stageEnd) {                      // current chunk used up: switch to the prefetched one
+                    if (pf == 0) { if (lane == 0) ticket = atomicAdd(head, 1u);  pf = 1; }
+                    if (pf == 1) {
+                        const unsigned c = __shfl_sync(FULL, ticket, 0);
+                        if (c >= chunksTotal) pf = 3;
+                        else {
+                            pfAny = c >= chunksC;
+                            const unsigned first = (pfAny ? c - chunksC : c) << 5, cnt = pfAny ? countS : countC;
+                            pfFirst = first;  pfEnd = min(first + 32u, cnt);
+                            if (first + lane < pfEnd) {
+                                cpAsync16(&stageO[warp][buf ^ 1][lane], (pfAny ? shO : rayO) + first + lane);
+                                cpAsync16(&stageD[warp][buf ^ 1][lane], (pfAny ? shD : rayD) + first + lane);
+                            }
+                            cpAsyncCommit();
+                            pf = 2;
+                        }
+                    }
+                    if (pf == 3) break;
+                    cpAsyncWaitAll();
                     __syncwarp();
-                    if (b + lane < count) { stageO[warp][lane] = rayO[b + lane];  stageD[warp][lane] = rayD[b + lane]; }
-                    __syncwarp();
-                    stageBase = b;  stageNext = b;  stageEnd = min(b + 32u, count);
+                    buf ^= 1;  stageFirst = pfFirst;  stageNext = pfFirst;  stageEnd = pfEnd;  stageAny = pfAny;  pf = 0;
                 }
                 const unsigned avail = stageEnd - stageNext;
                 const unsigned r = __popc(idle & ltMask);
                 if (!active && r < avail) {
                     const unsigned j = stageNext + r;
-                    const float4 o4 = stageO[warp][j - stageBase], d4 = stageD[warp][j - stageBase];
+                    const float4 o4 = stageO[warp][buf][j - stageFirst], d4 = stageD[warp][buf][j - stageFirst];
                     o = make_float3(o4.x, o4.y, o4.z);  d = make_float3(d4.x, d4.y, d4.z);  wO = o4.w;  wD = d4.w;
                     inv = make_float3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
-                    rayIdx = j;  active = true;
+                    rayIdx = j;  active = true;  isAny = stageAny != 0;
                     best.t = tmax;  best.slot = -1;  best.gid = 0xffffffffu;  best.u = best.v = 0.f;
                     cur = rootLink;  leaf = NO_LEAF;  sp = 0;
-                    if (COUNT) nRays++;
+                    if (COUNT) { nRays[isAny]++;  myNodes = 0;  myTris = 0; }
                 }
                 stageNext += min(avail, (unsigned)__popc(idle));
+                __syncwarp();
                 idle = __ballot_sync(FULL, !active);
             }
-            if (idle == FULL) break;                               // queue drained and every lane finished
+            if (idle == FULL) break;                               // queues drained and every lane finished
         }
 
         // ---------------------------------------------------------------- one inner-node step per lane that can take one
         bool occluded = false;
         if (active && (unsigned)cur < (unsigned)EMPTY) {
-            NODE_STEP()
+            const float4* p_ = S.nodes + 2 * (size_t)cur;
+            const Node8 L_ = ldgNode(p_), R_ = ldgNode(p_ + 2);
+            if (COUNT) myNodes += 2;
+            float tl_, tr_;
+            const bool hl_ = boxTest(L_.a, L_.b, o, inv, tmin, best.t, tl_);
+            const bool hr_ = boxTest(R_.a, R_.b, o, inv, tmin, best.t, tr_);
+            const int cl_ = __float_as_int(L_.a.w), cr_ = __float_as_int(R_.a.w);
+            if (hl_ && hr_) {
+                const bool sw_ = tr_ < tl_;
+                stack[sp++] = sw_ ? cl_ : cr_;
+                cur = sw_ ? cr_ : cl_;
+            } else if (hl_) cur = cl_;
+            else if (hr_) cur = cr_;
+            else cur = sp ? stack[--sp] : EMPTY;
             if (cur < 0 && leaf == NO_LEAF) {                      // first leaf: postpone it and keep walking
                 leaf = cur;
                 cur = sp ? stack[--sp] : EMPTY;
@@ -220,13 +281,14 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
             if (active && leaf != NO_LEAF) {
                 unsigned first, cnt;
                 leafDecode(leaf, first, cnt);
+                const bool cull = isAny && cullBack != 0;
                 for (unsigned k = 0; k < cnt; ++k) {
                     const float4* tp = S.tris + 3 * (size_t)(first + k);
                     const float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
-                    if (COUNT) nTris += 1;
+                    if (COUNT) myTris += 1;
                     TriHit h;
-                    if (triTest(a, b, c, o, d, tmin, tmax, cullBack != 0, h)) {
-                        if (ANY) { occluded = true;  break; }
+                    if (triTest(a, b, c, o, d, tmin, tmax, cull, h)) {
+                        if (isAny) { occluded = true;  break; }
                         const unsigned gid = (unsigned)__float_as_int(c.y);
                         if (h.t < best.t || (h.t == best.t && gid < best.gid)) {
                             best.t = h.t;  best.u = h.u;  best.v = h.v;  best.slot = (int)(first + k);  best.gid = gid;
@@ -234,13 +296,13 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
                     }
                 }
                 leaf = NO_LEAF;
-                if (ANY && occluded) cur = EMPTY;
+                if (occluded) cur = EMPTY;
                 else if (cur < 0) { leaf = cur;  cur = sp ? stack[--sp] : EMPTY; }   // (EMPTY is positive: never taken for it)
             }
         }
         // ---------------------------------------------------------------- retire finished rays
         if (active && cur == EMPTY && leaf == NO_LEAF) {
-            if (!ANY) {
+            if (!isAny) {
                 hit[rayIdx] = make_float4(best.t, best.u, best.v, __int_as_float(best.slot));
             } else {
                 // prd.radiance += pathThroughput * lightSample (sv4/deviceProgram.cu:659) resolved here.  Target 2 = alpha
@@ -255,10 +317,11 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
                     *acc = r;
                 }
             }
+            if (COUNT) { nNodes[isAny] += myNodes;  nTris[isAny] += myTris; }
             active = false;
         }
     }
-    if (COUNT) flushStats(stats, nNodes, nTris, nRays);
+    if (COUNT) { flushStats(stats, nNodes[0], nTris[0], nRays[0]);  flushStats(stats + 1, nNodes[1], nTris[1], nRays[1]); }
 }
 
 __global__ void traceRaysDebugKernel(SceneDev S, const float4* rayO, const float4* rayD, unsigned n, float tmin, float tmax,
@@ -296,19 +359,12 @@ static int leafThreshold() {
     return g_leafThreshold;
 }
 
-void launchTraceClosest(const SceneDev& scene, const float4* rayO, const float4* rayD, float4* hit, const unsigned* count,
-                        unsigned* head, float tmin, float tmax, TraceStats* stats, cudaStream_t stream) {
+void launchTrace(const SceneDev& scene, const float4* rayO, const float4* rayD, float4* hit, const unsigned* countC,
+                 const float4* shO, const float4* shD, const unsigned* countS, unsigned* head, float tmin, float tmax, int cullBack,
+                 const PathPool& pool, TraceStats* stats, cudaStream_t stream) {
     const dim3 grid(B200PT_NUM_SMS * TRACE_BLOCKS_PER_SM), block(TRACE_BLOCK);
-    const PathPool none{};
-    if (stats) traceKernel<false, true><<<grid, block, 0, stream>>>(scene, rayO, rayD, hit, count, head, tmin, tmax, 0, none, stats, refillThreshold(), leafThreshold());
-    else traceKernel<false, false><<<grid, block, 0, stream>>>(scene, rayO, rayD, hit, count, head, tmin, tmax, 0, none, nullptr, refillThreshold(), leafThreshold());
-}
-
-void launchTraceAny(const SceneDev& scene, const float4* shO, const float4* shD, const unsigned* count, unsigned* head,
-                    float tmin, float tmax, int cullBack, const PathPool& pool, TraceStats* stats, cudaStream_t stream) {
-    const dim3 grid(B200PT_NUM_SMS * TRACE_BLOCKS_PER_SM), block(TRACE_BLOCK);
-    if (stats) traceKernel<true, true><<<grid, block, 0, stream>>>(scene, shO, shD, nullptr, count, head, tmin, tmax, cullBack, pool, stats + 0, refillThreshold(), leafThreshold());
-    else traceKernel<true, false><<<grid, block, 0, stream>>>(scene, shO, shD, nullptr, count, head, tmin, tmax, cullBack, pool, nullptr, refillThreshold(), leafThreshold());
+    if (stats) traceKernel<true><<<grid, block, 0, stream>>>(scene, rayO, rayD, hit, countC, shO, shD, countS, head, tmin, tmax, cullBack, pool, stats, refillThreshold(), leafThreshold());
+    else traceKernel<false><<<grid, block, 0, stream>>>(scene, rayO, rayD, hit, countC, shO, shD, countS, head, tmin, tmax, cullBack, pool, nullptr, refillThreshold(), leafThreshold());
 }
 
 void launchTraceRaysDebug(const SceneDev& scene, const float4* rayO, const float4* rayD, unsigned n, float tmin, float tmax,
