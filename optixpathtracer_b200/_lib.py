@@ -6,7 +6,7 @@ import os
 from .structs import BvhInfo, Config, Counters, LaunchParams, Material
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libb200pt.so")
+LIB_PATH = os.environ.get("B200PT_LIB") or os.path.join(_HERE, "csrc", "libb200pt.so")   # B200PT_LIB: kernel-tuning builds only
 
 # every symbol include/b200pt.h declares (tests/test_cabi_symbols.py checks the header against this list)
 SYMBOLS = [

@@ -31,7 +31,7 @@ struct b200pt_ctx {
     // --- frame
     int W = 0, H = 0;
     DevBuf<uint32_t> frameBuf;  DevBuf<float4> accumBuf, normalBuf, albedoBuf, colorBuf;
-    DevBuf<float> probeData, probePdfX, probeCdfX, probePdfY, probeCdfY;
+    DevBuf<float> probeData, probePdfX, probeCdfX, probePdfY, probeCdfY, probeCoarse;  int probeW = 0, probeH = 0;
     // --- wavefront pool
     size_t poolCap = 0;
     DevBuf<uint2> rng;  DevBuf<float4> thr, direct, indirect, alpha, pending, aovN, aovA;  DevBuf<int> state;
@@ -91,7 +91,7 @@ void b200pt_destroy(b200pt_ctx* c) {
     bvhFree(c->bvh);
     c->dVertices.release();  c->dTexcoords.release();  c->dIndices.release();  c->dTriMesh.release();  c->dMeshes.release();  c->dTexels.release();
     c->frameBuf.release();  c->accumBuf.release();  c->normalBuf.release();  c->albedoBuf.release();  c->colorBuf.release();
-    c->probeData.release();  c->probePdfX.release();  c->probeCdfX.release();  c->probePdfY.release();  c->probeCdfY.release();
+    c->probeData.release();  c->probePdfX.release();  c->probeCdfX.release();  c->probePdfY.release();  c->probeCdfY.release();  c->probeCoarse.release();
     c->rng.release();  c->thr.release();  c->direct.release();  c->indirect.release();  c->alpha.release();  c->pending.release();
     c->aovN.release();  c->aovA.release();  c->state.release();
     for (int i = 0; i < 2; ++i) { c->rayO[i].release();  c->rayD[i].release(); }

@@ -121,11 +121,13 @@ static void buildSchedule(LaunchParams& P, const b200pt_config& cfg, std::vector
     }
 }
 
-static FrameParams frameOf(const LaunchParams& P, const b200pt_config& cfg) {
+static FrameParams frameOf(const LaunchParams& P, const b200pt_config& cfg, const b200pt_ctx* c = nullptr) {
     FrameParams F;
     F.W = P.frame.size.x;  F.H = P.frame.size.y;
     F.eye = P.camera.eye;  F.U = P.camera.U;  F.V = P.camera.V;  F.Wv = P.camera.W;
     F.probe = P.probe;
+    // the coarse CDF table belongs to the probe uploaded by b200pt_set_probe; a caller-substituted probe falls back
+    F.cdfXCoarse = (c && c->probeCoarse.p && P.probe.cdfValuesX == c->probeCdfX.p && P.probe.width == c->probeW && P.probe.height == c->probeH) ? c->probeCoarse.p : nullptr;
     F.tmin = cfg.tmin;  F.tmax = cfg.tmax;  F.maxDepth = cfg.max_depth;  F.shadowMode = cfg.shadow_mode;  F.display = cfg.display;
     F.accumMode = cfg.accum_mode;  F.writeAovs = cfg.write_aovs;  F.exposure = cfg.exposure;
     F.tileRank = cfg.tile_rank;  F.tileCount = cfg.tile_count;
@@ -150,7 +152,7 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
 
     std::vector<PassDesc> passes;
     buildSchedule(*params, cfg, passes);
-    const FrameParams F = frameOf(*params, cfg);
+    const FrameParams F = frameOf(*params, cfg, c);
     const SceneDev S = sceneOf(c);
     cudaStream_t s = c->stream;
 
@@ -272,6 +274,9 @@ int b200pt_set_probe(b200pt_ctx* c, int w, int h, const float* data, const float
     CUDA_OK(cudaMemcpyAsync(c->probeCdfX.p, cdfX, 4 * n, cudaMemcpyHostToDevice, c->stream));
     CUDA_OK(cudaMemcpyAsync(c->probePdfY.p, pdfY, 4 * (size_t)h, cudaMemcpyHostToDevice, c->stream));
     CUDA_OK(cudaMemcpyAsync(c->probeCdfY.p, cdfY, 4 * (size_t)h, cudaMemcpyHostToDevice, c->stream));
+    c->probeCoarse.ensure((size_t)((w + 31) / 32) * h);
+    launchProbeCoarse(c->probeCdfX.p, w, h, c->probeCoarse.p, c->stream);
+    c->probeW = w;  c->probeH = h;
     CUDA_OK(cudaStreamSynchronize(c->stream));
     params->probe.width = w;  params->probe.height = h;  params->probe.data = (Color*)c->probeData.p;
     params->probe.pdfValuesX = c->probePdfX.p;  params->probe.cdfValuesX = c->probeCdfX.p;

@@ -69,6 +69,7 @@ struct FrameParams {               // shared by every pass of a frame
     int W, H;
     float3 eye, U, V, Wv;
     Probe probe;                   // device pointers
+    const float* cdfXCoarse;       // every 32nd entry of each cdfValuesX row (nullptr: plain binary search)
     float tmin, tmax;
     int maxDepth, shadowMode, display, accumMode, writeAovs;
     float exposure;
@@ -135,6 +136,7 @@ void launchGather(const FrameParams& F, const PassParams& P, int k0, int k1, con
 void launchFinalize(const FrameParams& F, const PassParams& P, const float4* sumRad, const float4* sumAlpha,
                     const float4* sumNormal, const float4* sumAlbedo, cudaStream_t stream);
 void launchResolveSum(const FrameParams& F, int nPasses, cudaStream_t stream);
+void launchProbeCoarse(const float* cdfX, int W, int H, float* coarse, cudaStream_t stream);
 void launchTonemapSqrt(int w, int h, const float4* in, uint32_t* out, cudaStream_t stream);
 void launchPrimaryRays(const FrameParams& F, const PassParams& P, float4* rayO, float4* rayD, cudaStream_t stream);
 void launchResolvePrimary(const SceneDev& scene, const float4* hit, unsigned n, const float4* rayO, int32_t* prim, int32_t* mesh,

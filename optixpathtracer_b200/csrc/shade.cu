@@ -8,6 +8,9 @@
 #include "shade_math.cuh"
 
 #define SHADE_BLOCK 128
+#ifndef SHADE_MIN_BLOCKS
+#define SHADE_MIN_BLOCKS 8
+#endif
 
 DEV void enqueueRay(bool want, float4 o, float4 d, float4* qo, float4* qd, unsigned* counter) {
     const unsigned mask = __ballot_sync(0xffffffffu, want);
@@ -105,7 +108,7 @@ DEV float3 sampleTexture(const SceneDev& S, const MeshInfo* M, float s, float t)
     return f3(out[0], out[1], out[2]);
 }
 
-__global__ void __launch_bounds__(SHADE_BLOCK)
+__global__ void __launch_bounds__(SHADE_BLOCK, SHADE_MIN_BLOCKS)
 shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int launch) {
     const unsigned count = Q.counters[QC_STRIDE * launch + QC_RAYS];
     const int nxt = cur ^ 1;
@@ -168,7 +171,7 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                         Rng rng;  rng.s1 = rs.x;  rng.s2 = rs.y;
                         // SampleLights / SampleShadow, :301-384
                         float3 wi, skyColor;  float skyPdf;
-                        probeSample(F.probe, wi, skyColor, skyPdf, rng);
+                        probeSample(F.probe, F.cdfXCoarse, wi, skyColor, skyPdf, rng);
                         const float bp = bsdfPdf(mat, rayEta, outEta, N, wo, wi);
                         float3 pend = f3(0.f);
                         bool valid = false;
@@ -363,6 +366,19 @@ __global__ void resolvePrimaryKernel(SceneDev S, const float4* hit, unsigned n, 
     const int m = __float_as_int(c.z);
     mesh[i] = m;  prim[i] = (int)((unsigned)__float_as_int(c.y) - S.meshes[m].firstTri);
     t[i] = h.x;  u[i] = h.y;  v[i] = h.z;
+}
+
+// every 32nd entry (the LAST of each 32-block) of each CDF row; see lowerBoundRow
+__global__ void probeCoarseKernel(const float* __restrict__ cdfX, int W, int H, float* __restrict__ coarse) {
+    const int nc = (W + 31) >> 5;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nc * H) return;
+    const int row = i / nc, k = i % nc;
+    coarse[i] = cdfX[(size_t)row * W + min(W - 1, 32 * k + 31)];
+}
+void launchProbeCoarse(const float* cdfX, int W, int H, float* coarse, cudaStream_t s) {
+    const int n = ((W + 31) >> 5) * H;
+    if (n > 0) probeCoarseKernel<<<(n + 255) / 256, 256, 0, s>>>(cdfX, W, H, coarse);
 }
 
 // ---- launchers ---------------------------------------------------------------------------------------------

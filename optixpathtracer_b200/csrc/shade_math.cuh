@@ -268,11 +268,22 @@ DEV int lowerBound(const float* __restrict__ a, int lower, int upper, float valu
     }
     return lower;
 }
-DEV void probeSample(const Probe& P, float3& dir, float3& color, float& pdf, Rng& rand) {   // :138-169
+// Same index as LowerBound over the whole row (the row CDF is non-decreasing, so lower_bound is unique), found in
+// two steps: a search over every 32nd entry (coarse table built by b200pt_set_probe, 1/32 of the footprint, so it
+// stays cache-resident) and a search inside one 128-byte line of the full table: ~3 cache misses instead of ~11.
+DEV int lowerBoundRow(const Probe& P, const float* __restrict__ coarse, int row, float value) {
+    const int W = P.width, base = row * W;
+    if (!coarse) return lowerBound(P.cdfValuesX, base, base + W, value) - base;
+    const int nc = (W + 31) >> 5;
+    const int k = lowerBound(coarse, row * nc, (row + 1) * nc, value) - row * nc;
+    if (k == nc) return W;                                       // value above the last entry: LowerBound returns `upper`
+    return lowerBound(P.cdfValuesX, base + 32 * k, base + min(32 * k + 32, W), value) - base;
+}
+DEV void probeSample(const Probe& P, const float* __restrict__ coarse, float3& dir, float3& color, float& pdf, Rng& rand) {   // :138-169
     float r1, r2;
     sample2D(rand, r1, r2);
     const int row = lowerBound(P.cdfValuesY, 0, P.height, r1);
-    const int col = lowerBound(P.cdfValuesX, row * P.width, (row + 1) * P.width, r2) - row * P.width;
+    const int col = lowerBoundRow(P, coarse, row, r2);
     const float4 c = __ldg(reinterpret_cast<const float4*>(P.data) + (row * P.width + col));
     color = f3(c.x, c.y, c.z);
     pdf = __ldg(P.pdfValuesX + row * P.width + col) * __ldg(P.pdfValuesY + row);
