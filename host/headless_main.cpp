@@ -1,0 +1,152 @@
+// Headless driver: the reference application's call sequence (HelloPathtracing_sv4_vmv23/main.cpp:182-427) without the
+// GLFW/OpenGL window (no graphics stack on this box): loadOBJ -> probe -> camera -> SampleRenderer -> setCamera -> resize ->
+// setProbe -> loop { gaze -> render -> fps log } -> downloadPixels -> PPM.  The gaze point, which the reference takes from the
+// mouse cursor (main.cpp:310-314), follows a scripted Lissajous track.  fps is appended every 0.5 s in the reference's
+// log format (sutil/sutil.cpp:760-772: one value per line).
+//
+//   b200pt_headless [--obj file.obj | --boxes N] [--preset sv4_fov|sv4_uniform|sv3_uniform|orig] [--size WxH] [--frames N]
+//                   [--camera sponza|lost_empire|san_miguel|cornell] [--sky r,g,b] [--out image.ppm] [--log fps.tsv]
+//                   [--dump-model file.bin] [--no-render]
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <random>
+#include <string>
+#include <vector>
+
+#include "../include/ref_api/SimplePathtracer.h"
+
+static void loadColor(ProbeData& probe, const float3& color, int width, int height) {        // main.cpp:167-180
+    probe.width = width;  probe.height = height;
+    probe.data = new Color[(size_t)width * height];
+    for (size_t i = 0; i < (size_t)width * height; ++i) probe.data[i] = Color{color.x, color.y, color.z, 1.0f};
+    probe.BuildCDF();
+}
+
+static sutil::Camera cameraPreset(const std::string& name) {                                 // main.cpp:211-240
+    if (name == "sponza") return sutil::Camera({-1293.07f, 154.681f, 1.0f}, {0.f, 200.f, 0.f}, {0.f, 1.f, 0.f}, 35.f, 1.f);
+    if (name == "san_miguel") return sutil::Camera({26.f, 8.f, -2.f}, {0.f, 0.f, 0.f}, {0.f, 1.f, 0.f}, 35.f, 1.f);
+    if (name == "lost_empire") return sutil::Camera({-70.f, 40.f, 100.f}, {0.f, 0.f, 0.f}, {0.f, 1.f, 0.f}, 45.f, 1.f);
+    return sutil::Camera({0.f, 1.f, 3.2f}, {0.f, 1.f, 0.f}, {0.f, 1.f, 0.f}, 40.f, 1.f);
+}
+
+static Model* boxScene(int n, unsigned seed) {          // addBox-only scene (Model.cpp:218-290): a floor and n random boxes
+    Model* m = new Model;
+    std::mt19937 rng(seed);
+    std::uniform_real_distribution<float> u(0.f, 1.f);
+    Material floor = Material::origDefaults();
+    addBox(m, floor, {0.f, -0.05f, 0.f}, {3.f, 0.05f, 3.f});
+    for (int i = 0; i < n; ++i) {
+        Material mat = (i % 3 == 0) ? Material() : Material::origDefaults();
+        mat.color = {0.2f + 0.7f * u(rng), 0.2f + 0.7f * u(rng), 0.2f + 0.7f * u(rng)};
+        mat.emission = {0.f, 0.f, 0.f};
+        const float s = 0.08f + 0.25f * u(rng);
+        addBox(m, mat, {-1.5f + 3.f * u(rng), s, -1.5f + 3.f * u(rng)}, {s, s, s});
+    }
+    return m;
+}
+
+static void dumpModel(const Model* m, const char* path) {    // flat binary for the loadOBJ parity test (tests/test_cpp_host.py)
+    FILE* f = fopen(path, "wb");
+    if (!f) throw std::runtime_error(std::string("cannot write ") + path);
+    const int nm = (int)m->meshes.size(), nt = (int)m->textures.size();
+    fwrite(&nm, 4, 1, f);  fwrite(&nt, 4, 1, f);
+    for (auto mesh : m->meshes) {
+        const int c[5] = {(int)mesh->vertex.size(), (int)mesh->normal.size(), (int)mesh->texcoord.size(), (int)mesh->index.size(), mesh->diffuseTextureID};
+        fwrite(c, 4, 5, f);
+        fwrite(&mesh->material, sizeof(Material), 1, f);
+        fwrite(mesh->vertex.data(), 12, mesh->vertex.size(), f);
+        fwrite(mesh->normal.data(), 12, mesh->normal.size(), f);
+        fwrite(mesh->texcoord.data(), 8, mesh->texcoord.size(), f);
+        fwrite(mesh->index.data(), 12, mesh->index.size(), f);
+    }
+    for (auto t : m->textures) {
+        fwrite(&t->resolution, 8, 1, f);
+        fwrite(t->pixel, 4, (size_t)t->resolution.x * t->resolution.y, f);
+    }
+    fclose(f);
+}
+
+int main(int argc, char** argv) {
+    std::string obj, preset = "sv4_fov", cam = "cornell", out, log, dump;
+    int W = 1280, H = 720, frames = 16, boxes = 64;
+    float3 sky{1.f, 1.f, 1.f};
+    bool noRender = false;
+    for (int i = 1; i < argc; ++i) {
+        const std::string a = argv[i];
+        auto next = [&]() -> const char* { if (i + 1 >= argc) { fprintf(stderr, "missing value for %s\n", a.c_str());  exit(2); } return argv[++i]; };
+        if (a == "--obj") obj = next();
+        else if (a == "--boxes") boxes = atoi(next());
+        else if (a == "--preset") preset = next();
+        else if (a == "--camera") cam = next();
+        else if (a == "--size") { if (sscanf(next(), "%dx%d", &W, &H) != 2) { fprintf(stderr, "--size WxH\n");  return 2; } }
+        else if (a == "--frames") frames = atoi(next());
+        else if (a == "--sky") { if (sscanf(next(), "%f,%f,%f", &sky.x, &sky.y, &sky.z) != 3) { fprintf(stderr, "--sky r,g,b\n");  return 2; } }
+        else if (a == "--out") out = next();
+        else if (a == "--log") log = next();
+        else if (a == "--dump-model") dump = next();
+        else if (a == "--no-render") noRender = true;
+        else { fprintf(stderr, "unknown argument %s\n", a.c_str());  return 2; }
+    }
+    try {
+        std::unique_ptr<Model> model(obj.empty() ? boxScene(boxes, 0x5702A) : loadOBJ(obj));             // main.cpp:188
+        printf("model: %zu meshes, %zu textures, %zu triangles\n", model->meshes.size(), model->textures.size(), model->numTriangles());
+        if (!dump.empty()) dumpModel(model.get(), dump.c_str());
+        if (noRender) return 0;
+        ProbeData probe;
+        loadColor(probe, sky, 512, 256);                                                                    // main.cpp:205-206
+        sutil::Camera camera = cameraPreset(cam);                                                           // :213-217
+        SampleRenderer sample(model.get(), 0, preset.c_str());                                              // :252
+        sample.setCamera(camera);                                                                           // :253 (before resize, like the reference)
+        sample.resize(int2{W, H});                                                                          // :256-262
+        sample.setProbe(probe);                                                                             // :269
+        const b200pt_bvh_info bi = sample.bvhInfo();
+        printf("bvh: %llu nodes, %llu leaves, SAH %.2f (LBVH %.2f), build %.2f ms\n", (unsigned long long)bi.n_nodes,
+               (unsigned long long)bi.n_leaves, bi.sah_cost, bi.sah_cost_lbvh, bi.build_ms);
+        FILE* flog = log.empty() ? nullptr : fopen(log.c_str(), "a");
+        auto t0 = std::chrono::steady_clock::now(), tWindow = t0;
+        int windowFrames = 0;
+        unsigned long long samples = 0, rays = 0;
+        for (int f = 0; f < frames; ++f) {                                                                  // :308-394
+            const float ph = 0.37f * f;
+            sample.launchParams.frame.c = uint2{(unsigned)(W * (0.5f + 0.35f * std::sin(2.f * ph))),  // gaze = cursor, :310-314
+                                                     (unsigned)(H * (0.5f + 0.35f * std::sin(3.f * ph + 0.5f)))};
+            if (f == 0) sample.launchParams.frame.subframe_index = 0;                                       // camera_changed starts true, :319-320
+            sample.setCamera(camera);                                                                       // handleCameraUpdate, :328
+            sample.render();                                                                                // :335
+            const b200pt_counters c = sample.counters();
+            samples += c.samples;  rays += c.radiance_rays + c.shadow_rays;
+            ++windowFrames;
+            const auto now = std::chrono::steady_clock::now();
+            const double dt = std::chrono::duration<double>(now - tWindow).count();
+            if (dt > 0.5) {                                                                                 // displayStats, sutil.cpp:741-772
+                if (flog) fprintf(flog, "%f\n", windowFrames / dt);
+                tWindow = now;  windowFrames = 0;
+            }
+        }
+        const double total = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        printf("%d frames in %.3f s: %.2f fps, %.1f Msamples/s, %.1f Mrays/s\n", frames, total, frames / total, samples / total / 1e6, rays / total / 1e6);
+        if (flog) { fprintf(flog, "%f\n", frames / total);  fclose(flog); }
+        std::vector<uint32_t> px((size_t)W * H);
+        sample.downloadPixels(px.data());
+        unsigned long long sum = 0;
+        for (uint32_t p : px) sum += p & 0xffffffu;
+        printf("pixel checksum %llu\n", sum);
+        if (!out.empty()) {
+            FILE* fo = fopen(out.c_str(), "wb");
+            if (!fo) throw std::runtime_error("cannot write " + out);
+            fprintf(fo, "P6\n%d %d\n255\n", W, H);
+            for (int y = H - 1; y >= 0; --y)                                                                // image row 0 is the bottom row
+                for (int x = 0; x < W; ++x) { const uint32_t p = px[(size_t)y * W + x];  const unsigned char rgb[3] = {(unsigned char)p, (unsigned char)(p >> 8), (unsigned char)(p >> 16)};  fwrite(rgb, 1, 3, fo); }
+            fclose(fo);
+        }
+        delete[] probe.data;  delete[] probe.pdfValuesX;  delete[] probe.cdfValuesX;  delete[] probe.pdfValuesY;  delete[] probe.cdfValuesY;
+    } catch (const std::runtime_error& e) {                                                                // main.cpp:422-425
+        fprintf(stderr, "Caught exception: %s\n", e.what());
+        return 1;
+    }
+    return 0;
+}

@@ -1,0 +1,99 @@
+// class SampleRenderer — the reference's host renderer class (HelloPathtracing_sv4_vmv23/SimplePathtracer.h:45-188,
+// SimplePathtracer.cpp:42-311) re-implemented as a header-only forwarder over the C-ABI of include/b200pt.h.
+// Same member names, argument meaning and error behaviour: every failure throws std::runtime_error (the reference throws
+// sutil::Exception, which derives from it); `launchParams` and `stream` are public and live, and render() re-reads
+// launchParams (camera, frame.c, subframe_index, ...) on every call, exactly as main.cpp expects (main.cpp:310-320,392).
+// No OptiX, no GL: render(CUDAOutputBuffer&) becomes render(uint32_t* deviceFrameBuffer).
+#pragma once
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include "../b200pt.h"
+#include "Camera.h"
+#include "LaunchParams.h"
+#include "Model.h"
+#include "Probe.h"
+
+class SampleRenderer {
+public:
+    // ctor: uploads every mesh/texture and builds the acceleration structure (SimplePathtracer.cpp:42-75).
+    // `model` is borrowed and must outlive the renderer (SimplePathtracer.h:173).  `preset` selects the variant's literals:
+    // "sv4_fov" (the sv4 default, FOV_ON), "sv4_uniform", "sv3_uniform", "orig".
+    explicit SampleRenderer(const Model* model, int device = 0, const char* preset = "sv4_fov") : model(model) {
+        launchParams = LaunchParams{};
+        if (b200pt_config_preset(&config, preset) != 0) fail();
+        ctx = b200pt_create(device);
+        if (!ctx) fail();
+        try {
+            for (const Texture* t : model->textures)
+                if (b200pt_add_texture(ctx, t->pixel, t->resolution.x, t->resolution.y) < 0) fail();
+            for (const TriangleMesh* m : model->meshes) {
+                const bool hasN = m->normal.size() == m->vertex.size() && !m->normal.empty();
+                const bool hasT = m->texcoord.size() == m->vertex.size() && !m->texcoord.empty();
+                if (b200pt_add_mesh(ctx, reinterpret_cast<const float*>(m->vertex.data()), m->vertex.size(),
+                                    hasN ? reinterpret_cast<const float*>(m->normal.data()) : nullptr,
+                                    hasT ? reinterpret_cast<const float*>(m->texcoord.data()) : nullptr,
+                                    reinterpret_cast<const uint32_t*>(m->index.data()), m->index.size(), &m->material,
+                                    m->diffuseTextureID) < 0) fail();
+            }
+            uint64_t handle = 0;
+            if (b200pt_build_accel(ctx, &handle) != 0) fail();
+            launchParams.traversable = handle;
+            void* s = nullptr;
+            b200pt_device_buffers(ctx, nullptr, nullptr, &s);
+            stream = s;
+        } catch (...) { b200pt_destroy(ctx);  ctx = nullptr;  throw; }
+    }
+    ~SampleRenderer() { if (ctx) b200pt_destroy(ctx); }
+    SampleRenderer(const SampleRenderer&) = delete;
+    SampleRenderer& operator=(const SampleRenderer&) = delete;
+
+    // render one frame (SimplePathtracer.cpp:77-217): no-op before the first resize; uniform or 3-pass foveated schedule per
+    // `config`; increments launchParams.frame.subframe_index as the variant does; blocks until the GPU is idle.
+    void render() {
+        if (launchParams.frame.size.x == 0) return;
+        if (b200pt_render(ctx, &launchParams, &config) != 0) fail();
+    }
+    // headless stand-in for render(sutil::CUDAOutputBuffer<uint32_t>&) (:219-229): render into a caller-owned DEVICE buffer
+    // of W*H RGBA8.  As in the reference, frame_buffer keeps pointing at it afterwards.
+    void render(uint32_t* deviceFrameBuffer) {
+        launchParams.frame.frame_buffer = reinterpret_cast<uchar4*>(deviceFrameBuffer);
+        render();
+    }
+    // resize frame buffer to given resolution (:231-277); zero sizes are ignored; does not reset subframe_index.
+    void resize(const int2& newSize) {
+        if (newSize.x == 0 || newSize.y == 0) return;
+        if (b200pt_resize(ctx, newSize.x, newSize.y, &launchParams) != 0) fail();
+    }
+    // download the rendered color buffer (:279-283): W*H RGBA8, R in the low byte, from the internal frame buffer.
+    void downloadPixels(uint32_t h_pixels[]) { if (b200pt_download_pixels(ctx, h_pixels) != 0) fail(); }
+    // set camera to render with (:285-292): aspect is overridden by W/H.
+    void setCamera(const sutil::Camera& camera) {
+        lastSetCamera = camera;
+        lastSetCamera.setAspectRatio(float(launchParams.frame.size.x) / float(launchParams.frame.size.y));
+        lastSetCamera.UVWFrame(launchParams.camera.U, launchParams.camera.V, launchParams.camera.W);
+        launchParams.camera.eye = lastSetCamera.eye();
+    }
+    // (:295-311) requires probe.valid, else throws; the host arrays stay caller-owned.
+    void setProbe(const ProbeData& probe) {
+        if (!probe.valid) throw std::runtime_error("Probe Data is not valid");
+        const float off[3] = {probe.offset.x, probe.offset.y, probe.offset.z};
+        if (b200pt_set_probe(ctx, probe.width, probe.height, reinterpret_cast<const float*>(probe.data), probe.pdfValuesX,
+                             probe.cdfValuesX, probe.pdfValuesY, probe.cdfValuesY, off, &launchParams) != 0) fail();
+    }
+    // extras behind the same C-ABI
+    void downloadAccum(float* h_rgba) { if (b200pt_download_accum(ctx, h_rgba) != 0) fail(); }
+    b200pt_counters counters() { b200pt_counters c{};  if (b200pt_get_counters(ctx, &c) != 0) fail();  return c; }
+    b200pt_bvh_info bvhInfo() { b200pt_bvh_info b{};  if (b200pt_bvh_info_get(ctx, &b) != 0) fail();  return b; }
+
+    bool denoiserOn = true;              // carried for source compatibility; the reference's denoiser is a dead stub
+    LaunchParams launchParams;           // public and live, like the reference (SimplePathtracer.h:111-187)
+    void* stream = nullptr;              // CUstream of the context (public in the reference; main.cpp:284,300)
+    b200pt_config config;                // the variant's compile-time switches as run-time fields
+    b200pt_ctx* ctx = nullptr;
+    sutil::Camera lastSetCamera;
+    const Model* model;
+
+private:
+    [[noreturn]] static void fail() { throw std::runtime_error(b200pt_last_error()); }
+};
