@@ -327,3 +327,52 @@ def test_error_behaviour():
     r.render()
     assert r.downloadPixels().shape == (32, 32)
     r.close()
+
+
+# ------------------------------------------------------------------------------------------------ multi-GPU modes (§8e)
+def test_tile_split_is_bit_identical_to_full_frame(sponza_small):
+    """Two tile-split contexts (as two ranks would run them) assemble to exactly the single-GPU frame."""
+    from optixpathtracer_b200 import multi
+    probe = analytic_sky(64, 32)
+    size, cam = (96, 100), preset_camera("sponza")
+    full = make_renderer(sponza_small, probe, size, cam, preset("sv3_uniform", uniform_spl=2))
+    full.render()
+    want_px, want_acc = full.downloadPixels().copy(), full.downloadAccum().copy()
+    full.close()
+    got_px, got_acc = np.zeros_like(want_px), np.zeros_like(want_acc)
+    for rank in range(2):
+        r = make_renderer(sponza_small, probe, size, cam, preset("sv3_uniform", uniform_spl=2, tile_rank=rank, tile_count=2))
+        r.clearAccum()
+        r.render()
+        rows = multi.band_rows(rank, 2, size[1])
+        got_px[rows], got_acc[rows] = r.downloadPixels()[rows], r.downloadAccum()[rows]
+        r.close()
+    assert np.array_equal(got_px, want_px) and np.array_equal(got_acc.view(np.uint32), want_acc.view(np.uint32))
+
+
+def test_sample_split_sum_mode_matches_running_mean(sponza_small):
+    """ACCUM_SUM over sub-frames {0,2} + {1,3} on two contexts, summed and resolved == the 4-frame running mean (fp32 order only)."""
+    from optixpathtracer_b200.structs import ACCUM_SUM
+    probe = analytic_sky(64, 32)
+    size, cam = (96, 54), preset_camera("sponza")
+    ref = make_renderer(sponza_small, probe, size, cam, preset("sv3_uniform", uniform_spl=2))
+    for _ in range(4):
+        ref.render()
+    want = ref.downloadAccum()
+    ref.close()
+    total = np.zeros_like(want)
+    for rank in range(2):
+        r = make_renderer(sponza_small, probe, size, cam, preset("sv3_uniform", uniform_spl=2, accum_mode=ACCUM_SUM))
+        r.clearAccum()
+        for f in (rank, rank + 2):
+            r.launchParams.frame.subframe_index = f
+            r.render()
+        total += r.downloadAccum()
+        r.close()
+    assert np.array_equal(total[..., 3], np.full(total.shape[:2], 4.0, np.float32))
+    res = make_renderer(sponza_small, probe, size, cam, preset("sv3_uniform", uniform_spl=2, accum_mode=ACCUM_SUM))
+    res.uploadAccum(total)
+    res.resolveSum(4)
+    got = res.downloadAccum()
+    res.close()
+    assert rel_mismatch(got[..., :3], want[..., :3], 2e-5) == 0.0
