@@ -18,10 +18,15 @@
 
 #define TRACE_BLOCK 128
 #define TRACE_WARPS (TRACE_BLOCK / 32)
+#ifndef TRACE_BLOCKS_PER_SM
 #define TRACE_BLOCKS_PER_SM 8
+#endif
 #define FULL 0xffffffffu
 #define EMPTY 0x7fffffff          // "nothing left to visit"; also the root link of an empty scene
 #define NO_LEAF 0                 // leaf codes are < 0
+#ifndef NODE_ROUNDS
+#define NODE_ROUNDS 8
+#endif
 
 static int g_refillThreshold = -1, g_leafThreshold = -1;   // lanes that must be idle before a warp refills; tuned on B200
 
@@ -250,32 +255,38 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
             if (idle == FULL) break;                               // queues drained and every lane finished
         }
 
-        // ---------------------------------------------------------------- one inner-node step per lane that can take one
+        // ---------------------------------------------------------------- inner-node steps: one per lane per round, up to
+        // NODE_ROUNDS rounds before the staging logic above runs again; a round ends early once enough lanes are blocked on a leaf
         bool occluded = false;
-        if (active && (unsigned)cur < (unsigned)EMPTY) {
-            const float4* p_ = S.nodes + 2 * (size_t)cur;
-            const Node8 L_ = ldgNode(p_), R_ = ldgNode(p_ + 2);
-            if (COUNT) myNodes += 2;
-            float tl_, tr_;
-            const bool hl_ = boxTest(L_.a, L_.b, o, inv, tmin, best.t, tl_);
-            const bool hr_ = boxTest(R_.a, R_.b, o, inv, tmin, best.t, tr_);
-            const int cl_ = __float_as_int(L_.a.w), cr_ = __float_as_int(R_.a.w);
-            if (hl_ && hr_) {
-                const bool sw_ = tr_ < tl_;
-                stack[sp++] = sw_ ? cl_ : cr_;
-                cur = sw_ ? cr_ : cl_;
-            } else if (hl_) cur = cl_;
-            else if (hr_) cur = cr_;
-            else cur = sp ? stack[--sp] : EMPTY;
-            if (cur < 0 && leaf == NO_LEAF) {                      // first leaf: postpone it and keep walking
-                leaf = cur;
-                cur = sp ? stack[--sp] : EMPTY;
+        unsigned nodeMask, blockedMask;
+#pragma unroll 1
+        for (int round = 0; ; ++round) {
+            if (active && (unsigned)cur < (unsigned)EMPTY) {
+                const float4* p_ = S.nodes + 2 * (size_t)cur;
+                const Node8 L_ = ldgNode(p_), R_ = ldgNode(p_ + 2);
+                if (COUNT) myNodes += 2;
+                float tl_, tr_;
+                const bool hl_ = boxTest(L_.a, L_.b, o, inv, tmin, best.t, tl_);
+                const bool hr_ = boxTest(R_.a, R_.b, o, inv, tmin, best.t, tr_);
+                const int cl_ = __float_as_int(L_.a.w), cr_ = __float_as_int(R_.a.w);
+                if (hl_ && hr_) {
+                    const bool sw_ = tr_ < tl_;
+                    stack[sp++] = sw_ ? cl_ : cr_;
+                    cur = sw_ ? cr_ : cl_;
+                } else if (hl_) cur = cl_;
+                else if (hr_) cur = cr_;
+                else cur = sp ? stack[--sp] : EMPTY;
+                if (cur < 0 && leaf == NO_LEAF) {                  // first leaf: postpone it and keep walking
+                    leaf = cur;
+                    cur = sp ? stack[--sp] : EMPTY;
+                }
             }
+            const bool canNode = active && (unsigned)cur < (unsigned)EMPTY;
+            nodeMask = __ballot_sync(FULL, canNode);
+            blockedMask = __ballot_sync(FULL, active && !canNode);
+            if (nodeMask == 0u || (int)__popc(blockedMask) >= leafThreshold || round + 1 >= NODE_ROUNDS) break;
         }
         // ---------------------------------------------------------------- leaves, once enough lanes are blocked on one
-        const bool canNode = active && (unsigned)cur < (unsigned)EMPTY;
-        const unsigned nodeMask = __ballot_sync(FULL, canNode);
-        const unsigned blockedMask = __ballot_sync(FULL, active && !canNode);
         if (nodeMask == 0u || (int)__popc(blockedMask) >= leafThreshold) {
             if (active && leaf == NO_LEAF && cur < 0) { leaf = cur;  cur = sp ? stack[--sp] : EMPTY; }   // root leaf
             if (active && leaf != NO_LEAF) {
