@@ -193,6 +193,8 @@ def run_b200(a):
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     if world > 1:
+        if "B200PT_KEEP_NCCL_DEBUG" not in os.environ:
+            os.environ["NCCL_DEBUG"] = "WARN"                 # keep stdout to the one JSON line (NCCL prints its version at VERSION/INFO)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     model, cam, probe, cfg = build_workload(a)
@@ -363,7 +365,7 @@ def run_b200(a):
                          "nodes_per_shadow_ray": nodes_s / max(1, srays), "tris_per_shadow_ray": tris_s / max(1, srays),
                          "bytes_per_ray": (32 * nodes + 48 * tris) / max(1, crays) + 48,
                          "note": "algorithmic bytes = 32 B x node records + 48 B x triangle records fetched (counted by the kernel in a counters replay of the same frames) "
-                                 "+ 32 B ray in + 16 B hit (4 B flag for shadow rays) out; the 21 MB BVH is L1/L2-resident, so these bytes are served by the caches, not HBM"},
+                                 f"+ 32 B ray in + 16 B hit (4 B flag for shadow rays) out; BVH = {(info.node_bytes + info.tri_bytes) / 1e6:.0f} MB (L2 is 126 MB): when it is cache-resident these bytes are served by L1/L2, not HBM"},
             "stage_ms_per_step": {k: v / a.steps for k, v in stage.items()},
             "reduce_ms": reduce_ms, "wall_seconds_timed_region": wall, "clocks": clocks,
         }

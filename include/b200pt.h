@@ -51,7 +51,8 @@ typedef struct b200pt_config {
     int   write_aovs;         /* 1 = also write normal/color/albedo buffers (orig/deviceProgram.cu:472-474) */
     int   increment_subframe; /* 1 = render() does subframe_index++ (sv3/sv4); 0 = caller does (orig)    */
     int   accum_mode;         /* B200PT_ACCUM_*                                                          */
-    int   russian_roulette;   /* 0 = off (reference behaviour). Opt-in estimator extension; breaks RNG parity */
+    int   russian_roulette;   /* 0 = off (reference behaviour).  1 = opt-in extension: from the third segment on a path survives
+                                 with probability min(1, max(throughput)); one extra Randf per decision (RNG stream differs) */
     int   tile_rank, tile_count; /* multi-GPU tile split: this context renders launch rows whose 32-row band
                                     index % tile_count == tile_rank; tile_count <= 1 = whole frame        */
     int   profile;            /* bit 0: per-stage CUDA-event timings; bit 1: traversal counters (slower kernels) */

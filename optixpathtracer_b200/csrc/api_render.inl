@@ -129,7 +129,7 @@ static FrameParams frameOf(const LaunchParams& P, const b200pt_config& cfg, cons
     // the coarse CDF table belongs to the probe uploaded by b200pt_set_probe; a caller-substituted probe falls back
     F.cdfXCoarse = (c && c->probeCoarse.p && P.probe.cdfValuesX == c->probeCdfX.p && P.probe.width == c->probeW && P.probe.height == c->probeH) ? c->probeCoarse.p : nullptr;
     F.tmin = cfg.tmin;  F.tmax = cfg.tmax;  F.maxDepth = cfg.max_depth;  F.shadowMode = cfg.shadow_mode;  F.display = cfg.display;
-    F.accumMode = cfg.accum_mode;  F.writeAovs = cfg.write_aovs;  F.exposure = cfg.exposure;
+    F.accumMode = cfg.accum_mode;  F.writeAovs = cfg.write_aovs;  F.russianRoulette = cfg.russian_roulette;  F.exposure = cfg.exposure;
     F.tileRank = cfg.tile_rank;  F.tileCount = cfg.tile_count;
     F.accum = P.frame.accum_buffer;  F.frame = (uint32_t*)P.frame.frame_buffer;  F.normal = P.frame.normal_buffer;
     F.albedo = P.frame.albedo_buffer;  F.color = P.frame.color_buffer;
@@ -147,7 +147,6 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
     if (!params->probe.data || !params->probe.cdfValuesX) throw std::runtime_error("b200pt_render: no probe set (call b200pt_set_probe)");
     if (!params->frame.accum_buffer || !params->frame.frame_buffer) throw std::runtime_error("b200pt_render: frame buffers not allocated (call b200pt_resize)");
     if (cfg.max_depth < 0 || cfg.max_depth > QC_MAX_LAUNCHES - 8) throw std::runtime_error("b200pt_render: max_depth out of range");
-    if (cfg.russian_roulette) throw std::runtime_error("b200pt_render: russian_roulette is not implemented yet");
     c->countersPending = false;                                                  // totals of an un-synchronised previous frame are dropped
 
     std::vector<PassDesc> passes;

@@ -71,7 +71,7 @@ struct FrameParams {               // shared by every pass of a frame
     Probe probe;                   // device pointers
     const float* cdfXCoarse;       // every 32nd entry of each cdfValuesX row (nullptr: plain binary search)
     float tmin, tmax;
-    int maxDepth, shadowMode, display, accumMode, writeAovs;
+    int maxDepth, shadowMode, display, accumMode, writeAovs, russianRoulette;
     float exposure;
     int tileRank, tileCount;
     float4* accum;  uint32_t* frame;  float4* normal;  float4* albedo;  float4* color;

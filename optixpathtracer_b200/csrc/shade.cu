@@ -203,10 +203,17 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                                 if (dot3(bsdfDir, N) <= 0.0f) rayEta = outEta;    // :688-692
                                 T = T * (f * fabsf(dot3(N, bsdfDir)) / pdf);      // :695
                                 flags |= PF_SECONDARY;
+                                bool rrKill = false;
+                                if (F.russianRoulette && depth + 1 >= 2) {        // opt-in extension, same rule as oracle/render_core.h
+                                    const float p = fminf(1.0f, fmaxf(T.x, fmaxf(T.y, T.z)));
+                                    const float r = rng.randf();
+                                    if (!(r < p)) rrKill = true;
+                                    else T = T / p;
+                                }
                                 pool.thr[slot] = make_float4(T.x, T.y, T.z, rayEta);
                                 pool.rng[slot] = make_uint2(rng.s1, rng.s2);
                                 const int nd = depth + 1;
-                                if (nd >= F.maxDepth && (flags & PF_ALPHA_ONE)) flags |= PF_DONE;   // next segment could only be dropped
+                                if (rrKill || (nd >= F.maxDepth && (flags & PF_ALPHA_ONE))) flags |= PF_DONE;   // roulette, or the next segment could only be dropped
                                 else { wantRay = true;  ro = make_float4(Pp.x, Pp.y, Pp.z, o4.w);  rd = make_float4(bsdfDir.x, bsdfDir.y, bsdfDir.z, 0.f); }
                                 depth = nd;
                             }

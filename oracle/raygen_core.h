@@ -71,6 +71,7 @@ static inline bool oracleRaygen(const OTraceCtx& C, const LaunchParams& params, 
             if ((prd.stateFlags & RAY_STATE_FLAGS_DONE) || prd.depth >= cfg.max_depth) break;   // :495
             if (prd.depth == 0) directLight += prd.radiance;
             else indirectLight += prd.radiance;
+            if (prd.stateFlags & RAY_STATE_FLAGS_RR_KILLED) break;                              // opt-in Russian roulette
             ++prd.depth;
             ray_origin = prd.origin;
             ray_direction = prd.direction;

@@ -13,6 +13,7 @@
 
 static const int RAY_STATE_FLAGS_DONE = 1 << 0;
 static const int RAY_STATE_FLAGS_SECONDARY_RAY = 1 << 1;
+static const int RAY_STATE_FLAGS_RR_KILLED = 1 << 8;     // opt-in Russian roulette (not in the reference; TODO at sv4/deviceProgram.cu:498-500)
 
 struct RadiancePRD {                    // sv4/deviceProgram.cu:59-87
     float3 radiance, alpha, origin, direction, normal, albedo;
@@ -161,4 +162,13 @@ static inline void oracleClosestHitProgram(const OTraceCtx& C, const OHit& hit, 
     prd->direction = bsdfDir;
     prd->origin = P;
     prd->stateFlags |= RAY_STATE_FLAGS_SECONDARY_RAY;
+    // Opt-in extension (cfg.russian_roulette): from the third segment on, continue with probability p = min(1, max(T));
+    // one extra Randf per decision, so the RNG stream differs from the reference's from here on.  This segment's radiance is kept.
+    if (C.cfg->russian_roulette && prd->depth + 1 >= 2) {
+        const float3 T = prd->pathThroughput;
+        const float p = fminf(1.0f, fmaxf(T.x, fmaxf(T.y, T.z)));
+        const float r = prd->rand.Randf();
+        if (!(r < p)) prd->stateFlags |= RAY_STATE_FLAGS_RR_KILLED;
+        else prd->pathThroughput = prd->pathThroughput / p;
+    }
 }

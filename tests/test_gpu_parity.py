@@ -376,3 +376,23 @@ def test_sample_split_sum_mode_matches_running_mean(sponza_small):
     got = res.downloadAccum()
     res.close()
     assert rel_mismatch(got[..., :3], want[..., :3], 2e-5) == 0.0
+
+
+def test_russian_roulette_opt_in_matches_oracle_rule(port, sponza_small):
+    """cfg.russian_roulette (north_star extension, off by default): the CUDA path applies the same rule with the same
+    extra Randf draw as the oracle, so the two still agree path by path; and it really terminates paths early."""
+    probe = analytic_sky(256, 128)
+    cam = preset_camera("sponza")
+    out = {}
+    for rr in (0, 1):
+        cfg = preset("orig", uniform_spl=2, russian_roulette=rr)
+        r = make_renderer(sponza_small, probe, (160, 90), cam, cfg)
+        r.launchParams.samples_per_launch = 2
+        r.render()
+        got, cnt = r.downloadAccum(), r.counters()
+        r.close()
+        p = host_params(160, 90, cam, samples_per_launch=2)
+        want, _, ocnt, _ = port.scene(sponza_small, probe).render(p, cfg, np.zeros((90, 160, 4), np.float32))
+        assert rel_mismatch(got[..., :3], want[..., :3], 2e-4) < 1e-2
+        out[rr] = (cnt.radiance_rays, ocnt["radiance_rays"])
+    assert out[1][0] < 0.9 * out[0][0] and out[1][1] < 0.9 * out[0][1]

@@ -74,3 +74,18 @@ def test_oracle_schedule_mutates_params_like_the_reference(port):
     p.frame.subframe_index = 7
     sc.render(p, cfg_u)
     assert p.frame.subframe_index == 1 and p.samples_per_launch == 8          # FOV_OFF forces subframe 0, then ++
+
+
+def test_russian_roulette_is_unbiased_in_the_oracle(port):
+    """The opt-in roulette (oracle/render_core.h, mirrored in csrc/shade.cu) must not change the expected image."""
+    from optixpathtracer_b200 import host_params, loadColor, preset, preset_camera, scenes
+    import numpy as np
+    model = scenes.cornell("diffuse")
+    sc = port.scene(model, loadColor((1.0, 1.0, 1.0), 16, 8), brute_force=True)
+    means = []
+    for rr in (0, 1):
+        cfg = preset("orig", uniform_spl=256, russian_roulette=rr)
+        acc, _, cnt, _ = sc.render(host_params(24, 24, preset_camera("cornell"), samples_per_launch=256), cfg)
+        means.append((acc[..., :3].mean(), cnt["radiance_rays"]))
+    assert means[1][1] < means[0][1]
+    assert abs(means[1][0] - means[0][0]) < 0.02 * means[0][0]
