@@ -400,6 +400,7 @@ void bvhBuild(const float3* d_vertices, const uint3* d_indices, const unsigned* 
     const unsigned nFlag = nTris + 1, nTiles = (nFlag + SCAN_TILE - 1) / SCAN_TILE;
     unsigned* flagNext = dalloc<unsigned>(nFlag);  unsigned* rankA = dalloc<unsigned>(nFlag);  unsigned* rankB = dalloc<unsigned>(nFlag);
     unsigned* tileSum = dalloc<unsigned>(nTiles);  unsigned* tileOff = dalloc<unsigned>(nTiles);
+    static const float ciLeaf = getenv("B200PT_SAH_CI") ? (float)atof(getenv("B200PT_SAH_CI")) : SAH_CI;   // tuning knob
     const unsigned* rank = nullptr;                          // level 1: every triangle is an item
     float4* itemLo = nullptr;  float4* itemHi = nullptr;  int* itemLink = nullptr;  int* itemDepth = nullptr;
     unsigned levels = 0, depthHost = 0;
@@ -418,7 +419,7 @@ void bvhBuild(const float3* d_vertices, const uint3* d_indices, const unsigned* 
         SahJob* jobs = dalloc<SahJob>(nJobs);
         selectJobsKernel<<<GV, B, 0, s>>>(n, parent, range, rank, flagNext, rankNext, jobs);
         float4* nextLo = dalloc<float4>(nJobs);  float4* nextHi = dalloc<float4>(nJobs);  int* nextLink = dalloc<int>(nJobs);  int* nextDepth = dalloc<int>(nJobs);
-        SahLevelIn in{itemLo, itemHi, itemLink, itemDepth, triLo, triHi, vals, levels == 0 ? 1 : 0};
+        SahLevelIn in{itemLo, itemHi, itemLink, itemDepth, triLo, triHi, vals, levels == 0 ? 1 : 0, ciLeaf};
         SahLevelOut lo{nextLo, nextHi, nextLink, nextDepth, out.finalGid, (float4*)out.nodes, scalars + 0, scalars + 2};
         const bool last = nJobs == 1;
         sahJobKernel<<<nJobs, JOB_THREADS, sizeof(SahShared), s>>>(jobs, in, lo, last ? 1 : 0);

@@ -31,6 +31,7 @@ struct SahLevelIn {                     // items of this level
     const float4* triHi;
     const unsigned* sortedGid;
     int isTri;
+    float ciLeaf;                       // inner-node cost used in the leaf-vs-split decision (tuned to the traversal kernel)
 };
 struct SahLevelOut {
     float4* nextLo;  float4* nextHi;  int* nextLink;  int* nextDepth;   // indexed by job
@@ -154,7 +155,7 @@ __device__ void sahProcessTask(SahShared& S, const SahTask t, unsigned taskIndex
     // ---- leaf or split
     if (in.isTri && c <= B200PT_MAX_LEAF) {
         const float leafCost = SAH_CT * area * (float)c;
-        const float splitCost = bestCand >= 0 ? SAH_CI * area + SAH_CT * bestCost : FLT_MAX;
+        const float splitCost = bestCand >= 0 ? in.ciLeaf * area + SAH_CT * bestCost : FLT_MAX;
         if (leafCost <= splitCost) { makeLeaf();  return; }
     }
     unsigned nl;

@@ -40,6 +40,16 @@ __device__ __forceinline__ Node8 ldgNode(const float4* p) {
     return n;
 }
 
+__device__ __forceinline__ void prefetchL1(const void* p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
+#ifndef TRACE_PREFETCH
+#define TRACE_PREFETCH 0          // bit 0: child pair of a pushed node, bit 1: triangles of a postponed leaf.  Measured on B200: no gain (bit 0: -3 %), so off
+#endif
+// warms L1 for what a link refers to: the child pair of an inner node, or the first triangle lines of a leaf
+__device__ __forceinline__ void prefetchLink(const SceneDev& S, int link) {
+    if (link >= 0) prefetchL1(S.nodes + 2 * (size_t)link);
+    else { const unsigned c = (unsigned)(-(link + 1));  prefetchL1(S.tris + 3 * (size_t)(c >> 3)); }
+}
+
 struct TriHit { float t, u, v; };
 
 // Moeller-Trumbore, unfused.  det > 0 <=> triangle front-faces the ray.
@@ -65,6 +75,28 @@ __device__ __forceinline__ bool triTest(const float4 a, const float4 b, const fl
     if (!(t > tmin && t < tmax)) return false;
     h.t = t;  h.u = __fdiv_rn(U, det);  h.v = __fdiv_rn(V, det);
     return true;
+}
+
+// The same operation sequence as triTest up to the divisions, without early outs: the traversal kernel runs it for every
+// lane of a leaf phase in lock step and divides only for the lanes that pass.  `ok` is triTest's accept condition before the
+// t-range test (comparisons written in the same negated form, so NaNs fall through identically).
+__device__ __forceinline__ bool triEval(const float4 a, const float4 b, const float4 c, const float3 o, const float3 d, bool cullBack,
+                                        float& det, float& U, float& V, float& Tn) {
+    const float v0x = a.x, v0y = a.y, v0z = a.z, e1x = a.w, e1y = b.x, e1z = b.y, e2x = b.z, e2y = b.w, e2z = c.x;
+    const float px = __fsub_rn(__fmul_rn(d.y, e2z), __fmul_rn(d.z, e2y));
+    const float py = __fsub_rn(__fmul_rn(d.z, e2x), __fmul_rn(d.x, e2z));
+    const float pz = __fsub_rn(__fmul_rn(d.x, e2y), __fmul_rn(d.y, e2x));
+    det = __fadd_rn(__fadd_rn(__fmul_rn(e1x, px), __fmul_rn(e1y, py)), __fmul_rn(e1z, pz));
+    const float sx = __fsub_rn(o.x, v0x), sy = __fsub_rn(o.y, v0y), sz = __fsub_rn(o.z, v0z);
+    U = __fadd_rn(__fadd_rn(__fmul_rn(sx, px), __fmul_rn(sy, py)), __fmul_rn(sz, pz));
+    const float qx = __fsub_rn(__fmul_rn(sy, e1z), __fmul_rn(sz, e1y));
+    const float qy = __fsub_rn(__fmul_rn(sz, e1x), __fmul_rn(sx, e1z));
+    const float qz = __fsub_rn(__fmul_rn(sx, e1y), __fmul_rn(sy, e1x));
+    V = __fadd_rn(__fadd_rn(__fmul_rn(d.x, qx), __fmul_rn(d.y, qy)), __fmul_rn(d.z, qz));
+    Tn = __fadd_rn(__fadd_rn(__fmul_rn(e2x, qx), __fmul_rn(e2y, qy)), __fmul_rn(e2z, qz));
+    const float UV = __fadd_rn(U, V);
+    const bool inPos = !(U < 0.0f || V < 0.0f || UV > det), inNeg = !(U > 0.0f || V > 0.0f || UV < det);
+    return det != 0.0f && !(cullBack && det < 0.0f) && (det > 0.0f ? inPos : inNeg);
 }
 
 // slab test against one 32-byte node (boxes are padded at build time; far side widened by 2 ulp)
@@ -186,6 +218,7 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
     float3 o = make_float3(0, 0, 0), d = o, inv = o;
     float wO = 0.f, wD = 0.f;
     Best best;  best.t = tmax;  best.slot = -1;  best.gid = 0xffffffffu;  best.u = best.v = 0.f;
+    float bestDet = 1.f;
     int cur = EMPTY, leaf = NO_LEAF, sp = 0;
     int stack[B200PT_STACK];
 
@@ -271,13 +304,16 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
                 const int cl_ = __float_as_int(L_.a.w), cr_ = __float_as_int(R_.a.w);
                 if (hl_ && hr_) {
                     const bool sw_ = tr_ < tl_;
-                    stack[sp++] = sw_ ? cl_ : cr_;
+                    const int far_ = sw_ ? cl_ : cr_;
+                    stack[sp++] = far_;
+                    if (TRACE_PREFETCH & 1) prefetchLink(S, far_);   // it will be popped after the near subtree: have its data in L1 by then
                     cur = sw_ ? cr_ : cl_;
                 } else if (hl_) cur = cl_;
                 else if (hr_) cur = cr_;
                 else cur = sp ? stack[--sp] : EMPTY;
                 if (cur < 0 && leaf == NO_LEAF) {                  // first leaf: postpone it and keep walking
                     leaf = cur;
+                    if (TRACE_PREFETCH & 2) prefetchLink(S, leaf);
                     cur = sp ? stack[--sp] : EMPTY;
                 }
             }
@@ -297,12 +333,15 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
                     const float4* tp = S.tris + 3 * (size_t)(first + k);
                     const float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
                     if (COUNT) myTris += 1;
-                    TriHit h;
-                    if (triTest(a, b, c, o, d, tmin, tmax, cull, h)) {
-                        if (isAny) { occluded = true;  break; }
-                        const unsigned gid = (unsigned)__float_as_int(c.y);
-                        if (h.t < best.t || (h.t == best.t && gid < best.gid)) {
-                            best.t = h.t;  best.u = h.u;  best.v = h.v;  best.slot = (int)(first + k);  best.gid = gid;
+                    float det, U, V, Tn;
+                    if (triEval(a, b, c, o, d, cull, det, U, V, Tn)) {
+                        const float t = __fdiv_rn(Tn, det);       // the only division in the loop; u, v are divided at retirement
+                        if (t > tmin && t < tmax) {
+                            if (isAny) { occluded = true;  break; }
+                            const unsigned gid = (unsigned)__float_as_int(c.y);
+                            if (t < best.t || (t == best.t && gid < best.gid)) {
+                                best.t = t;  best.u = U;  best.v = V;  bestDet = det;  best.slot = (int)(first + k);  best.gid = gid;
+                            }
                         }
                     }
                 }
@@ -314,7 +353,9 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
         // ---------------------------------------------------------------- retire finished rays
         if (active && cur == EMPTY && leaf == NO_LEAF) {
             if (!isAny) {
-                hit[rayIdx] = make_float4(best.t, best.u, best.v, __int_as_float(best.slot));
+                // best.u/best.v hold the undivided U, V of the winning triangle: same quotients as dividing at hit time
+                const bool got = best.slot >= 0;
+                hit[rayIdx] = make_float4(best.t, got ? __fdiv_rn(best.u, bestDet) : 0.f, got ? __fdiv_rn(best.v, bestDet) : 0.f, __int_as_float(best.slot));
             } else {
                 // prd.radiance += pathThroughput * lightSample (sv4/deviceProgram.cu:659) resolved here.  Target 2 = alpha
                 // when OCCLUDED (shadow catcher, :663-664).  Single writer per slot per launch => deterministic.
