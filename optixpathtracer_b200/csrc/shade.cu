@@ -56,15 +56,20 @@ DEV unsigned lcgSkip(unsigned seed, int steps) {
 
 __global__ void __launch_bounds__(SHADE_BLOCK)
 raygenKernel(FrameParams F, PassParams P, int k0, int k1, PathPool pool, Queues Q) {
+    // Threads walk the launch grid in 8x4-pixel tiles (one warp = one tile when kc = 1), not in scanlines: the rays a warp
+    // appends to the queue together — and the bounce rays that inherit their order — then start close to each other.
     const unsigned kc = (unsigned)(k1 - k0);
-    const unsigned total = (unsigned)P.launchW * (unsigned)P.launchH * kc;
+    const unsigned tilesX = ((unsigned)P.launchW + 7u) >> 3, tilesY = ((unsigned)P.launchH + 3u) >> 2;
+    const unsigned total = tilesX * tilesY * 32u * kc;
     const unsigned stride = gridDim.x * blockDim.x;
     for (unsigned base = blockIdx.x * blockDim.x; base < total; base += stride) {     // warp-uniform trip count
         const unsigned t = base + threadIdx.x;
         bool want = false;
         float4 o4 = make_float4(0, 0, 0, 0), d4 = o4;
-        if (t < total) {
-            const unsigned li = t / kc, k = (unsigned)k0 + t % kc;
+        const unsigned cell = t / kc, tile = cell >> 5, within = cell & 31u;
+        const unsigned lx = (tile % tilesX) * 8u + (within & 7u), ly = (tile / tilesX) * 4u + (within >> 3);
+        if (t < total && lx < (unsigned)P.launchW && ly < (unsigned)P.launchH) {
+            const unsigned li = ly * (unsigned)P.launchW + lx, k = (unsigned)k0 + t % kc;
             const LaunchIdx L = decodeLaunch(F, P, li);
             if (L.live) {
                 const unsigned slot = P.slotBase + li * kc + (k - (unsigned)k0);       // chunk-local slot
