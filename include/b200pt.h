@@ -78,7 +78,7 @@ int b200pt_add_mesh(b200pt_ctx* ctx,
                     const struct Material* material,
                     int diffuse_texture_id);            /* -1 = none; returns meshID >= 0, or -1         */
 /* LBVH build: Morton codes -> radix sort -> Karras hierarchy -> refit -> SAH leaf collapse + treelet
- * refinement -> 32-byte nodes + 48-byte Woop triangles.  Replaces optixAccelBuild/optixAccelCompact
+ * refinement -> 32-byte two-child nodes (16-bit quantised boxes) + 48-byte triangle records.  Replaces optixAccelBuild/optixAccelCompact
  * (sv4/SimplePathtracer.cpp:670-737).  *handle_out receives the value for LaunchParams.traversable. */
 int b200pt_build_accel(b200pt_ctx* ctx, uint64_t* handle_out);
 
@@ -133,9 +133,14 @@ typedef struct b200pt_bvh_info {
     float    sah_cost_lbvh;      /* before refinement */
     float    build_ms;
     uint64_t node_bytes, tri_bytes;
+    int32_t  root_link;          /* >= 0: record index of the root's node; < 0: leaf code; 0x7fffffff: empty scene */
+    uint32_t refine_levels;      /* treelet-refinement levels run by the build */
+    double   grid_lo[3], grid_scale[3];   /* node boxes are quantised: g = 2 + (x - grid_lo) * grid_scale, 16 bits per bound */
 } b200pt_bvh_info;
 int b200pt_bvh_info_get(b200pt_ctx* ctx, b200pt_bvh_info* out);
-/* Copies of the flattened BVH for structural validation in tests (32-byte nodes). */
+/* Copies of the flattened BVH for structural validation in tests: n_nodes 32-byte records, one per inner node, each
+ * {6 x uint32: 12 quantised 16-bit bounds of child 0 then child 1 (lo.x|hi.x<<16, lo.y|hi.y<<16, lo.z|hi.z<<16), int32 link0, link1};
+ * tri_global_id = triangle ids in leaf order. */
 int b200pt_download_bvh(b200pt_ctx* ctx, void* nodes32, size_t max_nodes, uint32_t* tri_global_id, size_t max_tris);
 
 typedef struct b200pt_counters {      /* last render()                                                  */

@@ -165,7 +165,9 @@ int b200pt_build_accel(b200pt_ctx* c, uint64_t* handle_out) {
 
 static SceneDev sceneOf(b200pt_ctx* c) {
     SceneDev S;
-    S.nodes = (const float4*)c->bvh.nodes;  S.tris = c->bvh.tris;  S.meshes = c->dMeshes.p;  S.indices = c->dIndices.p;
+    S.nodes = (const uint4*)c->bvh.nodes;  S.rootLink = c->bvh.rootLink;
+    for (int a = 0; a < 3; ++a) { S.gridLo[a] = c->bvh.gridLo[a];  S.gridScale[a] = c->bvh.gridScale[a]; }
+    S.tris = c->bvh.tris;  S.meshes = c->dMeshes.p;  S.indices = c->dIndices.p;
     S.texcoords = c->dTexcoords.p;  S.texels = c->dTexels.p;  S.nTris = c->bvh.nTris;  S.nNodes = c->bvh.nNodes;
     return S;
 }

@@ -5,8 +5,8 @@
 //   3. radix sort        LSD, 8-bit digits, 64-bit key + 32-bit id, stable (== std::stable_sort order)
 //   4. karrasKernel      Karras 2012 binary radix tree over the sorted codes (index tie-break for duplicates)
 //   5. refitKernel       bottom-up AABBs + SAH cost of the plain LBVH (atomic arrival flags); reported, not traversed
-//   6. bvh_sah.cuh       binned-SAH treelet refinement, level by level, over the LBVH's ranges -> 64-byte sibling
-//                        pairs of 32-byte nodes (the tree the traversal kernels read)
+//   6. bvh_sah.cuh       binned-SAH treelet refinement, level by level, over the LBVH's ranges -> one 32-byte record per
+//                        inner node holding both child boxes, quantised to a 16-bit grid (the tree the traversal kernels read)
 //   7. emitTrisKernel    48-byte triangle records in final BVH order
 // Integer stages (2,3) are the ones north_star asks to be bit-exact against a host reference.
 #include "common.cuh"
@@ -301,16 +301,24 @@ __global__ void selectJobsKernel(int n, const int* __restrict__ parent, const in
     else jobs[rankNext[rg.x]] = SahJob{rank ? rank[rg.x] : (unsigned)rg.x, cnt, (unsigned)rg.x};
 }
 
-// SAH cost of the final tree: sum over records of Ci*A (inner) or Ct*count*A (leaf), over the root area.
-__global__ void sahCostKernel(const float4* __restrict__ nodes, unsigned nRecords, double* cost) {
+// SAH cost of the final tree over its (dequantised, i.e. padded) child boxes: sum of Ci*A per inner child and
+// Ct*count*A per leaf child; the host adds the root's own term and divides by the root area.
+__global__ void sahCostKernel(const BvhNode* __restrict__ nodes, unsigned nRecords, double invScaleX, double invScaleY, double invScaleZ,
+                              double* cost) {
     const unsigned r = blockIdx.x * blockDim.x + threadIdx.x;
     float c = 0.f;
-    if (r < nRecords && r != 1) {
-        const float4 lo = nodes[2 * (size_t)r], hi = nodes[2 * (size_t)r + 1];
-        const int link = __float_as_int(lo.w);
-        const float a = boxArea(lo, hi);
-        if (link >= 0) c = SAH_CI * a;
-        else { unsigned first, count;  leafDecode(link, first, count);  c = SAH_CT * a * (float)count; }
+    if (r < nRecords) {
+        const BvhNode n = nodes[r];
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const unsigned q0 = n.q[3 * k], q1 = n.q[3 * k + 1], q2 = n.q[3 * k + 2];
+            const float dx = (float)((double)((q0 >> 16) - (q0 & 0xffffu)) * invScaleX);
+            const float dy = (float)((double)((q1 >> 16) - (q1 & 0xffffu)) * invScaleY);
+            const float dz = (float)((double)((q2 >> 16) - (q2 & 0xffffu)) * invScaleZ);
+            const float a = 2.f * (dx * dy + dy * dz + dz * dx);
+            if (n.link[k] >= 0) c += SAH_CI * a;
+            else { unsigned first, count;  leafDecode(n.link[k], first, count);  c += SAH_CT * a * (float)count; }
+        }
     }
     for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
     if ((threadIdx.x & 31) == 0 && c != 0.f) atomicAdd(cost, (double)c);
@@ -351,11 +359,10 @@ void bvhBuild(const float3* d_vertices, const uint3* d_indices, const unsigned* 
               unsigned nTris, cudaStream_t s, BvhBuildResult& out) {
     out = BvhBuildResult();
     out.nTris = nTris;
-    if (nTris == 0) {                                        // empty scene: a root whose link is the EMPTY sentinel
-        out.nodes = dalloc<BvhNode>(2);
-        BvhNode h[2];  memset(h, 0, sizeof(h));  h[0].link = 0x7fffffff;
-        CUDA_OK(cudaMemcpy(out.nodes, h, sizeof(h), cudaMemcpyHostToDevice));
-        out.tris = dalloc<float4>(3);  out.nNodes = 2;
+    if (nTris == 0) {                                        // empty scene: the root link is the EMPTY sentinel
+        out.nodes = dalloc<BvhNode>(1);
+        CUDA_OK(cudaMemset(out.nodes, 0, sizeof(BvhNode)));
+        out.tris = dalloc<float4>(3);  out.nNodes = 0;  out.rootLink = 0x7fffffff;
         return;
     }
     const int n = (int)nTris;
@@ -391,8 +398,18 @@ void bvhBuild(const float3* d_vertices, const uint3* d_indices, const unsigned* 
     refitKernel<<<G, B, 0, s>>>(triLo, triHi, vals, n, left, right, parent, range, boxLo, boxHi, flags, collapse);
 
     // ---- binned-SAH treelet refinement, level by level (bvh_sah.cuh)
-    const size_t maxRecords = 4 + 2 * (size_t)n;
-    out.nodes = dalloc<BvhNode>(maxRecords);
+    out.nodes = dalloc<BvhNode>((size_t)n);                  // at most n-1 inner nodes
+    int* rootLinkDev = dalloc<int>(1);
+    {   // quantisation grid over the scene AABB (needs the bounds on the host: one small read-back)
+        unsigned hb[8];
+        CUDA_OK(cudaMemcpyAsync(hb, sceneBox, sizeof(hb), cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaStreamSynchronize(s));
+        for (int a = 0; a < 3; ++a) {
+            const double lo = (double)fUnorder(hb[a]), hi = (double)fUnorder(hb[3 + a]);
+            out.gridLo[a] = lo;
+            out.gridScale[a] = hi > lo ? B200PT_GRID_SPAN / (hi - lo) : 1.0;
+        }
+    }
     out.tris = dalloc<float4>(3 * (size_t)nTris);
     out.finalGid = dalloc<unsigned>(nTris);
     static bool attrSet = false;
@@ -420,7 +437,8 @@ void bvhBuild(const float3* d_vertices, const uint3* d_indices, const unsigned* 
         selectJobsKernel<<<GV, B, 0, s>>>(n, parent, range, rank, flagNext, rankNext, jobs);
         float4* nextLo = dalloc<float4>(nJobs);  float4* nextHi = dalloc<float4>(nJobs);  int* nextLink = dalloc<int>(nJobs);  int* nextDepth = dalloc<int>(nJobs);
         SahLevelIn in{itemLo, itemHi, itemLink, itemDepth, triLo, triHi, vals, levels == 0 ? 1 : 0, ciLeaf};
-        SahLevelOut lo{nextLo, nextHi, nextLink, nextDepth, out.finalGid, (float4*)out.nodes, scalars + 0, scalars + 2};
+        SahLevelOut lo{nextLo, nextHi, nextLink, nextDepth, out.finalGid, out.nodes, rootLinkDev,
+                       {out.gridLo[0], out.gridLo[1], out.gridLo[2]}, {out.gridScale[0], out.gridScale[1], out.gridScale[2]}, scalars + 0, scalars + 2};
         const bool last = nJobs == 1;
         sahJobKernel<<<nJobs, JOB_THREADS, sizeof(SahShared), s>>>(jobs, in, lo, last ? 1 : 0);
         ++levels;
@@ -437,15 +455,15 @@ void bvhBuild(const float3* d_vertices, const uint3* d_indices, const unsigned* 
     unsigned hs[4];
     CUDA_OK(cudaMemcpyAsync(hs, scalars, sizeof(hs), cudaMemcpyDeviceToHost, s));
     CUDA_OK(cudaStreamSynchronize(s));
-    out.nNodes = 2 + 2 * hs[0];
+    out.nNodes = hs[0];
+    CUDA_OK(cudaMemcpy(&out.rootLink, rootLinkDev, sizeof(int), cudaMemcpyDeviceToHost));
     double* costDev = dalloc<double>(1);
     CUDA_OK(cudaMemsetAsync(costDev, 0, sizeof(double), s));
-    sahCostKernel<<<(out.nNodes + B - 1) / B, B, 0, s>>>((const float4*)out.nodes, out.nNodes, costDev);
+    if (out.nNodes) sahCostKernel<<<(out.nNodes + B - 1) / B, B, 0, s>>>(out.nodes, out.nNodes, 1.0 / out.gridScale[0], 1.0 / out.gridScale[1], 1.0 / out.gridScale[2], costDev);
     CUDA_OK(cudaEventRecord(e1, s));
-    float4 rootLo, rootHi, finalRoot[2];  unsigned hostBox[8];  double costHost = 0.0;
+    float4 rootLo, rootHi;  unsigned hostBox[8];  double costHost = 0.0;
     CUDA_OK(cudaMemcpyAsync(&rootLo, boxLo, sizeof(float4), cudaMemcpyDeviceToHost, s));
     CUDA_OK(cudaMemcpyAsync(&rootHi, boxHi, sizeof(float4), cudaMemcpyDeviceToHost, s));
-    CUDA_OK(cudaMemcpyAsync(finalRoot, out.nodes, 2 * sizeof(float4), cudaMemcpyDeviceToHost, s));
     CUDA_OK(cudaMemcpyAsync(hostBox, sceneBox, sizeof(hostBox), cudaMemcpyDeviceToHost, s));
     CUDA_OK(cudaMemcpyAsync(&costHost, costDev, sizeof(double), cudaMemcpyDeviceToHost, s));
     CUDA_OK(cudaStreamSynchronize(s));
@@ -454,14 +472,13 @@ void bvhBuild(const float3* d_vertices, const uint3* d_indices, const unsigned* 
     out.maxDepth = depthHost + 1;  out.nLeaves = hs[2];  out.maxLeaf = hs[3];  out.refineLevels = levels;
     const float dx = rootHi.x - rootLo.x, dy = rootHi.y - rootLo.y, dz = rootHi.z - rootLo.z;
     const float rootArea = 2.f * (dx * dy + dy * dz + dz * dx);
-    const float fx = finalRoot[1].x - finalRoot[0].x, fy = finalRoot[1].y - finalRoot[0].y, fz = finalRoot[1].z - finalRoot[0].z;
-    const float finalArea = 2.f * (fx * fy + fy * fz + fz * fx);
-    out.sahCost = finalArea > 0.f ? (float)(costHost / finalArea) : 0.f;
+    if (out.rootLink >= 0) costHost += SAH_CI * rootArea;  else costHost += SAH_CT * rootArea * (double)nTris;   // the root's own term
+    out.sahCost = rootArea > 0.f ? (float)(costHost / rootArea) : 0.f;
     out.sahCostLbvh = rootArea > 0.f ? rootHi.w / rootArea : 0.f;
     for (int a = 0; a < 6; ++a) out.sceneBounds[a] = fUnorder(hostBox[a]);
     cudaFree(triLo);  cudaFree(triHi);  cudaFree(sceneBox);  cudaFree(keys);  cudaFree(valsTmp);  cudaFree(blockHist);  cudaFree(blockOffset);
     cudaFree(left);  cudaFree(right);  cudaFree(parent);  cudaFree(range);  cudaFree(boxLo);  cudaFree(boxHi);  cudaFree(flags);
     cudaFree(collapse);  cudaFree(scalars);  cudaFree(flagNext);  cudaFree(rankA);  cudaFree(rankB);  cudaFree(tileSum);  cudaFree(tileOff);
-    cudaFree(costDev);
+    cudaFree(costDev);  cudaFree(rootLinkDev);
     if (out.maxDepth > B200PT_STACK - 2) throw std::runtime_error("BVH deeper than the traversal stack");
 }

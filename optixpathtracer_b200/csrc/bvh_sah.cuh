@@ -8,7 +8,7 @@
 //   level k: the treelet roots of level k-1 are the items; every maximal LBVH subtree holding <= JOB_T items is
 //            rebuilt the same way (leaf = one item); repeated until a single job produces the root.
 // For 262 k triangles that is 3 levels (~1.5 k + 4 + 1 jobs); for 20 M, 3-4.  The result is a full SAH-quality
-// BVH2 in the same 32-byte-node / sibling-pair layout the traversal kernels read.
+// BVH2 whose inner nodes are written as 32-byte records holding both (quantised) child boxes.
 #pragma once
 
 #define JOB_T 512                       // max items per treelet job
@@ -36,7 +36,9 @@ struct SahLevelIn {                     // items of this level
 struct SahLevelOut {
     float4* nextLo;  float4* nextHi;  int* nextLink;  int* nextDepth;   // indexed by job
     unsigned* finalGid;                 // level 1: BVH-order triangle ids
-    float4* nodes;                      // node pool (32-byte records as float4 x2); record 0/1 = root + pad
+    BvhNode* nodes;                     // node pool: one 32-byte record per inner node
+    int* rootLink;                      // written by the last level's job
+    double gridLo[3], gridScale[3];     // quantisation grid (see BvhNode)
     unsigned* pairCounter;              // pairs allocated so far
     unsigned* stats;                    // [0] leaves, [1] max leaf size
 };
@@ -189,12 +191,6 @@ __device__ void sahProcessTask(SahShared& S, const SahTask t, unsigned taskIndex
     }
 }
 
-__device__ __forceinline__ void padRecord(float4& lo, float4& hi) {
-    const float mx = fmaxf(fabsf(lo.x), fabsf(hi.x)) * 4e-7f + 1e-30f, my = fmaxf(fabsf(lo.y), fabsf(hi.y)) * 4e-7f + 1e-30f,
-                mz = fmaxf(fabsf(lo.z), fabsf(hi.z)) * 4e-7f + 1e-30f;
-    lo.x -= mx;  lo.y -= my;  lo.z -= mz;  hi.x += mx;  hi.y += my;  hi.z += mz;
-}
-
 __global__ void __launch_bounds__(JOB_THREADS)
 sahJobKernel(const SahJob* __restrict__ jobs, SahLevelIn in, SahLevelOut out, int lastLevel) {
     extern __shared__ __align__(16) unsigned char smemRaw[];
@@ -246,32 +242,41 @@ sahJobKernel(const SahJob* __restrict__ jobs, SahLevelIn in, SahLevelOut out, in
         __syncthreads();
         cur ^= 1;
     }
-    // ---- write-out: reserve a contiguous block of the node pool, relocate local links, pad the boxes
+    // ---- write-out: reserve a contiguous block of the node pool, relocate local links, quantise both child boxes of every
+    // inner node into ONE 32-byte record (BvhNode, common.cuh)
     if (tid == 0) {
         S.base = S.pairCount ? atomicAdd(out.pairCounter, S.pairCount) : 0u;
         if (in.isTri) { atomicAdd(out.stats + 0, S.leafCount);  atomicMax(out.stats + 1, S.maxLeaf); }
     }
     __syncthreads();
     const unsigned base = S.base;
-    auto relocate = [&](int link) { return (link >= 0 && (link & LINK_LOCAL)) ? (int)(2u + 2u * (base + (unsigned)(link & ~LINK_LOCAL))) : link; };
-    for (unsigned r = tid; r < 2 * S.pairCount; r += JOB_THREADS) {
-        float4 lo = S.rec[2 * r], hi = S.rec[2 * r + 1];
-        const int link = relocate(__float_as_int(lo.w));
-        padRecord(lo, hi);
-        lo.w = __int_as_float(link);  hi.w = 0.f;
-        float4* dst = out.nodes + 2 * (size_t)(2u + 2u * base + r);
-        dst[0] = lo;  dst[1] = hi;
+    auto relocate = [&](int link) { return (link >= 0 && (link & LINK_LOCAL)) ? (int)(base + (unsigned)(link & ~LINK_LOCAL)) : link; };
+    for (unsigned p = tid; p < S.pairCount; p += JOB_THREADS) {
+        unsigned q[6];
+        int links[2];
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            const float4 lo = S.rec[4 * p + 2 * c], hi = S.rec[4 * p + 2 * c + 1];
+            links[c] = relocate(__float_as_int(lo.w));
+            const float l[3] = {lo.x, lo.y, lo.z}, h[3] = {hi.x, hi.y, hi.z};
+            unsigned ql[3], qh[3];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {                      // conservative: floor/ceil in double, then GRID_PAD cells outward
+                const double gl = B200PT_GRID_ORIGIN + ((double)l[a] - out.gridLo[a]) * out.gridScale[a];
+                const double gh = B200PT_GRID_ORIGIN + ((double)h[a] - out.gridLo[a]) * out.gridScale[a];
+                ql[a] = (unsigned)min(65535, max(0, (int)floor(gl) - B200PT_GRID_PAD));
+                qh[a] = (unsigned)min(65535, max(0, (int)ceil(gh) + B200PT_GRID_PAD));
+            }
+            q[3 * c + 0] = ql[0] | (qh[0] << 16);  q[3 * c + 1] = ql[1] | (qh[1] << 16);  q[3 * c + 2] = ql[2] | (qh[2] << 16);
+        }
+        uint4* dst = reinterpret_cast<uint4*>(out.nodes) + 2 * (size_t)(base + p);
+        dst[0] = make_uint4(q[0], q[1], q[2], q[3]);
+        dst[1] = make_uint4(q[4], q[5], (unsigned)links[0], (unsigned)links[1]);
     }
     if (tid == 0) {
-        float4 lo = S.rootRec[0], hi = S.rootRec[1];
+        const float4 lo = S.rootRec[0], hi = S.rootRec[1];
         const int link = relocate(__float_as_int(lo.w));
-        if (lastLevel) {
-            float4 plo = lo, phi = hi;
-            padRecord(plo, phi);
-            plo.w = __int_as_float(link);  phi.w = 0.f;
-            out.nodes[0] = plo;  out.nodes[1] = phi;
-            out.nodes[2] = make_float4(0, 0, 0, 0);  out.nodes[3] = make_float4(0, 0, 0, 0);
-        }
+        if (lastLevel) *out.rootLink = link;
         out.nextLo[blockIdx.x] = make_float4(lo.x, lo.y, lo.z, 0.f);
         out.nextHi[blockIdx.x] = make_float4(hi.x, hi.y, hi.z, 0.f);
         out.nextLink[blockIdx.x] = link;

@@ -18,8 +18,14 @@
 
 #define B200PT_NUM_SMS 148
 
-struct BvhNode { float lo[3]; int link; float hi[3]; int aux; };      // link >= 0: index of the child pair; < 0: leaf code
+// One 32-byte record per INNER node, holding both children: their boxes quantised (conservatively, 2 cells of padding) to a
+// 16-bit grid over the scene AABB, and their links.  link >= 0: record index of the child's own node; < 0: leaf code.
+//   q[0] = c0.lo.x | c0.hi.x << 16,  q[1] = c0.lo.y | c0.hi.y << 16,  q[2] = c0.lo.z | c0.hi.z << 16,  q[3..5]: child 1
+struct BvhNode { unsigned q[6]; int link[2]; };
 static_assert(sizeof(BvhNode) == 32, "BvhNode must be 32 bytes");
+#define B200PT_GRID_ORIGIN 2.0      // grid coordinate of the scene AABB's low corner ...
+#define B200PT_GRID_SPAN 65531.0    // ... and the span of the scene AABB in cells: padded boxes stay inside [0, 65535]
+#define B200PT_GRID_PAD 2
 // leaf code: -(1 + first*8 + (count-1)), count in 1..8
 __host__ __device__ inline int leafEncode(unsigned first, unsigned count) { return -(int)(1u + first * 8u + (count - 1u)); }
 __host__ __device__ inline void leafDecode(int link, unsigned& first, unsigned& count) {
@@ -42,7 +48,9 @@ struct MeshInfo {                  // device-side stand-in for the per-mesh SBT 
 static_assert(sizeof(MeshInfo) == 136, "MeshInfo");
 
 struct SceneDev {                  // everything the kernels need about the scene (passed by value)
-    const float4* nodes;           // BvhNode pairs viewed as float4 x2
+    const uint4* nodes;            // BvhNode records viewed as uint4 x2
+    int rootLink;                  // link of the root (EMPTY sentinel 0x7fffffff for an empty scene)
+    double gridLo[3], gridScale[3];   // world -> grid: g = GRID_ORIGIN + (x - gridLo) * gridScale
     const float4* tris;            // TriRecord viewed as float4 x3, BVH order
     const MeshInfo* meshes;
     const uint3* indices;          // global index buffer, LOCAL vertex ids (per mesh)
@@ -111,7 +119,8 @@ struct TraceStats { unsigned long long nodes, tris, rays; };
 // ---- launchers implemented in the .cu files ------------------------------------------------------------
 // bvh_build.cu
 struct BvhBuildResult {
-    BvhNode* nodes = nullptr;  float4* tris = nullptr;  unsigned nNodes = 0, nTris = 0, nLeaves = 0, maxLeaf = 0, maxDepth = 0;
+    BvhNode* nodes = nullptr;  int rootLink = 0x7fffffff;  double gridLo[3] = {0, 0, 0}, gridScale[3] = {1, 1, 1};
+    float4* tris = nullptr;  unsigned nNodes = 0, nTris = 0, nLeaves = 0, maxLeaf = 0, maxDepth = 0;
     float sahCost = 0.f, sahCostLbvh = 0.f, buildMs = 0.f;
     unsigned long long* mortonByGid = nullptr;  uint32_t* sortedGid = nullptr;  uint32_t* finalGid = nullptr;  unsigned refineLevels = 0;  float sceneBounds[6] = {0, 0, 0, 0, 0, 0};
 };

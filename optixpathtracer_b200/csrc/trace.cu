@@ -9,9 +9,10 @@
 // decided by a warp vote), so a warp never idles behind its slowest ray.  Every loop iteration each lane takes
 // ONE inner-node step if it can; a lane that reaches a leaf postpones it and keeps walking; once enough lanes
 // are blocked on a second leaf (warp vote) the warp intersects all pending leaves together.
-// A 32-byte node is ONE 256-bit load (LDG.E.256, new on sm_100); a sibling pair is two of them in one 64-byte
-// aligned half cache line; a 48-byte triangle is 3x128-bit.  All fetches go through the read-only path.
-// Roofline: L1/L2 gather bound; algorithmic bytes per ray = 32*nodes + 48*tris + 32 (ray) + 16 (hit).
+// A traversal step is ONE 256-bit load (LDG.E.256, new on sm_100): the 32-byte record of an inner node holds both child
+// boxes, quantised to a 16-bit grid over the scene AABB, and both links; a 48-byte triangle is 3x128-bit.  All fetches go
+// through the read-only path.  The kernel is bound by the L1 wavefront rate (one wavefront per lane per divergent load),
+// which is why a step costs one wavefront, not two.  Algorithmic bytes per ray = 32*nodes + 48*tris + 32 (ray) + 16 (hit).
 // The ray/triangle test is the exact fp32 operation sequence of oracle/scene_core.h (no FMA contraction,
 // enforced with __f*_rn intrinsics), which makes the chosen triangle and (t,u,v) BVH-independent.
 #include "common.cuh"
@@ -32,12 +33,50 @@ static int g_refillThreshold = -1, g_leafThreshold = -1;   // lanes that must be
 
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
 
-struct Node8 { float4 a, b; };    // {lo.xyz, link | hi.xyz, aux}
-__device__ __forceinline__ Node8 ldgNode(const float4* p) {
+struct Node8 { unsigned w[8]; };   // BvhNode: w[0..5] = 12 quantised bounds (two children), w[6], w[7] = links
+__device__ __forceinline__ Node8 ldgNode(const uint4* p) {        // ONE 256-bit load per traversal step
     Node8 n;
-    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-        : "=f"(n.a.x), "=f"(n.a.y), "=f"(n.a.z), "=f"(n.a.w), "=f"(n.b.x), "=f"(n.b.y), "=f"(n.b.z), "=f"(n.b.w) : "l"(p));
+    asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=r"(n.w[0]), "=r"(n.w[1]), "=r"(n.w[2]), "=r"(n.w[3]), "=r"(n.w[4]), "=r"(n.w[5]), "=r"(n.w[6]), "=r"(n.w[7]) : "l"(p));
     return n;
+}
+
+// Ray in grid coordinates.  A quantised plane q is decoded with one PRMT into the float 2^23 + q (exact), and the slab
+// distance is ONE FMA: t = (2^23 + q) * inv + c with c = -(2^23 + og) * inv, og = ray origin in cells, inv = 1 / (d * cells per
+// unit).  c is formed with a single rounding (fma of og*inv onto the exact 2^23*inv), so a plane is off by at most ~0.51 cell
+// (0.5 from c, 0.01 from og); the same `inv` multiplies both terms, so its own rounding only rescales t by 1 +- 2^-23.  Every
+// stored box carries GRID_PAD = 2 cells of padding, which covers this.  (fp32 only: plain FP64 is slow on this part.)
+struct GridRay { float ix, iy, iz, cx, cy, cz;  unsigned nx, ny, nz; };    // n*: PRMT selector of the NEAR plane's half-word on that axis
+__device__ __forceinline__ GridRay makeGridRay(const SceneDev& S, const float3 o, const float3 d) {
+    GridRay g;
+    const float sx = (float)S.gridScale[0], sy = (float)S.gridScale[1], sz = (float)S.gridScale[2];
+    const float ox = fmaf(o.x - (float)S.gridLo[0], sx, (float)B200PT_GRID_ORIGIN);
+    const float oy = fmaf(o.y - (float)S.gridLo[1], sy, (float)B200PT_GRID_ORIGIN);
+    const float oz = fmaf(o.z - (float)S.gridLo[2], sz, (float)B200PT_GRID_ORIGIN);
+    // a zero direction component must not turn the slab into NaNs (the axis would be ignored and the ray would walk the whole
+    // tree along it): clamp |d * s| to 2^-100, so inv stays finite and the 0.51-cell bound above still holds
+    const float tiny = 7.8886090522101181e-31f;
+    float dx = d.x * sx, dy = d.y * sy, dz = d.z * sz;
+    if (!(fabsf(dx) >= tiny)) dx = copysignf(tiny, dx);
+    if (!(fabsf(dy) >= tiny)) dy = copysignf(tiny, dy);
+    if (!(fabsf(dz) >= tiny)) dz = copysignf(tiny, dz);
+    g.ix = 1.0f / dx;  g.iy = 1.0f / dy;  g.iz = 1.0f / dz;
+    g.nx = dx < 0.f ? 0x7632u : 0x7610u;  g.ny = dy < 0.f ? 0x7632u : 0x7610u;  g.nz = dz < 0.f ? 0x7632u : 0x7610u;
+    g.cx = -fmaf(ox, g.ix, 8388608.0f * g.ix);  g.cy = -fmaf(oy, g.iy, 8388608.0f * g.iy);  g.cz = -fmaf(oz, g.iz, 8388608.0f * g.iz);
+    return g;
+}
+// 2^23 + one half-word of w: selector 0x7610 takes the low half (lo plane), 0x7632 the high half (hi plane)
+__device__ __forceinline__ float qSel(unsigned w, unsigned sel) { return __uint_as_float(__byte_perm(w, 0x4B000000u, sel)); }
+// slab test of one child: words {lo.x|hi.x<<16, lo.y|hi.y<<16, lo.z|hi.z<<16}.  The ray's direction signs pick the near and
+// the far plane of each axis directly (far selector = near ^ 0x22), so no per-axis min/max is needed.
+__device__ __forceinline__ bool boxTest(unsigned w0, unsigned w1, unsigned w2, const GridRay& g, float tmin, float tmax, float& tnear) {
+    const float ax = fmaf(qSel(w0, g.nx), g.ix, g.cx), bx = fmaf(qSel(w0, g.nx ^ 0x22u), g.ix, g.cx);
+    const float ay = fmaf(qSel(w1, g.ny), g.iy, g.cy), by = fmaf(qSel(w1, g.ny ^ 0x22u), g.iy, g.cy);
+    const float az = fmaf(qSel(w2, g.nz), g.iz, g.cz), bz = fmaf(qSel(w2, g.nz ^ 0x22u), g.iz, g.cz);
+    const float t0 = fmaxf(fmaxf(ax, ay), fmaxf(az, tmin));
+    const float t1 = fminf(fminf(bx, by), fminf(bz, tmax));
+    tnear = t0;
+    return t0 <= t1 * 1.0000004f;
 }
 
 __device__ __forceinline__ void prefetchL1(const void* p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
@@ -99,30 +138,17 @@ __device__ __forceinline__ bool triEval(const float4 a, const float4 b, const fl
     return det != 0.0f && !(cullBack && det < 0.0f) && (det > 0.0f ? inPos : inNeg);
 }
 
-// slab test against one 32-byte node (boxes are padded at build time; far side widened by 2 ulp)
-__device__ __forceinline__ bool boxTest(const float4 n0, const float4 n1, const float3 o, const float3 inv,
-                                        float tmin, float tmax, float& tnear) {
-    const float ax = (n0.x - o.x) * inv.x, bx = (n1.x - o.x) * inv.x;
-    const float ay = (n0.y - o.y) * inv.y, by = (n1.y - o.y) * inv.y;
-    const float az = (n0.z - o.z) * inv.z, bz = (n1.z - o.z) * inv.z;
-    const float t0 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), tmin));
-    const float t1 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), tmax));
-    tnear = t0;
-    return t0 <= t1 * 1.0000004f;
-}
-
 struct Best { float t, u, v; int slot; unsigned gid; };
 
-// One inner-node step: fetch the sibling pair `cur`, test both, descend into the nearer hit child and push the other.
+// One inner-node step: fetch node `cur` (both child boxes in one record), descend into the nearer hit child, push the other.
 #define NODE_STEP()                                                                              \
     {                                                                                            \
-        const float4* p_ = S.nodes + 2 * (size_t)cur;                                            \
-        const Node8 L_ = ldgNode(p_), R_ = ldgNode(p_ + 2);                                      \
-        if (COUNT) nNodes += 2;                                                                  \
+        const Node8 N_ = ldgNode(S.nodes + 2 * (size_t)cur);                                     \
+        if (COUNT) nNodes += 1;                                                                  \
         float tl_, tr_;                                                                          \
-        const bool hl_ = boxTest(L_.a, L_.b, o, inv, tmin, best.t, tl_);                         \
-        const bool hr_ = boxTest(R_.a, R_.b, o, inv, tmin, best.t, tr_);                         \
-        const int cl_ = __float_as_int(L_.a.w), cr_ = __float_as_int(R_.a.w);                    \
+        const bool hl_ = boxTest(N_.w[0], N_.w[1], N_.w[2], g, tmin, best.t, tl_);               \
+        const bool hr_ = boxTest(N_.w[3], N_.w[4], N_.w[5], g, tmin, best.t, tr_);               \
+        const int cl_ = (int)N_.w[6], cr_ = (int)N_.w[7];                                        \
         if (hl_ && hr_) {                                                                        \
             const bool sw_ = tr_ < tl_;                                                          \
             stack[sp++] = sw_ ? cl_ : cr_;                                                       \
@@ -136,11 +162,11 @@ struct Best { float t, u, v; int slot; unsigned gid; };
 template <bool ANY, bool COUNT>
 __device__ __forceinline__ bool traverse(const SceneDev& S, const float3 o, const float3 d, float tmin, float tmax,
                                          bool cullBack, Best& best, unsigned& nNodes, unsigned& nTris) {
-    const float3 inv = make_float3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    const GridRay g = makeGridRay(S, o, d);
     int stack[B200PT_STACK];
     int sp = 0;
     best.t = tmax;  best.slot = -1;  best.gid = 0xffffffffu;  best.u = best.v = 0.f;
-    int cur = __float_as_int(ldg4(S.nodes).w);            // root record's link
+    int cur = S.rootLink;
     while (cur != EMPTY) {
         if (cur >= 0) {
             NODE_STEP()
@@ -204,7 +230,7 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
     const unsigned chunksC = (countC + 31u) >> 5, chunksTotal = chunksC + ((countS + 31u) >> 5);
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned ltMask = (1u << lane) - 1u;
-    const int rootLink = __float_as_int(ldg4(S.nodes).w);
+    const int rootLink = S.rootLink;
     unsigned nNodes[2] = {0, 0}, nTris[2] = {0, 0}, nRays[2] = {0, 0}, myNodes = 0, myTris = 0;
 
     // warp-uniform staging state: rays [stageNext, stageEnd) of the current chunk are still unassigned
@@ -215,7 +241,8 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
     // per-lane ray state
     bool active = false, isAny = false;
     unsigned rayIdx = 0;
-    float3 o = make_float3(0, 0, 0), d = o, inv = o;
+    float3 o = make_float3(0, 0, 0), d = o;
+    GridRay g = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     float wO = 0.f, wD = 0.f;
     Best best;  best.t = tmax;  best.slot = -1;  best.gid = 0xffffffffu;  best.u = best.v = 0.f;
     float bestDet = 1.f;
@@ -275,7 +302,7 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
                     const unsigned j = stageNext + r;
                     const float4 o4 = stageO[warp][buf][j - stageFirst], d4 = stageD[warp][buf][j - stageFirst];
                     o = make_float3(o4.x, o4.y, o4.z);  d = make_float3(d4.x, d4.y, d4.z);  wO = o4.w;  wD = d4.w;
-                    inv = make_float3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+                    g = makeGridRay(S, o, d);
                     rayIdx = j;  active = true;  isAny = stageAny != 0;
                     best.t = tmax;  best.slot = -1;  best.gid = 0xffffffffu;  best.u = best.v = 0.f;
                     cur = rootLink;  leaf = NO_LEAF;  sp = 0;
@@ -295,13 +322,12 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
 #pragma unroll 1
         for (int round = 0; ; ++round) {
             if (active && (unsigned)cur < (unsigned)EMPTY) {
-                const float4* p_ = S.nodes + 2 * (size_t)cur;
-                const Node8 L_ = ldgNode(p_), R_ = ldgNode(p_ + 2);
-                if (COUNT) myNodes += 2;
+                const Node8 N_ = ldgNode(S.nodes + 2 * (size_t)cur);
+                if (COUNT) myNodes += 1;
                 float tl_, tr_;
-                const bool hl_ = boxTest(L_.a, L_.b, o, inv, tmin, best.t, tl_);
-                const bool hr_ = boxTest(R_.a, R_.b, o, inv, tmin, best.t, tr_);
-                const int cl_ = __float_as_int(L_.a.w), cr_ = __float_as_int(R_.a.w);
+                const bool hl_ = boxTest(N_.w[0], N_.w[1], N_.w[2], g, tmin, best.t, tl_);
+                const bool hr_ = boxTest(N_.w[3], N_.w[4], N_.w[5], g, tmin, best.t, tr_);
+                const int cl_ = (int)N_.w[6], cr_ = (int)N_.w[7];
                 if (hl_ && hr_) {
                     const bool sw_ = tr_ < tl_;
                     const int far_ = sw_ ? cl_ : cr_;

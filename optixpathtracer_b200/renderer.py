@@ -180,7 +180,7 @@ class SampleRenderer:
 
     def downloadBvh(self):
         info = self.bvhInfo()
-        nodes = np.empty((int(info.n_nodes), 8), np.float32)
+        nodes = np.empty((int(info.n_nodes), 8), np.uint32)
         tri_ids = np.empty(int(info.n_triangles), np.uint32)
         _lib.check(self._L.b200pt_download_bvh(self._h, _ptr(nodes), len(nodes), _ptr(tri_ids), len(tri_ids)))
         return nodes, tri_ids

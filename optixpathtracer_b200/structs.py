@@ -150,7 +150,8 @@ class BvhInfo(C.Structure):
     _fields_ = [("n_triangles", C.c_uint64), ("n_nodes", C.c_uint64), ("n_leaves", C.c_uint64),
                 ("max_leaf_size", C.c_uint32), ("max_depth", C.c_uint32), ("sah_cost", C.c_float),
                 ("sah_cost_lbvh", C.c_float), ("build_ms", C.c_float), ("node_bytes", C.c_uint64),
-                ("tri_bytes", C.c_uint64)]
+                ("tri_bytes", C.c_uint64), ("root_link", C.c_int32), ("refine_levels", C.c_uint32),
+                ("grid_lo", C.c_double * 3), ("grid_scale", C.c_double * 3)]
 
 
 class Counters(C.Structure):
