@@ -4,9 +4,9 @@
 // mouse cursor (main.cpp:310-314), follows a scripted Lissajous track.  fps is appended every 0.5 s in the reference's
 // log format (sutil/sutil.cpp:760-772: one value per line).
 //
-//   b200pt_headless [--obj file.obj | --boxes N] [--preset sv4_fov|sv4_uniform|sv3_uniform|orig] [--size WxH] [--frames N]
+//   b200pt_headless [--obj file.obj | --boxes N] [--preset sv4_fov|sv4_uniform|sv3_uniform|orig] [--size WxH] [--frames N] [--spl N]
 //                   [--camera sponza|lost_empire|san_miguel|cornell] [--sky r,g,b] [--out image.ppm] [--log fps.tsv]
-//                   [--dump-model file.bin] [--no-render]
+//                   [--hdr probe.hdr] [--gpu-cdf] [--dump-model file.bin] [--dump-probe file.bin] [--no-render]
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -18,13 +18,6 @@
 #include <vector>
 
 #include "../include/ref_api/SimplePathtracer.h"
-
-static void loadColor(ProbeData& probe, const float3& color, int width, int height) {        // main.cpp:167-180
-    probe.width = width;  probe.height = height;
-    probe.data = new Color[(size_t)width * height];
-    for (size_t i = 0; i < (size_t)width * height; ++i) probe.data[i] = Color{color.x, color.y, color.z, 1.0f};
-    probe.BuildCDF();
-}
 
 static sutil::Camera cameraPreset(const std::string& name) {                                 // main.cpp:211-240
     if (name == "sponza") return sutil::Camera({-1293.07f, 154.681f, 1.0f}, {0.f, 200.f, 0.f}, {0.f, 1.f, 0.f}, 35.f, 1.f);
@@ -71,10 +64,10 @@ static void dumpModel(const Model* m, const char* path) {    // flat binary for 
 }
 
 int main(int argc, char** argv) {
-    std::string obj, preset = "sv4_fov", cam = "cornell", out, log, dump;
-    int W = 1280, H = 720, frames = 16, boxes = 64;
+    std::string obj, preset = "sv4_fov", cam = "cornell", out, log, dump, hdr, dumpProbe;
+    int W = 1280, H = 720, frames = 16, boxes = 64, spl = 1;
     float3 sky{1.f, 1.f, 1.f};
-    bool noRender = false;
+    bool noRender = false, gpuCdf = false;
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
         auto next = [&]() -> const char* { if (i + 1 >= argc) { fprintf(stderr, "missing value for %s\n", a.c_str());  exit(2); } return argv[++i]; };
@@ -84,10 +77,14 @@ int main(int argc, char** argv) {
         else if (a == "--camera") cam = next();
         else if (a == "--size") { if (sscanf(next(), "%dx%d", &W, &H) != 2) { fprintf(stderr, "--size WxH\n");  return 2; } }
         else if (a == "--frames") frames = atoi(next());
+        else if (a == "--spl") spl = atoi(next());
         else if (a == "--sky") { if (sscanf(next(), "%f,%f,%f", &sky.x, &sky.y, &sky.z) != 3) { fprintf(stderr, "--sky r,g,b\n");  return 2; } }
         else if (a == "--out") out = next();
         else if (a == "--log") log = next();
         else if (a == "--dump-model") dump = next();
+        else if (a == "--hdr") hdr = next();
+        else if (a == "--gpu-cdf") gpuCdf = true;
+        else if (a == "--dump-probe") dumpProbe = next();
         else if (a == "--no-render") noRender = true;
         else { fprintf(stderr, "unknown argument %s\n", a.c_str());  return 2; }
     }
@@ -95,14 +92,26 @@ int main(int argc, char** argv) {
         std::unique_ptr<Model> model(obj.empty() ? boxScene(boxes, 0x5702A) : loadOBJ(obj));             // main.cpp:188
         printf("model: %zu meshes, %zu textures, %zu triangles\n", model->meshes.size(), model->textures.size(), model->numTriangles());
         if (!dump.empty()) dumpModel(model.get(), dump.c_str());
-        if (noRender) return 0;
         ProbeData probe;
-        loadColor(probe, sky, 512, 256);                                                                    // main.cpp:205-206
+        if (!hdr.empty()) {                                                                                 // main.cpp:201-202
+            if (gpuCdf) probe.data = readHDR(hdr, probe.width, probe.height);                               // tables built by setProbeImage
+            else loadProbe(probe, hdr);
+        } else if (!noRender || !dumpProbe.empty()) loadColor(probe, sky, 512, 256);                        // main.cpp:205-206
+        if (!dumpProbe.empty()) {                                  // flat binary for the reader parity test (tests/test_cpp_host.py)
+            FILE* fp = fopen(dumpProbe.c_str(), "wb");
+            if (!fp) throw std::runtime_error("cannot write " + dumpProbe);
+            const int wh[2] = {probe.width, probe.height};
+            fwrite(wh, 4, 2, fp);
+            fwrite(probe.data, 16, (size_t)probe.width * probe.height, fp);
+            fclose(fp);
+        }
+        if (noRender) return 0;
         sutil::Camera camera = cameraPreset(cam);                                                           // :213-217
         SampleRenderer sample(model.get(), 0, preset.c_str());                                              // :252
         sample.setCamera(camera);                                                                           // :253 (before resize, like the reference)
         sample.resize(int2{W, H});                                                                          // :256-262
-        sample.setProbe(probe);                                                                             // :269
+        if (gpuCdf) sample.setProbeImage(probe);  else sample.setProbe(probe);                              // :269
+        sample.launchParams.samples_per_launch = spl;       // read by the `orig` preset (orig/main.cpp sets it); the sv presets write their own
         const b200pt_bvh_info bi = sample.bvhInfo();
         printf("bvh: %llu nodes, %llu leaves, SAH %.2f (LBVH %.2f), build %.2f ms\n", (unsigned long long)bi.n_nodes,
                (unsigned long long)bi.n_leaves, bi.sah_cost, bi.sah_cost_lbvh, bi.build_ms);

@@ -56,7 +56,10 @@ typedef struct b200pt_config {
     int   tile_rank, tile_count; /* multi-GPU tile split: this context renders launch rows whose 32-row band
                                     index % tile_count == tile_rank; tile_count <= 1 = whole frame        */
     int   profile;            /* bit 0: per-stage CUDA-event timings; bit 1: traversal counters (slower kernels) */
-    int   reserved[4];
+    int   mis_on_miss;        /* 0 = off (reference behaviour: a BSDF-sampled ray that leaves the scene adds nothing, sv4/deviceProgram.cu:251-280).
+                                 1 = opt-in extension, the reference's commented-out MIS (:257-267): a secondary ray that misses adds
+                                 w * ProbeEval(dir) * throughput with w = p_bsdf / (p_bsdf + ProbePdf(dir)), the partner of the NEE weight */
+    int   reserved[3];
 } b200pt_config;
 
 /* Fill *cfg with a named preset: "orig", "sv3_uniform", "sv4_uniform", "sv4_fov". */
@@ -87,6 +90,14 @@ int b200pt_resize(b200pt_ctx* ctx, int width, int height, struct LaunchParams* p
 int b200pt_set_probe(b200pt_ctx* ctx, int width, int height, const float* data_rgba,
                      const float* pdfX, const float* cdfX, const float* pdfY, const float* cdfY,
                      const float* offset_xyz, struct LaunchParams* params /* probe pointers written */);
+
+/* loadProbe/loadColor + ProbeData::BuildCDF + setProbe in one call (sv4/main.cpp:154-180, sv4/Probe.h:29-77,
+ * sv4/SimplePathtracer.cpp:295-311): uploads width*height float4 texels and builds pdfValuesX/cdfValuesX/pdfValuesY/cdfValuesY ON THE
+ * DEVICE, bit-identical to the host's sequential fp32 BuildCDF (one warp per row keeps the accumulation order). */
+int b200pt_set_probe_image(b200pt_ctx* ctx, int width, int height, const float* data_rgba, const float* offset_xyz,
+                           struct LaunchParams* params /* probe pointers written */);
+/* Copies the current probe's device tables to the host (any pointer may be NULL): width*height, width*height, height, height floats. */
+int b200pt_download_probe(b200pt_ctx* ctx, float* pdfX, float* cdfX, float* pdfY, float* cdfY);
 
 /* ---- the hot path: SampleRenderer::render() (sv4/SimplePathtracer.cpp:77-217) ---------------------
  * Reads the caller's live LaunchParams (camera, frame.c, subframe_index, ...), runs the wavefront

@@ -6,6 +6,7 @@
 #pragma once
 #include <vector_types.h>
 #include <cstddef>
+#include <string>
 
 typedef float4 Color;
 
@@ -64,3 +65,9 @@ struct ProbeData {
         valid = true;
     }
 };
+
+// host/Probe.cpp — loadProbe / loadColor (sv4/main.cpp:154-180).  readHDR is our own Radiance .hdr reader with stbi_loadf(..., 4)
+// conventions; the returned array is new[]-allocated and owned by the caller (as probe.data is in the reference).
+Color* readHDR(const std::string& hdrFile, int& width, int& height);
+void loadProbe(ProbeData& probe, const std::string& hdrFile);
+void loadColor(ProbeData& probe, const float3& color, int width = 3840, int height = 2160);

@@ -81,6 +81,13 @@ public:
         if (b200pt_set_probe(ctx, probe.width, probe.height, reinterpret_cast<const float*>(probe.data), probe.pdfValuesX,
                              probe.cdfValuesX, probe.pdfValuesY, probe.cdfValuesY, off, &launchParams) != 0) fail();
     }
+    // loadProbe/loadColor without the host BuildCDF: uploads probe.data only and builds the four tables on the GPU (same bits as
+    // ProbeData::BuildCDF, Probe.h:29-77); probe.valid is not required.
+    void setProbeImage(const ProbeData& probe) {
+        if (!probe.data || probe.width <= 0 || probe.height <= 0) throw std::runtime_error("Probe Data is not valid");
+        const float off[3] = {probe.offset.x, probe.offset.y, probe.offset.z};
+        if (b200pt_set_probe_image(ctx, probe.width, probe.height, reinterpret_cast<const float*>(probe.data), off, &launchParams) != 0) fail();
+    }
     // extras behind the same C-ABI
     void downloadAccum(float* h_rgba) { if (b200pt_download_accum(ctx, h_rgba) != 0) fail(); }
     b200pt_counters counters() { b200pt_counters c{};  if (b200pt_get_counters(ctx, &c) != 0) fail();  return c; }

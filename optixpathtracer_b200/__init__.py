@@ -5,6 +5,6 @@ SampleRenderer(resize/setCamera/setProbe/render/downloadPixels) over the C-ABI i
 """
 from .structs import Material, LaunchParams, Config, preset          # noqa: F401
 from .model import Model, TriangleMesh, Texture, loadOBJ, addBox      # noqa: F401
-from .probe import ProbeData, loadColor, analytic_sky                 # noqa: F401
+from .probe import ProbeData, loadColor, loadProbe, read_hdr, write_hdr, analytic_sky                 # noqa: F401
 from .camera import Camera, preset_camera                             # noqa: F401
 from .renderer import SampleRenderer, host_params, set_camera         # noqa: F401

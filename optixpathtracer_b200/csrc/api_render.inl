@@ -24,7 +24,7 @@ static size_t poolLimit() {
     return std::max<size_t>(v, 1024);
 }
 
-static void ensurePool(b200pt_ctx* c, size_t slots, bool aovs) {
+static void ensurePool(b200pt_ctx* c, size_t slots, bool aovs, bool mis) {
     if (slots > c->poolCap) {
         c->rng.ensure(slots);  c->thr.ensure(slots);  c->state.ensure(slots);  c->direct.ensure(slots);  c->indirect.ensure(slots);
         c->alpha.ensure(slots);  c->pending.ensure(slots);
@@ -33,6 +33,7 @@ static void ensurePool(b200pt_ctx* c, size_t slots, bool aovs) {
         c->poolCap = slots;
     }
     if (aovs) { c->aovN.ensure(c->poolCap);  c->aovA.ensure(c->poolCap); }
+    if (mis) c->bsdfPdf.ensure(c->poolCap);
     c->counters.ensure(QC_STRIDE * QC_MAX_LAUNCHES + 8);                     // per-launch queue counters, then 8 frame totals
     c->stats.ensure(2);
 }
@@ -129,7 +130,7 @@ static FrameParams frameOf(const LaunchParams& P, const b200pt_config& cfg, cons
     // the coarse CDF table belongs to the probe uploaded by b200pt_set_probe; a caller-substituted probe falls back
     F.cdfXCoarse = (c && c->probeCoarse.p && P.probe.cdfValuesX == c->probeCdfX.p && P.probe.width == c->probeW && P.probe.height == c->probeH) ? c->probeCoarse.p : nullptr;
     F.tmin = cfg.tmin;  F.tmax = cfg.tmax;  F.maxDepth = cfg.max_depth;  F.shadowMode = cfg.shadow_mode;  F.display = cfg.display;
-    F.accumMode = cfg.accum_mode;  F.writeAovs = cfg.write_aovs;  F.russianRoulette = cfg.russian_roulette;  F.exposure = cfg.exposure;
+    F.accumMode = cfg.accum_mode;  F.writeAovs = cfg.write_aovs;  F.russianRoulette = cfg.russian_roulette;  F.misOnMiss = cfg.mis_on_miss;  F.exposure = cfg.exposure;
     F.tileRank = cfg.tile_rank;  F.tileCount = cfg.tile_count;
     F.accum = P.frame.accum_buffer;  F.frame = (uint32_t*)P.frame.frame_buffer;  F.normal = P.frame.normal_buffer;
     F.albedo = P.frame.albedo_buffer;  F.color = P.frame.color_buffer;
@@ -176,9 +177,9 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
         }
     }
     if (maxUsed >= ((size_t)1 << 31)) throw std::runtime_error("b200pt_render: pool too large");
-    ensurePool(c, std::max<size_t>(maxUsed, 1), cfg.write_aovs != 0);
+    ensurePool(c, std::max<size_t>(maxUsed, 1), cfg.write_aovs != 0, cfg.mis_on_miss != 0);
 
-    PathPool pool{c->rng.p, c->thr.p, c->state.p, c->direct.p, c->indirect.p, c->alpha.p, c->pending.p, c->aovN.p, c->aovA.p};
+    PathPool pool{c->rng.p, c->thr.p, c->state.p, c->direct.p, c->indirect.p, c->alpha.p, c->pending.p, c->bsdfPdf.p, c->aovN.p, c->aovA.p};
     Queues Q;
     for (int i = 0; i < 2; ++i) { Q.rayO[i] = c->rayO[i].p;  Q.rayD[i] = c->rayD[i].p; }
     Q.hit = c->hit.p;  Q.shO = c->shO.p;  Q.shD = c->shD.p;  Q.counters = c->counters.p;
@@ -281,6 +282,44 @@ int b200pt_set_probe(b200pt_ctx* c, int w, int h, const float* data, const float
     params->probe.pdfValuesX = c->probePdfX.p;  params->probe.cdfValuesX = c->probeCdfX.p;
     params->probe.pdfValuesY = c->probePdfY.p;  params->probe.cdfValuesY = c->probeCdfY.p;
     params->probe.offset = offset ? make_float3(offset[0], offset[1], offset[2]) : make_float3(0.f, 0.f, 0.f);
+    API_END
+}
+
+// loadProbe/loadColor + BuildCDF + setProbe in one call (sv4/main.cpp:154-180, Probe.h:29-77, SimplePathtracer.cpp:295-311): only the
+// texels cross PCIe; the four tables are built on the device, bit-identical to the host's sequential BuildCDF.
+int b200pt_set_probe_image(b200pt_ctx* c, int w, int h, const float* data, const float* offset, LaunchParams* params) {
+    if (!c || !params) return fail("b200pt_set_probe_image: null argument");
+    if (w <= 0 || h <= 0 || !data) return fail("Probe Data is not valid");
+    API_BEGIN
+    CUDA_OK(cudaSetDevice(c->device));
+    const size_t n = (size_t)w * h;
+    c->probeData.ensure(4 * n);  c->probePdfX.ensure(n);  c->probeCdfX.ensure(n);  c->probePdfY.ensure(h);  c->probeCdfY.ensure(h);
+    c->probeCoarse.ensure((size_t)((w + 31) / 32) * h);
+    c->probeRowTotal.ensure(h);
+    CUDA_OK(cudaMemcpyAsync(c->probeData.p, data, 16 * n, cudaMemcpyHostToDevice, c->stream));
+    launchProbeCdf((const float4*)c->probeData.p, w, h, c->probePdfX.p, c->probeCdfX.p, c->probePdfY.p, c->probeCdfY.p, c->probeRowTotal.p, c->stream);
+    launchProbeCoarse(c->probeCdfX.p, w, h, c->probeCoarse.p, c->stream);
+    CUDA_OK(cudaGetLastError());
+    c->probeW = w;  c->probeH = h;
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    params->probe.width = w;  params->probe.height = h;  params->probe.data = (Color*)c->probeData.p;
+    params->probe.pdfValuesX = c->probePdfX.p;  params->probe.cdfValuesX = c->probeCdfX.p;
+    params->probe.pdfValuesY = c->probePdfY.p;  params->probe.cdfValuesY = c->probeCdfY.p;
+    params->probe.offset = offset ? make_float3(offset[0], offset[1], offset[2]) : make_float3(0.f, 0.f, 0.f);
+    API_END
+}
+// the device-resident tables of the current probe, for hosts that want ProbeData's arrays back (and for the parity tests)
+int b200pt_download_probe(b200pt_ctx* c, float* pdfX, float* cdfX, float* pdfY, float* cdfY) {
+    if (!c) return fail("b200pt_download_probe: null context");
+    if (!c->probeW || !c->probeH) return fail("b200pt_download_probe: no probe set");
+    API_BEGIN
+    CUDA_OK(cudaSetDevice(c->device));
+    const size_t n = (size_t)c->probeW * c->probeH;
+    if (pdfX) CUDA_OK(cudaMemcpyAsync(pdfX, c->probePdfX.p, 4 * n, cudaMemcpyDeviceToHost, c->stream));
+    if (cdfX) CUDA_OK(cudaMemcpyAsync(cdfX, c->probeCdfX.p, 4 * n, cudaMemcpyDeviceToHost, c->stream));
+    if (pdfY) CUDA_OK(cudaMemcpyAsync(pdfY, c->probePdfY.p, 4 * (size_t)c->probeH, cudaMemcpyDeviceToHost, c->stream));
+    if (cdfY) CUDA_OK(cudaMemcpyAsync(cdfY, c->probeCdfY.p, 4 * (size_t)c->probeH, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
     API_END
 }
 

@@ -79,7 +79,7 @@ struct FrameParams {               // shared by every pass of a frame
     Probe probe;                   // device pointers
     const float* cdfXCoarse;       // every 32nd entry of each cdfValuesX row (nullptr: plain binary search)
     float tmin, tmax;
-    int maxDepth, shadowMode, display, accumMode, writeAovs, russianRoulette;
+    int maxDepth, shadowMode, display, accumMode, writeAovs, russianRoulette, misOnMiss;
     float exposure;
     int tileRank, tileCount;
     float4* accum;  uint32_t* frame;  float4* normal;  float4* albedo;  float4* color;
@@ -93,6 +93,7 @@ struct PathPool {                  // SoA path state, indexed by sample slot
     float4* indirect;              // radiance added at depth >= 1, in bounce order
     float4* alpha;                 // prd.alpha
     float4* pending;               // NEE contribution awaiting its shadow ray
+    float*  bsdfPdf;               // only with mis_on_miss: pdf of the BSDF sample that produced the current segment
     float4* aovNormal;             // only with write_aovs
     float4* aovAlbedo;
 };
@@ -146,6 +147,7 @@ void launchFinalize(const FrameParams& F, const PassParams& P, const float4* sum
                     const float4* sumNormal, const float4* sumAlbedo, cudaStream_t stream);
 void launchResolveSum(const FrameParams& F, int nPasses, cudaStream_t stream);
 void launchProbeCoarse(const float* cdfX, int W, int H, float* coarse, cudaStream_t stream);
+void launchProbeCdf(const float4* data, int W, int H, float* pdfX, float* cdfX, float* pdfY, float* cdfY, float* rowTotal, cudaStream_t stream);
 void launchTonemapSqrt(int w, int h, const float4* in, uint32_t* out, cudaStream_t stream);
 void launchPrimaryRays(const FrameParams& F, const PassParams& P, float4* rayO, float4* rayD, cudaStream_t stream);
 void launchResolvePrimary(const SceneDev& scene, const float4* hit, unsigned n, const float4* rayO, int32_t* prim, int32_t* mesh,

@@ -134,6 +134,17 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
             const float3 org = f3(o4.x, o4.y, o4.z), dir = f3(d4.x, d4.y, d4.z);
             if (triSlot < 0) {
                 flags |= PF_DONE;                                                 // __miss__radiance, :251-280
+                if (F.misOnMiss && (flags & PF_SECONDARY)) {                      // opt-in extension (:257-267), same rule as oracle/render_core.h
+                    const float skyPdf = probePdf(F.probe, dir);
+                    const float bp = pool.bsdfPdf[slot];
+                    const float weight = 0.5f * bp / (0.5f * bp + 0.5f * skyPdf);
+                    const float4 sky = probeEval(F.probe, probeDirToUV(dir));
+                    const float4 thr4 = pool.thr[slot];
+                    const float3 add = weight * f3(sky.x, sky.y, sky.z) * f3(thr4.x, thr4.y, thr4.z);
+                    float4 acc = pool.indirect[slot];
+                    acc.x += add.x;  acc.y += add.y;  acc.z += add.z;
+                    pool.indirect[slot] = acc;
+                }
             } else {
                 const float4 ta = __ldg(S.tris + 3 * (size_t)triSlot), tb = __ldg(S.tris + 3 * (size_t)triSlot + 1),
                              tc = __ldg(S.tris + 3 * (size_t)triSlot + 2);
@@ -217,8 +228,9 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                                 }
                                 pool.thr[slot] = make_float4(T.x, T.y, T.z, rayEta);
                                 pool.rng[slot] = make_uint2(rng.s1, rng.s2);
+                                if (F.misOnMiss) pool.bsdfPdf[slot] = pdf;
                                 const int nd = depth + 1;
-                                if (rrKill || (nd >= F.maxDepth && (flags & PF_ALPHA_ONE))) flags |= PF_DONE;   // roulette, or the next segment could only be dropped
+                                if (rrKill || (nd >= F.maxDepth && (flags & PF_ALPHA_ONE) && !F.misOnMiss)) flags |= PF_DONE;   // roulette, or the next segment could only be dropped
                                 else { wantRay = true;  ro = make_float4(Pp.x, Pp.y, Pp.z, o4.w);  rd = make_float4(bsdfDir.x, bsdfDir.y, bsdfDir.z, 0.f); }
                                 depth = nd;
                             }
@@ -391,6 +403,59 @@ __global__ void probeCoarseKernel(const float* __restrict__ cdfX, int W, int H, 
 void launchProbeCoarse(const float* cdfX, int W, int H, float* coarse, cudaStream_t s) {
     const int n = ((W + 31) >> 5) * H;
     if (n > 0) probeCoarseKernel<<<(n + 255) / 256, 256, 0, s>>>(cdfX, W, H, coarse);
+}
+
+// ---- ProbeData::BuildCDF on the device (sv4/Probe.h:29-77) ---------------------------------------------------
+// The reference accumulates each row's luminance SEQUENTIALLY in fp32, and that order defines the bits of the tables.  One warp
+// owns one row and keeps that order: 32 texels are loaded coalesced, then the running total walks over the 32 lanes' weights in
+// lane order (every lane carries the same total; lane k keeps the value after its own weight).  Rows are independent, so the
+// image is processed H rows at a time; the column pass is the same walk over the H row totals by a single warp.
+__global__ void probeRowCdfKernel(const float4* __restrict__ data, int W, int H, float* __restrict__ pdfX, float* __restrict__ cdfX,
+                                  float* __restrict__ rowTotal) {
+    const int row = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+    if (row >= H) return;
+    const float4* src = data + (size_t)row * W;
+    float* p = pdfX + (size_t)row * W;
+    float* c = cdfX + (size_t)row * W;
+    float total = 0.0f;                                                    // totalWeightX, Probe.h:41
+    for (int base = 0; base < W; base += 32) {
+        const int i = base + lane, n = min(32, W - base);
+        float wgt = 0.0f;
+        if (i < W) { const float4 t = src[i];  wgt = t.x * 0.3f + t.y * 0.6f + t.z * 0.1f; }           // Luminance, maths.h:165-168 (no FMA: -fmad=false)
+        float mine = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+            const float v = __shfl_sync(0xffffffffu, wgt, k);
+            if (k < n) total = total + v;                                  // :47
+            if (k == lane) mine = total;
+        }
+        if (i < W) { p[i] = wgt;  c[i] = mine; }                           // :49-50
+    }
+    const float inv = 1.0f / total;                                        // :53
+    for (int i = lane; i < W; i += 32) { p[i] = p[i] * inv;  c[i] = c[i] * inv; }     // :56-60 (each lane re-reads what it wrote)
+    if (lane == 0) rowTotal[row] = total;
+}
+__global__ void probeColCdfKernel(const float* __restrict__ rowTotal, int H, float* __restrict__ pdfY, float* __restrict__ cdfY) {
+    const int lane = threadIdx.x & 31;
+    float total = 0.0f;                                                    // totalWeightY, Probe.h:36
+    for (int base = 0; base < H; base += 32) {
+        const int j = base + lane, n = min(32, H - base);
+        const float wgt = j < H ? rowTotal[j] : 0.0f;
+        float mine = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+            const float v = __shfl_sync(0xffffffffu, wgt, k);
+            if (k < n) total = total + v;                                  // :63
+            if (k == lane) mine = total;
+        }
+        if (j < H) { pdfY[j] = wgt;  cdfY[j] = mine; }                     // :65-66
+    }
+    for (int j = lane; j < H; j += 32) { cdfY[j] = cdfY[j] / total;  pdfY[j] = pdfY[j] / total; }   // :70-74
+}
+void launchProbeCdf(const float4* data, int W, int H, float* pdfX, float* cdfX, float* pdfY, float* cdfY, float* rowTotal, cudaStream_t s) {
+    if (W <= 0 || H <= 0) return;
+    probeRowCdfKernel<<<(H + 3) / 4, 128, 0, s>>>(data, W, H, pdfX, cdfX, rowTotal);
+    probeColCdfKernel<<<1, 32, 0, s>>>(rowTotal, H, pdfY, cdfY);
 }
 
 // ---- launchers ---------------------------------------------------------------------------------------------

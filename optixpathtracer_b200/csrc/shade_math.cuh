@@ -260,6 +260,16 @@ DEV float4 probeEval(const Probe& P, float2 uv) {                               
     const int py = clampi((int)(uv.y * P.height), 0, P.height - 1);
     return __ldg(reinterpret_cast<const float4*>(P.data) + (py * P.width + px));
 }
+DEV float probePdf(const Probe& P, float3 d) {                                       // :69-93
+    const float2 uv = probeDirToUV(d);
+    const int col = clampi((int)(uv.x * P.width), 0, P.width - 1);
+    const int row = clampi((int)(uv.y * P.height), 0, P.height - 1);
+    float pdf = __ldg(P.pdfValuesX + (row * P.width + col)) * __ldg(P.pdfValuesY + row);
+    const float sinTheta = sinf(uv.y * kPi);
+    if (fabsf(sinTheta) < 0.0001f) pdf = 0.0f;
+    else pdf *= (float)P.width * (float)P.height / (2.0f * kPi * kPi * sinTheta);
+    return pdf;
+}
 DEV int lowerBound(const float* __restrict__ a, int lower, int upper, float value) {   // :119-136
     while (lower < upper) {
         const int mid = lower + (upper - lower) / 2;

@@ -113,6 +113,24 @@ class SampleRenderer:
                                             _ptr(probe.cdfX), _ptr(probe.pdfY), _ptr(probe.cdfY), _ptr(off),
                                             C.byref(self.launchParams)))
 
+    def setProbeImage(self, data, offset=(0.0, 0.0, 0.0)):
+        """loadProbe/loadColor + BuildCDF + setProbe with the CDF tables built on the GPU (bit-identical to
+        ProbeData.BuildCDF, sv4/Probe.h:29-77); `data` is (H, W, 4) float32."""
+        data = np.ascontiguousarray(data, np.float32)
+        if data.ndim != 3 or data.shape[2] != 4:
+            raise RuntimeError("Probe Data is not valid")
+        off = np.asarray(offset, np.float32)
+        _lib.check(self._L.b200pt_set_probe_image(self._h, data.shape[1], data.shape[0], _ptr(data), _ptr(off),
+                                                  C.byref(self.launchParams)))
+
+    def downloadProbe(self):
+        """(pdfX, cdfX, pdfY, cdfY) of the current probe, read back from the device."""
+        w, h = self.launchParams.probe.width, self.launchParams.probe.height
+        pdfX, cdfX = np.empty((h, w), np.float32), np.empty((h, w), np.float32)
+        pdfY, cdfY = np.empty(h, np.float32), np.empty(h, np.float32)
+        _lib.check(self._L.b200pt_download_probe(self._h, _ptr(pdfX), _ptr(cdfX), _ptr(pdfY), _ptr(cdfY)))
+        return pdfX, cdfX, pdfY, cdfY
+
     # ---- extras behind the same C-ABI -----------------------------------------------------------
     def downloadAccum(self):
         w, h = self.launchParams.frame.size.x, self.launchParams.frame.size.y

@@ -149,4 +149,22 @@ void oracle_camera_uvw(const float* eye, const float* lookat, const float* up, f
 
 }  // extern "C"
 
+#ifdef ORACLE_REF
+// The reference's HDR reader: loadProbe calls stbi_loadf(file, &w, &h, &channels, 4) (sv4/main.cpp:154-165) from the stb_image.h
+// vendored in the reference tree (support/stb/), compiled here in place.  Used only by tests/golden/make_golden.py to mint the
+// fixture that pins the product's own Radiance-HDR readers (host/Probe.cpp, optixpathtracer_b200/probe.py).
+#define STB_IMAGE_IMPLEMENTATION
+#define STBI_ONLY_HDR
+#include <support/stb/stb_image.h>
+extern "C" int oracle_ref_load_hdr(const char* path, int* w, int* h, float* out_rgba, size_t capacity_floats) {
+    int ch = 0;
+    float* px = stbi_loadf(path, w, h, &ch, 4);
+    if (!px) return -1;
+    const size_t n = (size_t)*w * *h * 4;
+    if (out_rgba && capacity_floats >= n) memcpy(out_rgba, px, n * sizeof(float));
+    stbi_image_free(px);
+    return 0;
+}
+#endif
+
 #include "oracle_scene_api.inl"

@@ -65,8 +65,12 @@ static inline bool oracleRaygen(const OTraceCtx& C, const LaunchParams& params, 
             C.counters->radianceRays++;
             if (oracleClosest(*C.scene, ray_origin, ray_direction, cfg.tmin, cfg.tmax, hit))
                 oracleClosestHitProgram(C, hit, ray_origin, ray_direction, &prd);
-            else
-                oracleMissProgram(&prd);
+            else {
+                oracleMissProgram(C, ray_direction, &prd);
+                // the reference's loop drops a DONE segment's radiance (:495); the opt-in miss term is kept, also for the last
+                // segment (depth == max_depth), which is the MIS partner of the NEE sample taken at depth max_depth - 1
+                if (cfg.mis_on_miss && prd.depth > 0) indirectLight += prd.radiance;
+            }
             if (prd.depth == 0.f) { normal += prd.normal;  albedo += prd.albedo; }
             if ((prd.stateFlags & RAY_STATE_FLAGS_DONE) || prd.depth >= cfg.max_depth) break;   // :495
             if (prd.depth == 0) directLight += prd.radiance;

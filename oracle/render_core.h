@@ -102,7 +102,15 @@ static inline float3 oracleSampleLights(const OTraceCtx& C, bool occludedWanted,
 }
 
 // sv4/deviceProgram.cu:251-280
-static inline void oracleMissProgram(RadiancePRD* prd) {
+static inline void oracleMissProgram(const OTraceCtx& C, const float3& ray_dir, RadiancePRD* prd) {
+    // Opt-in extension (cfg.mis_on_miss): the reference's commented-out block :257-267, with cbsdf = csky = 0.5 as in SampleLights
+    // (its own `kBsdfSamples / N` is an integer division).  Only secondary rays: the primary ray's miss is the backplate.
+    if (C.cfg->mis_on_miss && (prd->stateFlags & RAY_STATE_FLAGS_SECONDARY_RAY) != 0) {
+        const float skyPdf = ProbePdf(C.scene->probe, ray_dir);
+        const float cbsdf = 0.5f, csky = 0.5f;
+        const float weight = cbsdf * prd->bsdfPdf / (cbsdf * prd->bsdfPdf + csky * skyPdf);
+        prd->radiance += weight * make_float3(ProbeEval(C.scene->probe, ProbeDirToUV(ray_dir))) * prd->pathThroughput;
+    }
     prd->albedo = make_float3(0.f);
     prd->normal = make_float3(0.f);
     prd->stateFlags |= RAY_STATE_FLAGS_DONE;

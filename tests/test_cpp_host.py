@@ -93,3 +93,54 @@ def test_cpp_renderer_equals_python_mirror(exe, tmp_path):
     want = r.downloadPixels().view(np.uint8).reshape(64, 96, 4)[..., :3]
     r.close()
     assert np.array_equal(got, want)
+
+
+# ---- Radiance .hdr readers (loadProbe, sv4/main.cpp:154-165) against the reference's own stb_image (tests/golden/hdr.npz) ----
+HDR_CASES = ["rle", "flat", "narrow", "wide_rle"]
+
+
+@pytest.mark.parametrize("case", HDR_CASES)
+def test_hdr_readers_match_reference_stb(exe, tmp_path, case):
+    from conftest import golden
+    from optixpathtracer_b200.probe import read_hdr
+    g = golden("hdr")
+    blob, want = g[case + "_file"].tobytes(), g[case + "_pixels"]
+    got = read_hdr(blob)                                                              # Python mirror
+    assert got.shape == want.shape and np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    path = os.path.join(str(tmp_path), case + ".hdr")
+    open(path, "wb").write(blob)
+    dump = os.path.join(str(tmp_path), "probe.bin")
+    subprocess.check_call([exe, "--boxes", "1", "--hdr", path, "--dump-probe", dump, "--no-render"])   # C++ host (host/Probe.cpp)
+    raw = open(dump, "rb").read()
+    w, h = struct.unpack_from("ii", raw, 0)
+    px = np.frombuffer(raw, np.float32, w * h * 4, 8).reshape(h, w, 4)
+    assert (h, w, 4) == want.shape and np.array_equal(px.view(np.uint32), want.view(np.uint32))
+
+
+def test_hdr_reader_rejects_bad_files(exe, tmp_path):
+    from optixpathtracer_b200.probe import read_hdr, write_hdr
+    good = write_hdr(None, np.full((4, 16, 3), 0.5, np.float32))
+    for blob in (b"P6\n1 1\n255\n...", good.replace(b"FORMAT=32-bit_rle_rgbe", b"FORMAT=32-bit_rle_xyze"),
+                 good.replace(b"-Y 4 +X 16", b"+Y 4 +X 16"), good[:-5]):
+        with pytest.raises(RuntimeError):
+            read_hdr(blob)
+        path = os.path.join(str(tmp_path), "bad.hdr")
+        open(path, "wb").write(blob)
+        p = subprocess.run([exe, "--boxes", "1", "--hdr", path, "--no-render"], capture_output=True, text=True)
+        assert p.returncode == 1 and "Could not load HDR probe" in p.stderr
+    p = subprocess.run([exe, "--boxes", "1", "--hdr", "/nonexistent/sky.hdr", "--no-render"], capture_output=True, text=True)
+    assert p.returncode == 1 and "Could not load HDR probe" in p.stderr
+
+
+@pytest.mark.gpu
+def test_cpp_hdr_probe_with_device_cdf_equals_host_cdf(exe, tmp_path):
+    """--gpu-cdf (SampleRenderer::setProbeImage, tables built on the GPU) renders the same pixels as loadProbe + setProbe."""
+    from optixpathtracer_b200.probe import analytic_sky, write_hdr
+    path = os.path.join(str(tmp_path), "sky.hdr")
+    write_hdr(path, analytic_sky(256, 128).data)
+    outs = []
+    for extra in ([], ["--gpu-cdf"]):
+        out = os.path.join(str(tmp_path), "o%d.ppm" % len(outs))
+        subprocess.check_call([exe, "--boxes", "12", "--preset", "orig", "--size", "96x64", "--frames", "2", "--hdr", path, "--out", out] + extra)
+        outs.append(open(out, "rb").read())
+    assert outs[0] == outs[1] and len(outs[0]) > 96 * 64 * 3

@@ -89,3 +89,48 @@ def test_russian_roulette_is_unbiased_in_the_oracle(port):
         means.append((acc[..., :3].mean(), cnt["radiance_rays"]))
     assert means[1][1] < means[0][1]
     assert abs(means[1][0] - means[0][0]) < 0.02 * means[0][0]
+
+
+def test_mis_on_miss_completes_the_estimator(port):
+    """cfg.mis_on_miss (opt-in; the reference's commented-out block, sv4/deviceProgram.cu:257-267).  An open floor under a constant
+    sky has a closed form: L = integral of f * cos over the upper hemisphere.  NEE alone carries only its MIS weight (the reference's
+    live path, biased dark); with the miss term the two weights sum to one and the estimate matches a quadrature of BSDFEval."""
+    import numpy as np
+    from optixpathtracer_b200 import Material, Model, TriangleMesh, Camera, host_params, loadColor, preset
+    mat = Material(color=(0.7, 0.6, 0.5), emission=(0, 0, 0), metallic=0.0, transmission=0.0, subsurface=0.0, specular=0.5,
+                   roughness=0.1, clearcoat=0.0, specularTint=0.0, eta=1.5)
+    mesh = TriangleMesh()
+    mesh.vertex = np.array([[-500, 0, -500], [500, 0, -500], [500, 0, 500], [-500, 0, 500]], np.float32)
+    mesh.index = np.array([[0, 2, 1], [0, 3, 2]], np.uint32)                 # normal +y
+    mesh.material = mat
+    model = Model()
+    model.meshes.append(mesh)
+    # view along the normal and a narrow lobe: BSDF samples below the horizon (which end the path with pdf 0 and, as in the
+    # reference, take that vertex's NEE term with them, :679-682) stay under 1 %
+    eye = np.array([0.0, 5.0, 0.0])
+    cam = Camera(tuple(eye), (0.0, 0.0, 0.0), (0.0, 0.0, 1.0), 0.5, 1.0)      # half a degree: one view direction for all pixels
+    sc = port.scene(model, loadColor((1.0, 1.0, 1.0), 512, 256), brute_force=True)
+    means = {}
+    for mis in (0, 1):
+        cfg = preset("orig", uniform_spl=512, mis_on_miss=mis)
+        acc, _, _, _ = sc.render(host_params(16, 16, cam, samples_per_launch=512), cfg)
+        means[mis] = acc[..., :3].reshape(-1, 3).mean(0)
+    # quadrature on a theta-phi grid (fine in theta: the specular lobe is a few degrees wide)
+    n_th, n_phi = 4000, 64
+    th = (np.arange(n_th) + 0.5) / n_th * (np.pi / 2)
+    phi = (np.arange(n_phi) + 0.5) / n_phi * 2 * np.pi
+    th, phi = np.meshgrid(th, phi, indexing="ij")
+    mu, s = np.cos(th), np.sin(th)
+    L = np.stack([s * np.cos(phi), mu, s * np.sin(phi)], -1).reshape(-1, 3).astype(np.float32)
+    n = len(L)
+    V = np.tile((eye / np.linalg.norm(eye)).astype(np.float32), (n, 1))
+    N = np.tile(np.array([0, 1, 0], np.float32), (n, 1))
+    f, _ = port.bsdf_eval([mat] * n, np.tile(np.array(mat_color(mat), np.float32), (n, 1)), np.ones(n, np.float32),
+                          np.full(n, 1.5, np.float32), N, V, L)
+    want = (f * (mu * s).reshape(-1, 1)).mean(0) * (np.pi / 2) * (2 * np.pi)
+    assert np.all(np.abs(means[1] - want) < 0.02 * want), (means, want)
+    assert np.all(means[0] < 0.9 * want)                                      # NEE alone misses a visible share of the energy
+
+
+def mat_color(m):
+    return (m.color.x, m.color.y, m.color.z)
