@@ -6,7 +6,7 @@
 //
 //   b200pt_headless [--obj file.obj | --boxes N] [--preset sv4_fov|sv4_uniform|sv3_uniform|orig] [--size WxH] [--frames N] [--spl N]
 //                   [--camera sponza|lost_empire|san_miguel|cornell] [--sky r,g,b] [--out image.ppm] [--log fps.tsv]
-//                   [--hdr probe.hdr] [--gpu-cdf] [--dump-model file.bin] [--dump-probe file.bin] [--no-render]
+//                   [--hdr probe.hdr] [--gpu-cdf] [--whitted] [--dump-model file.bin] [--dump-probe file.bin] [--no-render]
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -67,7 +67,7 @@ int main(int argc, char** argv) {
     std::string obj, preset = "sv4_fov", cam = "cornell", out, log, dump, hdr, dumpProbe;
     int W = 1280, H = 720, frames = 16, boxes = 64, spl = 1;
     float3 sky{1.f, 1.f, 1.f};
-    bool noRender = false, gpuCdf = false;
+    bool noRender = false, gpuCdf = false, whitted = false;
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
         auto next = [&]() -> const char* { if (i + 1 >= argc) { fprintf(stderr, "missing value for %s\n", a.c_str());  exit(2); } return argv[++i]; };
@@ -84,6 +84,7 @@ int main(int argc, char** argv) {
         else if (a == "--dump-model") dump = next();
         else if (a == "--hdr") hdr = next();
         else if (a == "--gpu-cdf") gpuCdf = true;
+        else if (a == "--whitted") whitted = true;
         else if (a == "--dump-probe") dumpProbe = next();
         else if (a == "--no-render") noRender = true;
         else { fprintf(stderr, "unknown argument %s\n", a.c_str());  return 2; }
@@ -125,6 +126,7 @@ int main(int argc, char** argv) {
                                                      (unsigned)(H * (0.5f + 0.35f * std::sin(3.f * ph + 0.5f)))};
             if (f == 0) sample.launchParams.frame.subframe_index = 0;                                       // camera_changed starts true, :319-320
             sample.setCamera(camera);                                                                       // handleCameraUpdate, :328
+            if (whitted) sample.renderWhitted(camera);  else                                                // 04HelloRaytracing frame
             sample.render();                                                                                // :335
             const b200pt_counters c = sample.counters();
             samples += c.samples;  rays += c.radiance_rays + c.shadow_rays;

@@ -91,6 +91,18 @@ int b200pt_set_probe(b200pt_ctx* ctx, int width, int height, const float* data_r
                      const float* pdfX, const float* cdfX, const float* pdfY, const float* cdfY,
                      const float* offset_xyz, struct LaunchParams* params /* probe pointers written */);
 
+/* ---- second integrator on the same traversal kernels: 04HelloRaytracing (deviceProgram.cu:66-243) -----
+ * One primary ray per pixel centre (tmin 0, tmax 1e20), interpolated shading normal (geometric normal when the mesh has none),
+ * diffuse colour x texture, one shadow ray to a point light (origin + 1e-3 Ng, unnormalised direction, t in (1e-3, 1 - 1e-3),
+ * first hit terminates, no culling), colour = (0.1 + (0.2 + 0.8 vis) (0.1 + 0.8 |d.Ns|)) * diffuse, RGBA8 = int(255.99 c).
+ * Camera fields as SampleRenderer::setCamera fills them (04HelloRaytracing/SampleRenderer.cpp:125-138). */
+typedef struct b200pt_whitted_params {
+    float position[3], direction[3], horizontal[3], vertical[3];
+    float light_pos[3];                 /* the reference hard-codes (-907.108, 2205.875, -400.0267), deviceProgram.cu:125 */
+} b200pt_whitted_params;
+int b200pt_render_whitted(b200pt_ctx* ctx, const b200pt_whitted_params* params,
+                          uint32_t* device_color_buffer /* NULL = the context's frame buffer (b200pt_download_pixels) */);
+
 /* loadProbe/loadColor + ProbeData::BuildCDF + setProbe in one call (sv4/main.cpp:154-180, sv4/Probe.h:29-77,
  * sv4/SimplePathtracer.cpp:295-311): uploads width*height float4 texels and builds pdfValuesX/cdfValuesX/pdfValuesY/cdfValuesY ON THE
  * DEVICE, bit-identical to the host's sequential fp32 BuildCDF (one warp per row keeps the accumulation order). */

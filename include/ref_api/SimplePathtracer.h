@@ -6,6 +6,7 @@
 // No OptiX, no GL: render(CUDAOutputBuffer&) becomes render(uint32_t* deviceFrameBuffer).
 #pragma once
 #include <cstdint>
+#include <cmath>
 #include <stdexcept>
 #include <string>
 #include "../b200pt.h"
@@ -87,6 +88,22 @@ public:
         if (!probe.data || probe.width <= 0 || probe.height <= 0) throw std::runtime_error("Probe Data is not valid");
         const float off[3] = {probe.offset.x, probe.offset.y, probe.offset.z};
         if (b200pt_set_probe_image(ctx, probe.width, probe.height, reinterpret_cast<const float*>(probe.data), off, &launchParams) != 0) fail();
+    }
+    // Second integrator on the same traversal kernels: the 04HelloRaytracing frame (04HelloRaytracing/deviceProgram.cu:66-243) into the
+    // frame buffer; camera fields as 04HelloRaytracing/SampleRenderer.cpp:125-138 fills them.
+    void renderWhitted(const sutil::Camera& camera, const float3& lightPos = float3{-907.108f, 2205.875f, -400.0267f}) {
+        auto sub = [](const float3& a, const float3& b) { return float3{a.x - b.x, a.y - b.y, a.z - b.z}; };
+        auto cross = [](const float3& a, const float3& b) { return float3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; };
+        auto scaled = [](const float3& a, float s) { return float3{a.x * s, a.y * s, a.z * s}; };
+        auto normalized = [&](const float3& a) { return scaled(a, 1.0f / std::sqrt(a.x * a.x + a.y * a.y + a.z * a.z)); };
+        const float3 position = camera.eye(), direction = normalized(sub(camera.lookat(), camera.eye()));
+        const float cosFovy = 0.66f, aspect = launchParams.frame.size.x / float(launchParams.frame.size.y);
+        const float3 horizontal = scaled(normalized(cross(direction, camera.up())), cosFovy * aspect);
+        const float3 vertical = scaled(normalized(cross(horizontal, direction)), cosFovy);
+        b200pt_whitted_params wp = {{position.x, position.y, position.z}, {direction.x, direction.y, direction.z},
+                                    {horizontal.x, horizontal.y, horizontal.z}, {vertical.x, vertical.y, vertical.z},
+                                    {lightPos.x, lightPos.y, lightPos.z}};
+        if (b200pt_render_whitted(ctx, &wp, nullptr) != 0) fail();
     }
     // extras behind the same C-ABI
     void downloadAccum(float* h_rgba) { if (b200pt_download_accum(ctx, h_rgba) != 0) fail(); }

@@ -16,16 +16,16 @@ template <typename T> struct DevBuf {
     void release() { if (p) cudaFree(p);  p = nullptr;  n = 0; }
 };
 
-struct HostMesh { size_t firstVertex, nVertices, firstTri, nTris;  bool hasTexcoord;  int textureID;  Material material{Material::NoInit{}}; };
+struct HostMesh { size_t firstVertex, nVertices, firstTri, nTris;  bool hasTexcoord, hasNormal;  int textureID;  Material material{Material::NoInit{}}; };
 struct HostTexture { size_t offset;  int w, h; };
 
 struct b200pt_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     // --- scene staging (host) and device copies
-    std::vector<float3> hVertices;  std::vector<float2> hTexcoords;  std::vector<uint3> hIndices;  std::vector<unsigned> hTriMesh;
+    std::vector<float3> hVertices, hNormals;  std::vector<float2> hTexcoords;  std::vector<uint3> hIndices;  std::vector<unsigned> hTriMesh;
     std::vector<HostMesh> hMeshes;  std::vector<HostTexture> hTextures;  std::vector<uint32_t> hTexels;
-    DevBuf<float3> dVertices;  DevBuf<float2> dTexcoords;  DevBuf<uint3> dIndices;  DevBuf<unsigned> dTriMesh;
+    DevBuf<float3> dVertices, dNormals;  DevBuf<float2> dTexcoords;  DevBuf<uint3> dIndices;  DevBuf<unsigned> dTriMesh;
     DevBuf<MeshInfo> dMeshes;  DevBuf<uint32_t> dTexels;
     BvhBuildResult bvh;  bool built = false;  bool hasCatcher = false;
     // --- frame
@@ -89,7 +89,7 @@ void b200pt_destroy(b200pt_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     bvhFree(c->bvh);
-    c->dVertices.release();  c->dTexcoords.release();  c->dIndices.release();  c->dTriMesh.release();  c->dMeshes.release();  c->dTexels.release();
+    c->dVertices.release();  c->dNormals.release();  c->dTexcoords.release();  c->dIndices.release();  c->dTriMesh.release();  c->dMeshes.release();  c->dTexels.release();
     c->frameBuf.release();  c->accumBuf.release();  c->normalBuf.release();  c->albedoBuf.release();  c->colorBuf.release();
     c->probeData.release();  c->probePdfX.release();  c->probeCdfX.release();  c->probePdfY.release();  c->probeCdfY.release();  c->probeCoarse.release();  c->probeRowTotal.release();
     c->rng.release();  c->thr.release();  c->direct.release();  c->indirect.release();  c->alpha.release();  c->pending.release();
@@ -112,13 +112,17 @@ int b200pt_add_texture(b200pt_ctx* c, const uint32_t* rgba8, int w, int h) {
 
 int b200pt_add_mesh(b200pt_ctx* c, const float* vtx, size_t nv, const float* normal, const float* texcoord, const uint32_t* idx,
                     size_t ntri, const Material* material, int textureID) {
-    (void)normal;                                             // uploaded by the reference, never read by its shaders
     if (!c || !material || (nv && !vtx) || (ntri && !idx)) return fail("b200pt_add_mesh: bad argument");
     if (textureID >= (int)c->hTextures.size()) return fail("b200pt_add_mesh: texture id out of range");
     for (size_t i = 0; i < 3 * ntri; ++i) if (idx[i] >= nv) return fail("b200pt_add_mesh: vertex index out of range");
     HostMesh m;
     m.firstVertex = c->hVertices.size();  m.nVertices = nv;  m.firstTri = c->hIndices.size();  m.nTris = ntri;
-    m.hasTexcoord = texcoord != nullptr;  m.textureID = textureID;  m.material = *material;
+    m.hasTexcoord = texcoord != nullptr;  m.hasNormal = normal != nullptr;  m.textureID = textureID;  m.material = *material;
+    if (normal) {                                             // never read by the path tracer's shaders; the Whitted integrator interpolates them
+        const float3* n3 = reinterpret_cast<const float3*>(normal);
+        c->hNormals.resize(m.firstVertex, make_float3(0.f, 0.f, 0.f));
+        c->hNormals.insert(c->hNormals.end(), n3, n3 + nv);
+    }
     const float3* v3 = reinterpret_cast<const float3*>(vtx);
     c->hVertices.insert(c->hVertices.end(), v3, v3 + nv);
     if (texcoord) { const float2* t2 = reinterpret_cast<const float2*>(texcoord);  c->hTexcoords.insert(c->hTexcoords.end(), t2, t2 + nv); }
@@ -143,13 +147,15 @@ int b200pt_build_accel(b200pt_ctx* c, uint64_t* handle_out) {
         MeshInfo& d = infos[i];
         memset(&d, 0, sizeof(d));
         d.material = m.material;  d.firstTri = (unsigned)m.firstTri;  d.firstVertex = (unsigned)m.firstVertex;
-        d.textureID = m.textureID;  d.hasTexcoord = m.hasTexcoord ? 1 : 0;
+        d.textureID = m.textureID;  d.hasTexcoord = m.hasTexcoord ? 1 : 0;  d.hasNormal = m.hasNormal ? 1 : 0;
         if (m.textureID >= 0) { const HostTexture& t = c->hTextures[m.textureID];  d.texOffset = (unsigned)t.offset;  d.texW = t.w;  d.texH = t.h; }
     }
     auto up = [&](auto& buf, const auto& vec) {
         buf.ensure(std::max<size_t>(vec.size(), 1));
         if (!vec.empty()) CUDA_OK(cudaMemcpyAsync(buf.p, vec.data(), vec.size() * sizeof(vec[0]), cudaMemcpyHostToDevice, c->stream));
     };
+    if (!c->hNormals.empty()) c->hNormals.resize(c->hVertices.size(), make_float3(0.f, 0.f, 0.f));
+    up(c->dNormals, c->hNormals);
     up(c->dVertices, c->hVertices);  up(c->dTexcoords, c->hTexcoords);  up(c->dIndices, c->hIndices);  up(c->dTriMesh, c->hTriMesh);
     up(c->dMeshes, infos);  up(c->dTexels, c->hTexels);
     bvhFree(c->bvh);
@@ -168,6 +174,7 @@ static SceneDev sceneOf(b200pt_ctx* c) {
     S.nodes = (const uint4*)c->bvh.nodes;  S.rootLink = c->bvh.rootLink;
     for (int a = 0; a < 3; ++a) { S.gridLo[a] = c->bvh.gridLo[a];  S.gridScale[a] = c->bvh.gridScale[a]; }
     S.tris = c->bvh.tris;  S.meshes = c->dMeshes.p;  S.indices = c->dIndices.p;
+    S.vertices = c->dVertices.p;  S.normals = c->dNormals.p;
     S.texcoords = c->dTexcoords.p;  S.texels = c->dTexels.p;  S.nTris = c->bvh.nTris;  S.nNodes = c->bvh.nNodes;
     return S;
 }

@@ -285,6 +285,50 @@ int b200pt_set_probe(b200pt_ctx* c, int w, int h, const float* data, const float
     API_END
 }
 
+// Second integrator on the same traversal kernels: the Whitted-style frame of 04HelloRaytracing (deviceProgram.cu:66-243):
+// raygen -> traceKernel (closest, tmin 0, tmax 1e20) -> whittedShade -> traceKernel (any hit, tmin 1e-3, tmax 1 - 1e-3, no culling)
+// -> finish.  Output: W*H RGBA8 into `deviceColorBuffer`, or the context's frame buffer when NULL.
+int b200pt_render_whitted(b200pt_ctx* c, const b200pt_whitted_params* wp, uint32_t* deviceColorBuffer) {
+    if (!c || !wp) return fail("b200pt_render_whitted: null argument");
+    API_BEGIN
+    CUDA_OK(cudaSetDevice(c->device));
+    if (!c->built) throw std::runtime_error("b200pt_render_whitted: b200pt_build_accel has not been called");
+    if (c->W <= 0 || c->H <= 0) throw std::runtime_error("b200pt_render_whitted: frame buffers not allocated (call b200pt_resize)");
+    const size_t n = (size_t)c->W * c->H;
+    if (n >= ((size_t)1 << 31)) throw std::runtime_error("b200pt_render_whitted: frame too large");
+    ensurePool(c, n, false, false);
+    WhittedParams P;
+    P.W = c->W;  P.H = c->H;
+    P.position = make_float3(wp->position[0], wp->position[1], wp->position[2]);
+    P.direction = make_float3(wp->direction[0], wp->direction[1], wp->direction[2]);
+    P.horizontal = make_float3(wp->horizontal[0], wp->horizontal[1], wp->horizontal[2]);
+    P.vertical = make_float3(wp->vertical[0], wp->vertical[1], wp->vertical[2]);
+    P.lightPos = make_float3(wp->light_pos[0], wp->light_pos[1], wp->light_pos[2]);
+    const SceneDev S = sceneOf(c);
+    cudaStream_t s = c->stream;
+    PathPool pool{c->rng.p, c->thr.p, c->state.p, c->direct.p, c->indirect.p, c->alpha.p, c->pending.p, c->bsdfPdf.p, c->aovN.p, c->aovA.p};
+    Queues Q;
+    for (int i = 0; i < 2; ++i) { Q.rayO[i] = c->rayO[i].p;  Q.rayD[i] = c->rayD[i].p; }
+    Q.hit = c->hit.p;  Q.shO = c->shO.p;  Q.shD = c->shD.p;  Q.counters = c->counters.p;
+    c->countersPending = false;
+    CUDA_OK(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned) * (QC_STRIDE * QC_MAX_LAUNCHES + 8), s));
+    unsigned* c0 = Q.counters;
+    unsigned* c1 = Q.counters + QC_STRIDE;
+    launchWhittedRaygen(P, Q, pool, c0, s);
+    launchTrace(S, Q.rayO[0], Q.rayD[0], Q.hit, c0 + QC_RAYS, Q.shO, Q.shD, c0 + QC_SHADOWS /* 0 */, c0 + QC_HEAD, 0.f, 1e20f, 0, pool, nullptr, s);
+    launchWhittedShade(P, S, pool, Q, c1 + QC_SHADOWS, s);
+    launchTrace(S, Q.rayO[0], Q.rayD[0], Q.hit, c1 + 3 /* always 0 */, Q.shO, Q.shD, c1 + QC_SHADOWS, c1 + QC_HEAD, 1e-3f, 1.f - 1e-3f, 0, pool, nullptr, s);
+    launchWhittedFinish(P, pool, deviceColorBuffer ? deviceColorBuffer : (uint32_t*)c->frameBuf.p, s);
+    CUDA_OK(cudaGetLastError());
+    CUDA_OK(cudaStreamSynchronize(s));
+    std::vector<unsigned> hc(2 * QC_STRIDE);
+    CUDA_OK(cudaMemcpy(hc.data(), c->counters.p, sizeof(unsigned) * hc.size(), cudaMemcpyDeviceToHost));
+    c->last = b200pt_counters{};
+    c->last.samples = n;  c->last.radiance_rays = hc[QC_RAYS];  c->last.shadow_rays = hc[QC_STRIDE + QC_SHADOWS];
+    c->last.kernel_launches = 5;  c->last.n_trace_closest_launches = 1;  c->last.n_trace_any_launches = 1;
+    API_END
+}
+
 // loadProbe/loadColor + BuildCDF + setProbe in one call (sv4/main.cpp:154-180, Probe.h:29-77, SimplePathtracer.cpp:295-311): only the
 // texels cross PCIe; the four tables are built on the device, bit-identical to the host's sequential BuildCDF.
 int b200pt_set_probe_image(b200pt_ctx* c, int w, int h, const float* data, const float* offset, LaunchParams* params) {

@@ -43,7 +43,7 @@ struct MeshInfo {                  // device-side stand-in for the per-mesh SBT 
     int      hasTexcoord;
     unsigned texOffset;            // first texel of the texture in the RGBA8 pool
     int      texW, texH;
-    int      pad;
+    int      hasNormal;            // per-vertex normals uploaded (read by the Whitted integrator only)
 };
 static_assert(sizeof(MeshInfo) == 136, "MeshInfo");
 
@@ -55,6 +55,8 @@ struct SceneDev {                  // everything the kernels need about the scen
     const MeshInfo* meshes;
     const uint3* indices;          // global index buffer, LOCAL vertex ids (per mesh)
     const float2* texcoords;       // global, per vertex (zeros where a mesh has none)
+    const float3* vertices;        // global, per vertex (Whitted integrator: surfPos, :121-124)
+    const float3* normals;         // global, per vertex (zeros where a mesh has none)
     const uint32_t* texels;        // RGBA8 pool
     unsigned nTris, nNodes;
 };
@@ -146,6 +148,10 @@ void launchGather(const FrameParams& F, const PassParams& P, int k0, int k1, con
 void launchFinalize(const FrameParams& F, const PassParams& P, const float4* sumRad, const float4* sumAlpha,
                     const float4* sumNormal, const float4* sumAlbedo, cudaStream_t stream);
 void launchResolveSum(const FrameParams& F, int nPasses, cudaStream_t stream);
+struct WhittedParams { int W, H;  float3 position, direction, horizontal, vertical, lightPos; };
+void launchWhittedRaygen(const WhittedParams& P, const Queues& Q, const PathPool& pool, unsigned* counters, cudaStream_t stream);
+void launchWhittedShade(const WhittedParams& P, const SceneDev& scene, const PathPool& pool, const Queues& Q, unsigned* shadowCounter, cudaStream_t stream);
+void launchWhittedFinish(const WhittedParams& P, const PathPool& pool, uint32_t* colorBuffer, cudaStream_t stream);
 void launchProbeCoarse(const float* cdfX, int W, int H, float* coarse, cudaStream_t stream);
 void launchProbeCdf(const float4* data, int W, int H, float* pdfX, float* cdfX, float* pdfY, float* cdfY, float* rowTotal, cudaStream_t stream);
 void launchTonemapSqrt(int w, int h, const float4* in, uint32_t* out, cudaStream_t stream);

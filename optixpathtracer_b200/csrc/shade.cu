@@ -490,3 +490,94 @@ void launchResolvePrimary(const SceneDev& scene, const float4* hit, unsigned n, 
                           float* t, float* u, float* v, cudaStream_t s) {
     if (n) resolvePrimaryKernel<<<gridFor(n), SHADE_BLOCK, 0, s>>>(scene, hit, n, rayO, prim, mesh, t, u, v);
 }
+
+// ---- Whitted-style integrator (04HelloRaytracing/deviceProgram.cu:66-243) on the same trace kernels ---------------------------
+// raygen (:196-243): one ray through each pixel centre.  Pixel i is ray i and pool slot i.
+__global__ void whittedRaygenKernel(WhittedParams P, float4* __restrict__ rayO, float4* __restrict__ rayD, PathPool pool, unsigned* counters) {
+    const unsigned n = (unsigned)P.W * (unsigned)P.H;
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) counters[QC_RAYS] = n;
+    if (i >= n) return;
+    const int ix = (int)(i % (unsigned)P.W), iy = (int)(i / (unsigned)P.W);
+    const float sx = ((float)ix + .5f) / (float)P.W, sy = ((float)iy + .5f) / (float)P.H;                 // :213-214
+    const float3 dir = normalize3(P.direction + (sx - 0.5f) * P.horizontal + (sy - 0.5f) * P.vertical);    // :217-219
+    rayO[i] = make_float4(P.position.x, P.position.y, P.position.z, __int_as_float((int)i));
+    rayD[i] = make_float4(dir.x, dir.y, dir.z, 0.f);
+    pool.direct[i] = make_float4(0.f, 0.f, 0.f, 0.f);               // lightVisibility (:145): the shadow trace adds `pending` = 1 when unoccluded
+    pool.pending[i] = make_float4(1.f, 1.f, 1.f, 0.f);
+}
+// __closesthit__radiance up to the shadow trace (:66-165); parks diffuseColor and cosDN in pool.thr for the finish kernel
+__global__ void __launch_bounds__(SHADE_BLOCK)
+whittedShadeKernel(WhittedParams P, SceneDev S, PathPool pool, Queues Q, unsigned* shadowCounter) {
+    const unsigned n = (unsigned)P.W * (unsigned)P.H;
+    const unsigned stride = gridDim.x * blockDim.x;
+    for (unsigned base = blockIdx.x * blockDim.x; base < n; base += stride) {
+        const unsigned i = base + threadIdx.x;
+        bool wantShadow = false;
+        float4 so = make_float4(0, 0, 0, 0), sd = so;
+        if (i < n) {
+            const float4 d4 = Q.rayD[0][i], h = Q.hit[i];
+            const int triSlot = __float_as_int(h.w);
+            if (triSlot < 0) pool.thr[i] = make_float4(0.f, 0.f, 0.f, -1.0f);                            // __miss__radiance (:172-175)
+            else {
+                const float4 tc = __ldg(S.tris + 3 * (size_t)triSlot + 2);
+                const unsigned gid = (unsigned)__float_as_int(tc.y);
+                const MeshInfo* M = S.meshes + __float_as_int(tc.z);
+                const unsigned* ip = reinterpret_cast<const unsigned*>(S.indices + gid);
+                const uint3 id = make_uint3(__ldg(ip), __ldg(ip + 1), __ldg(ip + 2));
+                const float u = h.y, v = h.z, w0 = 1.f - u - v;
+                const float3 A = S.vertices[M->firstVertex + id.x], B = S.vertices[M->firstVertex + id.y], C = S.vertices[M->firstVertex + id.z];
+                float3 Ng = cross3(B - A, C - A);                                                       // :85
+                float3 Ns = M->hasNormal ? (w0 * S.normals[M->firstVertex + id.x] + u * S.normals[M->firstVertex + id.y]
+                                            + v * S.normals[M->firstVertex + id.z]) : Ng;               // :86-90
+                const float3 rayDir = f3(d4.x, d4.y, d4.z);
+                if (dot3(rayDir, Ng) > 0.f) Ng = -Ng;                                                   // :97-102
+                Ng = normalize3(Ng);
+                if (dot3(Ng, Ns) < 0.f) Ns = Ns - 2.f * dot3(Ng, Ns) * Ng;
+                Ns = normalize3(Ns);
+                float3 diffuse = M->material.color;                                                     // sbtData.color (:108)
+                if (M->textureID >= 0 && M->hasTexcoord) {                                              // :109-116
+                    const float2 t0 = __ldg(S.texcoords + M->firstVertex + id.x), t1 = __ldg(S.texcoords + M->firstVertex + id.y),
+                                 t2 = __ldg(S.texcoords + M->firstVertex + id.z);
+                    diffuse = diffuse * sampleTexture(S, M, w0 * t0.x + u * t1.x + v * t2.x, w0 * t0.y + u * t1.y + v * t2.y);
+                }
+                const float3 surfPos = w0 * A + u * B + v * C;                                          // :121-124
+                const float3 lightDir = P.lightPos - surfPos;                                           // :125-126
+                const float cosDN = 0.1f + .8f * fabsf(dot3(rayDir, Ns));                               // :158-160
+                pool.thr[i] = make_float4(diffuse.x, diffuse.y, diffuse.z, cosDN);
+                const float3 o = surfPos + 1e-3f * Ng;                                                  // :134
+                wantShadow = true;
+                so = make_float4(o.x, o.y, o.z, __int_as_float((int)i));
+                sd = make_float4(lightDir.x, lightDir.y, lightDir.z, __int_as_float(0));                // target 0: pool.direct
+            }
+        }
+        enqueueRay(wantShadow, so, sd, Q.shO, Q.shD, shadowCounter);
+    }
+}
+// the rest of __closesthit__radiance (:162-163) and the raygen epilogue (:232-242)
+__global__ void whittedFinishKernel(WhittedParams P, PathPool pool, uint32_t* __restrict__ colorBuffer) {
+    const unsigned n = (unsigned)P.W * (unsigned)P.H;
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 t = pool.thr[i];
+    float3 prd = f3(0.f);
+    if (t.w >= 0.f) {
+        const float4 vis4 = pool.direct[i];
+        const float3 vis = f3(vis4.x, vis4.y, vis4.z);
+        prd = (f3(.1f) + (f3(.2f) + .8f * vis) * t.w) * f3(t.x, t.y, t.z);
+    }
+    const int r = (int)(255.99f * prd.x), g = (int)(255.99f * prd.y), b = (int)(255.99f * prd.z);
+    colorBuffer[i] = 0xff000000u | ((unsigned)r << 0) | ((unsigned)g << 8) | ((unsigned)b << 16);
+}
+void launchWhittedRaygen(const WhittedParams& P, const Queues& Q, const PathPool& pool, unsigned* counters, cudaStream_t s) {
+    const unsigned n = (unsigned)P.W * (unsigned)P.H;
+    whittedRaygenKernel<<<gridFor(n), SHADE_BLOCK, 0, s>>>(P, Q.rayO[0], Q.rayD[0], pool, counters);
+}
+void launchWhittedShade(const WhittedParams& P, const SceneDev& scene, const PathPool& pool, const Queues& Q, unsigned* shadowCounter, cudaStream_t s) {
+    whittedShadeKernel<<<kPersistentGrid, SHADE_BLOCK, 0, s>>>(P, scene, pool, Q, shadowCounter);
+}
+void launchWhittedFinish(const WhittedParams& P, const PathPool& pool, uint32_t* colorBuffer, cudaStream_t s) {
+    const unsigned n = (unsigned)P.W * (unsigned)P.H;
+    whittedFinishKernel<<<gridFor(n), SHADE_BLOCK, 0, s>>>(P, pool, colorBuffer);
+}
+

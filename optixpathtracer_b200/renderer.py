@@ -39,6 +39,30 @@ def set_camera(p, camera):
     p.camera.eye = float3(*camera.eye)
 
 
+WHITTED_LIGHT_POS = (-907.108, 2205.875, -400.0267)          # 04HelloRaytracing/deviceProgram.cu:125
+
+
+def whitted_camera(camera, width, height):
+    """04HelloRaytracing/SampleRenderer.cpp:125-138 -> (4, 3) float32: position, direction, horizontal, vertical."""
+    f = np.float32
+
+    def norm(v):
+        v = v.astype(np.float32)
+        d = f(v[0] * v[0] + v[1] * v[1]) + f(v[2] * v[2])
+        return (v * (f(1.0) / np.sqrt(d, dtype=np.float32))).astype(np.float32)
+
+    def cross(a, b):
+        return np.array([a[1] * b[2] - a[2] * b[1], a[2] * b[0] - a[0] * b[2], a[0] * b[1] - a[1] * b[0]], np.float32)
+
+    eye, lookat, up = (np.asarray(v, np.float32) for v in (camera.eye, camera.lookat, camera.up))
+    direction = norm(lookat - eye)
+    cos_fovy = f(0.66)
+    aspect = f(width) / f(height)
+    horizontal = ((cos_fovy * aspect) * norm(cross(direction, up))).astype(np.float32)
+    vertical = (cos_fovy * norm(cross(horizontal, direction))).astype(np.float32)
+    return np.stack([eye, direction, horizontal, vertical]).astype(np.float32)
+
+
 class SampleRenderer:
     def __init__(self, model, device=0, config="sv4_fov"):
         """ctor: uploads every mesh/texture and builds the acceleration structure (LBVH) on the GPU."""
@@ -130,6 +154,13 @@ class SampleRenderer:
         pdfY, cdfY = np.empty(h, np.float32), np.empty(h, np.float32)
         _lib.check(self._L.b200pt_download_probe(self._h, _ptr(pdfX), _ptr(cdfX), _ptr(pdfY), _ptr(cdfY)))
         return pdfX, cdfX, pdfY, cdfY
+
+    def renderWhitted(self, camera, light_pos=WHITTED_LIGHT_POS):
+        """Second integrator on the same traversal kernels: the 04HelloRaytracing frame (deviceProgram.cu:66-243) into the
+        frame buffer (downloadPixels).  Camera set up as 04HelloRaytracing/SampleRenderer.cpp:125-138."""
+        cam = whitted_camera(camera, self.launchParams.frame.size.x, self.launchParams.frame.size.y)
+        buf = np.concatenate([cam.reshape(12), np.asarray(light_pos, np.float32)]).astype(np.float32)
+        _lib.check(self._L.b200pt_render_whitted(self._h, _ptr(buf), None))
 
     # ---- extras behind the same C-ABI -----------------------------------------------------------
     def downloadAccum(self):

@@ -327,3 +327,19 @@ def city_class(target_tris=20_000_000, seed=0x20000000, cell_tris=None):
 
 def by_name(name, **kw):
     return {"cornell": cornell, "sponza": sponza_class, "lost_empire": lost_empire_class, "city": city_class}[name](**kw)
+
+
+def add_smooth_normals(model):
+    """Area-weighted per-vertex normals for every mesh (the Whitted integrator interpolates them, 04HelloRaytracing/
+    deviceProgram.cu:86-90; the path tracer never reads normals).  Returns the model."""
+    for mesh in model.meshes:
+        v = np.asarray(mesh.vertex, np.float64)
+        idx = np.asarray(mesh.index, np.int64)
+        fn = np.cross(v[idx[:, 1]] - v[idx[:, 0]], v[idx[:, 2]] - v[idx[:, 0]])
+        n = np.zeros_like(v)
+        for k in range(3):
+            np.add.at(n, idx[:, k], fn)
+        length = np.linalg.norm(n, axis=1, keepdims=True)
+        n = np.where(length > 0, n / np.where(length > 0, length, 1.0), np.array([0.0, 1.0, 0.0]))
+        mesh.normal = np.ascontiguousarray(n, np.float32)
+    return model

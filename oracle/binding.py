@@ -180,8 +180,10 @@ class OracleScene:
         for mesh in model.meshes:
             v, idx = _f32(mesh.vertex), _u32(mesh.index)
             tc = _f32(mesh.texcoord) if mesh.texcoord is not None and len(mesh.texcoord) else None
-            self.lib.oracle_scene_add_mesh(self.h, _p(v), C.c_size_t(len(v)), _p(tc), _p(idx), C.c_size_t(len(idx)),
-                                           C.byref(mesh.material), int(mesh.diffuseTextureID))
+            mid = self.lib.oracle_scene_add_mesh(self.h, _p(v), C.c_size_t(len(v)), _p(tc), _p(idx), C.c_size_t(len(idx)),
+                                                 C.byref(mesh.material), int(mesh.diffuseTextureID))
+            if getattr(mesh, "normal", None) is not None and len(mesh.normal) == len(v) and len(v):
+                self.lib.oracle_scene_set_mesh_normals(self.h, int(mid), _p(_f32(mesh.normal)))
         self.lib.oracle_scene_build(self.h, int(brute_force))
         if probe is not None:
             self.set_probe(probe)
@@ -244,3 +246,11 @@ class OracleScene:
         self.lib.oracle_trace_rays(self.h, _p(org), _p(dirs), C.c_size_t(n), C.c_float(tmin), C.c_float(tmax), int(any_hit),
                                    int(shadow_mode), _p(prim), _p(mesh), _p(t), _p(u), _p(v))
         return prim, mesh, t, u, v
+
+    def render_whitted(self, width, height, cam12, light_pos):
+        """04HelloRaytracing frame: cam12 = position, direction, horizontal, vertical (4 x 3 floats)."""
+        cam = _f32(np.asarray(cam12, np.float32).reshape(12))
+        light = _f32(np.asarray(light_pos, np.float32).reshape(3))
+        out = np.zeros((height, width), np.uint32)
+        self.lib.oracle_render_whitted(self.h, int(width), int(height), _p(cam), _p(light), _p(out))
+        return out

@@ -39,6 +39,11 @@ int oracle_scene_add_mesh(OScene* s, const float* vtx, size_t nv, const float* t
     s->meshes.push_back(std::move(m));
     return (int)s->meshes.size() - 1;
 }
+void oracle_scene_set_mesh_normals(OScene* s, int meshID, const float* normal) {
+    OMesh& m = s->meshes[meshID];
+    m.normal.resize(m.vertex.size());
+    for (size_t i = 0; i < m.vertex.size(); ++i) m.normal[i] = make_float3(normal[3 * i], normal[3 * i + 1], normal[3 * i + 2]);
+}
 void oracle_scene_build(OScene* s, int force_brute_force) {
     oracleBuild(*s);
     if (force_brute_force) s->bruteForce = true;
@@ -154,6 +159,53 @@ void oracle_trace_rays(OScene* s, const float* org, const float* dir, size_t n, 
             mesh[i] = m;  prim[i] = h.gid - (int)s->meshes[m].firstGid;  t[i] = h.t;  u[i] = h.u;  v[i] = h.v;
         } else { prim[i] = -1;  mesh[i] = -1;  t[i] = 0.f;  u[i] = v[i] = 0.f; }
     }
+}
+
+
+// CPU restatement of 04HelloRaytracing/deviceProgram.cu:66-243 (raygen, closest hit with its shadow trace, miss, shadow any-hit)
+// over this oracle's traversal contract.  cam = position, direction, horizontal, vertical (SampleRenderer.cpp:125-138).
+void oracle_render_whitted(OScene* sp, int W, int H, const float* cam12, const float* light3, uint32_t* colorBuffer) {
+    const OScene& S = *sp;
+    const float3 position = ld3(cam12, 0), direction = ld3(cam12, 1), horizontal = ld3(cam12, 2), vertical = ld3(cam12, 3);
+    const float3 lightPos = ld3(light3, 0);
+    #pragma omp parallel for schedule(dynamic, 4)
+    for (int iy = 0; iy < H; ++iy)
+        for (int ix = 0; ix < W; ++ix) {
+            float3 prd = make_float3(0.f, 0.f, 0.f);
+            const float2 screen = make_float2((ix + .5f) / (float)W, (iy + .5f) / (float)H);                 // :213-214
+            const float3 rayDir = normalize(direction + (screen.x - 0.5f) * horizontal + (screen.y - 0.5f) * vertical);
+            OHit hit;
+            if (oracleClosest(S, position, rayDir, 0.f, 1e20f, hit)) {                                     // :221-232
+                const int meshID = S.meshOf[hit.gid];
+                const OMesh& mesh = S.meshes[meshID];
+                const uint3 index = mesh.index[hit.gid - (int)mesh.firstGid];
+                const float u = hit.u, v = hit.v;
+                const float3 A = mesh.vertex[index.x], B = mesh.vertex[index.y], C = mesh.vertex[index.z];
+                float3 Ng = cross(B - A, C - A);                                                           // :85
+                float3 Ns = !mesh.normal.empty()
+                    ? ((1.f - u - v) * mesh.normal[index.x] + u * mesh.normal[index.y] + v * mesh.normal[index.z]) : Ng;
+                if (dot(rayDir, Ng) > 0.f) Ng = -Ng;                                                       // :97-102
+                Ng = normalize(Ng);
+                if (dot(Ng, Ns) < 0.f) Ns = Ns - (2.f * dot(Ng, Ns)) * Ng;
+                Ns = normalize(Ns);
+                float3 diffuseColor = mesh.material.color;                                                 // :108
+                if (mesh.textureID >= 0 && !mesh.texcoord.empty()) {
+                    const float2 tc = (1.f - u - v) * mesh.texcoord[index.x] + u * mesh.texcoord[index.y] + v * mesh.texcoord[index.z];
+                    diffuseColor *= make_float3(oracleTex2D(S.textures[mesh.textureID], tc.x, tc.y));
+                }
+                const float3 surfPos = (1.f - u - v) * A + u * B + v * C;                                  // :121-124
+                const float3 lightDir = lightPos - surfPos;
+                // shadow ray: first hit terminates, no culling (:131-153); any hit -> 0, miss -> 1 (:177-191)
+                const bool occluded = oracleAnyHit(S, surfPos + 1e-3f * Ng, lightDir, 1e-3f, 1.f - 1e-3f, false);
+                const float3 lightVisibility = occluded ? make_float3(0.f) : make_float3(1.f);
+                const float cosDN = 0.1f + .8f * fabsf(dot(rayDir, Ns));                                   // :158-160
+                const float3 lv = .8f * lightVisibility;
+                const float3 shade = make_float3(.1f + (.2f + lv.x) * cosDN, .1f + (.2f + lv.y) * cosDN, .1f + (.2f + lv.z) * cosDN);
+                prd = shade * diffuseColor;                                                                // :163
+            }
+            const int r = int(255.99f * prd.x), g = int(255.99f * prd.y), b = int(255.99f * prd.z);         // :232-242
+            colorBuffer[ix + (size_t)iy * W] = 0xff000000u | (r << 0) | (g << 8) | (b << 16);
+        }
 }
 
 }  // extern "C"

@@ -20,6 +20,7 @@ struct OTexture { int w = 0, h = 0; std::vector<uint32_t> px; };
 struct OMesh {
     std::vector<float3> vertex;
     std::vector<float2> texcoord;      // may be empty
+    std::vector<float3> normal;        // may be empty (read by the Whitted restatement only)
     std::vector<uint3>  index;
     Material material;
     int textureID = -1;
