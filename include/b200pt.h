@@ -85,6 +85,14 @@ int b200pt_add_mesh(b200pt_ctx* ctx,
  * (sv4/SimplePathtracer.cpp:670-737).  *handle_out receives the value for LaunchParams.traversable. */
 int b200pt_build_accel(b200pt_ctx* ctx, uint64_t* handle_out);
 
+/* Animated geometry (rebuild-per-frame / refit; the reference builds once, sv4/SimplePathtracer.cpp:670-737).
+ * b200pt_update_vertices replaces one mesh's positions (same vertex count as b200pt_add_mesh; indices, normals, texcoords kept).
+ * Then either b200pt_refit_accel — topology kept: new triangle records, bottom-up bounds, re-quantisation over the new scene box,
+ * O(N) with no sort (OptiX's OPTIX_BUILD_OPERATION_UPDATE) — or b200pt_build_accel again for a full rebuild.  Hits stay exact
+ * either way (the triangle test does not depend on the tree); only traversal cost degrades with large deformations under refit. */
+int b200pt_update_vertices(b200pt_ctx* ctx, int mesh_id, const float* vertex_xyz, size_t n_vertices);
+int b200pt_refit_accel(b200pt_ctx* ctx);
+
 /* ---- frame state: SampleRenderer::resize / setProbe (sv4/SimplePathtracer.cpp:231-277, 295-311) ---- */
 int b200pt_resize(b200pt_ctx* ctx, int width, int height, struct LaunchParams* params /* buffers + size written */);
 int b200pt_set_probe(b200pt_ctx* ctx, int width, int height, const float* data_rgba,
@@ -159,6 +167,8 @@ typedef struct b200pt_bvh_info {
     int32_t  root_link;          /* >= 0: record index of the root's node; < 0: leaf code; 0x7fffffff: empty scene */
     uint32_t refine_levels;      /* treelet-refinement levels run by the build */
     double   grid_lo[3], grid_scale[3];   /* node boxes are quantised: g = 2 + (x - grid_lo) * grid_scale, 16 bits per bound */
+    float    refit_ms;           /* device time of the last b200pt_refit_accel (0 if none since the build) */
+    uint32_t reserved;
 } b200pt_bvh_info;
 int b200pt_bvh_info_get(b200pt_ctx* ctx, b200pt_bvh_info* out);
 /* Copies of the flattened BVH for structural validation in tests: n_nodes 32-byte records, one per inner node, each

@@ -105,6 +105,12 @@ public:
                                     {lightPos.x, lightPos.y, lightPos.z}};
         if (b200pt_render_whitted(ctx, &wp, nullptr) != 0) fail();
     }
+    // animated geometry: new positions for mesh `meshID` (same count), then refit (topology kept) or a full rebuild
+    void updateVertices(int meshID, const std::vector<float3>& vertex) {
+        if (b200pt_update_vertices(ctx, meshID, reinterpret_cast<const float*>(vertex.data()), vertex.size()) != 0) fail();
+    }
+    void refitAccel() { if (b200pt_refit_accel(ctx) != 0) fail(); }
+    void rebuildAccel() { uint64_t h = 0;  if (b200pt_build_accel(ctx, &h) != 0) fail();  launchParams.traversable = h; }
     // extras behind the same C-ABI
     void downloadAccum(float* h_rgba) { if (b200pt_download_accum(ctx, h_rgba) != 0) fail(); }
     b200pt_counters counters() { b200pt_counters c{};  if (b200pt_get_counters(ctx, &c) != 0) fail();  return c; }

@@ -22,6 +22,8 @@ struct HostTexture { size_t offset;  int w, h; };
 struct b200pt_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    bool stale = false;           // vertices updated since the last build/refit
+    float refitMs = 0.f;
     // --- scene staging (host) and device copies
     std::vector<float3> hVertices, hNormals;  std::vector<float2> hTexcoords;  std::vector<uint3> hIndices;  std::vector<unsigned> hTriMesh;
     std::vector<HostMesh> hMeshes;  std::vector<HostTexture> hTextures;  std::vector<uint32_t> hTexels;
@@ -136,6 +138,33 @@ int b200pt_add_mesh(b200pt_ctx* c, const float* vtx, size_t nv, const float* nor
     return (int)c->hMeshes.size() - 1;
 }
 
+// Animated geometry: replace one mesh's vertex positions (same count, same indices).  Follow with b200pt_refit_accel (cheap,
+// topology kept) or b200pt_build_accel (full rebuild).
+int b200pt_update_vertices(b200pt_ctx* c, int meshID, const float* vtx, size_t nv) {
+    if (!c || !vtx) return fail("b200pt_update_vertices: null argument");
+    if (meshID < 0 || meshID >= (int)c->hMeshes.size()) return fail("b200pt_update_vertices: mesh id out of range");
+    const HostMesh& m = c->hMeshes[meshID];
+    if (nv != m.nVertices) return fail("b200pt_update_vertices: vertex count differs from b200pt_add_mesh");
+    API_BEGIN
+    memcpy(c->hVertices.data() + m.firstVertex, vtx, nv * sizeof(float3));
+    if (c->built) {                                           // device copy is live: patch it in place
+        CUDA_OK(cudaSetDevice(c->device));
+        CUDA_OK(cudaMemcpyAsync(c->dVertices.p + m.firstVertex, vtx, nv * sizeof(float3), cudaMemcpyHostToDevice, c->stream));
+        CUDA_OK(cudaStreamSynchronize(c->stream));
+        c->stale = true;
+    }
+    API_END
+}
+int b200pt_refit_accel(b200pt_ctx* c) {
+    if (!c) return fail("b200pt_refit_accel: null context");
+    if (!c->built) return fail("b200pt_refit_accel: b200pt_build_accel has not been called");
+    API_BEGIN
+    CUDA_OK(cudaSetDevice(c->device));
+    bvhRefit(c->dVertices.p, c->dIndices.p, c->dTriMesh.p, c->dMeshes.p, c->stream, c->bvh, &c->refitMs);
+    c->stale = false;
+    API_END
+}
+
 int b200pt_build_accel(b200pt_ctx* c, uint64_t* handle_out) {
     if (!c) return fail("b200pt_build_accel: null context");
     API_BEGIN
@@ -162,7 +191,7 @@ int b200pt_build_accel(b200pt_ctx* c, uint64_t* handle_out) {
     bvhBuild(c->dVertices.p, c->dIndices.p, c->dTriMesh.p, c->dMeshes.p, (unsigned)c->hIndices.size(), c->stream, c->bvh);
     CUDA_OK(cudaStreamSynchronize(c->stream));
     CUDA_OK(cudaGetLastError());
-    c->built = true;
+    c->built = true;  c->stale = false;  c->refitMs = 0.f;
     if (handle_out) *handle_out = (uint64_t)(uintptr_t)c->bvh.nodes;
     API_END
 }

@@ -174,6 +174,7 @@ int b200pt_bvh_info_get(b200pt_ctx* c, b200pt_bvh_info* o) {
     o->n_triangles = c->bvh.nTris;  o->n_nodes = c->bvh.nNodes;  o->n_leaves = c->bvh.nLeaves;  o->max_leaf_size = c->bvh.maxLeaf;
     o->max_depth = c->bvh.maxDepth;  o->sah_cost = c->bvh.sahCost;  o->sah_cost_lbvh = c->bvh.sahCostLbvh;  o->build_ms = c->bvh.buildMs;
     o->node_bytes = (uint64_t)c->bvh.nNodes * sizeof(BvhNode);  o->tri_bytes = (uint64_t)c->bvh.nTris * 48;
+    o->refit_ms = c->refitMs;
     o->root_link = c->bvh.rootLink;  o->refine_levels = c->bvh.refineLevels;
     for (int a = 0; a < 3; ++a) { o->grid_lo[a] = c->bvh.gridLo[a];  o->grid_scale[a] = c->bvh.gridScale[a]; }
     return 0;

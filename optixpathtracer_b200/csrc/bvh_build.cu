@@ -482,3 +482,155 @@ void bvhBuild(const float3* d_vertices, const uint3* d_indices, const unsigned* 
     cudaFree(costDev);  cudaFree(rootLinkDev);
     if (out.maxDepth > B200PT_STACK - 2) throw std::runtime_error("BVH deeper than the traversal stack");
 }
+
+// ================================================================ refit: new vertex positions, same topology
+// (what OptiX calls OPTIX_BUILD_OPERATION_UPDATE; the reference always rebuilds, sv4/SimplePathtracer.cpp:670-737)
+//   1. refitTrisKernel    new 48-byte triangle records in the existing leaf order + per-slot AABB + scene AABB
+//   2. refitParentsKernel parent of every record (records carry child links only)
+//   3. refitBoundsKernel  bottom-up: a thread per record folds its leaf children, the second child to arrive at a record
+//                         unions the pair and carries it to the parent (Karras-style atomic visit counter)
+//   4. refitQuantKernel   exact child boxes -> the records' 16-bit grid cells over the NEW scene box
+__global__ void refitTrisKernel(const float3* __restrict__ vtx, const uint3* __restrict__ idx, const unsigned* __restrict__ triMesh,
+                                const MeshInfo* __restrict__ meshes, const unsigned* __restrict__ finalGid, unsigned n,
+                                float4* __restrict__ tris, float4* __restrict__ slotLo, float4* __restrict__ slotHi, unsigned* sceneBox) {
+    const unsigned s = blockIdx.x * blockDim.x + threadIdx.x;
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    if (s < n) {
+        const unsigned g = finalGid[s];
+        const unsigned m = triMesh[g];
+        const unsigned fv = meshes[m].firstVertex;
+        const uint3 id = idx[g];
+        const float3 a = vtx[fv + id.x], b = vtx[fv + id.y], c = vtx[fv + id.z];
+        const float e1x = __fsub_rn(b.x, a.x), e1y = __fsub_rn(b.y, a.y), e1z = __fsub_rn(b.z, a.z);
+        const float e2x = __fsub_rn(c.x, a.x), e2y = __fsub_rn(c.y, a.y), e2z = __fsub_rn(c.z, a.z);
+        tris[3 * (size_t)s] = make_float4(a.x, a.y, a.z, e1x);
+        tris[3 * (size_t)s + 1] = make_float4(e1y, e1z, e2x, e2y);
+        tris[3 * (size_t)s + 2] = make_float4(e2z, __int_as_float((int)g), __int_as_float((int)m), 0.f);
+        lo[0] = fminf(fminf(a.x, b.x), c.x);  hi[0] = fmaxf(fmaxf(a.x, b.x), c.x);
+        lo[1] = fminf(fminf(a.y, b.y), c.y);  hi[1] = fmaxf(fmaxf(a.y, b.y), c.y);
+        lo[2] = fminf(fminf(a.z, b.z), c.z);  hi[2] = fmaxf(fmaxf(a.z, b.z), c.z);
+        slotLo[s] = make_float4(lo[0], lo[1], lo[2], 0.f);
+        slotHi[s] = make_float4(hi[0], hi[1], hi[2], 0.f);
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        for (int o = 16; o; o >>= 1) {
+            lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
+            hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
+        }
+        if ((threadIdx.x & 31) == 0 && lo[a] <= hi[a]) { atomicMin(sceneBox + a, fOrder(lo[a]));  atomicMax(sceneBox + 3 + a, fOrder(hi[a])); }
+    }
+}
+__global__ void refitParentsKernel(const BvhNode* __restrict__ nodes, unsigned nRecords, int* __restrict__ parent) {
+    const unsigned r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= nRecords) return;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) { const int l = nodes[r].link[k];  if (l >= 0) parent[l] = (int)(2 * r + k); }
+}
+// childBox: 12 floats per record {c0.lo, c0.hi, c1.lo, c1.hi}; visit: one counter per record, zeroed
+__global__ void refitBoundsKernel(const BvhNode* __restrict__ nodes, unsigned nRecords, const int* __restrict__ parent,
+                                  const float4* __restrict__ slotLo, const float4* __restrict__ slotHi, float* childBox, unsigned* visit) {
+    const unsigned r0 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r0 >= nRecords) return;
+    for (int k = 0; k < 2; ++k) {
+        const int l = nodes[r0].link[k];
+        if (l >= 0) continue;
+        unsigned first, count;
+        leafDecode(l, first, count);
+        float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+        for (unsigned t = first; t < first + count; ++t) {
+            const float4 a = slotLo[t], b = slotHi[t];
+            lo[0] = fminf(lo[0], a.x);  lo[1] = fminf(lo[1], a.y);  lo[2] = fminf(lo[2], a.z);
+            hi[0] = fmaxf(hi[0], b.x);  hi[1] = fmaxf(hi[1], b.y);  hi[2] = fmaxf(hi[2], b.z);
+        }
+        unsigned r = r0;
+        int which = k;
+        for (;;) {
+            volatile float* cb = childBox + 12 * (size_t)r + 6 * which;
+            cb[0] = lo[0];  cb[1] = lo[1];  cb[2] = lo[2];  cb[3] = hi[0];  cb[4] = hi[1];  cb[5] = hi[2];
+            __threadfence();
+            if (atomicAdd(visit + r, 1u) == 0u) break;                  // the sibling has not arrived yet: it will carry on
+            __threadfence();
+            const volatile float* ob = childBox + 12 * (size_t)r + 6 * (which ^ 1);
+            lo[0] = fminf(lo[0], ob[0]);  lo[1] = fminf(lo[1], ob[1]);  lo[2] = fminf(lo[2], ob[2]);
+            hi[0] = fmaxf(hi[0], ob[3]);  hi[1] = fmaxf(hi[1], ob[4]);  hi[2] = fmaxf(hi[2], ob[5]);
+            const int p = parent[r];
+            if (p < 0) break;                                           // r is the root record
+            r = (unsigned)p >> 1;  which = p & 1;
+        }
+    }
+}
+__global__ void refitQuantKernel(BvhNode* __restrict__ nodes, unsigned nRecords, const float* __restrict__ childBox,
+                                 double gx, double gy, double gz, double sx, double sy, double sz) {
+    const unsigned r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= nRecords) return;
+    const double gl[3] = {gx, gy, gz}, gs[3] = {sx, sy, sz};
+    const float* cb = childBox + 12 * (size_t)r;
+    unsigned q[6];
+#pragma unroll
+    for (int c = 0; c < 2; ++c)
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {                              // same outward rounding as the SAH write-out (bvh_sah.cuh)
+            const double l = B200PT_GRID_ORIGIN + ((double)cb[6 * c + a] - gl[a]) * gs[a];
+            const double h = B200PT_GRID_ORIGIN + ((double)cb[6 * c + 3 + a] - gl[a]) * gs[a];
+            const unsigned ql = (unsigned)min(65535, max(0, (int)floor(l) - B200PT_GRID_PAD));
+            const unsigned qh = (unsigned)min(65535, max(0, (int)ceil(h) + B200PT_GRID_PAD));
+            q[3 * c + a] = ql | (qh << 16);
+        }
+    uint4* dst = reinterpret_cast<uint4*>(nodes) + 2 * (size_t)r;
+    const uint4 old1 = dst[1];
+    dst[0] = make_uint4(q[0], q[1], q[2], q[3]);
+    dst[1] = make_uint4(q[4], q[5], old1.z, old1.w);
+}
+
+void bvhRefit(const float3* d_vertices, const uint3* d_indices, const unsigned* d_triMesh, const MeshInfo* d_meshes, cudaStream_t s,
+              BvhBuildResult& io, float* refitMs) {
+    const unsigned n = io.nTris, nr = io.nNodes;
+    if (!n) { if (refitMs) *refitMs = 0.f;  return; }
+    const unsigned B = 256, G = (n + B - 1) / B, GR = (std::max(nr, 1u) + B - 1) / B;
+    cudaEvent_t e0, e1;
+    CUDA_OK(cudaEventCreate(&e0));  CUDA_OK(cudaEventCreate(&e1));
+    CUDA_OK(cudaEventRecord(e0, s));
+    float4* slotLo = dalloc<float4>(n);
+    float4* slotHi = dalloc<float4>(n);
+    unsigned* sceneBox = dalloc<unsigned>(8);
+    int* parent = dalloc<int>(nr);
+    float* childBox = dalloc<float>(12 * (size_t)nr);
+    unsigned* visit = dalloc<unsigned>(nr);
+    const unsigned initBox[8] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u, 0u, 0u};
+    CUDA_OK(cudaMemcpyAsync(sceneBox, initBox, sizeof(initBox), cudaMemcpyHostToDevice, s));
+    refitTrisKernel<<<G, B, 0, s>>>(d_vertices, d_indices, d_triMesh, d_meshes, io.finalGid, n, io.tris, slotLo, slotHi, sceneBox);
+    unsigned hb[8];
+    CUDA_OK(cudaMemcpyAsync(hb, sceneBox, sizeof(hb), cudaMemcpyDeviceToHost, s));
+    if (nr) {
+        CUDA_OK(cudaMemsetAsync(parent, 0xff, sizeof(int) * (size_t)nr, s));
+        CUDA_OK(cudaMemsetAsync(visit, 0, sizeof(unsigned) * (size_t)nr, s));
+        refitParentsKernel<<<GR, B, 0, s>>>(io.nodes, nr, parent);
+        refitBoundsKernel<<<GR, B, 0, s>>>(io.nodes, nr, parent, slotLo, slotHi, childBox, visit);
+    }
+    CUDA_OK(cudaStreamSynchronize(s));
+    for (int a = 0; a < 3; ++a) {
+        const double lo = (double)fUnorder(hb[a]), hi = (double)fUnorder(hb[3 + a]);
+        io.gridLo[a] = lo;
+        io.gridScale[a] = hi > lo ? B200PT_GRID_SPAN / (hi - lo) : 1.0;
+        io.sceneBounds[a] = (float)lo;  io.sceneBounds[3 + a] = (float)hi;
+    }
+    if (nr) refitQuantKernel<<<GR, B, 0, s>>>(io.nodes, nr, childBox, io.gridLo[0], io.gridLo[1], io.gridLo[2], io.gridScale[0], io.gridScale[1], io.gridScale[2]);
+    double* costDev = dalloc<double>(1);
+    CUDA_OK(cudaMemsetAsync(costDev, 0, sizeof(double), s));
+    if (nr) sahCostKernel<<<GR, B, 0, s>>>(io.nodes, nr, 1.0 / io.gridScale[0], 1.0 / io.gridScale[1], 1.0 / io.gridScale[2], costDev);
+    CUDA_OK(cudaEventRecord(e1, s));
+    double costHost = 0.0;
+    CUDA_OK(cudaMemcpyAsync(&costHost, costDev, sizeof(double), cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaStreamSynchronize(s));
+    CUDA_OK(cudaGetLastError());
+    float ms = 0.f;
+    CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
+    if (refitMs) *refitMs = ms;
+    cudaEventDestroy(e0);  cudaEventDestroy(e1);
+    const double dx = (double)io.sceneBounds[3] - io.sceneBounds[0], dy = (double)io.sceneBounds[4] - io.sceneBounds[1], dz = (double)io.sceneBounds[5] - io.sceneBounds[2];
+    const double rootArea = 2.0 * (dx * dy + dy * dz + dz * dx);
+    if (io.rootLink >= 0) costHost += SAH_CI * rootArea;  else costHost += SAH_CT * rootArea * (double)n;
+    io.sahCost = rootArea > 0.0 ? (float)(costHost / rootArea) : 0.f;
+    cudaFree(slotLo);  cudaFree(slotHi);  cudaFree(sceneBox);  cudaFree(parent);  cudaFree(childBox);  cudaFree(visit);  cudaFree(costDev);
+}

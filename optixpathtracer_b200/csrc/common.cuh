@@ -130,6 +130,9 @@ struct BvhBuildResult {
 void bvhBuild(const float3* d_vertices, const uint3* d_indices, const unsigned* d_triMesh, const MeshInfo* d_meshes,
               unsigned nTris, cudaStream_t stream, BvhBuildResult& out);
 void bvhFree(BvhBuildResult& r);
+// new vertex positions, same topology: triangle records + bottom-up bounds + re-quantisation (bvh_build.cu)
+void bvhRefit(const float3* d_vertices, const uint3* d_indices, const unsigned* d_triMesh, const MeshInfo* d_meshes, cudaStream_t stream,
+              BvhBuildResult& io, float* refitMs);
 
 // trace.cu  (compiled with FMA contraction; the triangle test itself uses explicit _rn intrinsics)
 void launchTrace(const SceneDev& scene, const float4* rayO, const float4* rayD, float4* hit, const unsigned* countC,

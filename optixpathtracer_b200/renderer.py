@@ -162,6 +162,20 @@ class SampleRenderer:
         buf = np.concatenate([cam.reshape(12), np.asarray(light_pos, np.float32)]).astype(np.float32)
         _lib.check(self._L.b200pt_render_whitted(self._h, _ptr(buf), None))
 
+    # ---- animated geometry: refit or rebuild per frame ----------------------------------------------
+    def updateVertices(self, meshID, vertex):
+        """New positions for one mesh (same count); follow with refitAccel() or rebuildAccel()."""
+        v = np.ascontiguousarray(vertex, np.float32)
+        _lib.check(self._L.b200pt_update_vertices(self._h, int(meshID), _ptr(v), len(v)))
+
+    def refitAccel(self):
+        _lib.check(self._L.b200pt_refit_accel(self._h))
+
+    def rebuildAccel(self):
+        handle = C.c_uint64(0)
+        _lib.check(self._L.b200pt_build_accel(self._h, C.byref(handle)))
+        self.launchParams.traversable = handle.value
+
     # ---- extras behind the same C-ABI -----------------------------------------------------------
     def downloadAccum(self):
         w, h = self.launchParams.frame.size.x, self.launchParams.frame.size.y
