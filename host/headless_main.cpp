@@ -5,8 +5,9 @@
 // log format (sutil/sutil.cpp:760-772: one value per line).
 //
 //   b200pt_headless [--obj file.obj | --boxes N] [--preset sv4_fov|sv4_uniform|sv3_uniform|orig] [--size WxH] [--frames N] [--spl N]
-//                   [--camera sponza|lost_empire|san_miguel|cornell] [--sky r,g,b] [--out image.ppm] [--log fps.tsv]
+//                   [--camera sponza|lost_empire|san_miguel|cornell] [--sky r,g,b] [--out image.ppm|image.png] [--log fps.tsv]
 //                   [--hdr probe.hdr] [--gpu-cdf] [--whitted] [--dump-model file.bin] [--dump-probe file.bin] [--no-render]
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -18,6 +19,47 @@
 #include <vector>
 
 #include "../include/ref_api/SimplePathtracer.h"
+
+// Minimal PNG writer (8-bit RGB, zlib "stored" blocks): the reference saves screenshots through stb_image_write (sutil.cpp:723-739),
+// which is third-party code of the reference and not copied.  rows: top row first.
+static void writePNG(const std::string& path, int W, int H, const std::vector<unsigned char>& rgbTopDown) {
+    auto be32 = [](std::vector<unsigned char>& v, uint32_t x) { for (int s = 24; s >= 0; s -= 8) v.push_back((unsigned char)(x >> s)); };
+    static uint32_t table[256];
+    if (!table[1]) for (uint32_t i = 0; i < 256; ++i) { uint32_t c = i;  for (int k = 0; k < 8; ++k) c = (c & 1) ? 0xEDB88320u ^ (c >> 1) : c >> 1;  table[i] = c; }
+    auto crc = [&](const unsigned char* p, size_t n) { uint32_t c = 0xffffffffu;  for (size_t i = 0; i < n; ++i) c = table[(c ^ p[i]) & 0xff] ^ (c >> 8);  return c ^ 0xffffffffu; };
+    std::vector<unsigned char> raw;                                          // filter byte 0 + RGB per row
+    raw.reserve((size_t)H * (3 * (size_t)W + 1));
+    for (int y = 0; y < H; ++y) { raw.push_back(0);  raw.insert(raw.end(), rgbTopDown.begin() + (size_t)y * 3 * W, rgbTopDown.begin() + (size_t)(y + 1) * 3 * W); }
+    std::vector<unsigned char> z = {0x78, 0x01};
+    uint32_t a = 1, b = 0;
+    for (size_t off = 0; off < raw.size() || off == 0; off += 65535) {
+        const size_t len = std::min<size_t>(65535, raw.size() - off);
+        z.push_back(off + len >= raw.size() ? 1 : 0);
+        z.push_back((unsigned char)(len & 255));  z.push_back((unsigned char)(len >> 8));
+        z.push_back((unsigned char)(~len & 255));  z.push_back((unsigned char)((~len >> 8) & 255));
+        z.insert(z.end(), raw.begin() + off, raw.begin() + off + len);
+        for (size_t i = 0; i < len; ++i) { a = (a + raw[off + i]) % 65521u;  b = (b + a) % 65521u; }
+        if (raw.empty()) break;
+    }
+    be32(z, (b << 16) | a);
+    FILE* f = fopen(path.c_str(), "wb");
+    if (!f) throw std::runtime_error("cannot write " + path);
+    const unsigned char sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
+    fwrite(sig, 1, 8, f);
+    auto chunk = [&](const char* type, const std::vector<unsigned char>& data) {
+        std::vector<unsigned char> c(type, type + 4);
+        c.insert(c.end(), data.begin(), data.end());
+        std::vector<unsigned char> hdr;  be32(hdr, (uint32_t)data.size());
+        std::vector<unsigned char> tail;  be32(tail, crc(c.data(), c.size()));
+        fwrite(hdr.data(), 1, 4, f);  fwrite(c.data(), 1, c.size(), f);  fwrite(tail.data(), 1, 4, f);
+    };
+    std::vector<unsigned char> ihdr;
+    be32(ihdr, (uint32_t)W);  be32(ihdr, (uint32_t)H);
+    const unsigned char rest[5] = {8, 2, 0, 0, 0};
+    ihdr.insert(ihdr.end(), rest, rest + 5);
+    chunk("IHDR", ihdr);  chunk("IDAT", z);  chunk("IEND", {});
+    fclose(f);
+}
 
 static sutil::Camera cameraPreset(const std::string& name) {                                 // main.cpp:211-240
     if (name == "sponza") return sutil::Camera({-1293.07f, 154.681f, 1.0f}, {0.f, 200.f, 0.f}, {0.f, 1.f, 0.f}, 35.f, 1.f);
@@ -147,12 +189,21 @@ int main(int argc, char** argv) {
         for (uint32_t p : px) sum += p & 0xffffffu;
         printf("pixel checksum %llu\n", sum);
         if (!out.empty()) {
-            FILE* fo = fopen(out.c_str(), "wb");
-            if (!fo) throw std::runtime_error("cannot write " + out);
-            fprintf(fo, "P6\n%d %d\n255\n", W, H);
-            for (int y = H - 1; y >= 0; --y)                                                                // image row 0 is the bottom row
-                for (int x = 0; x < W; ++x) { const uint32_t p = px[(size_t)y * W + x];  const unsigned char rgb[3] = {(unsigned char)p, (unsigned char)(p >> 8), (unsigned char)(p >> 16)};  fwrite(rgb, 1, 3, fo); }
-            fclose(fo);
+            std::vector<unsigned char> rgb((size_t)W * H * 3);                                              // image row 0 is the bottom row
+            for (int y = 0; y < H; ++y)
+                for (int x = 0; x < W; ++x) {
+                    const uint32_t p = px[(size_t)(H - 1 - y) * W + x];
+                    unsigned char* q = &rgb[((size_t)y * W + x) * 3];
+                    q[0] = (unsigned char)p;  q[1] = (unsigned char)(p >> 8);  q[2] = (unsigned char)(p >> 16);
+                }
+            if (out.size() > 4 && out.compare(out.size() - 4, 4, ".png") == 0) writePNG(out, W, H, rgb);   // sutil::saveImage, sutil.cpp:723-739
+            else {
+                FILE* fo = fopen(out.c_str(), "wb");
+                if (!fo) throw std::runtime_error("cannot write " + out);
+                fprintf(fo, "P6\n%d %d\n255\n", W, H);
+                fwrite(rgb.data(), 1, rgb.size(), fo);
+                fclose(fo);
+            }
         }
         delete[] probe.data;  delete[] probe.pdfValuesX;  delete[] probe.cdfValuesX;  delete[] probe.pdfValuesY;  delete[] probe.cdfValuesY;
     } catch (const std::runtime_error& e) {                                                                // main.cpp:422-425

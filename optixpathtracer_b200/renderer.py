@@ -33,7 +33,8 @@ def host_params(width, height, camera=None, samples_per_launch=1, subframe_index
 
 def set_camera(p, camera):
     """SimplePathtracer.cpp:285-292 — aspect is overridden by the frame size."""
-    camera.setAspectRatio(np.float32(p.frame.size.x) / np.float32(p.frame.size.y))
+    with np.errstate(invalid="ignore", divide="ignore"):      # before resize() the reference divides 0/0 here too (main.cpp:253 precedes :256)
+        camera.setAspectRatio(np.float32(p.frame.size.x) / np.float32(p.frame.size.y))
     U, V, W = camera.UVWFrame()
     p.camera.U, p.camera.V, p.camera.W = float3(*U), float3(*V), float3(*W)
     p.camera.eye = float3(*camera.eye)
@@ -57,7 +58,8 @@ def whitted_camera(camera, width, height):
     eye, lookat, up = (np.asarray(v, np.float32) for v in (camera.eye, camera.lookat, camera.up))
     direction = norm(lookat - eye)
     cos_fovy = f(0.66)
-    aspect = f(width) / f(height)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        aspect = f(width) / f(height)
     horizontal = ((cos_fovy * aspect) * norm(cross(direction, up))).astype(np.float32)
     vertical = (cos_fovy * norm(cross(horizontal, direction))).astype(np.float32)
     return np.stack([eye, direction, horizontal, vertical]).astype(np.float32)

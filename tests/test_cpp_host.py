@@ -93,6 +93,26 @@ def test_cpp_renderer_equals_python_mirror(exe, tmp_path):
     want = r.downloadPixels().view(np.uint8).reshape(64, 96, 4)[..., :3]
     r.close()
     assert np.array_equal(got, want)
+    # the same frames as a PNG (the reference's screenshot format, sutil.cpp:723-739): decode with zlib and compare
+    import zlib
+    png = os.path.join(str(tmp_path), "out.png")
+    subprocess.check_call([exe, "--obj", obj, "--preset", "sv4_uniform", "--size", "96x64", "--frames", "2", "--camera", "cornell",
+                           "--sky", "1,1,1", "--out", png])
+    raw = open(png, "rb").read()
+    assert raw[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, idat, ihdr = 8, b"", None
+    while pos < len(raw):
+        n, typ = struct.unpack(">I4s", raw[pos:pos + 8])
+        body = raw[pos + 8:pos + 8 + n]
+        assert zlib.crc32(typ + body) == struct.unpack(">I", raw[pos + 8 + n:pos + 12 + n])[0]
+        if typ == b"IHDR":
+            ihdr = struct.unpack(">IIBBBBB", body)
+        if typ == b"IDAT":
+            idat += body
+        pos += 12 + n
+    assert ihdr == (96, 64, 8, 2, 0, 0, 0)
+    rows = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(64, 1 + 96 * 3)
+    assert np.all(rows[:, 0] == 0) and np.array_equal(rows[:, 1:].reshape(64, 96, 3)[::-1], want)
 
 
 # ---- Radiance .hdr readers (loadProbe, sv4/main.cpp:154-165) against the reference's own stb_image (tests/golden/hdr.npz) ----
