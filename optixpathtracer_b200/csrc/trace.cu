@@ -26,7 +26,12 @@
 #define EMPTY 0x7fffffff          // "nothing left to visit"; also the root link of an empty scene
 #define NO_LEAF 0                 // leaf codes are < 0
 #ifndef NODE_ROUNDS
+#ifndef NODE_ROUNDS
 #define NODE_ROUNDS 8
+#endif
+#ifndef NODE_UNROLL
+#define NODE_UNROLL 3           // node steps per lane between two warp votes
+#endif
 #endif
 
 static int g_refillThreshold = -1, g_leafThreshold = -1;   // lanes that must be idle before a warp refills; tuned on B200
@@ -321,6 +326,8 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
         unsigned nodeMask, blockedMask;
 #pragma unroll 1
         for (int round = 0; ; ++round) {
+#pragma unroll
+            for (int sub_ = 0; sub_ < NODE_UNROLL; ++sub_)
             if (active && (unsigned)cur < (unsigned)EMPTY) {
                 const Node8 N_ = ldgNode(S.nodes + 2 * (size_t)cur);
                 if (COUNT) myNodes += 1;
