@@ -336,8 +336,8 @@ def run_b200(a):
     if rank == 0:
         peak, peak_src = _peaks()
         # one traceKernel launch per bounce traces the extension rays AND the previous pass's shadow rays
-        bytes_closest_per_frame = (32 * nodes + 48 * tris + (32 + 16) * crays) / replay
-        bytes_any_per_frame = (32 * nodes_s + 48 * tris_s + (32 + 4) * srays) / replay
+        bytes_closest_per_frame = (64 * nodes + 48 * tris + (32 + 16) * crays) / replay
+        bytes_any_per_frame = (64 * nodes_s + 48 * tris_s + (32 + 4) * srays) / replay
         launches_per_frame = n_closest / a.steps
         trace_ms = stage["trace_closest"] + stage["trace_any"]
         ms_per_launch = trace_ms / max(1, n_closest)
@@ -363,8 +363,8 @@ def run_b200(a):
                          "avg_launch_ms": ms_per_launch,
                          "nodes_per_ray": nodes / max(1, crays), "tris_per_ray": tris / max(1, crays),
                          "nodes_per_shadow_ray": nodes_s / max(1, srays), "tris_per_shadow_ray": tris_s / max(1, srays),
-                         "bytes_per_ray": (32 * nodes + 48 * tris) / max(1, crays) + 48,
-                         "note": "algorithmic bytes = 32 B x node records + 48 B x triangle records fetched (counted by the kernel in a counters replay of the same frames) "
+                         "bytes_per_ray": (64 * nodes + 48 * tris) / max(1, crays) + 48,
+                         "note": "algorithmic bytes = 64 B x 4-wide node records + 48 B x triangle records fetched (counted by the kernel in a counters replay of the same frames) "
                                  f"+ 32 B ray in + 16 B hit (4 B flag for shadow rays) out; BVH = {(info.node_bytes + info.tri_bytes) / 1e6:.0f} MB (L2 is 126 MB): when it is cache-resident these bytes are served by L1/L2, not HBM"},
             "stage_ms_per_step": {k: v / a.steps for k, v in stage.items()},
             "reduce_ms": reduce_ms, "wall_seconds_timed_region": wall, "clocks": clocks,

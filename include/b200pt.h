@@ -163,18 +163,22 @@ typedef struct b200pt_bvh_info {
     float    sah_cost;           /* SAH cost of the final tree (Ct = 1, Ci = 1.2) */
     float    sah_cost_lbvh;      /* before refinement */
     float    build_ms;
-    uint64_t node_bytes, tri_bytes;
+    uint64_t node_bytes, tri_bytes;      /* node_bytes = the 4-wide nodes */
     int32_t  root_link;          /* >= 0: record index of the root's node; < 0: leaf code; 0x7fffffff: empty scene */
     uint32_t refine_levels;      /* treelet-refinement levels run by the build */
     double   grid_lo[3], grid_scale[3];   /* node boxes are quantised: g = 2 + (x - grid_lo) * grid_scale, 16 bits per bound */
     float    refit_ms;           /* device time of the last b200pt_refit_accel (0 if none since the build) */
-    uint32_t reserved;
+    uint32_t n_wide_nodes;       /* 64-byte 4-wide nodes the traversal kernels read (the binary records collapsed) */
+    uint32_t wide_depth, reserved;
 } b200pt_bvh_info;
 int b200pt_bvh_info_get(b200pt_ctx* ctx, b200pt_bvh_info* out);
 /* Copies of the flattened BVH for structural validation in tests: n_nodes 32-byte records, one per inner node, each
  * {6 x uint32: 12 quantised 16-bit bounds of child 0 then child 1 (lo.x|hi.x<<16, lo.y|hi.y<<16, lo.z|hi.z<<16), int32 link0, link1};
  * tri_global_id = triangle ids in leaf order. */
 int b200pt_download_bvh(b200pt_ctx* ctx, void* nodes32, size_t max_nodes, uint32_t* tri_global_id, size_t max_tris);
+/* The 4-wide tree the traversal kernels read: n_wide_nodes 64-byte records {12 x uint32: child c's box in words 3c..3c+2 (same
+ * packing as above), int32 link[4]}; unused slots: box lo 65535 / hi 0, link 0x7fffffff; the root is record 0. */
+int b200pt_download_bvh4(b200pt_ctx* ctx, void* nodes64, size_t max_nodes);
 
 typedef struct b200pt_counters {      /* last render()                                                  */
     uint64_t samples;                 /* camera paths started                                           */

@@ -15,7 +15,7 @@ SYMBOLS = [
     "b200pt_render_whitted", "b200pt_render_async", "b200pt_synchronize", "b200pt_download_pixels", "b200pt_download_accum",
     "b200pt_upload_accum", "b200pt_download_aov", "b200pt_device_buffers", "b200pt_resolve_sum", "b200pt_clear_accum",
     "b200pt_tonemap_sqrt", "b200pt_tonemap_sqrt_host", "b200pt_trace_primary", "b200pt_trace_rays",
-    "b200pt_debug_morton", "b200pt_bvh_info_get", "b200pt_download_bvh", "b200pt_get_counters",
+    "b200pt_debug_morton", "b200pt_bvh_info_get", "b200pt_download_bvh", "b200pt_download_bvh4", "b200pt_get_counters",
     "computeFinalPixelColors",
 ]
 
@@ -49,6 +49,7 @@ def lib():
     L.b200pt_set_probe_image.argtypes = [vp, i32, i32, vp, vp, C.POINTER(LaunchParams)]
     L.b200pt_download_probe.argtypes = [vp, vp, vp, vp, vp]
     L.b200pt_render_whitted.argtypes = [vp, vp, vp]
+    L.b200pt_download_bvh4.argtypes = [vp, vp, C.c_size_t]
     L.b200pt_update_vertices.argtypes = [vp, i32, vp, C.c_size_t]
     L.b200pt_refit_accel.argtypes = [vp]
     for name in ("b200pt_render", "b200pt_render_async"):

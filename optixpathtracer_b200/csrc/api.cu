@@ -201,6 +201,7 @@ int b200pt_build_accel(b200pt_ctx* c, uint64_t* handle_out) {
 static SceneDev sceneOf(b200pt_ctx* c) {
     SceneDev S;
     S.nodes = (const uint4*)c->bvh.nodes;  S.rootLink = c->bvh.rootLink;
+    S.nodes4 = (const uint4*)c->bvh.nodes4;  S.rootLink4 = c->bvh.rootLink4;
     for (int a = 0; a < 3; ++a) { S.gridLo[a] = c->bvh.gridLo[a];  S.gridScale[a] = c->bvh.gridScale[a]; }
     S.tris = c->bvh.tris;  S.meshes = c->dMeshes.p;  S.indices = c->dIndices.p;
     S.vertices = c->dVertices.p;  S.normals = c->dNormals.p;

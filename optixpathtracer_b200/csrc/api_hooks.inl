@@ -173,7 +173,7 @@ int b200pt_bvh_info_get(b200pt_ctx* c, b200pt_bvh_info* o) {
     memset(o, 0, sizeof(*o));
     o->n_triangles = c->bvh.nTris;  o->n_nodes = c->bvh.nNodes;  o->n_leaves = c->bvh.nLeaves;  o->max_leaf_size = c->bvh.maxLeaf;
     o->max_depth = c->bvh.maxDepth;  o->sah_cost = c->bvh.sahCost;  o->sah_cost_lbvh = c->bvh.sahCostLbvh;  o->build_ms = c->bvh.buildMs;
-    o->node_bytes = (uint64_t)c->bvh.nNodes * sizeof(BvhNode);  o->tri_bytes = (uint64_t)c->bvh.nTris * 48;
+    o->node_bytes = (uint64_t)c->bvh.nNodes4 * sizeof(BvhNode4);  o->n_wide_nodes = c->bvh.nNodes4;  o->wide_depth = c->bvh.maxDepth4;  o->tri_bytes = (uint64_t)c->bvh.nTris * 48;
     o->refit_ms = c->refitMs;
     o->root_link = c->bvh.rootLink;  o->refine_levels = c->bvh.refineLevels;
     for (int a = 0; a < 3; ++a) { o->grid_lo[a] = c->bvh.gridLo[a];  o->grid_scale[a] = c->bvh.gridScale[a]; }
@@ -188,6 +188,16 @@ int b200pt_download_bvh(b200pt_ctx* c, void* nodes32, size_t maxNodes, uint32_t*
     CUDA_OK(cudaSetDevice(c->device));
     if (c->bvh.nNodes) CUDA_OK(cudaMemcpy(nodes32, c->bvh.nodes, sizeof(BvhNode) * (size_t)c->bvh.nNodes, cudaMemcpyDeviceToHost));
     if (c->bvh.nTris) CUDA_OK(cudaMemcpy(triGid, c->bvh.finalGid, 4 * (size_t)c->bvh.nTris, cudaMemcpyDeviceToHost));
+    API_END
+}
+
+int b200pt_download_bvh4(b200pt_ctx* c, void* nodes64, size_t maxNodes) {
+    if (!c || !nodes64) return fail("b200pt_download_bvh4: null argument");
+    API_BEGIN
+    if (!c->built) throw std::runtime_error("b200pt_download_bvh4: b200pt_build_accel has not been called");
+    if (maxNodes < c->bvh.nNodes4) throw std::runtime_error("b200pt_download_bvh4: buffer too small");
+    CUDA_OK(cudaSetDevice(c->device));
+    if (c->bvh.nNodes4) CUDA_OK(cudaMemcpy(nodes64, c->bvh.nodes4, sizeof(BvhNode4) * (size_t)c->bvh.nNodes4, cudaMemcpyDeviceToHost));
     API_END
 }
 

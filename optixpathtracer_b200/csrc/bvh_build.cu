@@ -11,6 +11,7 @@
 // Integer stages (2,3) are the ones north_star asks to be bit-exact against a host reference.
 #include "common.cuh"
 #include <cfloat>
+#include <chrono>
 
 #define SORT_THREADS 256
 #define SORT_ITEMS 16
@@ -350,8 +351,10 @@ __global__ void scatterCodesKernel(const unsigned long long* __restrict__ sorted
 // ---------------------------------------------------------------- host driver
 template <typename T> static T* dalloc(size_t n) { T* p = nullptr;  CUDA_OK(cudaMalloc((void**)&p, std::max<size_t>(n, 1) * sizeof(T)));  return p; }
 
+float bvhCollapse4(cudaStream_t s, BvhBuildResult& io);      // returns its own wall time in ms
+
 void bvhFree(BvhBuildResult& r) {
-    cudaFree(r.nodes);  cudaFree(r.tris);  cudaFree(r.mortonByGid);  cudaFree(r.sortedGid);  cudaFree(r.finalGid);
+    cudaFree(r.nodes);  cudaFree(r.nodes4);  cudaFree(r.tris);  cudaFree(r.mortonByGid);  cudaFree(r.sortedGid);  cudaFree(r.finalGid);
     r = BvhBuildResult();
 }
 
@@ -481,6 +484,81 @@ void bvhBuild(const float3* d_vertices, const uint3* d_indices, const unsigned* 
     cudaFree(collapse);  cudaFree(scalars);  cudaFree(flagNext);  cudaFree(rankA);  cudaFree(rankB);  cudaFree(tileSum);  cudaFree(tileOff);
     cudaFree(costDev);  cudaFree(rootLinkDev);
     if (out.maxDepth > B200PT_STACK - 2) throw std::runtime_error("BVH deeper than the traversal stack");
+    out.buildMs += bvhCollapse4(s, out);
+}
+
+// ================================================================ collapse: binary records -> 4-wide nodes
+// Top-down, one launch per level of the 4-wide tree: a frontier item (binary record r, output node i) takes r's two children and
+// twice replaces the inner child with the largest surface area (in grid cells) by that child's own two children.
+__device__ __forceinline__ float cellArea(const unsigned* q) {
+    const float dx = (float)((q[0] >> 16) - (q[0] & 0xffffu)), dy = (float)((q[1] >> 16) - (q[1] & 0xffffu)), dz = (float)((q[2] >> 16) - (q[2] & 0xffffu));
+    return dx * dy + dy * dz + dz * dx;
+}
+__global__ void collapse4Kernel(const BvhNode* __restrict__ n2, BvhNode4* __restrict__ n4, const int2* __restrict__ frontIn,
+                                const unsigned* __restrict__ countIn, int2* __restrict__ frontOut, unsigned* countOut, unsigned* nodeCounter) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= *countIn) return;
+    const int2 it = frontIn[i];
+    unsigned q[4][3];
+    int link[4];
+    {
+        const BvhNode a = n2[it.x];
+        for (int k = 0; k < 3; ++k) { q[0][k] = a.q[k];  q[1][k] = a.q[3 + k]; }
+        link[0] = a.link[0];  link[1] = a.link[1];
+    }
+    int n = 2;
+    for (int iter = 0; iter < 2; ++iter) {
+        int best = -1;
+        float bestA = -1.f;
+        for (int c = 0; c < n; ++c)
+            if (link[c] >= 0) { const float A = cellArea(q[c]);  if (A > bestA) { bestA = A;  best = c; } }
+        if (best < 0) break;
+        const BvhNode b = n2[link[best]];
+        for (int k = 0; k < 3; ++k) { q[best][k] = b.q[k];  q[n][k] = b.q[3 + k]; }
+        link[best] = b.link[0];  link[n] = b.link[1];
+        ++n;
+    }
+    for (int c = 0; c < n; ++c)
+        if (link[c] >= 0) {
+            const unsigned idx = atomicAdd(nodeCounter, 1u), pos = atomicAdd(countOut, 1u);
+            frontOut[pos] = make_int2(link[c], (int)idx);
+            link[c] = (int)idx;
+        }
+    for (int c = n; c < 4; ++c) { q[c][0] = q[c][1] = q[c][2] = 0x0000ffffu;  link[c] = B200PT_LINK_EMPTY; }
+    uint4* dst = reinterpret_cast<uint4*>(n4) + 4 * (size_t)it.y;
+    dst[0] = make_uint4(q[0][0], q[0][1], q[0][2], q[1][0]);
+    dst[1] = make_uint4(q[1][1], q[1][2], q[2][0], q[2][1]);
+    dst[2] = make_uint4(q[2][2], q[3][0], q[3][1], q[3][2]);
+    dst[3] = make_uint4((unsigned)link[0], (unsigned)link[1], (unsigned)link[2], (unsigned)link[3]);
+}
+// (re)derives io.nodes4 from io.nodes; io.nodes4 is allocated on first use (as many nodes as binary records at most)
+float bvhCollapse4(cudaStream_t s, BvhBuildResult& io) {
+    io.rootLink4 = io.rootLink;  io.nNodes4 = 0;  io.maxDepth4 = 0;
+    if (io.rootLink < 0 || io.rootLink == B200PT_LINK_EMPTY || !io.nNodes) return 0.f;
+    CUDA_OK(cudaStreamSynchronize(s));
+    const auto t0 = std::chrono::steady_clock::now();      // leaf root / empty scene: no inner nodes
+    const unsigned nr = io.nNodes;
+    if (!io.nodes4) io.nodes4 = dalloc<BvhNode4>(nr);
+    int2* front[2] = {dalloc<int2>(nr), dalloc<int2>(nr)};
+    unsigned* ctr = dalloc<unsigned>(4);                     // [0],[1] frontier sizes, [2] node counter
+    const unsigned init[4] = {1u, 0u, 1u, 0u};
+    const int2 root = make_int2(io.rootLink, 0);
+    CUDA_OK(cudaMemcpyAsync(ctr, init, sizeof(init), cudaMemcpyHostToDevice, s));
+    CUDA_OK(cudaMemcpyAsync(front[0], &root, sizeof(root), cudaMemcpyHostToDevice, s));
+    unsigned width = 1, depth = 0;
+    int cur = 0;
+    while (width) {                                           // one small read-back per level (the 4-wide tree is ~log4 deep)
+        CUDA_OK(cudaMemsetAsync(ctr + (cur ^ 1), 0, sizeof(unsigned), s));
+        collapse4Kernel<<<(width + 127) / 128, 128, 0, s>>>(io.nodes, io.nodes4, front[cur], ctr + cur, front[cur ^ 1], ctr + (cur ^ 1), ctr + 2);
+        CUDA_OK(cudaMemcpyAsync(&width, ctr + (cur ^ 1), sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaStreamSynchronize(s));
+        cur ^= 1;  ++depth;
+    }
+    CUDA_OK(cudaMemcpy(&io.nNodes4, ctr + 2, sizeof(unsigned), cudaMemcpyDeviceToHost));
+    io.rootLink4 = 0;  io.maxDepth4 = depth;
+    cudaFree(front[0]);  cudaFree(front[1]);  cudaFree(ctr);
+    if (3 * io.maxDepth4 + 4 > B200PT_STACK) throw std::runtime_error("4-wide BVH deeper than the traversal stack");
+    return std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
 }
 
 // ================================================================ refit: new vertex positions, same topology
@@ -633,4 +711,6 @@ void bvhRefit(const float3* d_vertices, const uint3* d_indices, const unsigned* 
     if (io.rootLink >= 0) costHost += SAH_CI * rootArea;  else costHost += SAH_CT * rootArea * (double)n;
     io.sahCost = rootArea > 0.0 ? (float)(costHost / rootArea) : 0.f;
     cudaFree(slotLo);  cudaFree(slotHi);  cudaFree(sceneBox);  cudaFree(parent);  cudaFree(childBox);  cudaFree(visit);  cudaFree(costDev);
+    const float cms = bvhCollapse4(s, io);                   // the 4-wide nodes are copies of the binary records' boxes
+    if (refitMs) *refitMs += cms;
 }

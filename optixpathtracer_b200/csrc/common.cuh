@@ -23,6 +23,11 @@
 //   q[0] = c0.lo.x | c0.hi.x << 16,  q[1] = c0.lo.y | c0.hi.y << 16,  q[2] = c0.lo.z | c0.hi.z << 16,  q[3..5]: child 1
 struct BvhNode { unsigned q[6]; int link[2]; };
 static_assert(sizeof(BvhNode) == 32, "BvhNode must be 32 bytes");
+// The tree the traversal kernels read: the binary tree above collapsed to 4 children per node (64 bytes = two 256-bit loads).
+// Child c: q[3c..3c+2] in the BvhNode word layout, link[c].  Unused slots: inverted box (lo 65535, hi 0: never hit), link EMPTY.
+struct BvhNode4 { unsigned q[12]; int link[4]; };
+static_assert(sizeof(BvhNode4) == 64, "BvhNode4 must be 64 bytes");
+#define B200PT_LINK_EMPTY 0x7fffffff
 #define B200PT_GRID_ORIGIN 2.0      // grid coordinate of the scene AABB's low corner ...
 #define B200PT_GRID_SPAN 65531.0    // ... and the span of the scene AABB in cells: padded boxes stay inside [0, 65535]
 #define B200PT_GRID_PAD 2
@@ -48,7 +53,9 @@ struct MeshInfo {                  // device-side stand-in for the per-mesh SBT 
 static_assert(sizeof(MeshInfo) == 136, "MeshInfo");
 
 struct SceneDev {                  // everything the kernels need about the scene (passed by value)
-    const uint4* nodes;            // BvhNode records viewed as uint4 x2
+    const uint4* nodes;            // BvhNode records viewed as uint4 x2 (binary tree: parity hooks, refit)
+    const uint4* nodes4;           // BvhNode4 records viewed as uint4 x4 (what traceKernel walks)
+    int rootLink4;
     int rootLink;                  // link of the root (EMPTY sentinel 0x7fffffff for an empty scene)
     double gridLo[3], gridScale[3];   // world -> grid: g = GRID_ORIGIN + (x - gridLo) * gridScale
     const float4* tris;            // TriRecord viewed as float4 x3, BVH order
@@ -122,7 +129,7 @@ struct TraceStats { unsigned long long nodes, tris, rays; };
 // ---- launchers implemented in the .cu files ------------------------------------------------------------
 // bvh_build.cu
 struct BvhBuildResult {
-    BvhNode* nodes = nullptr;  int rootLink = 0x7fffffff;  double gridLo[3] = {0, 0, 0}, gridScale[3] = {1, 1, 1};
+    BvhNode* nodes = nullptr;  int rootLink = 0x7fffffff;  BvhNode4* nodes4 = nullptr;  int rootLink4 = 0x7fffffff;  unsigned nNodes4 = 0, maxDepth4 = 0;  double gridLo[3] = {0, 0, 0}, gridScale[3] = {1, 1, 1};
     float4* tris = nullptr;  unsigned nNodes = 0, nTris = 0, nLeaves = 0, maxLeaf = 0, maxDepth = 0;
     float sahCost = 0.f, sahCostLbvh = 0.f, buildMs = 0.f;
     unsigned long long* mortonByGid = nullptr;  uint32_t* sortedGid = nullptr;  uint32_t* finalGid = nullptr;  unsigned refineLevels = 0;  float sceneBounds[6] = {0, 0, 0, 0, 0, 0};

@@ -163,6 +163,28 @@ struct Best { float t, u, v; int slot; unsigned gid; };
         else cur = sp ? stack[--sp] : EMPTY;                                                     \
     }
 
+// One step through a 4-wide node (two 256-bit loads): test the four child boxes, order the hit ones by entry distance with a
+// 5-exchange sorting network, continue with the nearest and push the others, farthest first.
+#define CEX_(ta, la, tb, lb) { const bool s_ = tb < ta;  const float tt_ = s_ ? tb : ta;  const int ll_ = s_ ? lb : la;  tb = s_ ? ta : tb;  lb = s_ ? la : lb;  ta = tt_;  la = ll_; }
+#define NODE_STEP4()                                                                             \
+    {                                                                                            \
+        const uint4* np_ = S.nodes4 + 4 * (size_t)cur;                                           \
+        const Node8 A_ = ldgNode(np_), B_ = ldgNode(np_ + 2);                                    \
+        float t0_, t1_, t2_, t3_;                                                                \
+        const bool h0_ = boxTest(A_.w[0], A_.w[1], A_.w[2], g, tmin, best.t, t0_);               \
+        const bool h1_ = boxTest(A_.w[3], A_.w[4], A_.w[5], g, tmin, best.t, t1_);               \
+        const bool h2_ = boxTest(A_.w[6], A_.w[7], B_.w[0], g, tmin, best.t, t2_);               \
+        const bool h3_ = boxTest(B_.w[1], B_.w[2], B_.w[3], g, tmin, best.t, t3_);               \
+        const float inf_ = __int_as_float(0x7f800000);                                           \
+        t0_ = h0_ ? t0_ : inf_;  t1_ = h1_ ? t1_ : inf_;  t2_ = h2_ ? t2_ : inf_;  t3_ = h3_ ? t3_ : inf_;   \
+        int l0_ = (int)B_.w[4], l1_ = (int)B_.w[5], l2_ = (int)B_.w[6], l3_ = (int)B_.w[7];      \
+        CEX_(t0_, l0_, t1_, l1_)  CEX_(t2_, l2_, t3_, l3_)  CEX_(t0_, l0_, t2_, l2_)  CEX_(t1_, l1_, t3_, l3_)  CEX_(t1_, l1_, t2_, l2_)   \
+        if (t3_ < inf_) stack[sp++] = l3_;                                                       \
+        if (t2_ < inf_) stack[sp++] = l2_;                                                       \
+        if (t1_ < inf_) stack[sp++] = l1_;                                                       \
+        cur = t0_ < inf_ ? l0_ : (sp ? stack[--sp] : EMPTY);                                     \
+    }
+
 // Reference single-ray traversal (parity hooks only; the production kernels below inline the same steps).
 template <bool ANY, bool COUNT>
 __device__ __forceinline__ bool traverse(const SceneDev& S, const float3 o, const float3 d, float tmin, float tmax,
@@ -171,10 +193,11 @@ __device__ __forceinline__ bool traverse(const SceneDev& S, const float3 o, cons
     int stack[B200PT_STACK];
     int sp = 0;
     best.t = tmax;  best.slot = -1;  best.gid = 0xffffffffu;  best.u = best.v = 0.f;
-    int cur = S.rootLink;
+    int cur = S.rootLink4;
     while (cur != EMPTY) {
         if (cur >= 0) {
-            NODE_STEP()
+            if (COUNT) nNodes += 1;
+            NODE_STEP4()
         } else {
             unsigned first, count;
             leafDecode(cur, first, count);
@@ -235,7 +258,7 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
     const unsigned chunksC = (countC + 31u) >> 5, chunksTotal = chunksC + ((countS + 31u) >> 5);
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned ltMask = (1u << lane) - 1u;
-    const int rootLink = S.rootLink;
+    const int rootLink = S.rootLink4;
     unsigned nNodes[2] = {0, 0}, nTris[2] = {0, 0}, nRays[2] = {0, 0}, myNodes = 0, myTris = 0;
 
     // warp-uniform staging state: rays [stageNext, stageEnd) of the current chunk are still unassigned
@@ -329,21 +352,8 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
 #pragma unroll
             for (int sub_ = 0; sub_ < NODE_UNROLL; ++sub_)
             if (active && (unsigned)cur < (unsigned)EMPTY) {
-                const Node8 N_ = ldgNode(S.nodes + 2 * (size_t)cur);
                 if (COUNT) myNodes += 1;
-                float tl_, tr_;
-                const bool hl_ = boxTest(N_.w[0], N_.w[1], N_.w[2], g, tmin, best.t, tl_);
-                const bool hr_ = boxTest(N_.w[3], N_.w[4], N_.w[5], g, tmin, best.t, tr_);
-                const int cl_ = (int)N_.w[6], cr_ = (int)N_.w[7];
-                if (hl_ && hr_) {
-                    const bool sw_ = tr_ < tl_;
-                    const int far_ = sw_ ? cl_ : cr_;
-                    stack[sp++] = far_;
-                    if (TRACE_PREFETCH & 1) prefetchLink(S, far_);   // it will be popped after the near subtree: have its data in L1 by then
-                    cur = sw_ ? cr_ : cl_;
-                } else if (hl_) cur = cl_;
-                else if (hr_) cur = cr_;
-                else cur = sp ? stack[--sp] : EMPTY;
+                NODE_STEP4()
                 if (cur < 0 && leaf == NO_LEAF) {                  // first leaf: postpone it and keep walking
                     leaf = cur;
                     if (TRACE_PREFETCH & 2) prefetchLink(S, leaf);
@@ -437,7 +447,7 @@ static int refillThreshold() {
 static int leafThreshold() {
     if (g_leafThreshold < 0) {
         const char* e = getenv("B200PT_LEAF");                    // lanes blocked on a leaf before the warp intersects triangles
-        g_leafThreshold = e ? atoi(e) : 8;
+        g_leafThreshold = e ? atoi(e) : 12;
         if (g_leafThreshold < 1) g_leafThreshold = 1;
         if (g_leafThreshold > 32) g_leafThreshold = 32;
     }

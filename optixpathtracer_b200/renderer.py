@@ -250,6 +250,13 @@ class SampleRenderer:
         _lib.check(self._L.b200pt_download_bvh(self._h, _ptr(nodes), len(nodes), _ptr(tri_ids), len(tri_ids)))
         return nodes, tri_ids
 
+    def downloadBvh4(self):
+        """(n_wide_nodes, 16) uint32: the 4-wide nodes the traversal kernels read (include/b200pt.h)."""
+        info = self.bvhInfo()
+        nodes = np.empty((int(info.n_wide_nodes), 16), np.uint32)
+        _lib.check(self._L.b200pt_download_bvh4(self._h, _ptr(nodes), len(nodes)))
+        return nodes
+
 
 def computeFinalPixelColors(renderer, rgba_f32):
     """toneMap.cu:41-70 through the host-buffer convenience entry point."""

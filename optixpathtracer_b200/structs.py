@@ -151,7 +151,7 @@ class BvhInfo(C.Structure):
                 ("max_leaf_size", C.c_uint32), ("max_depth", C.c_uint32), ("sah_cost", C.c_float),
                 ("sah_cost_lbvh", C.c_float), ("build_ms", C.c_float), ("node_bytes", C.c_uint64),
                 ("tri_bytes", C.c_uint64), ("root_link", C.c_int32), ("refine_levels", C.c_uint32),
-                ("grid_lo", C.c_double * 3), ("grid_scale", C.c_double * 3), ("refit_ms", C.c_float), ("reserved", C.c_uint32)]
+                ("grid_lo", C.c_double * 3), ("grid_scale", C.c_double * 3), ("refit_ms", C.c_float), ("n_wide_nodes", C.c_uint32), ("wide_depth", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 class Counters(C.Structure):

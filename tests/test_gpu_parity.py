@@ -56,7 +56,7 @@ def test_bvh_structure(sponza_small):
     info = r.bvhInfo()
     nodes, tri_ids = r.downloadBvh()
     n = sponza_small.num_triangles()
-    assert info.n_triangles == n and np.array_equal(np.sort(tri_ids), np.arange(n)) and info.node_bytes == 32 * len(nodes)
+    assert info.n_triangles == n and np.array_equal(np.sort(tri_ids), np.arange(n)) and info.n_nodes == len(nodes)
     glo, gs = np.array(info.grid_lo[:]), np.array(info.grid_scale[:])
 
     def boxes(rec, k):                      # child k of record rec -> world-space (lo, hi), conservative
@@ -90,6 +90,38 @@ def test_bvh_structure(sponza_small):
                 stack.append((l, lo, hi))
     assert np.all(seen == 1) and leaves == info.n_leaves
     assert info.max_leaf_size <= 8 and info.sah_cost > 0 and info.sah_cost_lbvh > 0 and info.refine_levels >= 1
+
+    # the 4-wide tree the traversal kernels walk: the same leaves, each exactly once; every child box contains its triangles;
+    # unused slots are inverted boxes with the EMPTY link; at most as many nodes as binary records
+    wide = r.downloadBvh4()
+    assert info.n_wide_nodes == len(wide) and 0 < len(wide) <= len(nodes) and info.node_bytes == 64 * len(wide)
+    assert 3 * info.wide_depth + 4 <= 96
+    wl = wide[:, 12:16].view(np.int32)
+    q = wide[:, :12].astype(np.int64).reshape(-1, 4, 3)
+    wlo = glo + ((q & 0xffff) - 2.0) / gs
+    whi = glo + ((q >> 16) - 2.0) / gs
+    empty = wl == 0x7fffffff
+    assert np.all((q[empty] & 0xffff) == 0xffff) and np.all((q[empty] >> 16) == 0)
+    assert np.all((~empty).sum(1) >= 2)
+    seen4 = np.zeros(n, np.int32)
+    visited = np.zeros(len(wide), np.int32)
+    todo = [0]
+    while todo:
+        rec = todo.pop()
+        visited[rec] += 1
+        for k in range(4):
+            l = int(wl[rec, k])
+            if l == 0x7fffffff:
+                continue
+            if l < 0:
+                c = -(l + 1)
+                first, count = c >> 3, (c & 7) + 1
+                seen4[first:first + count] += 1
+                assert np.all(tlo[first:first + count] >= wlo[rec, k]) and np.all(thi[first:first + count] <= whi[rec, k])
+            else:
+                assert 0 < l < len(wide)
+                todo.append(l)
+    assert np.all(seen4 == 1) and np.all(visited == 1)
     r.close()
 
 
