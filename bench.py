@@ -167,7 +167,7 @@ def run_reference(a):
             "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": last["cores"], "kind": last["kind"], "sample": last["sample"]},
             "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------ the B200 arm
@@ -372,15 +372,31 @@ def run_b200(a):
         if not a.no_cpu_baseline and world == 1:
             cb = cpu_baseline(a, model, cam, probe, cfg, a.cpu_seconds)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "mrays_per_s")}
-        print(json.dumps(line), flush=True)
+        emit(line)
     r.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+_JSON_OUT = None
+
+
+def emit(line):
+    """The one JSON line goes to the REAL stdout; everything else any library prints to fd 1 (NCCL's version banner, torchrun
+    notices) was pointed at stderr by main()."""
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    global _JSON_OUT
     a = parse()
+    if not (a.impl != "reference" and a.gpus > 1 and "WORLD_SIZE" not in os.environ):
+        sys.stdout.flush()
+        _JSON_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)                                     # fd 1 -> stderr for the rest of the process (C libraries included)
     if a.impl == "reference":
         run_reference(a)
         return
