@@ -336,6 +336,13 @@ def run_b200(a):
     if rank == 0:
         peak, peak_src = _peaks()
         # one traceKernel launch per bounce traces the extension rays AND the previous pass's shadow rays
+        traffic, traffic_src = None, None                  # DRAM bytes per traceKernel launch from the committed ncu --set full capture
+        try:
+            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")) as f:
+                tj = json.load(f)
+            traffic, traffic_src = float(tj["dram_bytes_per_launch"]), tj["source"]
+        except (OSError, KeyError, ValueError):
+            pass
         bytes_closest_per_frame = (64 * nodes + 48 * tris + (32 + 16) * crays) / replay
         bytes_any_per_frame = (64 * nodes_s + 48 * tris_s + (32 + 4) * srays) / replay
         launches_per_frame = n_closest / a.steps
@@ -358,7 +365,7 @@ def run_b200(a):
                             f"({ctor_s:.2f} s incl. LBVH build {float(info.build_ms):.2f} ms)"},
             "gpu_launches": int(all_launches),
             "roofline": {"bound": "hbm", "kernel": "traceKernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src,
+                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": bytes_per_launch, "launches_per_step": launches_per_frame,
                          "avg_launch_ms": ms_per_launch,
                          "nodes_per_ray": nodes / max(1, crays), "tris_per_ray": tris / max(1, crays),

@@ -99,7 +99,8 @@ DEV float3 sampleTexture(const SceneDev& S, const MeshInfo* M, float s, float t)
     const float fx = floorf(x), fy = floorf(y);
     const float a = x - fx, b = y - fy;
     int i0 = (int)fx, j0 = (int)fy, i1 = i0 + 1, j1 = j0 + 1;
-    i0 = ((i0 % W) + W) % W;  i1 = ((i1 % W) + W) % W;  j0 = ((j0 % H) + H) % H;  j1 = ((j1 % H) + H) % H;
+    // wrap: x is in [-0.5, W - 0.5], so i0 is in [-1, W - 1] and i1 in [0, W] (same for j): one conditional add replaces the modulo
+    i0 += i0 < 0 ? W : 0;  i1 -= i1 >= W ? W : 0;  j0 += j0 < 0 ? H : 0;  j1 -= j1 >= H ? H : 0;
     const uint32_t* px = S.texels + M->texOffset;
     const uint32_t p00 = __ldg(px + (size_t)j0 * W + i0), p10 = __ldg(px + (size_t)j0 * W + i1);
     const uint32_t p01 = __ldg(px + (size_t)j1 * W + i0), p11 = __ldg(px + (size_t)j1 * W + i1);
