@@ -1,0 +1,107 @@
+"""BASELINE.json's full-size configurations on the GPU, checked through size-independent properties (the CPU oracle would need
+minutes per frame at these sizes): conservation of samples and ray budgets, determinism, tile split = full frame bit for bit,
+sample-split sum = running mean, foveated schedule coverage, and primary-hit parity on a bounded random subset of pixels."""
+import numpy as np
+import pytest
+
+from optixpathtracer_b200 import SampleRenderer, host_params, preset, preset_camera, scenes
+from optixpathtracer_b200.probe import analytic_sky
+
+pytestmark = pytest.mark.gpu
+
+W, H = 1920, 1080
+
+
+@pytest.fixture(scope="module")
+def sponza_full():
+    return scenes.sponza_class(262144)
+
+
+@pytest.fixture(scope="module")
+def probe():
+    return analytic_sky(2048, 1024)
+
+
+def _renderer(model, probe, size, cfg, cam=None):
+    r = SampleRenderer(model, device=0, config=cfg)
+    r.resize(size)
+    r.setCamera(cam or preset_camera("sponza"))
+    r.setProbe(probe)
+    return r
+
+
+def test_c2_sponza_class_1080p_properties(port, sponza_full, probe):
+    """configs[1]: ~262k triangles, 1920x1080, 1 spp/frame, preset orig (depth 8)."""
+    cfg = preset("orig", uniform_spl=1)
+    cfg.accumulate = 1
+    r = _renderer(sponza_full, probe, (W, H), cfg)
+    r.launchParams.samples_per_launch = 1
+    info = r.bvhInfo()
+    assert abs(info.n_triangles - 262144) < 0.02 * 262144 and info.n_wide_nodes > 0 and info.sah_cost < info.sah_cost_lbvh
+    frames = []
+    for sub in range(2):
+        r.launchParams.frame.subframe_index = sub
+        r.render()
+        c = r.counters()
+        assert c.samples == W * H                                          # one camera path per pixel per frame
+        assert W * H <= c.radiance_rays <= 9 * W * H                       # <= max_depth + 1 radiance segments per sample
+        assert c.shadow_rays <= c.radiance_rays                            # at most one NEE ray per closest-hit event
+        frames.append(r.downloadAccum().copy())
+    a = frames[1]
+    assert np.isfinite(a).all() and a[..., :3].min() >= 0.0 and a[..., :3].max() <= 10.0 + 1e-3   # running mean of clamped passes (:547)
+    assert 0.005 < a[..., :3].mean() < 5.0
+    # determinism: the same two sub-frames again give the same bits
+    r2 = _renderer(sponza_full, probe, (W, H), cfg)
+    r2.launchParams.samples_per_launch = 1
+    for sub in range(2):
+        r2.launchParams.frame.subframe_index = sub
+        r2.render()
+    assert np.array_equal(r2.downloadAccum(), a)
+    # tile split over 4 ranks reassembles the full frame bit for bit
+    whole = frames[0]
+    parts = np.zeros_like(whole)
+    rows = np.arange(H)
+    for rank in range(4):
+        cfg_t = preset("orig", uniform_spl=1, tile_rank=rank, tile_count=4)
+        cfg_t.accumulate = 1
+        rt = _renderer(sponza_full, probe, (W, H), cfg_t)
+        rt.launchParams.samples_per_launch = 1
+        rt.launchParams.frame.subframe_index = 0
+        rt.render()
+        mine = ((rows // 32) % 4) == rank
+        parts[mine] = rt.downloadAccum()[mine]
+        rt.close()
+    assert np.array_equal(parts, whole)
+    # primary hits: a bounded random subset of pixels against the oracle (prim ids >= 99.99 %, t bit-equal where they agree)
+    r.launchParams.frame.subframe_index = 0
+    prim, mesh, t, _, _ = r.tracePrimary()
+    p = host_params(W, H, preset_camera("sponza"), samples_per_launch=1)
+    oprim, omesh, ot, _, _ = port.scene(sponza_full, probe).trace_primary(p, cfg)
+    sel = np.random.default_rng(3).choice(W * H, 200000, replace=False)
+    same = (prim[sel] == oprim[sel]) & (mesh[sel] == omesh[sel])
+    assert same.mean() >= 0.9999
+    assert np.array_equal(t[sel][same].view(np.uint32), ot[sel][same].view(np.uint32))
+    r.close();  r2.close()
+
+
+def test_c4_foveated_4k_schedule(sponza_full, probe):
+    """configs[3]: 3840x2160 sv4 foveated three-pass schedule, gaze at the centre: (almost) every pixel is written, the three rings carry the
+    reference's sample budgets (1 / 2 / 8 spl), and the frame is deterministic."""
+    cfg = preset("sv4_fov")
+    r = _renderer(sponza_full, probe, (3840, 2160), cfg)
+    r.launchParams.frame.c.x, r.launchParams.frame.c.y = 1920, 1080
+    r.launchParams.frame.subframe_index = 0
+    r.render()
+    c = r.counters()
+    px = r.downloadPixels()
+    written = ((px >> 24) == 255).mean()                                   # alpha byte set by make_color; like the reference, ring seams can stay unwritten
+    assert written > 0.98, written
+    # budgets: outer pass W/4 x H/4 launch indices outside the 515 ring, middle ring at half resolution x2, fovea at full x8
+    outer = 960 * 540
+    assert outer * 0.5 < c.samples < outer + 2 * (517 ** 2) + 8 * (316 ** 2)
+    acc = r.downloadAccum()
+    assert np.isfinite(acc).all()
+    r.launchParams.frame.subframe_index = 0
+    r.render()
+    assert np.array_equal(r.downloadPixels(), px)
+    r.close()
