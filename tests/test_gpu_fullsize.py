@@ -105,3 +105,29 @@ def test_c4_foveated_4k_schedule(sponza_full, probe):
     r.render()
     assert np.array_equal(r.downloadPixels(), px)
     r.close()
+
+
+def test_c1_cornell_converged_1024spp_rmse(port, probe):
+    """configs[0] at the north_star bar: Cornell box, 16 spp x 64 accumulated sub-frames = 1024 spp, 4 bounces (sv4 uniform preset),
+    Disney materials.  Converged image RMSE against the CPU oracle <= 1e-3 (256x256: the CPU oracle needs ~10 s for its 67 M samples)."""
+    from optixpathtracer_b200 import loadColor
+    model = scenes.cornell("disney")
+    sky = loadColor((1.0, 1.0, 1.0), 64, 32)
+    cfg = preset("sv4_uniform", uniform_spl=16)
+    cfg.accumulate = 1
+    cam = preset_camera("cornell")
+    r = _renderer(model, sky, (256, 256), cfg, cam)
+    for sub in range(64):
+        r.launchParams.frame.subframe_index = sub
+        r.render()
+    got = r.downloadAccum()
+    r.close()
+    sc = port.scene(model, sky, brute_force=True)
+    p = host_params(256, 256, cam, samples_per_launch=16)
+    accum = frame = None
+    for sub in range(64):
+        p.frame.subframe_index = sub
+        accum, frame, _, _ = sc.render(p, cfg, accum, frame)
+    rmse = float(np.sqrt(np.mean((got[..., :3] - accum[..., :3]) ** 2)))
+    assert rmse <= 1e-3, rmse
+    assert abs(float(got[..., :3].mean()) - float(accum[..., :3].mean())) < 1e-3 * float(accum[..., :3].mean())
