@@ -293,7 +293,7 @@ def run_b200(a):
     if world > 1:
         cfg.accum_mode = 0
         r.resize((a.width, a.height))
-    host_px = np.empty((a.height, a.width), np.uint32)
+    host_px = torch.empty((a.height, a.width), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)   # pinned host frame buffer
     for i in range(2):
         r.setCamera(cam)
         r.launchParams.frame.subframe_index = frame_index(i)
