@@ -132,6 +132,11 @@ def cpu_baseline(a, model, cam, probe, cfg, seconds, want_ref=True):
     from oracle import binding
     kind = "reference" if (want_ref and os.path.exists(binding.REF_SO)) else "port"
     orc = binding.Oracle(kind)
+    try:                                               # all host threads this process may use; torchrun exports OMP_NUM_THREADS=1, which
+        avail = len(os.sched_getaffinity(0))           # would silently turn the CPU arm into a single-thread run
+    except AttributeError:
+        avail = os.cpu_count() or 1
+    orc.set_threads(avail)
     cores = orc.max_threads()
     sc = orc.scene(model, probe)
     p = host_params(a.width, a.height, cam, samples_per_launch=a.spl)
