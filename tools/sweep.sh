@@ -5,6 +5,6 @@ for e in "$@"; do
   python - "$e" <<'PY'
 import json, sys
 d=json.load(open("gpurun_out/sweep.json"))
-print(sys.argv[1], "Msamples/s", round(d["value"],1), "Mrays/s", round(d["mrays_per_s"],1), {k:round(v,3) for k,v in d["stage_ms_per_step"].items()}, "nodes/ray", round(d["roofline"]["nodes_per_ray"],1))
+print(sys.argv[1], "Msamples/s", round(d["value"],1), "ms", round(d["ms_per_step"],3), "e2e", round(d["e2e"]["value"],1), "Mrays/s", round(d["mrays_per_s"],1), {k:round(v,3) for k,v in d["stage_ms_per_step"].items()}, "nodes/ray", round(d["roofline"]["nodes_per_ray"],1))
 PY
 done
