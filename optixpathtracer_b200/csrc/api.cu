@@ -33,7 +33,7 @@ struct b200pt_ctx {
     // --- frame
     int W = 0, H = 0;
     DevBuf<uint32_t> frameBuf;  DevBuf<float4> accumBuf, normalBuf, albedoBuf, colorBuf;
-    DevBuf<float> probeData, probePdfX, probeCdfX, probePdfY, probeCdfY, probeCoarse, probeRowTotal;  int probeW = 0, probeH = 0;
+    DevBuf<float> probeData, probePdfX, probeCdfX, probePdfY, probeCdfY, probeRowTotal;  DevBuf<int> probeGuide;  int probeW = 0, probeH = 0;
     // --- wavefront pool
     size_t poolCap = 0;
     DevBuf<uint2> rng;  DevBuf<float4> thr, direct, indirect, alpha, pending, aovN, aovA;  DevBuf<int> state;  DevBuf<float> bsdfPdf;
@@ -93,7 +93,7 @@ void b200pt_destroy(b200pt_ctx* c) {
     bvhFree(c->bvh);
     c->dVertices.release();  c->dNormals.release();  c->dTexcoords.release();  c->dIndices.release();  c->dTriMesh.release();  c->dMeshes.release();  c->dTexels.release();
     c->frameBuf.release();  c->accumBuf.release();  c->normalBuf.release();  c->albedoBuf.release();  c->colorBuf.release();
-    c->probeData.release();  c->probePdfX.release();  c->probeCdfX.release();  c->probePdfY.release();  c->probeCdfY.release();  c->probeCoarse.release();  c->probeRowTotal.release();
+    c->probeData.release();  c->probePdfX.release();  c->probeCdfX.release();  c->probePdfY.release();  c->probeCdfY.release();  c->probeGuide.release();  c->probeRowTotal.release();
     c->rng.release();  c->thr.release();  c->direct.release();  c->indirect.release();  c->alpha.release();  c->pending.release();
     c->aovN.release();  c->aovA.release();  c->state.release();  c->bsdfPdf.release();
     for (int i = 0; i < 2; ++i) { c->rayO[i].release();  c->rayD[i].release(); }

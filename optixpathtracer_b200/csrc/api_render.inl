@@ -127,8 +127,8 @@ static FrameParams frameOf(const LaunchParams& P, const b200pt_config& cfg, cons
     F.W = P.frame.size.x;  F.H = P.frame.size.y;
     F.eye = P.camera.eye;  F.U = P.camera.U;  F.V = P.camera.V;  F.Wv = P.camera.W;
     F.probe = P.probe;
-    // the coarse CDF table belongs to the probe uploaded by b200pt_set_probe; a caller-substituted probe falls back
-    F.cdfXCoarse = (c && c->probeCoarse.p && P.probe.cdfValuesX == c->probeCdfX.p && P.probe.width == c->probeW && P.probe.height == c->probeH) ? c->probeCoarse.p : nullptr;
+    // the guide tables belong to the probe uploaded by b200pt_set_probe*; a caller-substituted probe falls back to the plain search
+    F.probeGuide = (c && c->probeGuide.p && P.probe.cdfValuesX == c->probeCdfX.p && P.probe.cdfValuesY == c->probeCdfY.p && P.probe.width == c->probeW && P.probe.height == c->probeH) ? c->probeGuide.p : nullptr;
     F.tmin = cfg.tmin;  F.tmax = cfg.tmax;  F.maxDepth = cfg.max_depth;  F.shadowMode = cfg.shadow_mode;  F.display = cfg.display;
     F.accumMode = cfg.accum_mode;  F.writeAovs = cfg.write_aovs;  F.russianRoulette = cfg.russian_roulette;  F.misOnMiss = cfg.mis_on_miss;  F.exposure = cfg.exposure;
     F.tileRank = cfg.tile_rank;  F.tileCount = cfg.tile_count;
@@ -274,8 +274,8 @@ int b200pt_set_probe(b200pt_ctx* c, int w, int h, const float* data, const float
     CUDA_OK(cudaMemcpyAsync(c->probeCdfX.p, cdfX, 4 * n, cudaMemcpyHostToDevice, c->stream));
     CUDA_OK(cudaMemcpyAsync(c->probePdfY.p, pdfY, 4 * (size_t)h, cudaMemcpyHostToDevice, c->stream));
     CUDA_OK(cudaMemcpyAsync(c->probeCdfY.p, cdfY, 4 * (size_t)h, cudaMemcpyHostToDevice, c->stream));
-    c->probeCoarse.ensure((size_t)((w + 31) / 32) * h);
-    launchProbeCoarse(c->probeCdfX.p, w, h, c->probeCoarse.p, c->stream);
+    c->probeGuide.ensure(probeGuideSize(h));
+    launchProbeGuide(c->probeCdfX.p, c->probeCdfY.p, w, h, c->probeGuide.p, c->stream);
     c->probeW = w;  c->probeH = h;
     CUDA_OK(cudaStreamSynchronize(c->stream));
     params->probe.width = w;  params->probe.height = h;  params->probe.data = (Color*)c->probeData.p;
@@ -338,11 +338,11 @@ int b200pt_set_probe_image(b200pt_ctx* c, int w, int h, const float* data, const
     CUDA_OK(cudaSetDevice(c->device));
     const size_t n = (size_t)w * h;
     c->probeData.ensure(4 * n);  c->probePdfX.ensure(n);  c->probeCdfX.ensure(n);  c->probePdfY.ensure(h);  c->probeCdfY.ensure(h);
-    c->probeCoarse.ensure((size_t)((w + 31) / 32) * h);
+    c->probeGuide.ensure(probeGuideSize(h));
     c->probeRowTotal.ensure(h);
     CUDA_OK(cudaMemcpyAsync(c->probeData.p, data, 16 * n, cudaMemcpyHostToDevice, c->stream));
     launchProbeCdf((const float4*)c->probeData.p, w, h, c->probePdfX.p, c->probeCdfX.p, c->probePdfY.p, c->probeCdfY.p, c->probeRowTotal.p, c->stream);
-    launchProbeCoarse(c->probeCdfX.p, w, h, c->probeCoarse.p, c->stream);
+    launchProbeGuide(c->probeCdfX.p, c->probeCdfY.p, w, h, c->probeGuide.p, c->stream);
     CUDA_OK(cudaGetLastError());
     c->probeW = w;  c->probeH = h;
     CUDA_OK(cudaStreamSynchronize(c->stream));

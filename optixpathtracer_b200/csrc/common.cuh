@@ -86,7 +86,7 @@ struct FrameParams {               // shared by every pass of a frame
     int W, H;
     float3 eye, U, V, Wv;
     Probe probe;                   // device pointers
-    const float* cdfXCoarse;       // every 32nd entry of each cdfValuesX row (nullptr: plain binary search)
+    const int* probeGuide;         // guide tables of the probe's CDFs (shade_math.cuh; nullptr: plain binary search)
     float tmin, tmax;
     int maxDepth, shadowMode, display, accumMode, writeAovs, russianRoulette, misOnMiss;
     float exposure;
@@ -162,7 +162,8 @@ struct WhittedParams { int W, H;  float3 position, direction, horizontal, vertic
 void launchWhittedRaygen(const WhittedParams& P, const Queues& Q, const PathPool& pool, unsigned* counters, cudaStream_t stream);
 void launchWhittedShade(const WhittedParams& P, const SceneDev& scene, const PathPool& pool, const Queues& Q, unsigned* shadowCounter, cudaStream_t stream);
 void launchWhittedFinish(const WhittedParams& P, const PathPool& pool, uint32_t* colorBuffer, cudaStream_t stream);
-void launchProbeCoarse(const float* cdfX, int W, int H, float* coarse, cudaStream_t stream);
+size_t probeGuideSize(int H);
+void launchProbeGuide(const float* cdfX, const float* cdfY, int W, int H, int* guide, cudaStream_t stream);
 void launchProbeCdf(const float4* data, int W, int H, float* pdfX, float* cdfX, float* pdfY, float* cdfY, float* rowTotal, cudaStream_t stream);
 void launchTonemapSqrt(int w, int h, const float4* in, uint32_t* out, cudaStream_t stream);
 void launchPrimaryRays(const FrameParams& F, const PassParams& P, float4* rayO, float4* rayD, cudaStream_t stream);

@@ -188,7 +188,7 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                         Rng rng;  rng.s1 = rs.x;  rng.s2 = rs.y;
                         // SampleLights / SampleShadow, :301-384
                         float3 wi, skyColor;  float skyPdf;
-                        probeSample(F.probe, F.cdfXCoarse, wi, skyColor, skyPdf, rng);
+                        probeSample(F.probe, F.probeGuide, wi, skyColor, skyPdf, rng);
                         const float bp = bsdfPdf(mat, rayEta, outEta, N, wo, wi);
                         float3 pend = f3(0.f);
                         bool valid = false;
@@ -393,17 +393,20 @@ __global__ void resolvePrimaryKernel(SceneDev S, const float4* hit, unsigned n, 
     t[i] = h.x;  u[i] = h.y;  v[i] = h.z;
 }
 
-// every 32nd entry (the LAST of each 32-block) of each CDF row; see lowerBoundRow
-__global__ void probeCoarseKernel(const float* __restrict__ cdfX, int W, int H, float* __restrict__ coarse) {
-    const int nc = (W + 31) >> 5;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nc * H) return;
-    const int row = i / nc, k = i % nc;
-    coarse[i] = cdfX[(size_t)row * W + min(W - 1, 32 * k + 31)];
+// guide tables for probeSample (shade_math.cuh): [0, GY] for cdfValuesY, then GX + 1 entries per row of cdfValuesX
+__global__ void probeGuideKernel(const float* __restrict__ cdfX, const float* __restrict__ cdfY, int W, int H, int* __restrict__ guide) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t nY = B200PT_GUIDE_Y + 1, nX = (size_t)H * (B200PT_GUIDE_X + 1);
+    if (i < nY) guide[i] = lowerBound(cdfY, 0, H, (float)i / (float)B200PT_GUIDE_Y);
+    else if (i < nY + nX) {
+        const int row = (int)((i - nY) / (B200PT_GUIDE_X + 1)), k = (int)((i - nY) % (B200PT_GUIDE_X + 1));
+        guide[i] = lowerBound(cdfX, row * W, (row + 1) * W, (float)k / (float)B200PT_GUIDE_X) - row * W;
+    }
 }
-void launchProbeCoarse(const float* cdfX, int W, int H, float* coarse, cudaStream_t s) {
-    const int n = ((W + 31) >> 5) * H;
-    if (n > 0) probeCoarseKernel<<<(n + 255) / 256, 256, 0, s>>>(cdfX, W, H, coarse);
+size_t probeGuideSize(int H) { return (size_t)(B200PT_GUIDE_Y + 1) + (size_t)H * (B200PT_GUIDE_X + 1); }
+void launchProbeGuide(const float* cdfX, const float* cdfY, int W, int H, int* guide, cudaStream_t s) {
+    const size_t n = probeGuideSize(H);
+    probeGuideKernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(cdfX, cdfY, W, H, guide);
 }
 
 // ---- ProbeData::BuildCDF on the device (sv4/Probe.h:29-77) ---------------------------------------------------

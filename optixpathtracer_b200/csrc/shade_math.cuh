@@ -278,22 +278,28 @@ DEV int lowerBound(const float* __restrict__ a, int lower, int upper, float valu
     }
     return lower;
 }
-// Same index as LowerBound over the whole row (the row CDF is non-decreasing, so lower_bound is unique), found in
-// two steps: a search over every 32nd entry (coarse table built by b200pt_set_probe, 1/32 of the footprint, so it
-// stays cache-resident) and a search inside one 128-byte line of the full table: ~3 cache misses instead of ~11.
-DEV int lowerBoundRow(const Probe& P, const float* __restrict__ coarse, int row, float value) {
-    const int W = P.width, base = row * W;
-    if (!coarse) return lowerBound(P.cdfValuesX, base, base + W, value) - base;
-    const int nc = (W + 31) >> 5;
-    const int k = lowerBound(coarse, row * nc, (row + 1) * nc, value) - row * nc;
-    if (k == nc) return W;                                       // value above the last entry: LowerBound returns `upper`
-    return lowerBound(P.cdfValuesX, base + 32 * k, base + min(32 * k + 32, W), value) - base;
+// Guide tables (built by b200pt_set_probe*): guide[k] = LowerBound(cdf, k / G) for k = 0..G.  LowerBound is monotone in `value`, so
+// for value in [k/G, (k+1)/G) the answer lies in [guide[k], guide[k+1]] and a search of that short range with the SAME comparison
+// returns the SAME index as the reference's search of the whole array (each CDF is non-decreasing) — in ~3 dependent loads
+// instead of log2(n) ~ 10-11.  G is a power of two, so k/G and value*G are exact.
+#define B200PT_GUIDE_Y 1024
+#define B200PT_GUIDE_X 256
+DEV int guidedLowerBound(const float* __restrict__ a, int base, const int* __restrict__ guide, int G, float value) {
+    const int k = min(G - 1, max(0, (int)(value * (float)G)));
+    const int lo = __ldg(guide + k), hi = __ldg(guide + k + 1);
+    return lowerBound(a, base + lo, base + hi, value) - base;
 }
-DEV void probeSample(const Probe& P, const float* __restrict__ coarse, float3& dir, float3& color, float& pdf, Rng& rand) {   // :138-169
+DEV void probeSample(const Probe& P, const int* __restrict__ guide, float3& dir, float3& color, float& pdf, Rng& rand) {   // :138-169
     float r1, r2;
     sample2D(rand, r1, r2);
-    const int row = lowerBound(P.cdfValuesY, 0, P.height, r1);
-    const int col = lowerBoundRow(P, coarse, row, r2);
+    int row, col;
+    if (guide) {
+        row = guidedLowerBound(P.cdfValuesY, 0, guide, B200PT_GUIDE_Y, r1);
+        col = guidedLowerBound(P.cdfValuesX, row * P.width, guide + (B200PT_GUIDE_Y + 1) + (size_t)row * (B200PT_GUIDE_X + 1), B200PT_GUIDE_X, r2);
+    } else {
+        row = lowerBound(P.cdfValuesY, 0, P.height, r1);
+        col = lowerBound(P.cdfValuesX, row * P.width, (row + 1) * P.width, r2) - row * P.width;
+    }
     const float4 c = __ldg(reinterpret_cast<const float4*>(P.data) + (row * P.width + col));
     color = f3(c.x, c.y, c.z);
     pdf = __ldg(P.pdfValuesX + row * P.width + col) * __ldg(P.pdfValuesY + row);
