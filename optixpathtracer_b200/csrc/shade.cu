@@ -149,6 +149,13 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
             } else {
                 const float4 ta = __ldg(S.tris + 3 * (size_t)triSlot), tb = __ldg(S.tris + 3 * (size_t)triSlot + 1),
                              tc = __ldg(S.tris + 3 * (size_t)triSlot + 2);
+                // The probe sample of this vertex (SampleLights, :301-384) depends only on the path's RNG state: start its chain of
+                // dependent table lookups now, while the triangle / mesh / material loads above are still in flight.  The RNG state
+                // is committed further down, only where the reference really draws the sample.
+                const uint2 rs = pool.rng[slot];
+                Rng rng;  rng.s1 = rs.x;  rng.s2 = rs.y;
+                float3 wi, skyColor;  float skyPdf;
+                probeSample(F.probe, F.probeGuide, wi, skyColor, skyPdf, rng);
                 const float3 e1 = f3(ta.w, tb.x, tb.y), e2 = f3(tb.z, tb.w, tc.x);
                 const unsigned gid = (unsigned)__float_as_int(tc.y);
                 const MeshInfo* M = S.meshes + __float_as_int(tc.z);
@@ -184,11 +191,7 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                     if (last && !catcher) {
                         flags |= PF_DONE;
                     } else {
-                        const uint2 rs = pool.rng[slot];
-                        Rng rng;  rng.s1 = rs.x;  rng.s2 = rs.y;
-                        // SampleLights / SampleShadow, :301-384
-                        float3 wi, skyColor;  float skyPdf;
-                        probeSample(F.probe, F.probeGuide, wi, skyColor, skyPdf, rng);
+                        // SampleLights / SampleShadow, :301-384 (probe sample drawn above)
                         const float bp = bsdfPdf(mat, rayEta, outEta, N, wo, wi);
                         float3 pend = f3(0.f);
                         bool valid = false;
@@ -464,7 +467,7 @@ void launchProbeCdf(const float4* data, int W, int H, float* pdfX, float* cdfX, 
 
 // ---- launchers ---------------------------------------------------------------------------------------------
 static inline unsigned gridFor(unsigned n) { return (n + SHADE_BLOCK - 1) / SHADE_BLOCK; }
-static const unsigned kPersistentGrid = B200PT_NUM_SMS * 8;
+static const unsigned kPersistentGrid = B200PT_NUM_SMS * SHADE_MIN_BLOCKS;
 
 void launchRaygen(const FrameParams& F, const PassParams& P, int k0, int k1, const PathPool& pool, const Queues& Q, cudaStream_t s) {
     raygenKernel<<<kPersistentGrid, SHADE_BLOCK, 0, s>>>(F, P, k0, k1, pool, Q);
