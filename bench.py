@@ -320,7 +320,7 @@ def run_b200(a):
         t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
-    e2e_value = n_px * a.spl * a.steps * world / e2e_s / 1e6
+    e2e_value = all_samples / e2e_s / 1e6                                       # the same a.steps frames as the timed region: same sample count
 
     # ---- per-stage CUDA-event timings: the same frames again with a CUDA-event pair around every kernel of the frame
     cfg.profile = 1
