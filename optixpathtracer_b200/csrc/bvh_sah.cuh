@@ -14,7 +14,9 @@
 #define JOB_T 512                       // max items per treelet job
 #define JOB_THREADS 256
 #define JOB_WARPS (JOB_THREADS / 32)
+#ifndef SAH_BINS
 #define SAH_BINS 16
+#endif
 #define LINK_LOCAL 0x40000000           // job-local pair index (relocated on write-out)
 #define REC_ROOT 0xffffu
 

@@ -37,7 +37,9 @@ __host__ __device__ inline void leafDecode(int link, unsigned& first, unsigned& 
     unsigned c = (unsigned)(-(link + 1));
     first = c >> 3;  count = (c & 7u) + 1u;
 }
+#ifndef B200PT_MAX_LEAF
 #define B200PT_MAX_LEAF 8
+#endif
 #define B200PT_STACK 96
 
 struct MeshInfo {                  // device-side stand-in for the per-mesh SBT record (sv4/LaunchParams.h:38-47)
