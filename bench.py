@@ -70,6 +70,16 @@ def build_workload(a):
     return model, cam, probe, cfg
 
 
+def reference_optix_status():
+    """north_star asks for the reference's OptiX-on-B200 time beside ours.  The reference cannot be built without the NVIDIA OptiX SDK 7.5
+    headers (un-vendored: CMake/FindOptiX.cmake:32-76 expects them next to the source tree), so one look for optix.h decides."""
+    for root in ("/usr/include", "/usr/local/include", "/usr/local/cuda/include", "/opt"):
+        for sub in ("", "optix", "optix/include", "OptiX/include", "nvidia/optix/include"):
+            if os.path.isfile(os.path.join(root, sub, "optix.h")):
+                return {"available": False, "why": f"optix.h found under {os.path.join(root, sub)} but the reference's OptiX build is not wired into this bench"}
+    return {"available": False, "why": "unavailable in this environment: no optix.h on the box (the OptiX SDK 7.5 headers are an un-vendored dependency of the reference)"}
+
+
 def config_json(a, model, extra=None):
     c = {"workload": f"{a.scene}-class procedural scene, {model.num_triangles()} triangles, {a.width}x{a.height}, "
                      f"{a.spl} spp/frame progressive, preset {a.preset} (max depth {8 if a.preset == 'orig' else 4}), Disney BSDF + probe NEE",
@@ -381,6 +391,7 @@ def run_b200(a):
                     "note": "setCamera + render() (blocking) + downloadPixels() into host memory every step; scene/BVH upload is one-off in the ctor "
                             f"({ctor_s:.2f} s incl. LBVH build {float(info.build_ms):.2f} ms)"},
             "gpu_launches": int(all_launches),
+            "reference_optix": reference_optix_status(),
             "roofline": {"bound": "hbm", "kernel": "traceKernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": bytes_per_launch, "launches_per_step": launches_per_frame,
