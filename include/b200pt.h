@@ -81,7 +81,7 @@ int b200pt_add_mesh(b200pt_ctx* ctx,
                     const struct Material* material,
                     int diffuse_texture_id);            /* -1 = none; returns meshID >= 0, or -1         */
 /* LBVH build: Morton codes -> radix sort -> Karras hierarchy -> refit -> SAH leaf collapse + treelet
- * refinement -> 32-byte two-child nodes (16-bit quantised boxes) + 48-byte triangle records.  Replaces optixAccelBuild/optixAccelCompact
+ * refinement -> 32-byte two-child records (16-bit quantised boxes), collapsed to 64-byte 4-wide nodes, + 48-byte triangle records.  Replaces optixAccelBuild/optixAccelCompact
  * (sv4/SimplePathtracer.cpp:670-737).  *handle_out receives the value for LaunchParams.traversable. */
 int b200pt_build_accel(b200pt_ctx* ctx, uint64_t* handle_out);
 
@@ -183,7 +183,7 @@ int b200pt_download_bvh4(b200pt_ctx* ctx, void* nodes64, size_t max_nodes);
 typedef struct b200pt_counters {      /* last render()                                                  */
     uint64_t samples;                 /* camera paths started                                           */
     uint64_t radiance_rays, shadow_rays;
-    uint64_t nodes_fetched, tris_fetched;      /* 32-byte node records / 48-byte Woop triangles (profile=1) */
+    uint64_t nodes_fetched, tris_fetched;      /* 64-byte 4-wide nodes / 48-byte triangle records (profile bit 1) */
     uint64_t nodes_fetched_shadow, tris_fetched_shadow;
     float    ms_total, ms_raygen, ms_trace_closest, ms_trace_any, ms_shade, ms_accumulate;   /* profile=1 */
     uint32_t kernel_launches;         /* kernels launched by the last render()                          */

@@ -6,13 +6,13 @@
 // Persistent warps (a fixed grid of B200PT_NUM_SMS x k CTAs).  Each warp stages chunks of 32 rays from the
 // device-side queues into shared memory (one ticket atomic per chunk, cp.async, double-buffered and prefetched);
 // a lane whose ray terminates takes the next staged ray as soon as enough lanes are idle (per-lane replacement
-// decided by a warp vote), so a warp never idles behind its slowest ray.  Every loop iteration each lane takes
-// ONE inner-node step if it can; a lane that reaches a leaf postpones it and keeps walking; once enough lanes
+// decided by a warp vote), so a warp never idles behind its slowest ray.  Every loop iteration each lane takes up to
+// NODE_UNROLL inner-node steps if it can; a lane that reaches a leaf postpones it and keeps walking; once enough lanes
 // are blocked on a second leaf (warp vote) the warp intersects all pending leaves together.
-// A traversal step is ONE 256-bit load (LDG.E.256, new on sm_100): the 32-byte record of an inner node holds both child
-// boxes, quantised to a 16-bit grid over the scene AABB, and both links; a 48-byte triangle is 3x128-bit.  All fetches go
-// through the read-only path.  The kernel is bound by the L1 wavefront rate (one wavefront per lane per divergent load),
-// which is why a step costs one wavefront, not two.  Algorithmic bytes per ray = 32*nodes + 48*tris + 32 (ray) + 16 (hit).
+// A traversal step is TWO 256-bit loads (LDG.E.256, new on sm_100): the 64-byte record of a 4-wide node holds four child
+// boxes, quantised to a 16-bit grid over the scene AABB, and four links; a 48-byte triangle is 3x128-bit.  All fetches go
+// through the read-only path.  The kernel sits between the issue rate and the L1 wavefront rate (one wavefront per lane per
+// divergent load).  Algorithmic bytes per ray = 64*nodes + 48*tris + 32 (ray) + 16 (hit).
 // The ray/triangle test is the exact fp32 operation sequence of oracle/scene_core.h (no FMA contraction,
 // enforced with __f*_rn intrinsics), which makes the chosen triangle and (t,u,v) BVH-independent.
 #include "common.cuh"
