@@ -164,3 +164,23 @@ def test_cpp_hdr_probe_with_device_cdf_equals_host_cdf(exe, tmp_path):
         subprocess.check_call([exe, "--boxes", "12", "--preset", "orig", "--size", "96x64", "--frames", "2", "--hdr", path, "--out", out] + extra)
         outs.append(open(out, "rb").read())
     assert outs[0] == outs[1] and len(outs[0]) > 96 * 64 * 3
+
+
+@pytest.mark.gpu
+def test_cpp_whitted_frame_equals_python_mirror(exe, tmp_path):
+    """SampleRenderer::renderWhitted (C++ forwarder, camera set up as 04HelloRaytracing/SampleRenderer.cpp:125-138) gives the same
+    RGBA8 frame as the Python mirror."""
+    scenes.cornell("disney", directory=str(tmp_path))
+    obj = os.path.join(str(tmp_path), "cornell.obj")
+    out = os.path.join(str(tmp_path), "w.ppm")
+    subprocess.check_call([exe, "--obj", obj, "--size", "96x64", "--frames", "1", "--camera", "cornell", "--whitted", "--out", out])
+    raw = open(out, "rb").read()
+    got = np.frombuffer(raw, np.uint8, 96 * 64 * 3, len(b"P6\n96 64\n255\n")).reshape(64, 96, 3)[::-1]
+    r = SampleRenderer(loadOBJ(obj), device=0, config=preset("sv4_fov"))
+    r.resize((96, 64))
+    r.renderWhitted(preset_camera("cornell"))
+    want = r.downloadPixels().view(np.uint8).reshape(64, 96, 4)[..., :3]
+    r.close()
+    same = np.all(got == want, axis=-1)
+    assert same.mean() > 0.995 and np.abs(got.astype(int) - want.astype(int)).max() <= 1 + 254 * (same.mean() < 1.0)
+    assert got.max() > 50
