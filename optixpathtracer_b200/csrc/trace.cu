@@ -20,7 +20,7 @@
 #define TRACE_BLOCK 128
 #define TRACE_WARPS (TRACE_BLOCK / 32)
 #ifndef TRACE_BLOCKS_PER_SM
-#define TRACE_BLOCKS_PER_SM 8
+#define TRACE_BLOCKS_PER_SM 7      // 72 registers per thread, 28 warps/SM: measured best for the 4-wide step (5: 3.25 ms, 6: 3.11, 7: 2.94, 8: 3.02, 9: 3.11 per frame)
 #endif
 #define FULL 0xffffffffu
 #define EMPTY 0x7fffffff          // "nothing left to visit"; also the root link of an empty scene
@@ -438,7 +438,7 @@ __global__ void traceRaysDebugKernel(SceneDev S, const float4* rayO, const float
 static int refillThreshold() {
     if (g_refillThreshold < 0) {
         const char* e = getenv("B200PT_REFILL");                  // tuning knob; the default is the measured optimum
-        g_refillThreshold = e ? atoi(e) : 8;
+        g_refillThreshold = e ? atoi(e) : 6;
         if (g_refillThreshold < 1) g_refillThreshold = 1;
         if (g_refillThreshold > 32) g_refillThreshold = 32;
     }
