@@ -9,7 +9,7 @@
 
 #define SHADE_BLOCK 128
 #ifndef SHADE_MIN_BLOCKS
-#define SHADE_MIN_BLOCKS 8
+#define SHADE_MIN_BLOCKS 7          // CTAs per SM for shadeKernel (72 registers); measured per frame: 6: 1.55 ms, 7: 1.44, 8: 1.47, 9: 1.52, 10: 1.56, 12: 1.69
 #endif
 
 DEV void enqueueRay(bool want, float4 o, float4 d, float4* qo, float4* qd, unsigned* counter) {
