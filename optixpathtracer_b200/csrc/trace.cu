@@ -17,7 +17,9 @@
 // enforced with __f*_rn intrinsics), which makes the chosen triangle and (t,u,v) BVH-independent.
 #include "common.cuh"
 
+#ifndef TRACE_BLOCK
 #define TRACE_BLOCK 128
+#endif
 #define TRACE_WARPS (TRACE_BLOCK / 32)
 #ifndef TRACE_BLOCKS_PER_SM
 #define TRACE_BLOCKS_PER_SM 7      // 72 registers per thread, 28 warps/SM: measured best for the 4-wide step (5: 3.25 ms, 6: 3.11, 7: 2.94, 8: 3.02, 9: 3.11 per frame)
