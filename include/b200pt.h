@@ -59,7 +59,9 @@ typedef struct b200pt_config {
     int   mis_on_miss;        /* 0 = off (reference behaviour: a BSDF-sampled ray that leaves the scene adds nothing, sv4/deviceProgram.cu:251-280).
                                  1 = opt-in extension, the reference's commented-out MIS (:257-267): a secondary ray that misses adds
                                  w * ProbeEval(dir) * throughput with w = p_bsdf / (p_bsdf + ProbePdf(dir)), the partner of the NEE weight */
-    int   reserved[3];
+    float shadow_tmin;        /* tmin of the occlusion (NEE) rays: 0.01 in every variant — `orig` traces radiance rays from 0.001 (orig/deviceProgram.cu:420)
+                                 but occlusion rays from 0.01 (:268, :310); <= 0 means "same as tmin" */
+    int   reserved[2];
 } b200pt_config;
 
 /* Fill *cfg with a named preset: "orig", "sv3_uniform", "sv4_uniform", "sv4_fov". */

@@ -54,6 +54,7 @@ int b200pt_config_preset(b200pt_config* c, const char* name) {
     if (!c || !name) return fail("b200pt_config_preset: null argument");
     memset(c, 0, sizeof(*c));
     c->tmax = 1e16f;  c->exposure = 1.0f;
+    c->shadow_tmin = 0.01f;       // every variant traces occlusion rays from 0.01 (orig/deviceProgram.cu:268,310; sv3 :40; sv4), also orig whose radiance rays start at 0.001 (:420)
     const std::string n(name);
     if (n == "orig") {            // orig/deviceProgram.cu:198,429,467; orig/SimplePathtracer.cpp:73-97
         c->schedule = B200PT_SCHEDULE_UNIFORM;  c->max_depth = 8;  c->tmin = 0.001f;  c->shadow_mode = B200PT_SHADOW_ANY_HIT;

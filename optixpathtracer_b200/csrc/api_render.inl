@@ -195,6 +195,7 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
     T.begin(ST_TOTAL, ta, tb);
     const int bounces = cfg.max_depth + ((c->hasCatcher || cfg.max_depth == 0) ? 1 : 0);   // the dropped last segment is traced only if alpha can still change
     const int cullBack = cfg.shadow_mode == B200PT_SHADOW_CULL_BACK;
+    const float shadowTmin = cfg.shadow_tmin > 0.f ? cfg.shadow_tmin : cfg.tmin;
     for (auto& group : groups) {
         if (group.empty()) continue;
         T.begin(ST_RAYGEN, a, b);
@@ -208,7 +209,7 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
         for (int d = 0; d <= bounces; ++d) {
             unsigned* ctr = Q.counters + QC_STRIDE * d;
             T.begin(d < bounces ? ST_TRACE : ST_TRACE_TAIL, a, b);
-            launchTrace(S, Q.rayO[cur], Q.rayD[cur], Q.hit, ctr + (d < bounces ? QC_RAYS : 3 /* always 0 */), Q.shO, Q.shD, ctr + QC_SHADOWS, ctr + QC_HEAD, cfg.tmin, cfg.tmax,
+            launchTrace(S, Q.rayO[cur], Q.rayD[cur], Q.hit, ctr + (d < bounces ? QC_RAYS : 3 /* always 0 */), Q.shO, Q.shD, ctr + QC_SHADOWS, ctr + QC_HEAD, cfg.tmin, shadowTmin, cfg.tmax,
                         cullBack, pool, count ? c->stats.p : nullptr, s);
             T.end(b);  ++launches;  ++nClosest;
             if (d == bounces) break;
@@ -315,9 +316,9 @@ int b200pt_render_whitted(b200pt_ctx* c, const b200pt_whitted_params* wp, uint32
     unsigned* c0 = Q.counters;
     unsigned* c1 = Q.counters + QC_STRIDE;
     launchWhittedRaygen(P, Q, pool, c0, s);
-    launchTrace(S, Q.rayO[0], Q.rayD[0], Q.hit, c0 + QC_RAYS, Q.shO, Q.shD, c0 + QC_SHADOWS /* 0 */, c0 + QC_HEAD, 0.f, 1e20f, 0, pool, nullptr, s);
+    launchTrace(S, Q.rayO[0], Q.rayD[0], Q.hit, c0 + QC_RAYS, Q.shO, Q.shD, c0 + QC_SHADOWS /* 0 */, c0 + QC_HEAD, 0.f, 0.f, 1e20f, 0, pool, nullptr, s);
     launchWhittedShade(P, S, pool, Q, c1 + QC_SHADOWS, s);
-    launchTrace(S, Q.rayO[0], Q.rayD[0], Q.hit, c1 + 3 /* always 0 */, Q.shO, Q.shD, c1 + QC_SHADOWS, c1 + QC_HEAD, 1e-3f, 1.f - 1e-3f, 0, pool, nullptr, s);
+    launchTrace(S, Q.rayO[0], Q.rayD[0], Q.hit, c1 + 3 /* always 0 */, Q.shO, Q.shD, c1 + QC_SHADOWS, c1 + QC_HEAD, 1e-3f, 1e-3f, 1.f - 1e-3f, 0, pool, nullptr, s);
     launchWhittedFinish(P, pool, deviceColorBuffer ? deviceColorBuffer : (uint32_t*)c->frameBuf.p, s);
     CUDA_OK(cudaGetLastError());
     CUDA_OK(cudaStreamSynchronize(s));

@@ -145,7 +145,7 @@ void bvhRefit(const float3* d_vertices, const uint3* d_indices, const unsigned* 
 
 // trace.cu  (compiled with FMA contraction; the triangle test itself uses explicit _rn intrinsics)
 void launchTrace(const SceneDev& scene, const float4* rayO, const float4* rayD, float4* hit, const unsigned* countC,
-                 const float4* shO, const float4* shD, const unsigned* countS, unsigned* head, float tmin, float tmax, int cullBack,
+                 const float4* shO, const float4* shD, const unsigned* countS, unsigned* head, float tmin, float tminShadow, float tmax, int cullBack,
                  const PathPool& pool, TraceStats* stats /* [0] closest, [1] any; nullptr = no counting */, cudaStream_t stream);
 void launchTraceRaysDebug(const SceneDev& scene, const float4* rayO, const float4* rayD, unsigned n, float tmin, float tmax,
                           int anyHit, int cullBack, float4* hitOut, cudaStream_t stream);

@@ -253,7 +253,7 @@ template <bool COUNT>
 __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_BLOCKS_PER_SM)
 traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restrict__ rayD, float4* __restrict__ hit,
             const unsigned* __restrict__ countCPtr, const float4* __restrict__ shO, const float4* __restrict__ shD,
-            const unsigned* __restrict__ countSPtr, unsigned* head, float tmin, float tmax, int cullBack, PathPool pool,
+            const unsigned* __restrict__ countSPtr, unsigned* head, float tminC, float tminS, float tmax, int cullBack, PathPool pool,
             TraceStats* stats, int refillThreshold, int leafThreshold) {
     __shared__ float4 stageO[TRACE_WARPS][2][32], stageD[TRACE_WARPS][2][32];
     const unsigned countC = *countCPtr, countS = *countSPtr;
@@ -270,6 +270,7 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
 
     // per-lane ray state
     bool active = false, isAny = false;
+    float tmin = tminC;                    // per lane: occlusion rays have their own tmin (0.01 in every variant, also where radiance rays use 0.001)
     unsigned rayIdx = 0;
     float3 o = make_float3(0, 0, 0), d = o;
     GridRay g = {0, 0, 0, 0, 0, 0, 0, 0, 0};
@@ -333,7 +334,7 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
                     const float4 o4 = stageO[warp][buf][j - stageFirst], d4 = stageD[warp][buf][j - stageFirst];
                     o = make_float3(o4.x, o4.y, o4.z);  d = make_float3(d4.x, d4.y, d4.z);  wO = o4.w;  wD = d4.w;
                     g = makeGridRay(S, o, d);
-                    rayIdx = j;  active = true;  isAny = stageAny != 0;
+                    rayIdx = j;  active = true;  isAny = stageAny != 0;  tmin = isAny ? tminS : tminC;
                     best.t = tmax;  best.slot = -1;  best.gid = 0xffffffffu;  best.u = best.v = 0.f;
                     cur = rootLink;  leaf = NO_LEAF;  sp = 0;
                     if (COUNT) { nRays[isAny]++;  myNodes = 0;  myTris = 0; }
@@ -457,11 +458,11 @@ static int leafThreshold() {
 }
 
 void launchTrace(const SceneDev& scene, const float4* rayO, const float4* rayD, float4* hit, const unsigned* countC,
-                 const float4* shO, const float4* shD, const unsigned* countS, unsigned* head, float tmin, float tmax, int cullBack,
+                 const float4* shO, const float4* shD, const unsigned* countS, unsigned* head, float tmin, float tminShadow, float tmax, int cullBack,
                  const PathPool& pool, TraceStats* stats, cudaStream_t stream) {
     const dim3 grid(B200PT_NUM_SMS * TRACE_BLOCKS_PER_SM), block(TRACE_BLOCK);
-    if (stats) traceKernel<true><<<grid, block, 0, stream>>>(scene, rayO, rayD, hit, countC, shO, shD, countS, head, tmin, tmax, cullBack, pool, stats, refillThreshold(), leafThreshold());
-    else traceKernel<false><<<grid, block, 0, stream>>>(scene, rayO, rayD, hit, countC, shO, shD, countS, head, tmin, tmax, cullBack, pool, nullptr, refillThreshold(), leafThreshold());
+    if (stats) traceKernel<true><<<grid, block, 0, stream>>>(scene, rayO, rayD, hit, countC, shO, shD, countS, head, tmin, tminShadow, tmax, cullBack, pool, stats, refillThreshold(), leafThreshold());
+    else traceKernel<false><<<grid, block, 0, stream>>>(scene, rayO, rayD, hit, countC, shO, shD, countS, head, tmin, tminShadow, tmax, cullBack, pool, nullptr, refillThreshold(), leafThreshold());
 }
 
 void launchTraceRaysDebug(const SceneDev& scene, const float4* rayO, const float4* rayD, unsigned n, float tmin, float tmax,

@@ -118,22 +118,23 @@ class Config(C.Structure):
         ("accumulate", C.c_int), ("inner_radius", C.c_int), ("outer_radius", C.c_int),
         ("launch_w", C.c_int), ("launch_h", C.c_int), ("write_aovs", C.c_int), ("increment_subframe", C.c_int),
         ("accum_mode", C.c_int), ("russian_roulette", C.c_int), ("tile_rank", C.c_int), ("tile_count", C.c_int),
-        ("profile", C.c_int), ("mis_on_miss", C.c_int), ("reserved", C.c_int * 3),
+        ("profile", C.c_int), ("mis_on_miss", C.c_int), ("shadow_tmin", C.c_float), ("reserved", C.c_int * 2),
     ]
 
 
 _PRESETS = {
+    # occlusion rays start at 0.01 in every variant, radiance rays at 0.001 in orig only (orig/deviceProgram.cu:268,310 vs :420)
     # orig/deviceProgram.cu:198,429,467 ; orig/SimplePathtracer.cpp:73-97 (render() leaves subframe_index to main)
-    "orig": dict(schedule=SCHEDULE_UNIFORM, max_depth=8, tmin=0.001, tmax=1e16, shadow_mode=SHADOW_ANY_HIT,
+    "orig": dict(schedule=SCHEDULE_UNIFORM, max_depth=8, tmin=0.001, shadow_tmin=0.01, tmax=1e16, shadow_mode=SHADOW_ANY_HIT,
                  display=DISPLAY_SRGB, exposure=1.0, uniform_spl=0, accumulate=1, write_aovs=1, increment_subframe=0),
     # sv3/deviceProgram.cu:243,511,582 ; sv3/SimplePathtracer.cpp:81-128
-    "sv3_uniform": dict(schedule=SCHEDULE_UNIFORM, max_depth=4, tmin=0.01, tmax=1e16, shadow_mode=SHADOW_CULL_BACK,
+    "sv3_uniform": dict(schedule=SCHEDULE_UNIFORM, max_depth=4, tmin=0.01, shadow_tmin=0.01, tmax=1e16, shadow_mode=SHADOW_CULL_BACK,
                         display=DISPLAY_REINHARD, exposure=8.0, uniform_spl=32, accumulate=1, increment_subframe=1),
     # sv4/SimplePathtracer.cpp:85-131
-    "sv4_uniform": dict(schedule=SCHEDULE_UNIFORM, max_depth=4, tmin=0.01, tmax=1e16, shadow_mode=SHADOW_CULL_BACK,
+    "sv4_uniform": dict(schedule=SCHEDULE_UNIFORM, max_depth=4, tmin=0.01, shadow_tmin=0.01, tmax=1e16, shadow_mode=SHADOW_CULL_BACK,
                         display=DISPLAY_REINHARD, exposure=4.0, uniform_spl=8, accumulate=0, increment_subframe=1),
     # sv4/SimplePathtracer.cpp:20-21,132-216
-    "sv4_fov": dict(schedule=SCHEDULE_FOVEATED, max_depth=4, tmin=0.01, tmax=1e16, shadow_mode=SHADOW_CULL_BACK,
+    "sv4_fov": dict(schedule=SCHEDULE_FOVEATED, max_depth=4, tmin=0.01, shadow_tmin=0.01, tmax=1e16, shadow_mode=SHADOW_CULL_BACK,
                     display=DISPLAY_REINHARD, exposure=4.0, inner_radius=157, outer_radius=515, increment_subframe=1),
 }
 

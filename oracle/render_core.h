@@ -70,7 +70,8 @@ struct OTraceCtx {
 
 static inline bool oracleTraceOcclusion(const OTraceCtx& C, const float3& o, const float3& d) {
     C.counters->shadowRays++;
-    return oracleAnyHit(*C.scene, o, d, C.cfg->tmin, C.cfg->tmax, C.cfg->shadow_mode == B200PT_SHADOW_CULL_BACK);
+    const float tminShadow = C.cfg->shadow_tmin > 0.f ? C.cfg->shadow_tmin : C.cfg->tmin;      // 0.01 in every variant (orig/deviceProgram.cu:268,310)
+    return oracleAnyHit(*C.scene, o, d, tminShadow, C.cfg->tmax, C.cfg->shadow_mode == B200PT_SHADOW_CULL_BACK);
 }
 
 // sv4/deviceProgram.cu:301-341 (occludedWanted=false) and :344-384 (occludedWanted=true)
