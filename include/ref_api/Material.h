@@ -47,6 +47,11 @@ struct Material {
         return m;
     }
     // HelloPathtracing_original/Material.h:13-36 (the plain diffuse-ish Disney default).
+    static Material sv3Defaults() {                       // HelloPathtracing_sv3/Material.h:13-37
+        Material m = origDefaults();
+        m.color = {0.6f, 1.6f, 0.6f};  m.eta = 1.4f;
+        return m;
+    }
     static Material origDefaults() {
         Material m{NoInit{}};
         m.emission = {0.f, 0.f, 0.f};  m.color = {0.6f, 0.6f, 0.6f};  m.absorption = {0.f, 0.f, 0.f};

@@ -61,6 +61,15 @@ class Material(C.Structure):
         d.update(kw)
         return cls(**d)
 
+    @classmethod
+    def sv3_defaults(cls, **kw):
+        """HelloPathtracing_sv3/Material.h:13-37 (the green tint 1.6 is the reference's literal)."""
+        d = dict(emission=(0, 0, 0), color=(0.6, 1.6, 0.6), absorption=(0, 0, 0), eta=1.4, metallic=0.0,
+                 subsurface=0.0, specular=0.5, roughness=1.0, specularTint=0.0, clearcoat=0.0, clearcoatGloss=1.0,
+                 transmission=0.0, bump=0.0, bumpTile=(10, 10, 10), flags=0)
+        d.update(kw)
+        return cls(**d)
+
 
 MATERIAL_FLAG_SHADOW_CATCHER = 1
 
