@@ -40,7 +40,7 @@ SPL = 1
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=16)
+    ap.add_argument("--steps", type=int, default=64)          # configs[1]: 1 spp/frame x 64 frames
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--width", type=int, default=W)
@@ -99,7 +99,7 @@ class ClockSampler:
         self.path = tempfile.mktemp(suffix=".csv")
         self.proc = None
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(index)],
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20", "-i", str(index)],
                                          stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
@@ -267,6 +267,10 @@ def run_b200(a):
     for i in range(a.warmup):
         one_step(i, False)
     if world > 1:
+        with torch.cuda.stream(stream):                                         # warm-up of the collective itself: NCCL sets up its channels
+            for _ in range(2):                                                  # for this message size on first use, which is not a cost of the
+                dist.reduce(accum_t, dst=0, op=dist.ReduceOp.SUM)               # render path
+        stream.synchronize()
         accum_t.zero_()
         dist.barrier()
     torch.cuda.synchronize()

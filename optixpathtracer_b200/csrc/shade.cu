@@ -191,26 +191,41 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                     if (last && !catcher) {
                         flags |= PF_DONE;
                     } else {
-                        // SampleLights / SampleShadow, :301-384 (probe sample drawn above)
-                        const float bp = bsdfPdf(mat, rayEta, outEta, N, wo, wi);
+                        // The continuation direction is drawn first (the RNG order is the reference's: the probe sample was drawn above,
+                        // DisneySample comes next, and nothing in between consumes random numbers) ...
+                        float3 bsdfDir = f3(0.f);  float pdf = 0.0f;  int type = 0;  bool dirNeedsPdf = false;
+                        if (!last) {
+                            float3 u, v;
+                            basisFromVector(N, u, v);                             // :671-677
+                            bsdfSampleDir(mat, rayEta, outEta, u, v, N, wo, bsdfDir, pdf, type, dirNeedsPdf, rng);
+                        }
+                        // ... so that DisneyPdf / DisneyEval of the two directions of this vertex — k = 0: the NEE direction wi (SampleLights,
+                        // :301-384), k = 1: the drawn direction (:683-695) — run through ONE rolled copy of the code.
+                        float bp = 0.0f;  float3 fNee = f3(0.f), fDir = f3(0.f);  bool evalNee = false;
+#pragma unroll 1
+                        for (int k = 0; k < 2; ++k) {
+                            const float3 L = k ? bsdfDir : wi;
+                            float p = pdf;
+                            if (k == 0 || dirNeedsPdf) p = bsdfPdf(mat, rayEta, outEta, N, wo, L);
+                            bool ev;
+                            if (k == 0) ev = p > 0.0f && 0.5f * skyPdf / (0.5f * p + 0.5f * skyPdf) > 0.0f;
+                            else ev = !last && p > 0.0f;
+                            float3 f = f3(0.f);
+                            if (ev) f = bsdfEval(mat, albedo, rayEta, outEta, N, wo, L);
+                            if (k == 0) { bp = p;  fNee = f;  evalNee = ev; }
+                            else { pdf = p;  fDir = f; }
+                        }
                         float3 pend = f3(0.f);
                         bool valid = false;
-                        if (bp > 0.0f) {
+                        if (evalNee) {
                             const float weight = 0.5f * skyPdf / (0.5f * bp + 0.5f * skyPdf);
-                            if (weight > 0.0f) {
-                                const float3 f = bsdfEval(mat, albedo, rayEta, outEta, N, wo, wi);
-                                const float3 val = weight * skyColor * f * fabsf(dot3(wi, N)) / skyPdf * 1.0f;
-                                pend = T * val;
-                                valid = !(pend.x == 0.f && pend.y == 0.f && pend.z == 0.f);
-                            }
+                            const float3 val = weight * skyColor * fNee * fabsf(dot3(wi, N)) / skyPdf * 1.0f;
+                            pend = T * val;
+                            valid = !(pend.x == 0.f && pend.y == 0.f && pend.z == 0.f);
                         }
                         if (last) {                                               // catcher hit by the primary ray at max depth
                             flags |= PF_DONE;
                         } else {
-                            float3 u, v;
-                            basisFromVector(N, u, v);                             // :671-677
-                            float3 bsdfDir;  float pdf;  int type;
-                            bsdfSample(mat, rayEta, outEta, u, v, N, wo, bsdfDir, pdf, type, rng);
                             if (pdf <= 0.0f) {
                                 flags |= PF_DONE;  valid = false;                 // :679-682: this segment's radiance is dropped
                             } else {
@@ -219,7 +234,7 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                                     dacc.x += mat.emission.x;  dacc.y += mat.emission.y;  dacc.z += mat.emission.z;
                                     pool.direct[slot] = dacc;
                                 }
-                                const float3 f = bsdfEval(mat, albedo, rayEta, outEta, N, wo, bsdfDir);
+                                const float3 f = fDir;
                                 if (dot3(bsdfDir, N) <= 0.0f) rayEta = outEta;    // :688-692
                                 T = T * (f * fabsf(dot3(N, bsdfDir)) / pdf);      // :695
                                 flags |= PF_SECONDARY;

@@ -93,6 +93,17 @@ DEV float3 cosineSampleHemisphere(float u1, float u2) {
     return f3(sx, sy, z);
 }
 
+// code-size knobs (tuning builds): out-of-line copies of the small helpers with IEEE divisions / square roots
+#ifdef SHADE_NI_GGX
+#define SHADE_NI_GGX_ATTR __device__ __noinline__
+#else
+#define SHADE_NI_GGX_ATTR DEV
+#endif
+#ifdef SHADE_NI_FRESNEL
+#define SHADE_NI_FRESNEL_ATTR __device__ __noinline__
+#else
+#define SHADE_NI_FRESNEL_ATTR DEV
+#endif
 // ---- Disney BSDF: sv4/Disney.cuh ---------------------------------------------------------------------
 enum { eReflected = 0, eTransmitted = 1, eSpecular = 2 };
 
@@ -117,11 +128,11 @@ DEV float GTR2(float NDotH, float a) {
     const float t = 1.0f + (a2 - 1.0f) * NDotH * NDotH;
     return a2 / (kPi * t * t);
 }
-DEV float smithGGX(float NDotv, float alphaG) {
+SHADE_NI_GGX_ATTR float smithGGX(float NDotv, float alphaG) {
     const float a = alphaG * alphaG, b = NDotv * NDotv;
     return 1.0f / (NDotv + sqrtf(a + b - a * b));
 }
-DEV float fresnelDielectric(float VDotN, float etaI, float etaT) {                 // Fr, :81-98
+SHADE_NI_FRESNEL_ATTR float fresnelDielectric(float VDotN, float etaI, float etaT) {                 // Fr, :81-98
     const float sinT2 = sqrf(etaI / etaT) * (1.0f - VDotN * VDotN);
     if (sinT2 > 1.0f) return 1.0f;
     const float LDotN = sqrtf(1.0f - sinT2);
@@ -160,8 +171,12 @@ DEV float3 ggxReflect(const Material& mat, float3 U, float3 V, float3 N, float3 
     return 2.0f * dot3(view, half) * half - view;
 }
 
-DEV void bsdfSample(const Material& mat, float etaI, float etaO, float3 U, float3 V, float3 N, float3 view,
-                    float3& light, float& pdf, int& type, Rng& rand) {            // :197-315
+// The direction-drawing half of DisneySample (:197-315).  needPdf = the reference goes on to `pdf = DisneyPdf(...)` for the drawn
+// direction (every branch but the two refraction returns, which set pdf themselves); shadeKernel evaluates that pdf in the same
+// rolled loop as the NEE direction's, so the kernel holds ONE copy of bsdfPdf/bsdfEval instead of two (instruction-cache footprint).
+DEV void bsdfSampleDir(const Material& mat, float etaI, float etaO, float3 U, float3 V, float3 N, float3 view,
+                       float3& light, float& pdf, int& type, bool& needPdf, Rng& rand) {
+    needPdf = false;
     if (rand.randf() < mat.transmission) {
         const float F = fresnelDielectric(dot3(N, view), etaI, etaO);
         if (rand.randf() < F) {
@@ -193,7 +208,13 @@ DEV void bsdfSample(const Material& mat, float etaI, float etaO, float3 U, float
             type = eReflected;
         }
     }
-    pdf = bsdfPdf(mat, etaI, etaO, N, view, light);
+    needPdf = true;
+}
+DEV void bsdfSample(const Material& mat, float etaI, float etaO, float3 U, float3 V, float3 N, float3 view,
+                    float3& light, float& pdf, int& type, Rng& rand) {            // :197-315
+    bool needPdf;
+    bsdfSampleDir(mat, etaI, etaO, U, V, N, view, light, pdf, type, needPdf, rand);
+    if (needPdf) pdf = bsdfPdf(mat, etaI, etaO, N, view, light);
 }
 
 DEV float3 bsdfEval(const Material& mat, float3 albedo, float etaI, float etaO, float3 N, float3 V, float3 L) {   // :318-427
