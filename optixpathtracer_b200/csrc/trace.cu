@@ -166,6 +166,36 @@ __device__ __forceinline__ bool triEval(const float4 a, const float4 b, const fl
 
 struct Best { float t, u, v; int slot; unsigned gid; };
 
+// Traversal stack: a per-thread array in local memory.  TRACE_TOS = 1 is a measured-and-rejected variant kept for sweeps: the top entry in a
+// register and the local-memory accesses as predicated PTX (`@p ld.local`) instead of nvcc's divergent branch around the LDL.  It removes the
+// BSSY/BRA/BSYNC regions that 3-4 lanes of 32 run in 88 % of the node steps, but every push then carries the spill of the old top and the warp
+// waits on the refill load anyway: 2.85 ms against 2.76 ms per frame on B200.
+#ifndef TRACE_TOS
+#define TRACE_TOS 0
+#endif
+#if TRACE_TOS
+// Predicated local-memory accesses written in PTX: nvcc turns `if (c) tos = stack[i]` into a divergent branch region (BSSY/BRA/BSYNC, run by
+// 3-4 lanes of 32 in 88 % of the node steps - r01h2 source-level profile); `@p ld.local` is one instruction and no reconvergence point.
+// The array is only ever touched through these two helpers (its address escapes into them), so the compiler keeps it in local memory.
+__device__ __forceinline__ void stLocalIf(unsigned long long addr, int v, bool p) {
+    asm volatile("{ .reg .pred q;  setp.ne.s32 q, %2, 0;  @q st.local.b32 [%0], %1; }" :: "l"(addr), "r"(v), "r"((int)p) : "memory");
+}
+__device__ __forceinline__ void ldLocalIf(int& v, unsigned long long addr, bool p) {
+    asm volatile("{ .reg .pred q;  setp.ne.s32 q, %2, 0;  @q ld.local.b32 %0, [%1]; }" : "+r"(v) : "l"(addr), "r"((int)p) : "memory");
+}
+#define SADDR_(i) (stackAddr + 4ull * (unsigned)(i))
+#define STACK_DECL_ int stack[B200PT_STACK];  const unsigned long long stackAddr = (unsigned long long)__cvta_generic_to_local(stack);  int sp = 0, tos = EMPTY;
+// push x if c;  pop into dst if c (dst keeps its value otherwise)
+#define PUSH_IF_(x, c) { const bool c_ = (c);  stLocalIf(SADDR_(sp - 1), tos, c_ && sp > 0);  tos = c_ ? (x) : tos;  sp += c_ ? 1 : 0; }
+#define POP_IF_(dst, c) { const bool c_ = (c), p_ = c_ && sp > 0;  dst = c_ ? (sp > 0 ? tos : EMPTY) : dst;  sp -= p_ ? 1 : 0;  ldLocalIf(tos, SADDR_(sp - 1), p_ && sp > 0); }
+#else
+#define STACK_DECL_ int stack[B200PT_STACK];  int sp = 0;
+#define PUSH_IF_(x, c) { if (c) stack[sp++] = (x); }
+#define POP_IF_(dst, c) { if (c) dst = sp ? stack[--sp] : EMPTY; }
+#endif
+#define PUSH_(x) PUSH_IF_(x, true)
+#define POP_(dst) POP_IF_(dst, true)
+
 // One inner-node step: fetch node `cur` (both child boxes in one record), descend into the nearer hit child, push the other.
 #define NODE_STEP()                                                                              \
     {                                                                                            \
@@ -177,11 +207,11 @@ struct Best { float t, u, v; int slot; unsigned gid; };
         const int cl_ = (int)N_.w[6], cr_ = (int)N_.w[7];                                        \
         if (hl_ && hr_) {                                                                        \
             const bool sw_ = tr_ < tl_;                                                          \
-            stack[sp++] = sw_ ? cl_ : cr_;                                                       \
+            PUSH_(sw_ ? cl_ : cr_)                                                               \
             cur = sw_ ? cr_ : cl_;                                                               \
         } else if (hl_) cur = cl_;                                                               \
         else if (hr_) cur = cr_;                                                                 \
-        else cur = sp ? stack[--sp] : EMPTY;                                                     \
+        else POP_(cur)                                                                           \
     }
 
 // One step through a 4-wide node (two 256-bit loads): test the four child boxes, order the hit ones by entry distance with a
@@ -202,10 +232,8 @@ struct Best { float t, u, v; int slot; unsigned gid; };
         CEX_(t0_, l0_, t1_, l1_)  CEX_(t2_, l2_, t3_, l3_)  CEX_(t0_, l0_, t2_, l2_)                    \
         if (TRACE_SORT_CEX >= 4) CEX_(t1_, l1_, t3_, l3_)                                        \
         if (TRACE_SORT_CEX >= 5) CEX_(t1_, l1_, t2_, l2_)                                        \
-        if (t3_ < inf_) stack[sp++] = l3_;                                                       \
-        if (t2_ < inf_) stack[sp++] = l2_;                                                       \
-        if (t1_ < inf_) stack[sp++] = l1_;                                                       \
-        cur = t0_ < inf_ ? l0_ : (sp ? stack[--sp] : EMPTY);                                     \
+        PUSH_IF_(l3_, t3_ < inf_)  PUSH_IF_(l2_, t2_ < inf_)  PUSH_IF_(l1_, t1_ < inf_)             \
+        { const bool any_ = t0_ < inf_;  cur = any_ ? l0_ : cur;  POP_IF_(cur, !any_) }                 \
     }
 
 // Reference single-ray traversal (parity hooks only; the production kernels below inline the same steps).
@@ -213,8 +241,7 @@ template <bool ANY, bool COUNT>
 __device__ __forceinline__ bool traverse(const SceneDev& S, const float3 o, const float3 d, float tmin, float tmax,
                                          bool cullBack, Best& best, unsigned& nNodes, unsigned& nTris) {
     const GridRay g = makeGridRay(S, o, d);
-    int stack[B200PT_STACK];
-    int sp = 0;
+    STACK_DECL_
     best.t = tmax;  best.slot = -1;  best.gid = 0xffffffffu;  best.u = best.v = 0.f;
     int cur = S.rootLink4;
     while (cur != EMPTY) {
@@ -237,7 +264,7 @@ __device__ __forceinline__ bool traverse(const SceneDev& S, const float3 o, cons
                     }
                 }
             }
-            cur = sp ? stack[--sp] : EMPTY;
+            POP_(cur)
         }
     }
     return best.slot >= 0;
@@ -298,8 +325,8 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
     float wO = 0.f, wD = 0.f;
     Best best;  best.t = tmax;  best.slot = -1;  best.gid = 0xffffffffu;  best.u = best.v = 0.f;
     float bestDet = 1.f;
-    int cur = EMPTY, leaf = NO_LEAF, sp = 0;
-    int stack[B200PT_STACK];
+    int cur = EMPTY, leaf = NO_LEAF;
+    STACK_DECL_
 
     while (true) {
         // ---------------------------------------------------------------- prefetch the next chunk (warp-uniform)
@@ -378,10 +405,10 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
             if (active && (unsigned)cur < (unsigned)EMPTY) {
                 if (COUNT) myNodes += 1;
                 NODE_STEP4()
-                if (cur < 0 && leaf == NO_LEAF) {                  // first leaf: postpone it and keep walking
-                    leaf = cur;
-                    if (TRACE_PREFETCH & 2) prefetchLink(S, leaf);
-                    cur = sp ? stack[--sp] : EMPTY;
+                {                                                   // first leaf: postpone it and keep walking
+                    const bool first_ = cur < 0 && leaf == NO_LEAF;
+                    leaf = first_ ? cur : leaf;
+                    POP_IF_(cur, first_)
                 }
             }
             const bool canNode = active && (unsigned)cur < (unsigned)EMPTY;
@@ -391,7 +418,7 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
         }
         // ---------------------------------------------------------------- leaves, once enough lanes are blocked on one
         if (nodeMask == 0u || (int)__popc(blockedMask) >= leafThreshold) {
-            if (active && leaf == NO_LEAF && cur < 0) { leaf = cur;  cur = sp ? stack[--sp] : EMPTY; }   // root leaf
+            if (active && leaf == NO_LEAF && cur < 0) { leaf = cur;  POP_(cur) }   // root leaf
             if (active && leaf != NO_LEAF) {
                 unsigned first, cnt;
                 leafDecode(leaf, first, cnt);
@@ -417,7 +444,7 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
                 }
                 leaf = NO_LEAF;
                 if (occluded) cur = EMPTY;
-                else if (cur < 0) { leaf = cur;  cur = sp ? stack[--sp] : EMPTY; }   // (EMPTY is positive: never taken for it)
+                else if (cur < 0) { leaf = cur;  POP_(cur) }   // (EMPTY is positive: never taken for it)
             }
         }
         // ---------------------------------------------------------------- retire finished rays
