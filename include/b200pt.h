@@ -61,7 +61,12 @@ typedef struct b200pt_config {
                                  w * ProbeEval(dir) * throughput with w = p_bsdf / (p_bsdf + ProbePdf(dir)), the partner of the NEE weight */
     float shadow_tmin;        /* tmin of the occlusion (NEE) rays: 0.01 in every variant — `orig` traces radiance rays from 0.001 (orig/deviceProgram.cu:420)
                                  but occlusion rays from 0.01 (:268, :310); <= 0 means "same as tmin" */
-    int   reserved[2];
+    int   frames_in_flight;   /* b200pt_render_async only: how many frames may be in flight at once (1..4; 0 = 1).  Each extra frame owns a second
+                                 stream, path pool and queue set; its wavefront runs concurrently with its neighbours' (one frame's drain phases
+                                 and thin late bounces overlap the next frame's wide early ones) and the frames still fold into the accumulation
+                                 buffer in submission order, so the pixels are those of the one-at-a-time sequence, bit for bit.  b200pt_render
+                                 (blocking) and instrumented frames (profile != 0) always run one at a time on the context's primary stream. */
+    int   reserved[1];
 } b200pt_config;
 
 /* Fill *cfg with a named preset: "orig", "sv3_uniform", "sv4_uniform", "sv4_fov". */
@@ -126,9 +131,14 @@ int b200pt_download_probe(b200pt_ctx* ctx, float* pdfX, float* cdfX, float* pdfY
  * integrator for the configured schedule, writes accum/frame buffers, updates *params exactly as the
  * reference's render() leaves its public `launchParams`, and blocks until the GPU is idle. */
 int b200pt_render(b200pt_ctx* ctx, struct LaunchParams* params, const b200pt_config* cfg);
-/* Same, without the trailing device synchronisation (for back-to-back timing on ctx's stream). */
+/* Same, without the trailing device synchronisation; with cfg->frames_in_flight > 1 consecutive calls overlap on the device (see above). */
 int b200pt_render_async(b200pt_ctx* ctx, struct LaunchParams* params, const b200pt_config* cfg);
+/* Blocks until every frame submitted so far has finished. */
 int b200pt_synchronize(b200pt_ctx* ctx);
+/* Orders the context's primary stream (b200pt_device_buffers) after every frame in flight, without blocking the host: work the caller then
+ * enqueues on that stream - an event, a copy, an NCCL reduce of the accumulation buffer - sees all submitted frames.  Every other entry
+ * point that touches the frame buffers, the scene or the probe does this itself. */
+int b200pt_join(b200pt_ctx* ctx);
 
 /* SampleRenderer::downloadPixels (sv4/SimplePathtracer.cpp:279-283): W*H RGBA8, R in the low byte. */
 int b200pt_download_pixels(b200pt_ctx* ctx, uint32_t* host_rgba8);

@@ -19,6 +19,32 @@ template <typename T> struct DevBuf {
 struct HostMesh { size_t firstVertex, nVertices, firstTri, nTris;  bool hasTexcoord, hasNormal;  int textureID;  Material material{Material::NoInit{}}; };
 struct HostTexture { size_t offset;  int w, h; };
 
+// Everything one frame in flight owns: its stream, the path pool, the ray queues, the per-launch counters and the per-launch-index sums.
+// b200pt_render always uses lane 0; b200pt_render_async rotates over cfg.frames_in_flight lanes, so that the drain phases and the thin late
+// bounces of one frame overlap the wide early bounces of the next.  Frames still fold into the accumulation buffer in submission order:
+// each frame's finalize pass waits for the `done` event of the frame before it.
+#define B200PT_MAX_LANES 4
+struct Lane {
+    cudaStream_t stream = nullptr;
+    size_t poolCap = 0;
+    DevBuf<uint2> rng;  DevBuf<float4> thr, direct, indirect, alpha, pending, aovN, aovA;  DevBuf<int> state;  DevBuf<float> bsdfPdf;
+    DevBuf<float4> rayO[2], rayD[2], hit, shO, shD;
+    DevBuf<unsigned> counters;          // QC_COUNT queue counters + 8 running totals
+    DevBuf<float4> sumRad, sumAlpha, sumNormal, sumAlbedo;
+    DevBuf<TraceStats> stats;           // [0] closest, [1] any
+    cudaEvent_t done = nullptr;         // recorded after the last kernel of the lane's latest frame
+    bool busy = false;                  // has work the primary stream has not been ordered after yet
+    bool forked = false;                // already ordered after the primary stream's earlier work (since the last join)
+    void release() {
+        rng.release();  thr.release();  direct.release();  indirect.release();  alpha.release();  pending.release();
+        aovN.release();  aovA.release();  state.release();  bsdfPdf.release();
+        for (int i = 0; i < 2; ++i) { rayO[i].release();  rayD[i].release(); }
+        hit.release();  shO.release();  shD.release();  counters.release();
+        sumRad.release();  sumAlpha.release();  sumNormal.release();  sumAlbedo.release();  stats.release();
+        poolCap = 0;
+    }
+};
+
 struct b200pt_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -34,17 +60,27 @@ struct b200pt_ctx {
     int W = 0, H = 0;
     DevBuf<uint32_t> frameBuf;  DevBuf<float4> accumBuf, normalBuf, albedoBuf, colorBuf;
     DevBuf<float> probeData, probePdfX, probeCdfX, probePdfY, probeCdfY, probeRowTotal;  DevBuf<int> probeGuide;  int probeW = 0, probeH = 0;
-    // --- wavefront pool
-    size_t poolCap = 0;
-    DevBuf<uint2> rng;  DevBuf<float4> thr, direct, indirect, alpha, pending, aovN, aovA;  DevBuf<int> state;  DevBuf<float> bsdfPdf;
-    DevBuf<float4> rayO[2], rayD[2], hit, shO, shD;
-    DevBuf<unsigned> counters;          // QC_COUNT queue counters + 8 running totals
-    DevBuf<float4> sumRad, sumAlpha, sumNormal, sumAlbedo;
-    DevBuf<TraceStats> stats;           // [0] closest, [1] any
+    // --- wavefront state: one Lane per frame in flight (lane 0 runs on `stream`, the reference's single stream)
+    Lane lanes[B200PT_MAX_LANES];
+    int lastLane = -1;                  // lane of the most recently enqueued frame (its `done` event orders the next frame's accumulation)
+    int countersLane = 0;               // lane whose device counters `last` will be read from
+    unsigned seq = 0;                   // round-robin lane pick of b200pt_render_async
+    cudaEvent_t forkEv = nullptr;
     b200pt_counters last{};
     bool countersPending = false;  int profiled = 0;
     std::vector<cudaEvent_t> evPool;  std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> evUsed;  size_t evNext = 0;
 };
+
+// Orders the primary stream after every frame in flight on the other lanes (no host synchronisation): what the entry points that touch
+// shared state (frame buffers, scene, probe, counters) do first, and what b200pt_join exposes to callers that time or copy on that stream.
+static void joinLanes(b200pt_ctx* c) {
+    for (int k = 1; k < B200PT_MAX_LANES; ++k) {
+        Lane& L = c->lanes[k];
+        if (L.busy) CUDA_OK(cudaStreamWaitEvent(c->stream, L.done, 0));
+        L.busy = false;  L.forked = false;
+    }
+}
+static void enterCtx(b200pt_ctx* c) { CUDA_OK(cudaSetDevice(c->device));  joinLanes(c); }
 
 extern "C" {
 
@@ -83,6 +119,8 @@ b200pt_ctx* b200pt_create(int device) {
         b200pt_ctx* c = new b200pt_ctx();
         c->device = device;
         CUDA_OK(cudaStreamCreate(&c->stream));                 // the reference's single stream, SimplePathtracer.cpp:342
+        c->lanes[0].stream = c->stream;
+        CUDA_OK(cudaEventCreateWithFlags(&c->forkEv, cudaEventDisableTiming));
         return c;
     } catch (const std::exception& ex) { fail(ex.what());  return nullptr; }
 }
@@ -90,16 +128,19 @@ b200pt_ctx* b200pt_create(int device) {
 void b200pt_destroy(b200pt_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
-    cudaStreamSynchronize(c->stream);
+    for (int k = 0; k < B200PT_MAX_LANES; ++k) if (c->lanes[k].stream) cudaStreamSynchronize(c->lanes[k].stream);
     bvhFree(c->bvh);
     c->dVertices.release();  c->dNormals.release();  c->dTexcoords.release();  c->dIndices.release();  c->dTriMesh.release();  c->dMeshes.release();  c->dTexels.release();
     c->frameBuf.release();  c->accumBuf.release();  c->normalBuf.release();  c->albedoBuf.release();  c->colorBuf.release();
     c->probeData.release();  c->probePdfX.release();  c->probeCdfX.release();  c->probePdfY.release();  c->probeCdfY.release();  c->probeGuide.release();  c->probeRowTotal.release();
-    c->rng.release();  c->thr.release();  c->direct.release();  c->indirect.release();  c->alpha.release();  c->pending.release();
-    c->aovN.release();  c->aovA.release();  c->state.release();  c->bsdfPdf.release();
-    for (int i = 0; i < 2; ++i) { c->rayO[i].release();  c->rayD[i].release(); }
-    c->hit.release();  c->shO.release();  c->shD.release();  c->counters.release();
-    c->sumRad.release();  c->sumAlpha.release();  c->sumNormal.release();  c->sumAlbedo.release();  c->stats.release();
+    for (int k = 0; k < B200PT_MAX_LANES; ++k) {
+        Lane& L = c->lanes[k];
+        if (L.stream) cudaStreamSynchronize(L.stream);
+        L.release();
+        if (L.done) cudaEventDestroy(L.done);
+        if (k > 0 && L.stream) cudaStreamDestroy(L.stream);
+    }
+    if (c->forkEv) cudaEventDestroy(c->forkEv);
     for (auto ev : c->evPool) cudaEventDestroy(ev);
     cudaStreamDestroy(c->stream);
     delete c;
@@ -149,7 +190,7 @@ int b200pt_update_vertices(b200pt_ctx* c, int meshID, const float* vtx, size_t n
     API_BEGIN
     memcpy(c->hVertices.data() + m.firstVertex, vtx, nv * sizeof(float3));
     if (c->built) {                                           // device copy is live: patch it in place
-        CUDA_OK(cudaSetDevice(c->device));
+        enterCtx(c);
         CUDA_OK(cudaMemcpyAsync(c->dVertices.p + m.firstVertex, vtx, nv * sizeof(float3), cudaMemcpyHostToDevice, c->stream));
         CUDA_OK(cudaStreamSynchronize(c->stream));
         c->stale = true;
@@ -160,7 +201,7 @@ int b200pt_refit_accel(b200pt_ctx* c) {
     if (!c) return fail("b200pt_refit_accel: null context");
     if (!c->built) return fail("b200pt_refit_accel: b200pt_build_accel has not been called");
     API_BEGIN
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     bvhRefit(c->dVertices.p, c->dIndices.p, c->dTriMesh.p, c->dMeshes.p, c->stream, c->bvh, &c->refitMs);
     c->stale = false;
     API_END
@@ -169,7 +210,7 @@ int b200pt_refit_accel(b200pt_ctx* c) {
 int b200pt_build_accel(b200pt_ctx* c, uint64_t* handle_out) {
     if (!c) return fail("b200pt_build_accel: null context");
     API_BEGIN
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     if (c->hIndices.size() >= (1u << 28)) throw std::runtime_error("b200pt_build_accel: more than 2^28 triangles");
     std::vector<MeshInfo> infos(c->hMeshes.size());
     for (size_t i = 0; i < infos.size(); ++i) {

@@ -4,7 +4,7 @@ extern "C" {
 int b200pt_download_pixels(b200pt_ctx* c, uint32_t* host) {
     if (!c || !host) return fail("b200pt_download_pixels: null argument");
     API_BEGIN
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     CUDA_OK(cudaMemcpyAsync(host, c->frameBuf.p, sizeof(uint32_t) * (size_t)c->W * c->H, cudaMemcpyDeviceToHost, c->stream));
     CUDA_OK(cudaStreamSynchronize(c->stream));
     API_END
@@ -12,7 +12,7 @@ int b200pt_download_pixels(b200pt_ctx* c, uint32_t* host) {
 int b200pt_download_accum(b200pt_ctx* c, float* host) {
     if (!c || !host) return fail("b200pt_download_accum: null argument");
     API_BEGIN
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     CUDA_OK(cudaMemcpyAsync(host, c->accumBuf.p, sizeof(float4) * (size_t)c->W * c->H, cudaMemcpyDeviceToHost, c->stream));
     CUDA_OK(cudaStreamSynchronize(c->stream));
     API_END
@@ -20,7 +20,7 @@ int b200pt_download_accum(b200pt_ctx* c, float* host) {
 int b200pt_upload_accum(b200pt_ctx* c, const float* host) {
     if (!c || !host) return fail("b200pt_upload_accum: null argument");
     API_BEGIN
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     CUDA_OK(cudaMemcpyAsync(c->accumBuf.p, host, sizeof(float4) * (size_t)c->W * c->H, cudaMemcpyHostToDevice, c->stream));
     CUDA_OK(cudaStreamSynchronize(c->stream));
     API_END
@@ -28,7 +28,7 @@ int b200pt_upload_accum(b200pt_ctx* c, const float* host) {
 int b200pt_download_aov(b200pt_ctx* c, int which, float* host) {
     if (!c || !host || which < 0 || which > 2) return fail("b200pt_download_aov: bad argument");
     API_BEGIN
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     const float4* src = which == 0 ? c->normalBuf.p : (which == 1 ? c->albedoBuf.p : c->colorBuf.p);
     CUDA_OK(cudaMemcpyAsync(host, src, sizeof(float4) * (size_t)c->W * c->H, cudaMemcpyDeviceToHost, c->stream));
     CUDA_OK(cudaStreamSynchronize(c->stream));
@@ -44,7 +44,7 @@ int b200pt_device_buffers(b200pt_ctx* c, void** accum, void** frame, void** stre
 int b200pt_clear_accum(b200pt_ctx* c) {
     if (!c) return fail("b200pt_clear_accum: null context");
     API_BEGIN
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     if (c->accumBuf.p) CUDA_OK(cudaMemsetAsync(c->accumBuf.p, 0, sizeof(float4) * (size_t)c->W * c->H, c->stream));
     if (c->frameBuf.p) CUDA_OK(cudaMemsetAsync(c->frameBuf.p, 0, sizeof(uint32_t) * (size_t)c->W * c->H, c->stream));
     API_END
@@ -52,7 +52,7 @@ int b200pt_clear_accum(b200pt_ctx* c) {
 int b200pt_resolve_sum(b200pt_ctx* c, const LaunchParams* params, const b200pt_config* cfg, int nPasses) {
     if (!c || !params || !cfg || nPasses <= 0) return fail("b200pt_resolve_sum: bad argument");
     API_BEGIN
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     launchResolveSum(frameOf(*params, *cfg), nPasses, c->stream);
     CUDA_OK(cudaStreamSynchronize(c->stream));
     API_END
@@ -75,7 +75,7 @@ int b200pt_tonemap_sqrt_host(b200pt_ctx* c, int w, int h, const float* in, uint3
     API_BEGIN
     const size_t n = (size_t)w * h;
     if (!n) return 0;
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     DevBuf<float4> din;  DevBuf<uint32_t> dout;
     din.ensure(n);  dout.ensure(n);
     CUDA_OK(cudaMemcpyAsync(din.p, in, 16 * n, cudaMemcpyHostToDevice, c->stream));
@@ -91,7 +91,7 @@ int b200pt_trace_primary(b200pt_ctx* c, const LaunchParams* params, const b200pt
     if (!c || !params || !cfg || !prim || !mesh || !t || !u || !v) return fail("b200pt_trace_primary: null argument");
     API_BEGIN
     if (!c->built) throw std::runtime_error("b200pt_trace_primary: b200pt_build_accel has not been called");
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     LaunchParams P = *params;
     std::vector<PassDesc> passes;
     b200pt_config one = *cfg;
@@ -124,7 +124,7 @@ int b200pt_trace_rays(b200pt_ctx* c, const float* org, const float* dir, size_t 
     API_BEGIN
     if (!c->built) throw std::runtime_error("b200pt_trace_rays: b200pt_build_accel has not been called");
     if (!n) return 0;
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     std::vector<float4> ho(n), hd(n);
     for (size_t i = 0; i < n; ++i) { ho[i] = make_float4(org[3 * i], org[3 * i + 1], org[3 * i + 2], 1.f);  hd[i] = make_float4(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2], 0.f); }
     DevBuf<float4> ro, rd, hit;  DevBuf<int32_t> dp, dm;  DevBuf<float> dt, du, dv;
@@ -157,7 +157,7 @@ int b200pt_debug_morton(b200pt_ctx* c, uint64_t* codes, uint32_t* order, float* 
     if (!c || !codes || !order || !bounds) return fail("b200pt_debug_morton: null argument");
     API_BEGIN
     if (!c->built) throw std::runtime_error("b200pt_debug_morton: b200pt_build_accel has not been called");
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     const size_t n = c->bvh.nTris;
     if (n) {
         CUDA_OK(cudaMemcpy(codes, c->bvh.mortonByGid, 8 * n, cudaMemcpyDeviceToHost));
@@ -185,7 +185,7 @@ int b200pt_download_bvh(b200pt_ctx* c, void* nodes32, size_t maxNodes, uint32_t*
     API_BEGIN
     if (!c->built) throw std::runtime_error("b200pt_download_bvh: b200pt_build_accel has not been called");
     if (maxNodes < c->bvh.nNodes || maxTris < c->bvh.nTris) throw std::runtime_error("b200pt_download_bvh: buffers too small");
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     if (c->bvh.nNodes) CUDA_OK(cudaMemcpy(nodes32, c->bvh.nodes, sizeof(BvhNode) * (size_t)c->bvh.nNodes, cudaMemcpyDeviceToHost));
     if (c->bvh.nTris) CUDA_OK(cudaMemcpy(triGid, c->bvh.finalGid, 4 * (size_t)c->bvh.nTris, cudaMemcpyDeviceToHost));
     API_END
@@ -196,7 +196,7 @@ int b200pt_download_bvh4(b200pt_ctx* c, void* nodes64, size_t maxNodes) {
     API_BEGIN
     if (!c->built) throw std::runtime_error("b200pt_download_bvh4: b200pt_build_accel has not been called");
     if (maxNodes < c->bvh.nNodes4) throw std::runtime_error("b200pt_download_bvh4: buffer too small");
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     if (c->bvh.nNodes4) CUDA_OK(cudaMemcpy(nodes64, c->bvh.nodes4, sizeof(BvhNode4) * (size_t)c->bvh.nNodes4, cudaMemcpyDeviceToHost));
     API_END
 }
@@ -204,7 +204,7 @@ int b200pt_download_bvh4(b200pt_ctx* c, void* nodes64, size_t maxNodes) {
 int b200pt_get_counters(b200pt_ctx* c, b200pt_counters* o) {
     if (!c || !o) return fail("b200pt_get_counters: null argument");
     API_BEGIN
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     if (c->countersPending) { CUDA_OK(cudaStreamSynchronize(c->stream));  collectCounters(c); }
     *o = c->last;
     API_END

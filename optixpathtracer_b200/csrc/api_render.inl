@@ -24,18 +24,32 @@ static size_t poolLimit() {
     return std::max<size_t>(v, 1024);
 }
 
-static void ensurePool(b200pt_ctx* c, size_t slots, bool aovs, bool mis) {
-    if (slots > c->poolCap) {
-        c->rng.ensure(slots);  c->thr.ensure(slots);  c->state.ensure(slots);  c->direct.ensure(slots);  c->indirect.ensure(slots);
-        c->alpha.ensure(slots);  c->pending.ensure(slots);
-        for (int i = 0; i < 2; ++i) { c->rayO[i].ensure(slots);  c->rayD[i].ensure(slots); }
-        c->hit.ensure(slots);  c->shO.ensure(slots);  c->shD.ensure(slots);
-        c->poolCap = slots;
+static void ensurePool(Lane& c, size_t slots, bool aovs, bool mis) {
+    if (slots > c.poolCap) {
+        c.rng.ensure(slots);  c.thr.ensure(slots);  c.state.ensure(slots);  c.direct.ensure(slots);  c.indirect.ensure(slots);
+        c.alpha.ensure(slots);  c.pending.ensure(slots);
+        for (int i = 0; i < 2; ++i) { c.rayO[i].ensure(slots);  c.rayD[i].ensure(slots); }
+        c.hit.ensure(slots);  c.shO.ensure(slots);  c.shD.ensure(slots);
+        c.poolCap = slots;
     }
-    if (aovs) { c->aovN.ensure(c->poolCap);  c->aovA.ensure(c->poolCap); }
-    if (mis) c->bsdfPdf.ensure(c->poolCap);
-    c->counters.ensure(QC_STRIDE * QC_MAX_LAUNCHES + 8);                     // per-launch queue counters, then 8 frame totals
-    c->stats.ensure(2);
+    if (aovs) { c.aovN.ensure(c.poolCap);  c.aovA.ensure(c.poolCap); }
+    if (mis) c.bsdfPdf.ensure(c.poolCap);
+    c.counters.ensure(QC_STRIDE * QC_MAX_LAUNCHES + 8);                      // per-launch queue counters, then 8 frame totals
+    c.stats.ensure(2);
+}
+static PathPool poolOf(Lane& L) { return PathPool{L.rng.p, L.thr.p, L.state.p, L.direct.p, L.indirect.p, L.alpha.p, L.pending.p, L.bsdfPdf.p, L.aovN.p, L.aovA.p}; }
+static Queues queuesOf(Lane& L) {
+    Queues Q;
+    for (int i = 0; i < 2; ++i) { Q.rayO[i] = L.rayO[i].p;  Q.rayD[i] = L.rayD[i].p; }
+    Q.hit = L.hit.p;  Q.shO = L.shO.p;  Q.shD = L.shD.p;  Q.counters = L.counters.p;
+    return Q;
+}
+// lane k > 0 gets its stream and `done` event on first use
+static Lane& laneOf(b200pt_ctx* c, int k) {
+    Lane& L = c->lanes[k];
+    if (!L.stream) CUDA_OK(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
+    if (!L.done) CUDA_OK(cudaEventCreateWithFlags(&L.done, cudaEventDisableTiming));
+    return L;
 }
 
 struct StageTimer {          // CUDA-event pairs per stage, resolved after the frame (profile=1 only)
@@ -54,11 +68,12 @@ enum { ST_RAYGEN = 0, ST_TRACE, ST_TRACE_TAIL, ST_SHADE, ST_ACCUM, ST_TOTAL };
 static void collectCounters(b200pt_ctx* c) {
     if (!c->countersPending) return;
     unsigned h[8];
-    CUDA_OK(cudaMemcpy(h, c->counters.p + QC_STRIDE * QC_MAX_LAUNCHES, sizeof(h), cudaMemcpyDeviceToHost));
+    Lane& L = c->lanes[c->countersLane];
+    CUDA_OK(cudaMemcpy(h, L.counters.p + QC_STRIDE * QC_MAX_LAUNCHES, sizeof(h), cudaMemcpyDeviceToHost));
     c->last.radiance_rays = h[0];  c->last.shadow_rays = h[1];  c->last.samples = h[2];
     if (c->profiled & 2) {
         TraceStats st[2];
-        CUDA_OK(cudaMemcpy(st, c->stats.p, sizeof(st), cudaMemcpyDeviceToHost));
+        CUDA_OK(cudaMemcpy(st, L.stats.p, sizeof(st), cudaMemcpyDeviceToHost));
         c->last.nodes_fetched = st[0].nodes;  c->last.tris_fetched = st[0].tris;
         c->last.nodes_fetched_shadow = st[1].nodes;  c->last.tris_fetched_shadow = st[1].tris;
     }
@@ -154,13 +169,23 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
     buildSchedule(*params, cfg, passes);
     const FrameParams F = frameOf(*params, cfg, c);
     const SceneDev S = sceneOf(c);
-    cudaStream_t s = c->stream;
+    // Lane of this frame: blocking and instrumented frames run on lane 0 (the primary stream); asynchronous frames rotate over
+    // cfg.frames_in_flight lanes.  A lane other than 0 is first ordered after whatever the primary stream held when the batch began.
+    const int nLanes = (sync || (cfg.profile & 3)) ? 1 : std::min(std::max(cfg.frames_in_flight, 1), B200PT_MAX_LANES);
+    const int laneIdx = nLanes > 1 ? (int)(c->seq++ % (unsigned)nLanes) : 0;
+    Lane& L = laneOf(c, laneIdx);
+    cudaStream_t s = L.stream;
+    if (laneIdx > 0 && !L.forked) {
+        CUDA_OK(cudaEventRecord(c->forkEv, c->stream));
+        CUDA_OK(cudaStreamWaitEvent(s, c->forkEv, 0));
+        L.forked = true;
+    }
 
     // launch-index records and chunks
     size_t nRec = 0;
     for (auto& p : passes) { if (p.P.spl <= 0) throw std::runtime_error("b200pt_render: samples_per_launch must be > 0");  p.P.launchBase = (unsigned)nRec;  nRec += p.nLaunch; }
-    c->sumRad.ensure(std::max<size_t>(nRec, 1));  c->sumAlpha.ensure(std::max<size_t>(nRec, 1));
-    if (cfg.write_aovs) { c->sumNormal.ensure(std::max<size_t>(nRec, 1));  c->sumAlbedo.ensure(std::max<size_t>(nRec, 1)); }
+    L.sumRad.ensure(std::max<size_t>(nRec, 1));  L.sumAlpha.ensure(std::max<size_t>(nRec, 1));
+    if (cfg.write_aovs) { L.sumNormal.ensure(std::max<size_t>(nRec, 1));  L.sumAlbedo.ensure(std::max<size_t>(nRec, 1)); }
     const size_t limit = poolLimit();
     std::vector<std::vector<Chunk>> groups(1);
     size_t used = 0, maxUsed = 0;
@@ -177,21 +202,19 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
         }
     }
     if (maxUsed >= ((size_t)1 << 31)) throw std::runtime_error("b200pt_render: pool too large");
-    ensurePool(c, std::max<size_t>(maxUsed, 1), cfg.write_aovs != 0, cfg.mis_on_miss != 0);
+    ensurePool(L, std::max<size_t>(maxUsed, 1), cfg.write_aovs != 0, cfg.mis_on_miss != 0);
 
-    PathPool pool{c->rng.p, c->thr.p, c->state.p, c->direct.p, c->indirect.p, c->alpha.p, c->pending.p, c->bsdfPdf.p, c->aovN.p, c->aovA.p};
-    Queues Q;
-    for (int i = 0; i < 2; ++i) { Q.rayO[i] = c->rayO[i].p;  Q.rayD[i] = c->rayD[i].p; }
-    Q.hit = c->hit.p;  Q.shO = c->shO.p;  Q.shD = c->shD.p;  Q.counters = c->counters.p;
+    PathPool pool = poolOf(L);
+    Queues Q = queuesOf(L);
 
     const bool prof = (cfg.profile & 1) != 0, count = (cfg.profile & 2) != 0;   // 1: stage events, 2: traversal counters
     c->evUsed.clear();  c->evNext = 0;  c->profiled = cfg.profile & 3;
     StageTimer T{c, prof};
     cudaEvent_t a = nullptr, b = nullptr, ta = nullptr, tb = nullptr;
     unsigned launches = 0, nClosest = 0, nAny = 0;
-    unsigned* totals = c->counters.p + QC_STRIDE * QC_MAX_LAUNCHES;
-    CUDA_OK(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned) * (QC_STRIDE * QC_MAX_LAUNCHES + 8), s));
-    if (count) CUDA_OK(cudaMemsetAsync(c->stats.p, 0, 2 * sizeof(TraceStats), s));
+    unsigned* totals = L.counters.p + QC_STRIDE * QC_MAX_LAUNCHES;
+    CUDA_OK(cudaMemsetAsync(L.counters.p, 0, sizeof(unsigned) * (QC_STRIDE * QC_MAX_LAUNCHES + 8), s));
+    if (count) CUDA_OK(cudaMemsetAsync(L.stats.p, 0, 2 * sizeof(TraceStats), s));
     T.begin(ST_TOTAL, ta, tb);
     const int bounces = cfg.max_depth + ((c->hasCatcher || cfg.max_depth == 0) ? 1 : 0);   // the dropped last segment is traced only if alpha can still change
     const int cullBack = cfg.shadow_mode == B200PT_SHADOW_CULL_BACK;
@@ -210,7 +233,7 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
             unsigned* ctr = Q.counters + QC_STRIDE * d;
             T.begin(d < bounces ? ST_TRACE : ST_TRACE_TAIL, a, b);
             launchTrace(S, Q.rayO[cur], Q.rayD[cur], Q.hit, ctr + (d < bounces ? QC_RAYS : 3 /* always 0 */), Q.shO, Q.shD, ctr + QC_SHADOWS, ctr + QC_HEAD, cfg.tmin, shadowTmin, cfg.tmax,
-                        cullBack, pool, count ? c->stats.p : nullptr, s);
+                        cullBack, pool, count ? L.stats.p : nullptr, s);
             T.end(b);  ++launches;  ++nClosest;
             if (d == bounces) break;
             T.begin(ST_SHADE, a, b);
@@ -222,18 +245,22 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
         T.begin(ST_ACCUM, a, b);
         for (auto& ch : group) {
             PassParams P = passes[ch.pass].P;  P.slotBase = ch.slotBase;
-            launchGather(F, P, ch.k0, ch.k1, pool, c->sumRad.p, c->sumAlpha.p, c->sumNormal.p, c->sumAlbedo.p, s);  ++launches;
+            launchGather(F, P, ch.k0, ch.k1, pool, L.sumRad.p, L.sumAlpha.p, L.sumNormal.p, L.sumAlbedo.p, s);  ++launches;
         }
         T.end(b);
     }
+    // frames fold into the accumulation / frame / AOV buffers in submission order, whatever lane they ran on
+    if (c->lastLane >= 0 && c->lastLane != laneIdx) CUDA_OK(cudaStreamWaitEvent(s, c->lanes[c->lastLane].done, 0));
     T.begin(ST_ACCUM, a, b);
     for (auto& p : passes) {                                                     // pass order = the reference's launch order (overwrite semantics)
         if (!p.nLaunch) continue;
-        launchFinalize(F, p.P, c->sumRad.p, c->sumAlpha.p, c->sumNormal.p, c->sumAlbedo.p, s);  ++launches;
+        launchFinalize(F, p.P, L.sumRad.p, L.sumAlpha.p, L.sumNormal.p, L.sumAlbedo.p, s);  ++launches;
     }
     T.end(b);
     T.end(tb);
     CUDA_OK(cudaGetLastError());
+    CUDA_OK(cudaEventRecord(L.done, s));
+    c->lastLane = laneIdx;  c->countersLane = laneIdx;  L.busy = laneIdx > 0;
     c->last = b200pt_counters{};
     c->last.kernel_launches = launches;  c->last.n_trace_closest_launches = nClosest;  c->last.n_trace_any_launches = nAny;
     c->countersPending = true;
@@ -250,7 +277,7 @@ int b200pt_resize(b200pt_ctx* c, int w, int h, LaunchParams* params) {
     if (w == 0 || h == 0) return 0;                                              // minimised window, SimplePathtracer.cpp:233
     if (w < 0 || h < 0) return fail("b200pt_resize: negative size");
     API_BEGIN
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     CUDA_OK(cudaStreamSynchronize(c->stream));
     const size_t n = (size_t)w * h;
     c->frameBuf.release();  c->accumBuf.release();  c->normalBuf.release();  c->albedoBuf.release();  c->colorBuf.release();
@@ -267,7 +294,7 @@ int b200pt_set_probe(b200pt_ctx* c, int w, int h, const float* data, const float
     if (!c || !params) return fail("b200pt_set_probe: null argument");
     if (w <= 0 || h <= 0 || !data || !pdfX || !cdfX || !pdfY || !cdfY) return fail("Probe Data is not valid");   // Probe.h:104-105
     API_BEGIN
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     const size_t n = (size_t)w * h;
     c->probeData.ensure(4 * n);  c->probePdfX.ensure(n);  c->probeCdfX.ensure(n);  c->probePdfY.ensure(h);  c->probeCdfY.ensure(h);
     CUDA_OK(cudaMemcpyAsync(c->probeData.p, data, 16 * n, cudaMemcpyHostToDevice, c->stream));
@@ -292,12 +319,13 @@ int b200pt_set_probe(b200pt_ctx* c, int w, int h, const float* data, const float
 int b200pt_render_whitted(b200pt_ctx* c, const b200pt_whitted_params* wp, uint32_t* deviceColorBuffer) {
     if (!c || !wp) return fail("b200pt_render_whitted: null argument");
     API_BEGIN
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     if (!c->built) throw std::runtime_error("b200pt_render_whitted: b200pt_build_accel has not been called");
     if (c->W <= 0 || c->H <= 0) throw std::runtime_error("b200pt_render_whitted: frame buffers not allocated (call b200pt_resize)");
     const size_t n = (size_t)c->W * c->H;
     if (n >= ((size_t)1 << 31)) throw std::runtime_error("b200pt_render_whitted: frame too large");
-    ensurePool(c, n, false, false);
+    Lane& L = c->lanes[0];
+    ensurePool(L, n, false, false);
     WhittedParams P;
     P.W = c->W;  P.H = c->H;
     P.position = make_float3(wp->position[0], wp->position[1], wp->position[2]);
@@ -307,12 +335,10 @@ int b200pt_render_whitted(b200pt_ctx* c, const b200pt_whitted_params* wp, uint32
     P.lightPos = make_float3(wp->light_pos[0], wp->light_pos[1], wp->light_pos[2]);
     const SceneDev S = sceneOf(c);
     cudaStream_t s = c->stream;
-    PathPool pool{c->rng.p, c->thr.p, c->state.p, c->direct.p, c->indirect.p, c->alpha.p, c->pending.p, c->bsdfPdf.p, c->aovN.p, c->aovA.p};
-    Queues Q;
-    for (int i = 0; i < 2; ++i) { Q.rayO[i] = c->rayO[i].p;  Q.rayD[i] = c->rayD[i].p; }
-    Q.hit = c->hit.p;  Q.shO = c->shO.p;  Q.shD = c->shD.p;  Q.counters = c->counters.p;
+    PathPool pool = poolOf(L);
+    Queues Q = queuesOf(L);
     c->countersPending = false;
-    CUDA_OK(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned) * (QC_STRIDE * QC_MAX_LAUNCHES + 8), s));
+    CUDA_OK(cudaMemsetAsync(L.counters.p, 0, sizeof(unsigned) * (QC_STRIDE * QC_MAX_LAUNCHES + 8), s));
     unsigned* c0 = Q.counters;
     unsigned* c1 = Q.counters + QC_STRIDE;
     launchWhittedRaygen(P, Q, pool, c0, s);
@@ -323,7 +349,7 @@ int b200pt_render_whitted(b200pt_ctx* c, const b200pt_whitted_params* wp, uint32
     CUDA_OK(cudaGetLastError());
     CUDA_OK(cudaStreamSynchronize(s));
     std::vector<unsigned> hc(2 * QC_STRIDE);
-    CUDA_OK(cudaMemcpy(hc.data(), c->counters.p, sizeof(unsigned) * hc.size(), cudaMemcpyDeviceToHost));
+    CUDA_OK(cudaMemcpy(hc.data(), L.counters.p, sizeof(unsigned) * hc.size(), cudaMemcpyDeviceToHost));
     c->last = b200pt_counters{};
     c->last.samples = n;  c->last.radiance_rays = hc[QC_RAYS];  c->last.shadow_rays = hc[QC_STRIDE + QC_SHADOWS];
     c->last.kernel_launches = 5;  c->last.n_trace_closest_launches = 1;  c->last.n_trace_any_launches = 1;
@@ -336,7 +362,7 @@ int b200pt_set_probe_image(b200pt_ctx* c, int w, int h, const float* data, const
     if (!c || !params) return fail("b200pt_set_probe_image: null argument");
     if (w <= 0 || h <= 0 || !data) return fail("Probe Data is not valid");
     API_BEGIN
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     const size_t n = (size_t)w * h;
     c->probeData.ensure(4 * n);  c->probePdfX.ensure(n);  c->probeCdfX.ensure(n);  c->probePdfY.ensure(h);  c->probeCdfY.ensure(h);
     c->probeGuide.ensure(probeGuideSize(h));
@@ -358,7 +384,7 @@ int b200pt_download_probe(b200pt_ctx* c, float* pdfX, float* cdfX, float* pdfY, 
     if (!c) return fail("b200pt_download_probe: null context");
     if (!c->probeW || !c->probeH) return fail("b200pt_download_probe: no probe set");
     API_BEGIN
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);
     const size_t n = (size_t)c->probeW * c->probeH;
     if (pdfX) CUDA_OK(cudaMemcpyAsync(pdfX, c->probePdfX.p, 4 * n, cudaMemcpyDeviceToHost, c->stream));
     if (cdfX) CUDA_OK(cudaMemcpyAsync(cdfX, c->probeCdfX.p, 4 * n, cudaMemcpyDeviceToHost, c->stream));
@@ -381,9 +407,15 @@ int b200pt_render_async(b200pt_ctx* c, LaunchParams* params, const b200pt_config
 int b200pt_synchronize(b200pt_ctx* c) {
     if (!c) return fail("b200pt_synchronize: null context");
     API_BEGIN
-    CUDA_OK(cudaSetDevice(c->device));
+    enterCtx(c);                                                                 // orders the primary stream after every lane in flight
     CUDA_OK(cudaStreamSynchronize(c->stream));
     collectCounters(c);
+    API_END
+}
+int b200pt_join(b200pt_ctx* c) {
+    if (!c) return fail("b200pt_join: null context");
+    API_BEGIN
+    enterCtx(c);
     API_END
 }
 

@@ -114,6 +114,10 @@ class SampleRenderer:
     def synchronize(self):
         _lib.check(self._L.b200pt_synchronize(self._h))
 
+    def join(self):
+        """Order the renderer's primary stream after every frame in flight (config.frames_in_flight > 1), without blocking the host."""
+        _lib.check(self._L.b200pt_join(self._h))
+
     def resize(self, newSize):
         w, h = int(newSize[0]), int(newSize[1])
         if w == 0 or h == 0:

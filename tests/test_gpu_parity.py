@@ -327,6 +327,38 @@ def test_render_is_deterministic_and_progressive(sponza_small):
     r.close()
 
 
+@pytest.mark.parametrize("pname", ["orig", "sv4_fov"])
+def test_frames_in_flight_fold_in_submission_order(sponza_small, pname):
+    """b200pt_render_async with cfg.frames_in_flight = 3: consecutive frames overlap on the device (three lanes: stream + pool + queues each)
+    but fold into the accumulation buffer in submission order, so accumulation, pixels and AOVs equal the one-at-a-time sequence bit for bit;
+    a blocking render() in the middle of the batch and the copies that follow it see every frame submitted before them."""
+    probe = analytic_sky(128, 64)
+    cam = preset_camera("sponza")
+
+    def run(in_flight):
+        cfg = preset(pname)
+        if pname == "orig":
+            cfg.uniform_spl = 1
+        cfg.frames_in_flight = in_flight
+        r = make_renderer(sponza_small, probe, (200, 120), cam, cfg)
+        if pname == "sv4_fov":
+            r.launchParams.frame.c.x, r.launchParams.frame.c.y = 100, 60
+            r.config.inner_radius, r.config.outer_radius = 20, 50
+        for k in range(7):
+            if pname == "orig":
+                r.launchParams.frame.subframe_index = k
+            r.render(sync=(in_flight == 1 or k == 3))
+        acc, px = r.downloadAccum(), r.downloadPixels()             # no explicit synchronize: the copies order themselves after the lanes
+        cnt = r.counters()
+        r.close()
+        return acc, px, cnt
+
+    acc1, px1, cnt1 = run(1)
+    acc3, px3, cnt3 = run(3)
+    assert np.array_equal(acc1, acc3) and np.array_equal(px1, px3)
+    assert (cnt1.samples, cnt1.radiance_rays, cnt1.shadow_rays) == (cnt3.samples, cnt3.radiance_rays, cnt3.shadow_rays)   # of the last frame
+
+
 def test_tonemap_sqrt_exact():
     g = golden("display")
     rgba = np.concatenate([g["rgb"], np.ones((len(g["rgb"]), 1), np.float32)], 1).reshape(1, -1, 4)
