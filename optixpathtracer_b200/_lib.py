@@ -12,7 +12,7 @@ LIB_PATH = os.environ.get("B200PT_LIB") or os.path.join(_HERE, "csrc", "libb200p
 SYMBOLS = [
     "b200pt_config_preset", "b200pt_create", "b200pt_destroy", "b200pt_last_error", "b200pt_add_texture",
     "b200pt_add_mesh", "b200pt_update_vertices", "b200pt_refit_accel", "b200pt_build_accel", "b200pt_resize", "b200pt_set_probe", "b200pt_set_probe_image", "b200pt_download_probe", "b200pt_render",
-    "b200pt_render_whitted", "b200pt_render_async", "b200pt_synchronize", "b200pt_join", "b200pt_download_pixels", "b200pt_download_accum",
+    "b200pt_render_whitted", "b200pt_render_async", "b200pt_synchronize", "b200pt_join", "b200pt_download_pixels", "b200pt_download_pixels_async", "b200pt_download_accum",
     "b200pt_upload_accum", "b200pt_download_aov", "b200pt_device_buffers", "b200pt_resolve_sum", "b200pt_clear_accum",
     "b200pt_tonemap_sqrt", "b200pt_tonemap_sqrt_host", "b200pt_trace_primary", "b200pt_trace_rays",
     "b200pt_debug_morton", "b200pt_bvh_info_get", "b200pt_download_bvh", "b200pt_download_bvh4", "b200pt_get_counters",
@@ -57,6 +57,7 @@ def lib():
     L.b200pt_synchronize.argtypes = [vp]
     L.b200pt_join.argtypes = [vp]
     L.b200pt_download_pixels.argtypes = [vp, vp]
+    L.b200pt_download_pixels_async.argtypes = [vp, vp]
     L.b200pt_download_accum.argtypes = [vp, vp]
     L.b200pt_upload_accum.argtypes = [vp, vp]
     L.b200pt_download_aov.argtypes = [vp, i32, vp]

@@ -9,6 +9,20 @@ int b200pt_download_pixels(b200pt_ctx* c, uint32_t* host) {
     CUDA_OK(cudaStreamSynchronize(c->stream));
     API_END
 }
+// downloadPixels for frames in flight: the copy is enqueued right behind the finalize pass of the most recently submitted frame, on that
+// frame's own stream, and the frame's `done` event moves behind it - so the next frame (whose finalize overwrites the frame buffer) waits for
+// the copy while every other lane keeps tracing.  `host` should be pinned; it is valid after b200pt_synchronize.
+int b200pt_download_pixels_async(b200pt_ctx* c, uint32_t* host) {
+    if (!c || !host) return fail("b200pt_download_pixels_async: null argument");
+    API_BEGIN
+    CUDA_OK(cudaSetDevice(c->device));
+    const int k = c->lastLane < 0 ? 0 : c->lastLane;
+    Lane& L = c->lanes[k];
+    if (!L.stream) throw std::runtime_error("b200pt_download_pixels_async: no frame has been rendered");
+    CUDA_OK(cudaMemcpyAsync(host, c->frameBuf.p, sizeof(uint32_t) * (size_t)c->W * c->H, cudaMemcpyDeviceToHost, L.stream));
+    if (L.done) CUDA_OK(cudaEventRecord(L.done, L.stream));
+    API_END
+}
 int b200pt_download_accum(b200pt_ctx* c, float* host) {
     if (!c || !host) return fail("b200pt_download_accum: null argument");
     API_BEGIN

@@ -131,6 +131,10 @@ class SampleRenderer:
         _lib.check(self._L.b200pt_download_pixels(self._h, _ptr(h_pixels)))
         return h_pixels
 
+    def downloadPixelsAsync(self, h_pixels):
+        """downloadPixels behind the most recently submitted frame (render(sync=False)); h_pixels: pinned (h, w) uint32, valid after synchronize()."""
+        _lib.check(self._L.b200pt_download_pixels_async(self._h, _ptr(h_pixels)))
+
     def setCamera(self, camera):
         self.lastSetCamera = camera
         set_camera(self.launchParams, camera)
