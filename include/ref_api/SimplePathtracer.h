@@ -61,6 +61,16 @@ public:
         launchParams.frame.frame_buffer = reinterpret_cast<uchar4*>(deviceFrameBuffer);
         render();
     }
+    // Extensions with no reference counterpart (its render() always ends in CUDA_SYNC_CHECK): submit a frame without waiting, with
+    // config.frames_in_flight (1..4) frames overlapping on the device - they still fold into the accumulation buffer in submission order,
+    // so the pixels are those of consecutive render() calls; downloadPixelsAsync queues the copy behind the frame just submitted (pinned
+    // h_pixels, valid after synchronize()).
+    void renderAsync() {
+        if (launchParams.frame.size.x == 0) return;
+        if (b200pt_render_async(ctx, &launchParams, &config) != 0) fail();
+    }
+    void downloadPixelsAsync(uint32_t h_pixels[]) { if (b200pt_download_pixels_async(ctx, h_pixels) != 0) fail(); }
+    void synchronize() { if (b200pt_synchronize(ctx) != 0) fail(); }
     // resize frame buffer to given resolution (:231-277); zero sizes are ignored; does not reset subframe_index.
     void resize(const int2& newSize) {
         if (newSize.x == 0 || newSize.y == 0) return;
