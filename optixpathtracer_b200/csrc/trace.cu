@@ -166,53 +166,14 @@ __device__ __forceinline__ bool triEval(const float4 a, const float4 b, const fl
 
 struct Best { float t, u, v; int slot; unsigned gid; };
 
-// Traversal stack: a per-thread array in local memory.  TRACE_TOS = 1 is a measured-and-rejected variant kept for sweeps: the top entry in a
-// register and the local-memory accesses as predicated PTX (`@p ld.local`) instead of nvcc's divergent branch around the LDL.  It removes the
-// BSSY/BRA/BSYNC regions that 3-4 lanes of 32 run in 88 % of the node steps, but every push then carries the spill of the old top and the warp
-// waits on the refill load anyway: 2.85 ms against 2.76 ms per frame on B200.
-#ifndef TRACE_TOS
-#define TRACE_TOS 0
-#endif
-#if TRACE_TOS
-// Predicated local-memory accesses written in PTX: nvcc turns `if (c) tos = stack[i]` into a divergent branch region (BSSY/BRA/BSYNC, run by
-// 3-4 lanes of 32 in 88 % of the node steps - r01h2 source-level profile); `@p ld.local` is one instruction and no reconvergence point.
-// The array is only ever touched through these two helpers (its address escapes into them), so the compiler keeps it in local memory.
-__device__ __forceinline__ void stLocalIf(unsigned long long addr, int v, bool p) {
-    asm volatile("{ .reg .pred q;  setp.ne.s32 q, %2, 0;  @q st.local.b32 [%0], %1; }" :: "l"(addr), "r"(v), "r"((int)p) : "memory");
-}
-__device__ __forceinline__ void ldLocalIf(int& v, unsigned long long addr, bool p) {
-    asm volatile("{ .reg .pred q;  setp.ne.s32 q, %2, 0;  @q ld.local.b32 %0, [%1]; }" : "+r"(v) : "l"(addr), "r"((int)p) : "memory");
-}
-#define SADDR_(i) (stackAddr + 4ull * (unsigned)(i))
-#define STACK_DECL_ int stack[B200PT_STACK];  const unsigned long long stackAddr = (unsigned long long)__cvta_generic_to_local(stack);  int sp = 0, tos = EMPTY;
-// push x if c;  pop into dst if c (dst keeps its value otherwise)
-#define PUSH_IF_(x, c) { const bool c_ = (c);  stLocalIf(SADDR_(sp - 1), tos, c_ && sp > 0);  tos = c_ ? (x) : tos;  sp += c_ ? 1 : 0; }
-#define POP_IF_(dst, c) { const bool c_ = (c), p_ = c_ && sp > 0;  dst = c_ ? (sp > 0 ? tos : EMPTY) : dst;  sp -= p_ ? 1 : 0;  ldLocalIf(tos, SADDR_(sp - 1), p_ && sp > 0); }
-#else
+// Traversal stack: a per-thread array of links in local memory (the hardware interleaves it by lane, so lanes at the same depth share a line).
+// Measured on B200 and rejected (profiles/README.md, r01h): the top entry in a register with predicated PTX ld.local/st.local instead of nvcc's
+// branch around the LDL (2.85 against 2.76 ms per frame); entry distances stored beside the links and stale entries culled on pop (node visits
+// per ray 14.8 -> 14.0, but 3.28 ms: the second array doubles the stack's L1 traffic).
 #define STACK_DECL_ int stack[B200PT_STACK];  int sp = 0;
 #define PUSH_IF_(x, c) { if (c) stack[sp++] = (x); }
 #define POP_IF_(dst, c) { if (c) dst = sp ? stack[--sp] : EMPTY; }
-#endif
-#define PUSH_(x) PUSH_IF_(x, true)
 #define POP_(dst) POP_IF_(dst, true)
-
-// One inner-node step: fetch node `cur` (both child boxes in one record), descend into the nearer hit child, push the other.
-#define NODE_STEP()                                                                              \
-    {                                                                                            \
-        const Node8 N_ = ldgNode(S.nodes + 2 * (size_t)cur);                                     \
-        if (COUNT) nNodes += 1;                                                                  \
-        float tl_, tr_;                                                                          \
-        const bool hl_ = boxTest(N_.w[0], N_.w[1], N_.w[2], g, tmin, best.t, tl_);               \
-        const bool hr_ = boxTest(N_.w[3], N_.w[4], N_.w[5], g, tmin, best.t, tr_);               \
-        const int cl_ = (int)N_.w[6], cr_ = (int)N_.w[7];                                        \
-        if (hl_ && hr_) {                                                                        \
-            const bool sw_ = tr_ < tl_;                                                          \
-            PUSH_(sw_ ? cl_ : cr_)                                                               \
-            cur = sw_ ? cr_ : cl_;                                                               \
-        } else if (hl_) cur = cl_;                                                               \
-        else if (hr_) cur = cr_;                                                                 \
-        else POP_(cur)                                                                           \
-    }
 
 // One step through a 4-wide node (two 256-bit loads): test the four child boxes, order the hit ones by entry distance with a
 // 5-exchange sorting network, continue with the nearest and push the others, farthest first.

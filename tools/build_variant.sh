@@ -11,7 +11,7 @@ flags="-gencode arch=compute_100a,code=sm_100a -std=c++17 -O3 -lineinfo -Xcompil
 ( cd "$src"
   nvcc $flags -c bvh_build.cu -o "$out/bvh_build.o" &
   nvcc $flags -c trace.cu -o "$out/trace.o" &
-  nvcc $flags -fmad=false -c shade.cu -o "$out/shade.o" &
+  nvcc $flags -fmad=${SHADE_FMAD:-false} -c shade.cu -o "$out/shade.o" &
   nvcc $flags -c api.cu -o "$out/api.o" &
   wait )
 nvcc -gencode arch=compute_100a,code=sm_100a -shared -o "$root/build/variants/libb200pt_$name.so" "$out"/*.o -lcudart

@@ -1,7 +1,7 @@
 #!/bin/bash
 # usage: tools/sweep.sh "<env assignments>" ...   — runs bench.py per env set and prints one summary line each
 for e in "$@"; do
-  env $e python bench.py --steps 8 --warmup 3 --no-cpu-baseline > gpurun_out/sweep.json 2> gpurun_out/sweep.err || { echo "$e FAILED"; tail -3 gpurun_out/sweep.err; continue; }
+  env $e python bench.py --steps 24 --warmup 3 --no-cpu-baseline > gpurun_out/sweep.json 2> gpurun_out/sweep.err || { echo "$e FAILED"; tail -3 gpurun_out/sweep.err; continue; }
   python - "$e" <<'PY'
 import json, sys
 d=json.load(open("gpurun_out/sweep.json"))
