@@ -244,10 +244,17 @@ __device__ __forceinline__ void flushStats(TraceStats* stats, unsigned nNodes, u
     }
 }
 
+#ifndef TRACE_STREAM_BYPASS_L1
+#define TRACE_STREAM_BYPASS_L1 1
+#endif
 // cp.async (LDGSTS): 16 bytes global -> shared without a register round trip; completion via wait_all.
 __device__ __forceinline__ void cpAsync16(void* smemDst, const void* gmemSrc) {
     const unsigned d = (unsigned)__cvta_generic_to_shared(smemDst);
+#if TRACE_STREAM_BYPASS_L1
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(d), "l"(gmemSrc) : "memory");   // rays are read once: keep them out of L1 (L2 only)
+#else
     asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" :: "r"(d), "l"(gmemSrc) : "memory");
+#endif
 }
 __device__ __forceinline__ void cpAsyncCommit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cpAsyncWaitAll() { asm volatile("cp.async.wait_all;" ::: "memory"); }
@@ -420,9 +427,14 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
                 const int target = __float_as_int(wD);
                 if (occluded == (target == 2)) {
                     const unsigned slot = (unsigned)__float_as_int(wO);
-                    const float4 pend = pool.pending[slot];
                     float4* acc = (target == 0 ? pool.direct : (target == 1 ? pool.indirect : pool.alpha)) + slot;
+#if TRACE_STREAM_BYPASS_L1
+                    const float4 pend = __ldcg(pool.pending + slot);          // touched once per launch: L2 only, L1 stays with the tree
+                    float4 r = __ldcg(acc);
+#else
+                    const float4 pend = pool.pending[slot];
                     float4 r = *acc;
+#endif
                     r.x = __fadd_rn(r.x, pend.x);  r.y = __fadd_rn(r.y, pend.y);  r.z = __fadd_rn(r.z, pend.z);
                     *acc = r;
                 }
