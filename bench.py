@@ -11,7 +11,7 @@ value   = whole-job Msamples/s with everything resident in HBM: K frames submitt
           primary stream, max over ranks (value_one_at_a_time: one frame at a time, L2 flushed between frames).
 e2e     = the same metric through the reference-facing call sequence with HOST buffers: poke launchParams,
           render() (blocking), downloadPixels() into host memory — every step.
-roofline= the dominant kernel (traceKernel, one launch per bounce): algorithmic bytes (32 B/node + 48 B/triangle + 32 B ray +
+roofline= the dominant kernel (traceKernel, one launch per bounce): algorithmic bytes (64 B/4-wide node + 48 B/triangle + 32 B ray +
           16 B hit, counted by the kernel itself in a counters replay of the same frames) / its CUDA-event time.
 N > 1   = sample split: rank r renders sub-frames r, r+N, ... into an fp32 SUM buffer, one NCCL
           reduce to rank 0 at the end + divide/tone-map there.  Weak scaling: one frame per rank per step.
@@ -419,11 +419,13 @@ def run_b200(a):
     if rank == 0:
         peak, peak_src = _peaks()
         # one traceKernel launch per bounce traces the extension rays AND the previous pass's shadow rays
+        limiter = {}
         traffic, traffic_src = None, None                  # DRAM bytes per traceKernel launch from the committed ncu --set full capture
         try:
             with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")) as f:
                 tj = json.load(f)
             traffic, traffic_src = float(tj["dram_bytes_per_launch"]), tj["source"]
+            limiter = {k: tj[k] for k in ("ipc_per_sm", "active_threads_per_warp_inst", "l1_wavefront_pct", "l1_hit_pct", "l2_hit_pct", "dram_pct_of_peak") if k in tj}
         except (OSError, KeyError, ValueError):
             pass
         bytes_closest_per_frame = (64 * nodes + 48 * tris + (32 + 16) * crays) / replay
@@ -458,7 +460,8 @@ def run_b200(a):
             "gpu_launches": int(all_launches),
             "reference_optix": reference_optix_status(),
             "roofline": {"bound": "hbm", "kernel": "traceKernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                         "traffic": traffic, "traffic_source": traffic_src,
+                         "ncu": limiter, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": bytes_per_launch, "launches_per_step": launches_per_frame,
                          "avg_launch_ms": ms_per_launch,
                          "nodes_per_ray": nodes / max(1, crays), "tris_per_ray": tris / max(1, crays),

@@ -32,7 +32,12 @@ units = out[1]
 mul = {"Mbyte": 1e6, "Kbyte": 1e3, "Gbyte": 1e9, "byte": 1}
 tr = [r for r in out[2:] if "traceKernel" in r[0]]
 traffic = sum(float(r[4]) * mul[units[4]] + float(r[5]) * mul[units[5]] for r in tr) / len(tr)
+def avg(col):
+    return sum(float(r[cols.index(col)]) for r in tr) / len(tr)
 json.dump({"kernel": "traceKernel", "dram_bytes_per_launch": traffic, "launches_captured": len(tr),
+           "ipc_per_sm": avg("sm__inst_issued.avg.per_cycle_active"), "active_threads_per_warp_inst": avg("smsp__thread_inst_executed_per_inst_executed.ratio"),
+           "l1_wavefront_pct": avg("l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed"), "l1_hit_pct": avg("l1tex__t_sector_hit_rate.pct"),
+           "l2_hit_pct": avg("lts__t_sector_hit_rate.pct"), "dram_pct_of_peak": avg("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"),
            "source": f"profiles/{tag}_trace_shade_ncu_full_summary.csv (ncu --set full --clock-control none, bounces 2-3 of a frame; dram__bytes_read.sum + dram__bytes_write.sum)"},
           open(os.path.join(P, "traffic.json"), "w"), indent=1)
 print("traffic per traceKernel launch:", traffic)
