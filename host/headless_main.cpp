@@ -4,7 +4,7 @@
 // mouse cursor (main.cpp:310-314), follows a scripted Lissajous track.  fps is appended every 0.5 s in the reference's
 // log format (sutil/sutil.cpp:760-772: one value per line).
 //
-//   b200pt_headless [--obj file.obj | --boxes N] [--preset sv4_fov|sv4_uniform|sv3_uniform|orig] [--size WxH] [--frames N] [--spl N]
+//   b200pt_headless [--obj file.obj | --boxes N] [--preset sv4_fov|sv4_uniform|sv3_uniform|orig] [--size WxH] [--frames N] [--spl N] [--in-flight N]
 //                   [--camera sponza|lost_empire|san_miguel|cornell] [--sky r,g,b] [--out image.ppm|image.png] [--log fps.tsv]
 //                   [--hdr probe.hdr] [--gpu-cdf] [--whitted] [--dump-model file.bin] [--dump-probe file.bin] [--no-render]
 #include <algorithm>
@@ -107,7 +107,7 @@ static void dumpModel(const Model* m, const char* path) {    // flat binary for 
 
 int main(int argc, char** argv) {
     std::string obj, preset = "sv4_fov", cam = "cornell", out, log, dump, hdr, dumpProbe;
-    int W = 1280, H = 720, frames = 16, boxes = 64, spl = 1;
+    int W = 1280, H = 720, frames = 16, boxes = 64, spl = 1, inFlight = 1;
     float3 sky{1.f, 1.f, 1.f};
     bool noRender = false, gpuCdf = false, whitted = false;
     for (int i = 1; i < argc; ++i) {
@@ -120,6 +120,7 @@ int main(int argc, char** argv) {
         else if (a == "--size") { if (sscanf(next(), "%dx%d", &W, &H) != 2) { fprintf(stderr, "--size WxH\n");  return 2; } }
         else if (a == "--frames") frames = atoi(next());
         else if (a == "--spl") spl = atoi(next());
+        else if (a == "--in-flight") inFlight = atoi(next());      // frames in flight (b200pt_config.frames_in_flight): frames are submitted without waiting
         else if (a == "--sky") { if (sscanf(next(), "%f,%f,%f", &sky.x, &sky.y, &sky.z) != 3) { fprintf(stderr, "--sky r,g,b\n");  return 2; } }
         else if (a == "--out") out = next();
         else if (a == "--log") log = next();
@@ -168,10 +169,12 @@ int main(int argc, char** argv) {
                                                      (unsigned)(H * (0.5f + 0.35f * std::sin(3.f * ph + 0.5f)))};
             if (f == 0) sample.launchParams.frame.subframe_index = 0;                                       // camera_changed starts true, :319-320
             sample.setCamera(camera);                                                                       // handleCameraUpdate, :328
-            if (whitted) sample.renderWhitted(camera);  else                                                // 04HelloRaytracing frame
-            sample.render();                                                                                // :335
+            if (whitted) sample.renderWhitted(camera);
+            else if (inFlight > 1) { sample.config.frames_in_flight = inFlight;  sample.renderAsync();  if (f + 1 == frames) sample.synchronize();  else continue; }
+            else sample.render();                                                                           // :335
             const b200pt_counters c = sample.counters();
-            samples += c.samples;  rays += c.radiance_rays + c.shadow_rays;
+            const unsigned long long mult = (!whitted && inFlight > 1) ? (unsigned long long)frames : 1ull;     // in flight: counters of the last frame stand for all
+            samples += mult * c.samples;  rays += mult * (c.radiance_rays + c.shadow_rays);
             ++windowFrames;
             const auto now = std::chrono::steady_clock::now();
             const double dt = std::chrono::duration<double>(now - tWindow).count();

@@ -115,6 +115,20 @@ def test_cpp_renderer_equals_python_mirror(exe, tmp_path):
     assert np.all(rows[:, 0] == 0) and np.array_equal(rows[:, 1:].reshape(64, 96, 3)[::-1], want)
 
 
+@pytest.mark.gpu
+def test_cpp_frames_in_flight_give_the_same_image(exe, tmp_path):
+    """The C++ host through renderAsync() with 3 frames in flight (--in-flight 3) writes the same pixels as blocking render() calls."""
+    scenes.cornell("disney", directory=str(tmp_path))
+    obj = os.path.join(str(tmp_path), "cornell.obj")
+    imgs = []
+    for k in (1, 3):
+        out = os.path.join(str(tmp_path), f"out{k}.ppm")
+        subprocess.check_call([exe, "--obj", obj, "--preset", "sv3_uniform", "--spl", "2", "--size", "96x64", "--frames", "6", "--camera", "cornell",
+                               "--sky", "1,1,1", "--in-flight", str(k), "--out", out])
+        imgs.append(open(out, "rb").read())
+    assert imgs[0] == imgs[1] and len(imgs[0]) > 96 * 64 * 3
+
+
 # ---- Radiance .hdr readers (loadProbe, sv4/main.cpp:154-165) against the reference's own stb_image (tests/golden/hdr.npz) ----
 HDR_CASES = ["rle", "flat", "narrow", "wide_rle"]
 
