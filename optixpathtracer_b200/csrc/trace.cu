@@ -28,12 +28,10 @@
 #define EMPTY 0x7fffffff          // "nothing left to visit"; also the root link of an empty scene
 #define NO_LEAF 0                 // leaf codes are < 0
 #ifndef NODE_ROUNDS
-#ifndef NODE_ROUNDS
-#define NODE_ROUNDS 8
+#define NODE_ROUNDS 8           // vote rounds before the staging logic runs again
 #endif
 #ifndef NODE_UNROLL
 #define NODE_UNROLL 3           // node steps per lane between two warp votes
-#endif
 #endif
 
 static int g_refillThreshold = -1, g_leafThreshold = -1;   // lanes that must be idle before a warp refills; tuned on B200
