@@ -7,6 +7,9 @@
 // All HBM-streaming / gather bound; compiled with -fmad=false (see shade_math.cuh).
 #include "shade_math.cuh"
 
+#ifndef SHADE_HOIST_THR
+#define SHADE_HOIST_THR 1
+#endif
 #define SHADE_BLOCK 128
 #ifndef SHADE_MIN_BLOCKS
 #define SHADE_MIN_BLOCKS 7          // CTAs per SM for shadeKernel (72 registers); measured per frame: 6: 1.55 ms, 7: 1.44, 8: 1.47, 9: 1.52, 10: 1.56, 12: 1.69
@@ -153,6 +156,9 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                 // dependent table lookups now, while the triangle / mesh / material loads above are still in flight.  The RNG state
                 // is committed further down, only where the reference really draws the sample.
                 const uint2 rs = pool.rng[slot];
+#if SHADE_HOIST_THR
+                const float4 thr4 = pool.thr[slot];                               // issued with the other slot gathers, used far below
+#endif
                 Rng rng;  rng.s1 = rs.x;  rng.s2 = rs.y;
                 float3 wi, skyColor;  float skyPdf;
                 probeSample(F.probe, F.probeGuide, wi, skyColor, skyPdf, rng);
@@ -182,12 +188,16 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                         pool.aovNormal[slot] = make_float4(N.x, N.y, N.z, 0.f);
                         pool.aovAlbedo[slot] = make_float4(albedo.x, albedo.y, albedo.z, 0.f);
                     }
+#if !SHADE_HOIST_THR
                     const float4 thr4 = pool.thr[slot];
+#endif
                     float3 T = f3(thr4.x, thr4.y, thr4.z);
                     float rayEta = thr4.w;
                     const float outEta = rayEta == 1.0f ? (mat.eta == 0.0f ? 2.0f / (1.0f - sqrtf(0.08f * mat.specular)) - 1.0f : mat.eta) : 1.0f;   // :644-654
                     const bool last = depth >= F.maxDepth;                        // its radiance is dropped at :495
-                    if (!catcher) { pool.alpha[slot] = make_float4(1.f, 1.f, 1.f, 0.f);  flags |= PF_ALPHA_ONE; }   // :660
+                    // prd.alpha = 1 at every non-catcher hit (:660).  Once it is 1 nothing can change it again (only a PRIMARY catcher hit emits an
+                    // alpha-targeted shadow ray, and that one resolves before this pass), so the 16-byte scattered store happens once per path.
+                    if (!catcher && !(flags & PF_ALPHA_ONE)) { pool.alpha[slot] = make_float4(1.f, 1.f, 1.f, 0.f);  flags |= PF_ALPHA_ONE; }
                     if (last && !catcher) {
                         flags |= PF_DONE;
                     } else {
