@@ -27,6 +27,9 @@
 #define FULL 0xffffffffu
 #define EMPTY 0x7fffffff          // "nothing left to visit"; also the root link of an empty scene
 #define NO_LEAF 0                 // leaf codes are < 0
+#ifndef TRACE_LEAF_PASSES
+#define TRACE_LEAF_PASSES 2     // a lane blocked on a second leaf intersects both of its leaves in the same leaf phase
+#endif
 #ifndef NODE_ROUNDS
 #define NODE_ROUNDS 8           // vote rounds before the staging logic runs again
 #endif
@@ -385,6 +388,8 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
         // ---------------------------------------------------------------- leaves, once enough lanes are blocked on one
         if (nodeMask == 0u || (int)__popc(blockedMask) >= leafThreshold) {
             if (active && leaf == NO_LEAF && cur < 0) { leaf = cur;  POP_(cur) }   // root leaf
+#pragma unroll 1
+            for (int pass_ = 0; pass_ < TRACE_LEAF_PASSES; ++pass_)
             if (active && leaf != NO_LEAF) {
                 unsigned first, cnt;
                 leafDecode(leaf, first, cnt);
