@@ -274,7 +274,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_BLOCKS_PER_SM)
 traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restrict__ rayD, float4* __restrict__ hit,
             const unsigned* __restrict__ countCPtr, const float4* __restrict__ shO, const float4* __restrict__ shD,
             const unsigned* __restrict__ countSPtr, unsigned* head, float tminC, float tminS, float tmax, int cullBack, PathPool pool,
-            TraceStats* stats, int refillThreshold, int leafThreshold) {
+            TraceStats* stats, int refillThreshold, int leafThreshold, int nodeMin) {
     __shared__ float4 stageO[TRACE_WARPS][2][32], stageD[TRACE_WARPS][2][32];
     const unsigned countC = *countCPtr, countS = *countSPtr;
     const unsigned chunksC = (countC + 31u) >> 5, chunksTotal = chunksC + ((countS + 31u) >> 5);
@@ -387,6 +387,7 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
             nodeMask = __ballot_sync(FULL, canNode);
             blockedMask = __ballot_sync(FULL, active && !canNode);
             if (nodeMask == 0u || (int)__popc(blockedMask) >= leafThreshold || round + 1 >= NODE_ROUNDS) break;
+            if ((int)__popc(nodeMask) <= nodeMin && blockedMask != 0u) { nodeMask = 0u;  break; }      // too few walkers left: intersect the pending leaves now
         }
         // ---------------------------------------------------------------- leaves, once enough lanes are blocked on one
         if (nodeMask == 0u || (int)__popc(blockedMask) >= leafThreshold) {
@@ -518,6 +519,11 @@ static int refillThreshold() {
     }
     return g_refillThreshold;
 }
+static int nodeMinThreshold() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("B200PT_NODEMIN");  v = e ? atoi(e) : 8;  if (v < 0) v = 0;  if (v > 31) v = 31; }   // tuning knob; measured per frame: 0: 2.63 ms, 4-16: 2.59-2.60
+    return v;
+}
 static int leafThreshold() {
     if (g_leafThreshold < 0) {
         const char* e = getenv("B200PT_LEAF");                    // lanes blocked on a leaf before the warp intersects triangles
@@ -532,8 +538,8 @@ void launchTrace(const SceneDev& scene, const float4* rayO, const float4* rayD, 
                  const float4* shO, const float4* shD, const unsigned* countS, unsigned* head, float tmin, float tminShadow, float tmax, int cullBack,
                  const PathPool& pool, TraceStats* stats, cudaStream_t stream) {
     const dim3 grid(B200PT_NUM_SMS * TRACE_BLOCKS_PER_SM), block(TRACE_BLOCK);
-    if (stats) traceKernel<true><<<grid, block, 0, stream>>>(scene, rayO, rayD, hit, countC, shO, shD, countS, head, tmin, tminShadow, tmax, cullBack, pool, stats, refillThreshold(), leafThreshold());
-    else traceKernel<false><<<grid, block, 0, stream>>>(scene, rayO, rayD, hit, countC, shO, shD, countS, head, tmin, tminShadow, tmax, cullBack, pool, nullptr, refillThreshold(), leafThreshold());
+    if (stats) traceKernel<true><<<grid, block, 0, stream>>>(scene, rayO, rayD, hit, countC, shO, shD, countS, head, tmin, tminShadow, tmax, cullBack, pool, stats, refillThreshold(), leafThreshold(), nodeMinThreshold());
+    else traceKernel<false><<<grid, block, 0, stream>>>(scene, rayO, rayD, hit, countC, shO, shD, countS, head, tmin, tminShadow, tmax, cullBack, pool, nullptr, refillThreshold(), leafThreshold(), nodeMinThreshold());
 }
 
 void launchTraceRaysDebug(const SceneDev& scene, const float4* rayO, const float4* rayD, unsigned n, float tmin, float tmax,
