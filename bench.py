@@ -321,32 +321,44 @@ def run_b200(a):
     # ---- e2e: the reference-facing call sequence with HOST buffers, every step (N ranks in parallel), one frame at a time.  The same
     # a.steps frames as the timed region, so their ray / sample / launch counters (read after each blocking render) are the timed region's.
     cfg.profile = 0
-    cfg.frames_in_flight = 1
     if world > 1:
         cfg.accum_mode = 0
         r.resize((a.width, a.height))
     host_px = torch.empty((a.height, a.width), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)   # pinned host frame buffer
-    for i in range(2):
-        r.setCamera(cam)
-        r.launchParams.frame.subframe_index = frame_index(i)
-        r.render()
-        r.downloadPixels(host_px)
+
+    def e2e_loop(steps, count):
+        for i in range(3):
+            r.setCamera(cam)
+            r.launchParams.frame.subframe_index = frame_index(i)
+            r.render()
+            r.downloadPixels(host_px)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        sec = 0.0
+        for i in range(steps):
+            t0 = time.perf_counter()
+            r.setCamera(cam)                                                    # host -> LaunchParams (312 B, re-read by every render)
+            r.launchParams.frame.subframe_index = frame_index(a.warmup + i)
+            r.render()                                                          # blocking, as the reference's render()
+            r.downloadPixels(host_px)                                           # D2H W*H RGBA8
+            sec += time.perf_counter() - t0
+            if count:
+                tally(r.counters())                                             # host-side read of counters already fetched by render(): outside the clock
+        if world > 1:
+            t = torch.tensor([sec], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            sec = float(t.item())
+        return sec
+
+    # strictly one frame at a time first (frames_in_flight = 1: no speculative next sub-frame), on a bounded number of steps ...
+    cfg.frames_in_flight = 1
+    e2e_serial_steps = min(a.steps, 16)
+    e2e_serial_s = e2e_loop(e2e_serial_steps, False)
+    # ... then the same blocking calls with the library allowed to start the predicted next sub-frame while it blocks (frames_in_flight > 1)
+    cfg.frames_in_flight = a.in_flight
+    e2e_s = e2e_loop(a.steps, True)
     if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    e2e_s = 0.0
-    for i in range(a.steps):
-        t0 = time.perf_counter()
-        r.setCamera(cam)                                                        # host -> LaunchParams (312 B, re-read by every render)
-        r.launchParams.frame.subframe_index = frame_index(a.warmup + i)
-        r.render()                                                              # blocking, as the reference's render()
-        r.downloadPixels(host_px)                                               # D2H W*H RGBA8
-        e2e_s += time.perf_counter() - t0
-        tally(r.counters())                                                     # host-side read of counters already fetched by render(): outside the clock
-    if world > 1:
-        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
         tot = torch.tensor([rays["samples"], rays["radiance"], rays["shadow"], launches], dtype=torch.float64, device="cuda")
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
         all_samples, all_rad, all_sh, all_launches = (float(x) for x in tot.tolist())
@@ -355,6 +367,7 @@ def run_b200(a):
     value = all_samples / (ms * 1e-3) / 1e6
     mrays = (all_rad + all_sh) / (ms * 1e-3) / 1e6
     e2e_value = all_samples / e2e_s / 1e6
+    e2e_serial_value = (all_samples / a.steps) * e2e_serial_steps / e2e_serial_s / 1e6
 
     # ---- the same end-to-end step through the asynchronous entry points: setCamera + b200pt_render_async + b200pt_download_pixels_async
     # into a ring of pinned host frames every step, `in_flight` frames in flight, one b200pt_synchronize at the end (inside the clock)
@@ -452,10 +465,13 @@ def run_b200(a):
                           f"value_one_at_a_time = {serial_steps} of the same frames with a blocking wait and an L2 flush between them",
             "mrays_per_s": mrays, "radiance_rays_per_sample": all_rad / max(1.0, all_samples), "shadow_rays_per_sample": all_sh / max(1.0, all_samples),
             "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": 312, "d2h_bytes_per_step": 4 * n_px,
+                    "one_at_a_time_value": e2e_serial_value,
                     "async_value": e2e_async_value,
                     "async_note": f"the same step through b200pt_render_async + b200pt_download_pixels_async ({a.in_flight} frames in flight, ring of pinned host frames, "
                                   "one synchronize at the end, wall clock): what a caller that adopts the asynchronous entry points gets; `value` is the reference's blocking sequence",
-                    "note": "setCamera + render() (blocking, one frame at a time) + downloadPixels() into pinned host memory every step; scene/BVH upload is one-off in the ctor "
+                    "note": f"setCamera + render() (blocking) + downloadPixels() into pinned host memory every step, the reference's call sequence; cfg.frames_in_flight = {a.in_flight}: while render() blocks on "
+                            "frame i the library has already started the wavefront of the predicted next call (same launchParams, next subframe_index - progressive accumulation; a wrong guess is "
+                            "dropped, pixels are bit-identical either way); one_at_a_time_value = the same calls with frames_in_flight = 1; scene/BVH upload is one-off in the ctor "
                             f"({ctor_s:.2f} s incl. LBVH build {float(info.build_ms):.2f} ms)"},
             "gpu_launches": int(all_launches),
             "reference_optix": reference_optix_status(),

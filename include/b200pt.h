@@ -61,11 +61,17 @@ typedef struct b200pt_config {
                                  w * ProbeEval(dir) * throughput with w = p_bsdf / (p_bsdf + ProbePdf(dir)), the partner of the NEE weight */
     float shadow_tmin;        /* tmin of the occlusion (NEE) rays: 0.01 in every variant — `orig` traces radiance rays from 0.001 (orig/deviceProgram.cu:420)
                                  but occlusion rays from 0.01 (:268, :310); <= 0 means "same as tmin" */
-    int   frames_in_flight;   /* b200pt_render_async only: how many frames may be in flight at once (1..4; 0 = 1).  Each extra frame owns a second
-                                 stream, path pool and queue set; its wavefront runs concurrently with its neighbours' (one frame's drain phases
-                                 and thin late bounces overlap the next frame's wide early ones) and the frames still fold into the accumulation
-                                 buffer in submission order, so the pixels are those of the one-at-a-time sequence, bit for bit.  b200pt_render
-                                 (blocking) and instrumented frames (profile != 0) always run one at a time on the context's primary stream. */
+    int   frames_in_flight;   /* how many frames may be in flight at once (1..4; 0 = 1).  Each frame in flight owns a stream, a path pool and a queue set;
+                                 its wavefront runs concurrently with its neighbours' (one frame's drain phases and thin late bounces overlap the next
+                                 frame's wide early ones) and frames still fold into the accumulation buffer in submission order, so the pixels are
+                                 those of the one-at-a-time sequence, bit for bit.
+                                 b200pt_render_async: consecutive calls overlap.
+                                 b200pt_render (blocking): once two consecutive calls have looked like progressive accumulation (same launchParams,
+                                 subframe_index advanced by a constant stride), the wavefronts of the predicted next frames_in_flight - 1 calls are
+                                 enqueued before the call blocks on its own frame; a call that matches its prediction byte for byte (launchParams and
+                                 config) only adds its finalize passes, any other call - a camera move, a new gaze point - drops the speculative
+                                 wavefronts, which have written nothing outside their own lanes.  Entry points that change the scene, the probe or the
+                                 frame buffers drop them too.  Instrumented frames (profile != 0) always run one at a time on the primary stream. */
     int   reserved[1];
 } b200pt_config;
 

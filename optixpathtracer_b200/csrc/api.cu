@@ -2,6 +2,7 @@
 // the LBVH build, the wavefront loop of one render() and the parity hooks.  No CPU fallback anywhere.
 #include "common.cuh"
 #include <algorithm>
+#include <deque>
 #include <cstring>
 #include <cstdlib>
 
@@ -45,6 +46,23 @@ struct Lane {
     }
 };
 
+struct PassDesc { PassParams P;  size_t nLaunch; };
+// One frame's wavefront as enqueued on a lane: everything up to, but not including, its finalize passes (the only stage that touches the
+// shared accumulation / frame / AOV buffers).
+struct FrameJob { int lane = -1;  std::vector<PassDesc> passes;  FrameParams F;  unsigned launches = 0, nClosest = 0;  cudaEvent_t totalEnd = nullptr; };
+// Speculative next sub-frame (blocking b200pt_render with cfg.frames_in_flight > 1).  Progressive accumulation calls render() again and again with
+// the same launchParams and the next subframe_index; once two consecutive calls have looked like that, render() enqueues the wavefront of the
+// PREDICTED next call(s) on the other lanes before it blocks on the current frame.  The next call either matches the prediction byte for byte
+// (LaunchParams and config) - then only the finalize passes remain to be enqueued - or the speculative wavefront is dropped: it has touched
+// nothing but its own lane.  Pixels are those of plain blocking calls, bit for bit; a moving camera just never gets a prediction right.
+struct SpecFrame { LaunchParams input, output;  FrameJob job; };   // a predicted call: its launchParams on entry / as render() leaves them, and its wavefront
+struct Speculation {
+    std::deque<SpecFrame> ahead;        // wavefronts already enqueued for the next calls, oldest first (at most frames_in_flight - 1)
+    bool havePrev = false;  unsigned prevIndex = 0;   // subframe_index of the previous blocking call (prediction = last index + last stride)
+    bool havePrediction = false;  LaunchParams predicted;  b200pt_config predictedCfg;  int hits = 0;   // consecutive calls that matched their prediction
+    void drop() { ahead.clear();  havePrediction = false;  hits = 0; }
+};
+
 struct b200pt_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -66,6 +84,7 @@ struct b200pt_ctx {
     int countersLane = 0;               // lane whose device counters `last` will be read from
     unsigned seq = 0;                   // round-robin lane pick of b200pt_render_async
     cudaEvent_t forkEv = nullptr;
+    Speculation spec;
     b200pt_counters last{};
     bool countersPending = false;  int profiled = 0;
     std::vector<cudaEvent_t> evPool;  std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> evUsed;  size_t evNext = 0;
@@ -81,6 +100,8 @@ static void joinLanes(b200pt_ctx* c) {
     }
 }
 static void enterCtx(b200pt_ctx* c) { CUDA_OK(cudaSetDevice(c->device));  joinLanes(c); }
+// entry points that change what a frame reads or writes (scene, probe, frame buffers, lane 0's pool) also drop the speculative next sub-frame
+static void enterCtxMutating(b200pt_ctx* c) { enterCtx(c);  c->spec.drop(); }
 
 extern "C" {
 
@@ -190,7 +211,7 @@ int b200pt_update_vertices(b200pt_ctx* c, int meshID, const float* vtx, size_t n
     API_BEGIN
     memcpy(c->hVertices.data() + m.firstVertex, vtx, nv * sizeof(float3));
     if (c->built) {                                           // device copy is live: patch it in place
-        enterCtx(c);
+        enterCtxMutating(c);
         CUDA_OK(cudaMemcpyAsync(c->dVertices.p + m.firstVertex, vtx, nv * sizeof(float3), cudaMemcpyHostToDevice, c->stream));
         CUDA_OK(cudaStreamSynchronize(c->stream));
         c->stale = true;
@@ -201,7 +222,7 @@ int b200pt_refit_accel(b200pt_ctx* c) {
     if (!c) return fail("b200pt_refit_accel: null context");
     if (!c->built) return fail("b200pt_refit_accel: b200pt_build_accel has not been called");
     API_BEGIN
-    enterCtx(c);
+    enterCtxMutating(c);
     bvhRefit(c->dVertices.p, c->dIndices.p, c->dTriMesh.p, c->dMeshes.p, c->stream, c->bvh, &c->refitMs);
     c->stale = false;
     API_END
@@ -210,7 +231,7 @@ int b200pt_refit_accel(b200pt_ctx* c) {
 int b200pt_build_accel(b200pt_ctx* c, uint64_t* handle_out) {
     if (!c) return fail("b200pt_build_accel: null context");
     API_BEGIN
-    enterCtx(c);
+    enterCtxMutating(c);
     if (c->hIndices.size() >= (1u << 28)) throw std::runtime_error("b200pt_build_accel: more than 2^28 triangles");
     std::vector<MeshInfo> infos(c->hMeshes.size());
     for (size_t i = 0; i < infos.size(); ++i) {

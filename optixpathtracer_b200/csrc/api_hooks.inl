@@ -34,7 +34,7 @@ int b200pt_download_accum(b200pt_ctx* c, float* host) {
 int b200pt_upload_accum(b200pt_ctx* c, const float* host) {
     if (!c || !host) return fail("b200pt_upload_accum: null argument");
     API_BEGIN
-    enterCtx(c);
+    enterCtxMutating(c);
     CUDA_OK(cudaMemcpyAsync(c->accumBuf.p, host, sizeof(float4) * (size_t)c->W * c->H, cudaMemcpyHostToDevice, c->stream));
     CUDA_OK(cudaStreamSynchronize(c->stream));
     API_END
@@ -58,7 +58,7 @@ int b200pt_device_buffers(b200pt_ctx* c, void** accum, void** frame, void** stre
 int b200pt_clear_accum(b200pt_ctx* c) {
     if (!c) return fail("b200pt_clear_accum: null context");
     API_BEGIN
-    enterCtx(c);
+    enterCtxMutating(c);
     if (c->accumBuf.p) CUDA_OK(cudaMemsetAsync(c->accumBuf.p, 0, sizeof(float4) * (size_t)c->W * c->H, c->stream));
     if (c->frameBuf.p) CUDA_OK(cudaMemsetAsync(c->frameBuf.p, 0, sizeof(uint32_t) * (size_t)c->W * c->H, c->stream));
     API_END
@@ -66,7 +66,7 @@ int b200pt_clear_accum(b200pt_ctx* c) {
 int b200pt_resolve_sum(b200pt_ctx* c, const LaunchParams* params, const b200pt_config* cfg, int nPasses) {
     if (!c || !params || !cfg || nPasses <= 0) return fail("b200pt_resolve_sum: bad argument");
     API_BEGIN
-    enterCtx(c);
+    enterCtxMutating(c);
     launchResolveSum(frameOf(*params, *cfg), nPasses, c->stream);
     CUDA_OK(cudaStreamSynchronize(c->stream));
     API_END

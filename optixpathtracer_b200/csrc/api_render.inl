@@ -1,6 +1,5 @@
 // b200pt — frame state + SampleRenderer::render() orchestration (included by api.cu).
 
-struct PassDesc { PassParams P;  size_t nLaunch; };
 
 // Folds the per-launch queue counters of one group into the frame totals {radiance rays, shadow rays, samples}
 // and clears them for the next group (one tiny launch per group instead of two per bounce).
@@ -154,28 +153,19 @@ static FrameParams frameOf(const LaunchParams& P, const b200pt_config& cfg, cons
 
 struct Chunk { int pass, k0, k1;  unsigned slotBase; };
 
-static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config* cfgp, bool sync) {
-    if (!c || !params || !cfgp) throw std::runtime_error("b200pt_render: null argument");
-    if (params->frame.size.x == 0) return;                                       // SimplePathtracer.cpp:81
-    const b200pt_config cfg = *cfgp;
-    CUDA_OK(cudaSetDevice(c->device));
-    if (!c->built) throw std::runtime_error("b200pt_render: b200pt_build_accel has not been called");
-    if (!params->probe.data || !params->probe.cdfValuesX) throw std::runtime_error("b200pt_render: no probe set (call b200pt_set_probe)");
-    if (!params->frame.accum_buffer || !params->frame.frame_buffer) throw std::runtime_error("b200pt_render: frame buffers not allocated (call b200pt_resize)");
-    if (cfg.max_depth < 0 || cfg.max_depth > QC_MAX_LAUNCHES - 8) throw std::runtime_error("b200pt_render: max_depth out of range");
-    c->countersPending = false;                                                  // totals of an un-synchronised previous frame are dropped
-
-    std::vector<PassDesc> passes;
-    buildSchedule(*params, cfg, passes);
-    const FrameParams F = frameOf(*params, cfg, c);
+// Enqueues one frame's wavefront (raygen, the bounce loop, counters, per-launch-index sums) on lane `laneIdx`.  `params` is mutated exactly as
+// the reference's render() leaves its public launchParams; nothing outside the lane is written.
+static void enqueueWavefront(b200pt_ctx* c, LaunchParams& params, const b200pt_config& cfg, int laneIdx, FrameJob& job) {
+    job = FrameJob();
+    job.lane = laneIdx;
+    std::vector<PassDesc>& passes = job.passes;
+    buildSchedule(params, cfg, passes);
+    job.F = frameOf(params, cfg, c);
+    const FrameParams& F = job.F;
     const SceneDev S = sceneOf(c);
-    // Lane of this frame: blocking and instrumented frames run on lane 0 (the primary stream); asynchronous frames rotate over
-    // cfg.frames_in_flight lanes.  A lane other than 0 is first ordered after whatever the primary stream held when the batch began.
-    const int nLanes = (sync || (cfg.profile & 3)) ? 1 : std::min(std::max(cfg.frames_in_flight, 1), B200PT_MAX_LANES);
-    const int laneIdx = nLanes > 1 ? (int)(c->seq++ % (unsigned)nLanes) : 0;
     Lane& L = laneOf(c, laneIdx);
     cudaStream_t s = L.stream;
-    if (laneIdx > 0 && !L.forked) {
+    if (laneIdx > 0 && !L.forked) {                                              // first ordered after whatever the primary stream held when the batch began
         CUDA_OK(cudaEventRecord(c->forkEv, c->stream));
         CUDA_OK(cudaStreamWaitEvent(s, c->forkEv, 0));
         L.forked = true;
@@ -208,14 +198,14 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
     Queues Q = queuesOf(L);
 
     const bool prof = (cfg.profile & 1) != 0, count = (cfg.profile & 2) != 0;   // 1: stage events, 2: traversal counters
-    c->evUsed.clear();  c->evNext = 0;  c->profiled = cfg.profile & 3;
+    if (prof) { c->evUsed.clear();  c->evNext = 0; }
     StageTimer T{c, prof};
-    cudaEvent_t a = nullptr, b = nullptr, ta = nullptr, tb = nullptr;
-    unsigned launches = 0, nClosest = 0, nAny = 0;
+    cudaEvent_t a = nullptr, b = nullptr, ta = nullptr;
+    unsigned& launches = job.launches;
     unsigned* totals = L.counters.p + QC_STRIDE * QC_MAX_LAUNCHES;
     CUDA_OK(cudaMemsetAsync(L.counters.p, 0, sizeof(unsigned) * (QC_STRIDE * QC_MAX_LAUNCHES + 8), s));
     if (count) CUDA_OK(cudaMemsetAsync(L.stats.p, 0, 2 * sizeof(TraceStats), s));
-    T.begin(ST_TOTAL, ta, tb);
+    T.begin(ST_TOTAL, ta, job.totalEnd);
     const int bounces = cfg.max_depth + ((c->hasCatcher || cfg.max_depth == 0) ? 1 : 0);   // the dropped last segment is traced only if alpha can still change
     const int cullBack = cfg.shadow_mode == B200PT_SHADOW_CULL_BACK;
     const float shadowTmin = cfg.shadow_tmin > 0.f ? cfg.shadow_tmin : cfg.tmin;
@@ -234,7 +224,7 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
             T.begin(d < bounces ? ST_TRACE : ST_TRACE_TAIL, a, b);
             launchTrace(S, Q.rayO[cur], Q.rayD[cur], Q.hit, ctr + (d < bounces ? QC_RAYS : 3 /* always 0 */), Q.shO, Q.shD, ctr + QC_SHADOWS, ctr + QC_HEAD, cfg.tmin, shadowTmin, cfg.tmax,
                         cullBack, pool, count ? L.stats.p : nullptr, s);
-            T.end(b);  ++launches;  ++nClosest;
+            T.end(b);  ++launches;  ++job.nClosest;
             if (d == bounces) break;
             T.begin(ST_SHADE, a, b);
             launchShade(F, S, pool, Q, cur, d, s);
@@ -249,25 +239,96 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
         }
         T.end(b);
     }
-    // frames fold into the accumulation / frame / AOV buffers in submission order, whatever lane they ran on
-    if (c->lastLane >= 0 && c->lastLane != laneIdx) CUDA_OK(cudaStreamWaitEvent(s, c->lanes[c->lastLane].done, 0));
+    CUDA_OK(cudaGetLastError());
+}
+
+// The finalize passes of an enqueued wavefront: frames fold into the accumulation / frame / AOV buffers in submission order, whatever lane they ran on.
+static void enqueueFinalize(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& job) {
+    Lane& L = c->lanes[job.lane];
+    cudaStream_t s = L.stream;
+    if (c->lastLane >= 0 && c->lastLane != job.lane) CUDA_OK(cudaStreamWaitEvent(s, c->lanes[c->lastLane].done, 0));
+    StageTimer T{c, (cfg.profile & 1) != 0};
+    cudaEvent_t a = nullptr, b = nullptr;
     T.begin(ST_ACCUM, a, b);
-    for (auto& p : passes) {                                                     // pass order = the reference's launch order (overwrite semantics)
+    for (auto& p : job.passes) {                                                 // pass order = the reference's launch order (overwrite semantics)
         if (!p.nLaunch) continue;
-        launchFinalize(F, p.P, L.sumRad.p, L.sumAlpha.p, L.sumNormal.p, L.sumAlbedo.p, s);  ++launches;
+        launchFinalize(job.F, p.P, L.sumRad.p, L.sumAlpha.p, L.sumNormal.p, L.sumAlbedo.p, s);  ++job.launches;
     }
     T.end(b);
-    T.end(tb);
+    T.end(job.totalEnd);
     CUDA_OK(cudaGetLastError());
     CUDA_OK(cudaEventRecord(L.done, s));
-    c->lastLane = laneIdx;  c->countersLane = laneIdx;  L.busy = laneIdx > 0;
+    c->lastLane = job.lane;  c->countersLane = job.lane;  L.busy = job.lane > 0;
+    c->profiled = cfg.profile & 3;
     c->last = b200pt_counters{};
-    c->last.kernel_launches = launches;  c->last.n_trace_closest_launches = nClosest;  c->last.n_trace_any_launches = nAny;
+    c->last.kernel_launches = job.launches;  c->last.n_trace_closest_launches = job.nClosest;  c->last.n_trace_any_launches = 0;
     c->countersPending = true;
-    if (sync) {
-        CUDA_OK(cudaStreamSynchronize(s));                                       // CUDA_SYNC_CHECK, SimplePathtracer.cpp:214
-        collectCounters(c);
+}
+
+static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config* cfgp, bool sync) {
+    if (!c || !params || !cfgp) throw std::runtime_error("b200pt_render: null argument");
+    if (params->frame.size.x == 0) return;                                       // SimplePathtracer.cpp:81
+    const b200pt_config cfg = *cfgp;
+    CUDA_OK(cudaSetDevice(c->device));
+    if (!c->built) throw std::runtime_error("b200pt_render: b200pt_build_accel has not been called");
+    if (!params->probe.data || !params->probe.cdfValuesX) throw std::runtime_error("b200pt_render: no probe set (call b200pt_set_probe)");
+    if (!params->frame.accum_buffer || !params->frame.frame_buffer) throw std::runtime_error("b200pt_render: frame buffers not allocated (call b200pt_resize)");
+    if (cfg.max_depth < 0 || cfg.max_depth > QC_MAX_LAUNCHES - 8) throw std::runtime_error("b200pt_render: max_depth out of range");
+    c->countersPending = false;                                                  // totals of an un-synchronised previous frame are dropped
+
+    // Lanes: instrumented frames run on lane 0 (the primary stream); everything else rotates over cfg.frames_in_flight lanes.  With one lane
+    // there is nothing to overlap and nothing to speculate on.
+    Speculation& sp = c->spec;
+    const int nLanes = (cfg.profile & 3) ? 1 : std::min(std::max(cfg.frames_in_flight, 1), B200PT_MAX_LANES);
+    auto nextLane = [&]() { return nLanes > 1 ? (int)(c->seq++ % (unsigned)nLanes) : 0; };
+    if (!sync || nLanes == 1) {                                                  // asynchronous submission, or strictly one frame at a time
+        sp.drop();  sp.havePrev = false;
+        FrameJob job;
+        enqueueWavefront(c, *params, cfg, nextLane(), job);
+        enqueueFinalize(c, cfg, job);
+        if (sync) { CUDA_OK(cudaStreamSynchronize(c->lanes[job.lane].stream));  collectCounters(c); }   // CUDA_SYNC_CHECK, SimplePathtracer.cpp:214
+        return;
     }
+
+    // ---- blocking call with lanes to spare: consume the oldest speculative wavefront if this call is the one that was predicted
+    const unsigned thisIndex = params->frame.subframe_index;
+    const bool predictedRight = sp.havePrediction && memcmp(params, &sp.predicted, sizeof(LaunchParams)) == 0 && memcmp(&cfg, &sp.predictedCfg, sizeof(cfg)) == 0;
+    sp.hits = predictedRight ? sp.hits + 1 : 0;
+    FrameJob job;
+    if (predictedRight && !sp.ahead.empty()) {
+        job = std::move(sp.ahead.front().job);
+        memcpy(params, &sp.ahead.front().output, sizeof(LaunchParams));
+        sp.ahead.pop_front();
+    } else {
+        sp.ahead.clear();                                                        // wrong guesses are simply left behind on their lanes
+        enqueueWavefront(c, *params, cfg, nextLane(), job);
+    }
+    enqueueFinalize(c, cfg, job);
+    const b200pt_counters mine = c->last;
+    const int myLane = job.lane;
+
+    // ---- predict the next calls: the launchParams as a call leaves them, subframe_index advanced by the stride seen between the last two calls
+    const unsigned stride = sp.havePrev ? thisIndex - sp.prevIndex : 1u;        // (0 for a caller that keeps re-rendering one sub-frame; wraps like the index itself)
+    sp.prevIndex = thisIndex;  sp.havePrev = true;
+    memcpy(&sp.predicted, params, sizeof(LaunchParams));
+    sp.predicted.frame.subframe_index = thisIndex + stride;
+    sp.predictedCfg = cfg;  sp.havePrediction = true;
+    if (sp.hits >= 2) {                                                          // two right guesses in a row: keep nLanes - 1 predicted frames' wavefronts in flight
+        while ((int)sp.ahead.size() < nLanes - 1) {
+            SpecFrame f;
+            if (sp.ahead.empty()) memcpy(&f.input, &sp.predicted, sizeof(LaunchParams));
+            else {
+                memcpy(&f.input, &sp.ahead.back().output, sizeof(LaunchParams));
+                f.input.frame.subframe_index = sp.ahead.back().input.frame.subframe_index + stride;
+            }
+            memcpy(&f.output, &f.input, sizeof(LaunchParams));
+            sp.ahead.push_back(std::move(f));
+            enqueueWavefront(c, sp.ahead.back().output, cfg, nextLane(), sp.ahead.back().job);
+        }
+    } else sp.ahead.clear();
+    CUDA_OK(cudaStreamSynchronize(c->lanes[myLane].stream));                      // CUDA_SYNC_CHECK, SimplePathtracer.cpp:214 - this frame only
+    c->last = mine;  c->countersLane = myLane;  c->countersPending = true;
+    collectCounters(c);
 }
 
 extern "C" {
@@ -277,11 +338,17 @@ int b200pt_resize(b200pt_ctx* c, int w, int h, LaunchParams* params) {
     if (w == 0 || h == 0) return 0;                                              // minimised window, SimplePathtracer.cpp:233
     if (w < 0 || h < 0) return fail("b200pt_resize: negative size");
     API_BEGIN
-    enterCtx(c);
+    enterCtxMutating(c);
     CUDA_OK(cudaStreamSynchronize(c->stream));
     const size_t n = (size_t)w * h;
     c->frameBuf.release();  c->accumBuf.release();  c->normalBuf.release();  c->albedoBuf.release();  c->colorBuf.release();
     c->frameBuf.ensure(n);  c->accumBuf.ensure(n);  c->normalBuf.ensure(n);  c->albedoBuf.ensure(n);  c->colorBuf.ensure(n);
+    // The reference's CUDABuffer::resize leaves the new buffers uninitialised; a render() that keeps accumulating across a resize (subframe_index > 0)
+    // would then average against whatever the allocator handed out.  Zeroed here, so that sequence is at least deterministic.
+    CUDA_OK(cudaMemsetAsync(c->frameBuf.p, 0, sizeof(uint32_t) * n, c->stream));  CUDA_OK(cudaMemsetAsync(c->accumBuf.p, 0, sizeof(float4) * n, c->stream));
+    CUDA_OK(cudaMemsetAsync(c->normalBuf.p, 0, sizeof(float4) * n, c->stream));  CUDA_OK(cudaMemsetAsync(c->albedoBuf.p, 0, sizeof(float4) * n, c->stream));
+    CUDA_OK(cudaMemsetAsync(c->colorBuf.p, 0, sizeof(float4) * n, c->stream));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
     c->W = w;  c->H = h;
     params->frame.size = make_int2(w, h);
     params->frame.frame_buffer = (uchar4*)c->frameBuf.p;  params->frame.accum_buffer = c->accumBuf.p;
@@ -294,7 +361,7 @@ int b200pt_set_probe(b200pt_ctx* c, int w, int h, const float* data, const float
     if (!c || !params) return fail("b200pt_set_probe: null argument");
     if (w <= 0 || h <= 0 || !data || !pdfX || !cdfX || !pdfY || !cdfY) return fail("Probe Data is not valid");   // Probe.h:104-105
     API_BEGIN
-    enterCtx(c);
+    enterCtxMutating(c);
     const size_t n = (size_t)w * h;
     c->probeData.ensure(4 * n);  c->probePdfX.ensure(n);  c->probeCdfX.ensure(n);  c->probePdfY.ensure(h);  c->probeCdfY.ensure(h);
     CUDA_OK(cudaMemcpyAsync(c->probeData.p, data, 16 * n, cudaMemcpyHostToDevice, c->stream));
@@ -319,7 +386,7 @@ int b200pt_set_probe(b200pt_ctx* c, int w, int h, const float* data, const float
 int b200pt_render_whitted(b200pt_ctx* c, const b200pt_whitted_params* wp, uint32_t* deviceColorBuffer) {
     if (!c || !wp) return fail("b200pt_render_whitted: null argument");
     API_BEGIN
-    enterCtx(c);
+    enterCtxMutating(c);
     if (!c->built) throw std::runtime_error("b200pt_render_whitted: b200pt_build_accel has not been called");
     if (c->W <= 0 || c->H <= 0) throw std::runtime_error("b200pt_render_whitted: frame buffers not allocated (call b200pt_resize)");
     const size_t n = (size_t)c->W * c->H;
@@ -362,7 +429,7 @@ int b200pt_set_probe_image(b200pt_ctx* c, int w, int h, const float* data, const
     if (!c || !params) return fail("b200pt_set_probe_image: null argument");
     if (w <= 0 || h <= 0 || !data) return fail("Probe Data is not valid");
     API_BEGIN
-    enterCtx(c);
+    enterCtxMutating(c);
     const size_t n = (size_t)w * h;
     c->probeData.ensure(4 * n);  c->probePdfX.ensure(n);  c->probeCdfX.ensure(n);  c->probePdfY.ensure(h);  c->probeCdfY.ensure(h);
     c->probeGuide.ensure(probeGuideSize(h));

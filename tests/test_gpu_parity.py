@@ -359,6 +359,52 @@ def test_frames_in_flight_fold_in_submission_order(sponza_small, pname):
     assert (cnt1.samples, cnt1.radiance_rays, cnt1.shadow_rays) == (cnt3.samples, cnt3.radiance_rays, cnt3.shadow_rays)   # of the last frame
 
 
+@pytest.mark.parametrize("pname", ["orig", "sv3_uniform", "sv4_fov"])
+def test_blocking_render_with_speculative_next_subframe(sponza_small, pname):
+    """Blocking render() with cfg.frames_in_flight = 3: after two calls that looked like progressive accumulation (same launchParams, next
+    subframe_index) the library starts the predicted next sub-frame's wavefront before it blocks.  Right or wrong guesses, the accumulation buffer
+    and the pixels after every call equal those of plain one-at-a-time calls: static camera, a camera move, a jump of the sub-frame index, a probe
+    change and a resize in the middle of the sequence."""
+    probe, probe2 = analytic_sky(128, 64), loadColor((0.7, 0.8, 1.0), 64, 32)
+    cam, cam2 = preset_camera("sponza"), preset_camera("sponza")
+    cam2.eye = (cam2.eye[0] + 0.5, cam2.eye[1], cam2.eye[2])
+
+    def run(in_flight):
+        cfg = preset(pname)
+        if pname != "sv4_fov":
+            cfg.uniform_spl = 1
+        cfg.frames_in_flight = in_flight
+        r = make_renderer(sponza_small, probe, (160, 96), cam, cfg)
+        if pname == "sv4_fov":
+            r.launchParams.frame.c.x, r.launchParams.frame.c.y = 80, 48
+            r.config.inner_radius, r.config.outer_radius = 16, 40
+        out, idx = [], 0
+        for k in range(22):
+            if k == 8:
+                r.setCamera(cam2)                                   # a wrong guess: the speculative wavefront is dropped
+            if k == 12:
+                idx += 5                                            # the caller jumps ahead
+            if k == 15:
+                r.setProbe(probe2)
+            if k == 18:
+                r.resize((144, 92))                                 # (the foveal rings must stay inside the frame: where the reference clamps block
+                r.setCamera(cam2)                                   # replication to the border, :534, several launch indices write one pixel - a race in any build)
+            if pname == "orig":
+                r.launchParams.frame.subframe_index = idx           # orig: the caller owns the index (increment_subframe = 0)
+            idx += 1
+            r.render()
+            if k % 3 == 0 or k >= 18:                                # (AOVs / pixels / counters of the frame just rendered)
+                out.append((r.downloadAccum().copy(), r.downloadPixels().copy(), r.launchParams.frame.subframe_index, r.counters().radiance_rays))
+        r.close()
+        return out
+
+    a, b = run(1), run(3)
+    assert len(a) == len(b)
+    for (acc1, px1, i1, n1), (acc3, px3, i3, n3) in zip(a, b):
+        assert i1 == i3 and n1 == n3
+        assert np.array_equal(acc1, acc3) and np.array_equal(px1, px3)
+
+
 def test_tonemap_sqrt_exact():
     g = golden("display")
     rgba = np.concatenate([g["rgb"], np.ones((len(g["rgb"]), 1), np.float32)], 1).reshape(1, -1, 4)
