@@ -4,7 +4,7 @@
 // mouse cursor (main.cpp:310-314), follows a scripted Lissajous track.  fps is appended every 0.5 s in the reference's
 // log format (sutil/sutil.cpp:760-772: one value per line).
 //
-//   b200pt_headless [--obj file.obj | --boxes N] [--preset sv4_fov|sv4_uniform|sv3_uniform|orig] [--size WxH] [--frames N] [--spl N] [--in-flight N]
+//   b200pt_headless [--obj file.obj | --boxes N] [--preset sv4_fov|sv4_uniform|sv3_uniform|orig] [--size WxH] [--frames N] [--spl N] [--in-flight N [--async]]
 //                   [--camera sponza|lost_empire|san_miguel|cornell] [--sky r,g,b] [--out image.ppm|image.png] [--log fps.tsv]
 //                   [--hdr probe.hdr] [--gpu-cdf] [--whitted] [--dump-model file.bin] [--dump-probe file.bin] [--no-render]
 #include <algorithm>
@@ -109,7 +109,7 @@ int main(int argc, char** argv) {
     std::string obj, preset = "sv4_fov", cam = "cornell", out, log, dump, hdr, dumpProbe;
     int W = 1280, H = 720, frames = 16, boxes = 64, spl = 1, inFlight = 1;
     float3 sky{1.f, 1.f, 1.f};
-    bool noRender = false, gpuCdf = false, whitted = false;
+    bool noRender = false, gpuCdf = false, whitted = false, async = false;
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
         auto next = [&]() -> const char* { if (i + 1 >= argc) { fprintf(stderr, "missing value for %s\n", a.c_str());  exit(2); } return argv[++i]; };
@@ -120,7 +120,8 @@ int main(int argc, char** argv) {
         else if (a == "--size") { if (sscanf(next(), "%dx%d", &W, &H) != 2) { fprintf(stderr, "--size WxH\n");  return 2; } }
         else if (a == "--frames") frames = atoi(next());
         else if (a == "--spl") spl = atoi(next());
-        else if (a == "--in-flight") inFlight = atoi(next());      // frames in flight (b200pt_config.frames_in_flight): frames are submitted without waiting
+        else if (a == "--in-flight") inFlight = atoi(next());      // b200pt_config.frames_in_flight: render() starts the predicted next sub-frames before it blocks
+        else if (a == "--async") async = true;                     // with --in-flight N: submit frames through renderAsync() and synchronize once at the end
         else if (a == "--sky") { if (sscanf(next(), "%f,%f,%f", &sky.x, &sky.y, &sky.z) != 3) { fprintf(stderr, "--sky r,g,b\n");  return 2; } }
         else if (a == "--out") out = next();
         else if (a == "--log") log = next();
@@ -170,10 +171,10 @@ int main(int argc, char** argv) {
             if (f == 0) sample.launchParams.frame.subframe_index = 0;                                       // camera_changed starts true, :319-320
             sample.setCamera(camera);                                                                       // handleCameraUpdate, :328
             if (whitted) sample.renderWhitted(camera);
-            else if (inFlight > 1) { sample.config.frames_in_flight = inFlight;  sample.renderAsync();  if (f + 1 == frames) sample.synchronize();  else continue; }
-            else sample.render();                                                                           // :335
+            else if (async) { sample.config.frames_in_flight = inFlight;  sample.renderAsync();  if (f + 1 == frames) sample.synchronize();  else continue; }
+            else { sample.config.frames_in_flight = inFlight;  sample.render(); }                           // :335
             const b200pt_counters c = sample.counters();
-            const unsigned long long mult = (!whitted && inFlight > 1) ? (unsigned long long)frames : 1ull;     // in flight: counters of the last frame stand for all
+            const unsigned long long mult = (!whitted && async) ? (unsigned long long)frames : 1ull;            // asynchronous: counters of the last frame stand for all
             samples += mult * c.samples;  rays += mult * (c.radiance_rays + c.shadow_rays);
             ++windowFrames;
             const auto now = std::chrono::steady_clock::now();

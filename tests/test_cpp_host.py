@@ -117,16 +117,17 @@ def test_cpp_renderer_equals_python_mirror(exe, tmp_path):
 
 @pytest.mark.gpu
 def test_cpp_frames_in_flight_give_the_same_image(exe, tmp_path):
-    """The C++ host through renderAsync() with 3 frames in flight (--in-flight 3) writes the same pixels as blocking render() calls."""
+    """The C++ host with 3 frames in flight - blocking render() with speculative next sub-frames (--in-flight 3) and renderAsync()
+    (--in-flight 3 --async) - writes the same pixels as plain blocking render() calls."""
     scenes.cornell("disney", directory=str(tmp_path))
     obj = os.path.join(str(tmp_path), "cornell.obj")
     imgs = []
-    for k in (1, 3):
-        out = os.path.join(str(tmp_path), f"out{k}.ppm")
-        subprocess.check_call([exe, "--obj", obj, "--preset", "sv3_uniform", "--spl", "2", "--size", "96x64", "--frames", "6", "--camera", "cornell",
-                               "--sky", "1,1,1", "--in-flight", str(k), "--out", out])
+    for k, extra in ((1, []), (3, []), (3, ["--async"])):
+        out = os.path.join(str(tmp_path), f"out{len(imgs)}.ppm")
+        subprocess.check_call([exe, "--obj", obj, "--preset", "sv3_uniform", "--spl", "2", "--size", "96x64", "--frames", "7", "--camera", "cornell",
+                               "--sky", "1,1,1", "--in-flight", str(k), "--out", out] + extra)
         imgs.append(open(out, "rb").read())
-    assert imgs[0] == imgs[1] and len(imgs[0]) > 96 * 64 * 3
+    assert imgs[0] == imgs[1] == imgs[2] and len(imgs[0]) > 96 * 64 * 3
 
 
 # ---- Radiance .hdr readers (loadProbe, sv4/main.cpp:154-165) against the reference's own stb_image (tests/golden/hdr.npz) ----
