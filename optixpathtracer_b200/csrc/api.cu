@@ -101,7 +101,11 @@ static void joinLanes(b200pt_ctx* c) {
 }
 static void enterCtx(b200pt_ctx* c) { CUDA_OK(cudaSetDevice(c->device));  joinLanes(c); }
 // entry points that change what a frame reads or writes (scene, probe, frame buffers, lane 0's pool) also drop the speculative next sub-frame
-static void enterCtxMutating(b200pt_ctx* c) { enterCtx(c);  c->spec.drop(); }
+static void enterCtxMutating(b200pt_ctx* c) {
+    enterCtx(c);
+    for (auto& f : c->spec.ahead) if (f.job.lane >= 0 && c->lanes[f.job.lane].stream) CUDA_OK(cudaStreamSynchronize(c->lanes[f.job.lane].stream));   // still reading what is about to change
+    c->spec.drop();
+}
 
 extern "C" {
 
