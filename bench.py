@@ -327,14 +327,15 @@ def run_b200(a):
     host_px = torch.empty((a.height, a.width), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)   # pinned host frame buffer
 
     def e2e_loop(steps, count):
-        for i in range(3):
-            r.setCamera(cam)
-            r.launchParams.frame.subframe_index = frame_index(i)
+        for i in range(3):                                                      # warm-up on sub-frame indices that do NOT lead into the timed ones: the first
+            r.setCamera(cam)                                                    # timed call is then a wrong guess, the speculative wavefronts of the warm-up are
+            r.launchParams.frame.subframe_index = frame_index(100000 + i)       # dropped, and the timed region starts without work done before its clock
             r.render()
             r.downloadPixels(host_px)
+        r.synchronize()
         if world > 1:
             dist.barrier()
-        torch.cuda.synchronize()
+        torch.cuda.synchronize()                                                # every lane drained, dropped wavefronts included
         sec = 0.0
         for i in range(steps):
             t0 = time.perf_counter()
