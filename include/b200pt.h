@@ -66,7 +66,7 @@ typedef struct b200pt_config {
                                  frame's wide early ones) and frames still fold into the accumulation buffer in submission order, so the pixels are
                                  those of the one-at-a-time sequence, bit for bit.
                                  b200pt_render_async: consecutive calls overlap.
-                                 b200pt_render (blocking): once two consecutive calls have looked like progressive accumulation (same launchParams,
+                                 b200pt_render (blocking): once a call has looked like progressive accumulation (the previous call's launchParams,
                                  subframe_index advanced by a constant stride), the wavefronts of the predicted next frames_in_flight - 1 calls are
                                  enqueued before the call blocks on its own frame; a call that matches its prediction byte for byte (launchParams and
                                  config) only adds its finalize passes, any other call - a camera move, a new gaze point - drops the speculative

@@ -51,14 +51,14 @@ struct PassDesc { PassParams P;  size_t nLaunch; };
 // shared accumulation / frame / AOV buffers).
 struct FrameJob { int lane = -1;  std::vector<PassDesc> passes;  FrameParams F;  unsigned launches = 0, nClosest = 0;  cudaEvent_t totalEnd = nullptr; };
 // Speculative next sub-frame (blocking b200pt_render with cfg.frames_in_flight > 1).  Progressive accumulation calls render() again and again with
-// the same launchParams and the next subframe_index; once two consecutive calls have looked like that, render() enqueues the wavefront of the
+// the same launchParams and the next subframe_index; once a call has been predicted right, render() enqueues the wavefront of the
 // PREDICTED next call(s) on the other lanes before it blocks on the current frame.  The next call either matches the prediction byte for byte
 // (LaunchParams and config) - then only the finalize passes remain to be enqueued - or the speculative wavefront is dropped: it has touched
 // nothing but its own lane.  Pixels are those of plain blocking calls, bit for bit; a moving camera just never gets a prediction right.
 struct SpecFrame { LaunchParams input, output;  FrameJob job; };   // a predicted call: its launchParams on entry / as render() leaves them, and its wavefront
 struct Speculation {
     std::deque<SpecFrame> ahead;        // wavefronts already enqueued for the next calls, oldest first (at most frames_in_flight - 1)
-    bool havePrev = false;  unsigned prevIndex = 0;   // subframe_index of the previous blocking call (prediction = last index + last stride)
+    bool havePrev = false;  unsigned prevIndex = 0, stride = 1;   // subframe_index of the previous blocking call (prediction = last index + stride)
     bool havePrediction = false;  LaunchParams predicted;  b200pt_config predictedCfg;  int hits = 0;   // consecutive calls that matched their prediction
     void drop() { ahead.clear();  havePrediction = false;  hits = 0; }
 };

@@ -292,7 +292,15 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
 
     // ---- blocking call with lanes to spare: consume the oldest speculative wavefront if this call is the one that was predicted
     const unsigned thisIndex = params->frame.subframe_index;
-    const bool predictedRight = sp.havePrediction && memcmp(params, &sp.predicted, sizeof(LaunchParams)) == 0 && memcmp(&cfg, &sp.predictedCfg, sizeof(cfg)) == 0;
+    // "the previous call again, apart from subframe_index" (progressive accumulation) / "... and with exactly the predicted index"
+    bool sameButIndex = false;
+    if (sp.havePrediction && memcmp(&cfg, &sp.predictedCfg, sizeof(cfg)) == 0) {
+        LaunchParams a, b;
+        memcpy(&a, params, sizeof(LaunchParams));  memcpy(&b, &sp.predicted, sizeof(LaunchParams));
+        a.frame.subframe_index = 0;  b.frame.subframe_index = 0;
+        sameButIndex = memcmp(&a, &b, sizeof(LaunchParams)) == 0;
+    }
+    const bool predictedRight = sameButIndex && thisIndex == sp.predicted.frame.subframe_index;
     sp.hits = predictedRight ? sp.hits + 1 : 0;
     FrameJob job;
     if (predictedRight && !sp.ahead.empty()) {
@@ -308,12 +316,19 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
     const int myLane = job.lane;
 
     // ---- predict the next calls: the launchParams as a call leaves them, subframe_index advanced by the stride seen between the last two calls
-    const unsigned stride = sp.havePrev ? thisIndex - sp.prevIndex : 1u;        // (0 for a caller that keeps re-rendering one sub-frame; wraps like the index itself)
+    // stride of the index: kept while the guesses are right; re-learnt from the last two calls when only the index was off (a caller striding over
+    // sub-frames, e.g. one rank of a sample split; 0 for a caller that keeps re-rendering one sub-frame); 1 after any other change (the reference's
+    // loop restarts at index 0 and counts up, sv4/main.cpp:319-320,392)
+    if (!predictedRight) {
+        sp.stride = (sameButIndex && sp.havePrev) ? thisIndex - sp.prevIndex : 1u;
+        if ((int)sp.stride < 0) sp.stride = 1u;                                  // the index went backwards: an accumulation restarted, it counts up from here
+    }
+    const unsigned stride = sp.stride;
     sp.prevIndex = thisIndex;  sp.havePrev = true;
     memcpy(&sp.predicted, params, sizeof(LaunchParams));
     sp.predicted.frame.subframe_index = thisIndex + stride;
     sp.predictedCfg = cfg;  sp.havePrediction = true;
-    if (sp.hits >= 2) {                                                          // two right guesses in a row: keep nLanes - 1 predicted frames' wavefronts in flight
+    if (sp.hits >= 1) {                                                          // a right guess: keep nLanes - 1 predicted frames' wavefronts in flight
         while ((int)sp.ahead.size() < nLanes - 1) {
             SpecFrame f;
             if (sp.ahead.empty()) memcpy(&f.input, &sp.predicted, sizeof(LaunchParams));
