@@ -359,7 +359,7 @@ def test_frames_in_flight_fold_in_submission_order(sponza_small, pname):
     assert (cnt1.samples, cnt1.radiance_rays, cnt1.shadow_rays) == (cnt3.samples, cnt3.radiance_rays, cnt3.shadow_rays)   # of the last frame
 
 
-@pytest.mark.parametrize("pname", ["orig", "sv3_uniform", "sv4_fov"])
+@pytest.mark.parametrize("pname", ["orig", "orig_stride2", "sv3_uniform", "sv4_fov"])
 def test_blocking_render_with_speculative_next_subframe(sponza_small, pname):
     """Blocking render() with cfg.frames_in_flight = 3: after two calls that looked like progressive accumulation (same launchParams, next
     subframe_index) the library starts the predicted next sub-frame's wavefront before it blocks.  Right or wrong guesses, the accumulation buffer
@@ -368,6 +368,9 @@ def test_blocking_render_with_speculative_next_subframe(sponza_small, pname):
     probe, probe2 = analytic_sky(128, 64), loadColor((0.7, 0.8, 1.0), 64, 32)
     cam, cam2 = preset_camera("sponza"), preset_camera("sponza")
     cam2.eye = (cam2.eye[0] + 0.5, cam2.eye[1], cam2.eye[2])
+
+    step = 2 if pname == "orig_stride2" else 1                     # one rank of a 2-GPU sample split strides over the sub-frames
+    pname = "orig" if pname == "orig_stride2" else pname
 
     def run(in_flight):
         cfg = preset(pname)
@@ -391,7 +394,7 @@ def test_blocking_render_with_speculative_next_subframe(sponza_small, pname):
                 r.setCamera(cam2)                                   # replication to the border, :534, several launch indices write one pixel - a race in any build)
             if pname == "orig":
                 r.launchParams.frame.subframe_index = idx           # orig: the caller owns the index (increment_subframe = 0)
-            idx += 1
+            idx += step
             r.render()
             if k % 3 == 0 or k >= 18:                                # (AOVs / pixels / counters of the frame just rendered)
                 out.append((r.downloadAccum().copy(), r.downloadPixels().copy(), r.launchParams.frame.subframe_index, r.counters().radiance_rays))
