@@ -10,7 +10,9 @@
 #ifndef SHADE_HOIST_THR
 #define SHADE_HOIST_THR 1
 #endif
+#ifndef SHADE_BLOCK
 #define SHADE_BLOCK 128
+#endif
 #ifndef SHADE_MIN_BLOCKS
 #define SHADE_MIN_BLOCKS 7          // CTAs per SM for shadeKernel (72 registers); measured per frame: 6: 1.55 ms, 7: 1.44, 8: 1.47, 9: 1.52, 10: 1.56, 12: 1.69
 #endif
