@@ -343,7 +343,10 @@ def run_b200(a):
             r.launchParams.frame.subframe_index = frame_index(a.warmup + i)
             r.render()                                                          # blocking, as the reference's render()
             r.downloadPixels(host_px)                                           # D2H W*H RGBA8
-            sec += time.perf_counter() - t0
+            dt = time.perf_counter() - t0
+            sec += dt
+            if os.environ.get("B200PT_BENCH_TRACE"):
+                print(f"e2e step {i}: {dt * 1e3:.3f} ms", file=sys.stderr)
             if count:
                 tally(r.counters())                                             # host-side read of counters already fetched by render(): outside the clock
         if world > 1:

@@ -21,10 +21,12 @@ struct HostMesh { size_t firstVertex, nVertices, firstTri, nTris;  bool hasTexco
 struct HostTexture { size_t offset;  int w, h; };
 
 // Everything one frame in flight owns: its stream, the path pool, the ray queues, the per-launch counters and the per-launch-index sums.
-// b200pt_render always uses lane 0; b200pt_render_async rotates over cfg.frames_in_flight lanes, so that the drain phases and the thin late
-// bounces of one frame overlap the wide early bounces of the next.  Frames still fold into the accumulation buffer in submission order:
+// With cfg.frames_in_flight <= 1 every frame runs on lane 0, the context's primary stream; otherwise frames rotate over lanes 1..frames_in_flight,
+// so that the drain phases and the thin late bounces of one frame overlap the wide early bounces of the next - and so that the primary stream, where
+// downloads, uploads and the caller's own work are ordered, never queues behind a wavefront that is still speculative.  Frames still fold into the accumulation buffer in submission order:
 // each frame's finalize pass waits for the `done` event of the frame before it.
-#define B200PT_MAX_LANES 4
+#define B200PT_MAX_FRAMES_IN_FLIGHT 4
+#define B200PT_MAX_LANES (B200PT_MAX_FRAMES_IN_FLIGHT + 1)      // lane 0 = the primary stream: frames that run one at a time; lanes 1.. = frames in flight
 struct Lane {
     cudaStream_t stream = nullptr;
     size_t poolCap = 0;

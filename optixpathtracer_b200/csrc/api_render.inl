@@ -279,8 +279,8 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
     // Lanes: instrumented frames run on lane 0 (the primary stream); everything else rotates over cfg.frames_in_flight lanes.  With one lane
     // there is nothing to overlap and nothing to speculate on.
     Speculation& sp = c->spec;
-    const int nLanes = (cfg.profile & 3) ? 1 : std::min(std::max(cfg.frames_in_flight, 1), B200PT_MAX_LANES);
-    auto nextLane = [&]() { return nLanes > 1 ? (int)(c->seq++ % (unsigned)nLanes) : 0; };
+    const int nLanes = (cfg.profile & 3) ? 1 : std::min(std::max(cfg.frames_in_flight, 1), B200PT_MAX_FRAMES_IN_FLIGHT);
+    auto nextLane = [&]() { return nLanes > 1 ? 1 + (int)(c->seq++ % (unsigned)nLanes) : 0; };
     if (!sync || nLanes == 1) {                                                  // asynchronous submission, or strictly one frame at a time
         sp.drop();  sp.havePrev = false;
         FrameJob job;
