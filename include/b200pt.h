@@ -72,7 +72,10 @@ typedef struct b200pt_config {
                                  config) only adds its finalize passes, any other call - a camera move, a new gaze point - drops the speculative
                                  wavefronts, which have written nothing outside their own lanes.  Entry points that change the scene, the probe or the
                                  frame buffers drop them too.  Instrumented frames (profile != 0) always run one at a time on the primary stream. */
-    int   reserved[1];
+    int   intra_frame_split;  /* 0/1 = off.  2..4: with frames_in_flight <= 1 (strictly one frame at a time, e.g. a camera or gaze point that moves every frame, so
+                                 that nothing can be rendered ahead) the frame is split into that many interleaved sets of 32-row bands, each a wavefront on
+                                 its own stream; the sets' kernels fill each other's drain phases and thin late bounces.  Same partition as tile_rank/tile_count,
+                                 same seeds per launch index: pixels are bit-identical to the unsplit frame. */
 } b200pt_config;
 
 /* Fill *cfg with a named preset: "orig", "sv3_uniform", "sv4_uniform", "sv4_fov". */

@@ -30,8 +30,8 @@ struct HostTexture { size_t offset;  int w, h; };
 struct Lane {
     cudaStream_t stream = nullptr;
     size_t poolCap = 0;
-    DevBuf<uint2> rng;  DevBuf<float4> thr, direct, indirect, alpha, pending, aovN, aovA;  DevBuf<int> state;  DevBuf<float> bsdfPdf;
-    DevBuf<float4> rayO[2], rayD[2], hit, shO, shD;
+    DevBuf<PathState> st;  DevBuf<float4> direct, indirect, alpha, aovN, aovA;
+    DevBuf<float4> rayO[2], rayD[2], hitA, hitB, hitC, shO, shD, shP;
     DevBuf<unsigned> counters;          // QC_COUNT queue counters + 8 running totals
     DevBuf<float4> sumRad, sumAlpha, sumNormal, sumAlbedo;
     DevBuf<TraceStats> stats;           // [0] closest, [1] any
@@ -39,10 +39,9 @@ struct Lane {
     bool busy = false;                  // has work the primary stream has not been ordered after yet
     bool forked = false;                // already ordered after the primary stream's earlier work (since the last join)
     void release() {
-        rng.release();  thr.release();  direct.release();  indirect.release();  alpha.release();  pending.release();
-        aovN.release();  aovA.release();  state.release();  bsdfPdf.release();
+        st.release();  direct.release();  indirect.release();  alpha.release();  aovN.release();  aovA.release();
         for (int i = 0; i < 2; ++i) { rayO[i].release();  rayD[i].release(); }
-        hit.release();  shO.release();  shD.release();  counters.release();
+        hitA.release();  hitB.release();  hitC.release();  shO.release();  shD.release();  shP.release();  counters.release();
         sumRad.release();  sumAlpha.release();  sumNormal.release();  sumAlbedo.release();  stats.release();
         poolCap = 0;
     }
@@ -51,7 +50,9 @@ struct Lane {
 struct PassDesc { PassParams P;  size_t nLaunch; };
 // One frame's wavefront as enqueued on a lane: everything up to, but not including, its finalize passes (the only stage that touches the
 // shared accumulation / frame / AOV buffers).
-struct FrameJob { int lane = -1;  std::vector<PassDesc> passes;  FrameParams F;  unsigned launches = 0, nClosest = 0;  cudaEvent_t totalEnd = nullptr; };
+// `lane` runs the wavefront - or, for a frame split into interleaved band sets (cfg.intra_frame_split), part 0 of it, with the other parts on `extraLanes`;
+// the finalize passes always run on `lane`, whose sumRad/sumAlpha buffers collect the per-launch-index sums of every part.
+struct FrameJob { int lane = -1;  std::vector<int> extraLanes;  std::vector<PassDesc> passes;  FrameParams F;  unsigned launches = 0, nClosest = 0;  cudaEvent_t totalEnd = nullptr; };
 // Speculative next sub-frame (blocking b200pt_render with cfg.frames_in_flight > 1).  Progressive accumulation calls render() again and again with
 // the same launchParams and the next subframe_index; once a call has been predicted right, render() enqueues the wavefront of the
 // PREDICTED next call(s) on the other lanes before it blocks on the current frame.  The next call either matches the prediction byte for byte
@@ -83,7 +84,8 @@ struct b200pt_ctx {
     // --- wavefront state: one Lane per frame in flight (lane 0 runs on `stream`, the reference's single stream)
     Lane lanes[B200PT_MAX_LANES];
     int lastLane = -1;                  // lane of the most recently enqueued frame (its `done` event orders the next frame's accumulation)
-    int countersLane = 0;               // lane whose device counters `last` will be read from
+    int countersLane = 0;               // lane whose device counters `last` will be read from ...
+    std::vector<int> countersExtra;     // ... plus the lanes of the other parts of a split frame
     unsigned seq = 0;                   // round-robin lane pick of b200pt_render_async
     cudaEvent_t forkEv = nullptr;
     Speculation spec;
@@ -105,8 +107,22 @@ static void enterCtx(b200pt_ctx* c) { CUDA_OK(cudaSetDevice(c->device));  joinLa
 // entry points that change what a frame reads or writes (scene, probe, frame buffers, lane 0's pool) also drop the speculative next sub-frame
 static void enterCtxMutating(b200pt_ctx* c) {
     enterCtx(c);
-    for (auto& f : c->spec.ahead) if (f.job.lane >= 0 && c->lanes[f.job.lane].stream) CUDA_OK(cudaStreamSynchronize(c->lanes[f.job.lane].stream));   // still reading what is about to change
+    // Every lane, not only those still listed in spec.ahead: a mispredicted or dropped speculative wavefront keeps running on its lane after it
+    // has been forgotten, and it reads the scene / probe / pool that the caller is about to change.
+    for (int k = 1; k < B200PT_MAX_LANES; ++k) if (c->lanes[k].stream) CUDA_OK(cudaStreamSynchronize(c->lanes[k].stream));
     c->spec.drop();
+}
+
+int numSMs() {
+    static int cache[64];                                     // 0 = not queried yet
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (!cache[dev]) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cache[dev] = n;
+    }
+    return cache[dev];
 }
 
 extern "C" {

@@ -21,6 +21,7 @@ int b200pt_download_pixels_async(b200pt_ctx* c, uint32_t* host) {
     if (!L.stream) throw std::runtime_error("b200pt_download_pixels_async: no frame has been rendered");
     CUDA_OK(cudaMemcpyAsync(host, c->frameBuf.p, sizeof(uint32_t) * (size_t)c->W * c->H, cudaMemcpyDeviceToHost, L.stream));
     if (L.done) CUDA_OK(cudaEventRecord(L.done, L.stream));
+    L.busy = k > 0;                                  // the copy is work the primary stream has not been ordered after: b200pt_synchronize / b200pt_join must wait for it
     API_END
 }
 int b200pt_download_accum(b200pt_ctx* c, float* host) {

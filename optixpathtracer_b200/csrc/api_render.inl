@@ -23,24 +23,22 @@ static size_t poolLimit() {
     return std::max<size_t>(v, 1024);
 }
 
-static void ensurePool(Lane& c, size_t slots, bool aovs, bool mis) {
+static void ensurePool(Lane& c, size_t slots, bool aovs) {
     if (slots > c.poolCap) {
-        c.rng.ensure(slots);  c.thr.ensure(slots);  c.state.ensure(slots);  c.direct.ensure(slots);  c.indirect.ensure(slots);
-        c.alpha.ensure(slots);  c.pending.ensure(slots);
+        c.st.ensure(slots);  c.direct.ensure(slots);  c.indirect.ensure(slots);  c.alpha.ensure(slots);
         for (int i = 0; i < 2; ++i) { c.rayO[i].ensure(slots);  c.rayD[i].ensure(slots); }
-        c.hit.ensure(slots);  c.shO.ensure(slots);  c.shD.ensure(slots);
+        c.hitA.ensure(slots);  c.hitB.ensure(slots);  c.hitC.ensure(slots);  c.shO.ensure(slots);  c.shD.ensure(slots);  c.shP.ensure(slots);
         c.poolCap = slots;
     }
     if (aovs) { c.aovN.ensure(c.poolCap);  c.aovA.ensure(c.poolCap); }
-    if (mis) c.bsdfPdf.ensure(c.poolCap);
     c.counters.ensure(QC_STRIDE * QC_MAX_LAUNCHES + 8);                      // per-launch queue counters, then 8 frame totals
     c.stats.ensure(2);
 }
-static PathPool poolOf(Lane& L) { return PathPool{L.rng.p, L.thr.p, L.state.p, L.direct.p, L.indirect.p, L.alpha.p, L.pending.p, L.bsdfPdf.p, L.aovN.p, L.aovA.p}; }
+static PathPool poolOf(Lane& L) { return PathPool{L.st.p, L.direct.p, L.indirect.p, L.alpha.p, L.aovN.p, L.aovA.p}; }
 static Queues queuesOf(Lane& L) {
     Queues Q;
     for (int i = 0; i < 2; ++i) { Q.rayO[i] = L.rayO[i].p;  Q.rayD[i] = L.rayD[i].p; }
-    Q.hit = L.hit.p;  Q.shO = L.shO.p;  Q.shD = L.shD.p;  Q.counters = L.counters.p;
+    Q.hitA = L.hitA.p;  Q.hitB = L.hitB.p;  Q.hitC = L.hitC.p;  Q.shO = L.shO.p;  Q.shD = L.shD.p;  Q.shP = L.shP.p;  Q.counters = L.counters.p;
     return Q;
 }
 // lane k > 0 gets its stream and `done` event on first use
@@ -66,10 +64,15 @@ enum { ST_RAYGEN = 0, ST_TRACE, ST_TRACE_TAIL, ST_SHADE, ST_ACCUM, ST_TOTAL };
 
 static void collectCounters(b200pt_ctx* c) {
     if (!c->countersPending) return;
-    unsigned h[8];
+    c->last.radiance_rays = 0;  c->last.shadow_rays = 0;  c->last.samples = 0;
+    std::vector<int> lanes(1, c->countersLane);
+    lanes.insert(lanes.end(), c->countersExtra.begin(), c->countersExtra.end());
+    for (int k : lanes) {                                                    // a split frame: one set of totals per part
+        unsigned h[8];
+        CUDA_OK(cudaMemcpy(h, c->lanes[k].counters.p + QC_STRIDE * QC_MAX_LAUNCHES, sizeof(h), cudaMemcpyDeviceToHost));
+        c->last.radiance_rays += h[0];  c->last.shadow_rays += h[1];  c->last.samples += h[2];
+    }
     Lane& L = c->lanes[c->countersLane];
-    CUDA_OK(cudaMemcpy(h, L.counters.p + QC_STRIDE * QC_MAX_LAUNCHES, sizeof(h), cudaMemcpyDeviceToHost));
-    c->last.radiance_rays = h[0];  c->last.shadow_rays = h[1];  c->last.samples = h[2];
     if (c->profiled & 2) {
         TraceStats st[2];
         CUDA_OK(cudaMemcpy(st, L.stats.p, sizeof(st), cudaMemcpyDeviceToHost));
@@ -153,15 +156,20 @@ static FrameParams frameOf(const LaunchParams& P, const b200pt_config& cfg, cons
 
 struct Chunk { int pass, k0, k1;  unsigned slotBase; };
 
-// Enqueues one frame's wavefront (raygen, the bounce loop, counters, per-launch-index sums) on lane `laneIdx`.  `params` is mutated exactly as
-// the reference's render() leaves its public launchParams; nothing outside the lane is written.
-static void enqueueWavefront(b200pt_ctx* c, LaunchParams& params, const b200pt_config& cfg, int laneIdx, FrameJob& job) {
-    job = FrameJob();
-    job.lane = laneIdx;
+// A shadow-catcher pass-through (sv4/deviceProgram.cu:617-622) re-traces a segment without consuming depth, so a path that crosses catcher
+// geometry k times needs max_depth + 1 + k trace launches; the wavefront allows this many crossings per path (launches on empty queues cost ~2 us).
+#define B200PT_CATCHER_EXTRA_LAUNCHES 8
+
+// Enqueues one wavefront (raygen, the bounce loop, counters, per-launch-index sums) of `job` on lane `laneIdx`: the whole frame (nParts = 1)
+// or the launch rows of band set `part` of `nParts` (a frame split into interleaved 32-row band sets that run concurrently on their own lanes;
+// the same partition as the multi-GPU tile split, so the pixels are those of the unsplit frame bit for bit).  The sums land in sumLane's buffers.
+static void enqueuePart(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& job, int laneIdx, int part, int nParts, Lane& sumLane) {
     std::vector<PassDesc>& passes = job.passes;
-    buildSchedule(params, cfg, passes);
-    job.F = frameOf(params, cfg, c);
-    const FrameParams& F = job.F;
+    FrameParams F = job.F;
+    if (nParts > 1) {                                                            // band b belongs to the part iff b % (tc * nParts) == tr + tc * part
+        const int tc = std::max(F.tileCount, 1), tr = F.tileCount > 1 ? F.tileRank : 0;
+        F.tileRank = tr + tc * part;  F.tileCount = tc * nParts;
+    }
     const SceneDev S = sceneOf(c);
     Lane& L = laneOf(c, laneIdx);
     cudaStream_t s = L.stream;
@@ -170,12 +178,9 @@ static void enqueueWavefront(b200pt_ctx* c, LaunchParams& params, const b200pt_c
         CUDA_OK(cudaStreamWaitEvent(s, c->forkEv, 0));
         L.forked = true;
     }
+    // a part writes its sums into ANOTHER lane's buffers: wait until the previous frame's finalize passes have read them
+    if (nParts > 1 && c->lastLane >= 0 && c->lastLane != laneIdx && c->lanes[c->lastLane].done) CUDA_OK(cudaStreamWaitEvent(s, c->lanes[c->lastLane].done, 0));
 
-    // launch-index records and chunks
-    size_t nRec = 0;
-    for (auto& p : passes) { if (p.P.spl <= 0) throw std::runtime_error("b200pt_render: samples_per_launch must be > 0");  p.P.launchBase = (unsigned)nRec;  nRec += p.nLaunch; }
-    L.sumRad.ensure(std::max<size_t>(nRec, 1));  L.sumAlpha.ensure(std::max<size_t>(nRec, 1));
-    if (cfg.write_aovs) { L.sumNormal.ensure(std::max<size_t>(nRec, 1));  L.sumAlbedo.ensure(std::max<size_t>(nRec, 1)); }
     const size_t limit = poolLimit();
     std::vector<std::vector<Chunk>> groups(1);
     size_t used = 0, maxUsed = 0;
@@ -192,7 +197,7 @@ static void enqueueWavefront(b200pt_ctx* c, LaunchParams& params, const b200pt_c
         }
     }
     if (maxUsed >= ((size_t)1 << 31)) throw std::runtime_error("b200pt_render: pool too large");
-    ensurePool(L, std::max<size_t>(maxUsed, 1), cfg.write_aovs != 0, cfg.mis_on_miss != 0);
+    ensurePool(L, std::max<size_t>(maxUsed, 1), cfg.write_aovs != 0);
 
     PathPool pool = poolOf(L);
     Queues Q = queuesOf(L);
@@ -206,7 +211,8 @@ static void enqueueWavefront(b200pt_ctx* c, LaunchParams& params, const b200pt_c
     CUDA_OK(cudaMemsetAsync(L.counters.p, 0, sizeof(unsigned) * (QC_STRIDE * QC_MAX_LAUNCHES + 8), s));
     if (count) CUDA_OK(cudaMemsetAsync(L.stats.p, 0, 2 * sizeof(TraceStats), s));
     T.begin(ST_TOTAL, ta, job.totalEnd);
-    const int bounces = cfg.max_depth + ((c->hasCatcher || cfg.max_depth == 0) ? 1 : 0);   // the dropped last segment is traced only if alpha can still change
+    // the dropped last segment is traced only if alpha can still change (a catcher in the scene) or the miss carries radiance (mis_on_miss)
+    const int bounces = cfg.max_depth + ((c->hasCatcher || cfg.max_depth == 0) ? 1 : 0) + (c->hasCatcher ? B200PT_CATCHER_EXTRA_LAUNCHES : 0);
     const int cullBack = cfg.shadow_mode == B200PT_SHADOW_CULL_BACK;
     const float shadowTmin = cfg.shadow_tmin > 0.f ? cfg.shadow_tmin : cfg.tmin;
     for (auto& group : groups) {
@@ -220,10 +226,8 @@ static void enqueueWavefront(b200pt_ctx* c, LaunchParams& params, const b200pt_c
         int cur = 0;
         // trace launch d: extension rays of bounce d + the shadow rays shade pass d-1 emitted; launch `bounces` only shadows
         for (int d = 0; d <= bounces; ++d) {
-            unsigned* ctr = Q.counters + QC_STRIDE * d;
             T.begin(d < bounces ? ST_TRACE : ST_TRACE_TAIL, a, b);
-            launchTrace(S, Q.rayO[cur], Q.rayD[cur], Q.hit, ctr + (d < bounces ? QC_RAYS : 3 /* always 0 */), Q.shO, Q.shD, ctr + QC_SHADOWS, ctr + QC_HEAD, cfg.tmin, shadowTmin, cfg.tmax,
-                        cullBack, pool, count ? L.stats.p : nullptr, s);
+            launchTrace(S, Q, cur, d < bounces ? 1 : 0, Q.counters + QC_STRIDE * d, cfg.tmin, shadowTmin, cfg.tmax, cullBack, cfg.mis_on_miss, pool, count ? L.stats.p : nullptr, s);
             T.end(b);  ++launches;  ++job.nClosest;
             if (d == bounces) break;
             T.begin(ST_SHADE, a, b);
@@ -235,11 +239,34 @@ static void enqueueWavefront(b200pt_ctx* c, LaunchParams& params, const b200pt_c
         T.begin(ST_ACCUM, a, b);
         for (auto& ch : group) {
             PassParams P = passes[ch.pass].P;  P.slotBase = ch.slotBase;
-            launchGather(F, P, ch.k0, ch.k1, pool, L.sumRad.p, L.sumAlpha.p, L.sumNormal.p, L.sumAlbedo.p, s);  ++launches;
+            launchGather(F, P, ch.k0, ch.k1, pool, sumLane.sumRad.p, sumLane.sumAlpha.p, sumLane.sumNormal.p, sumLane.sumAlbedo.p, s);  ++launches;
         }
         T.end(b);
     }
     CUDA_OK(cudaGetLastError());
+}
+
+// Enqueues one frame's wavefront on `lanes` (one lane: the whole frame; several: the frame split into that many band sets).  `params` is mutated
+// exactly as the reference's render() leaves its public launchParams; nothing outside the lanes is written.
+static void enqueueWavefront(b200pt_ctx* c, LaunchParams& params, const b200pt_config& cfg, const std::vector<int>& lanes, FrameJob& job) {
+    job = FrameJob();
+    job.lane = lanes[0];
+    job.extraLanes.assign(lanes.begin() + 1, lanes.end());
+    buildSchedule(params, cfg, job.passes);
+    job.F = frameOf(params, cfg, c);
+    size_t nRec = 0;                                                             // launch-index records
+    for (auto& p : job.passes) { if (p.P.spl <= 0) throw std::runtime_error("b200pt_render: samples_per_launch must be > 0");  p.P.launchBase = (unsigned)nRec;  nRec += p.nLaunch; }
+    Lane& L0 = laneOf(c, job.lane);
+    L0.sumRad.ensure(std::max<size_t>(nRec, 1));  L0.sumAlpha.ensure(std::max<size_t>(nRec, 1));
+    if (cfg.write_aovs) { L0.sumNormal.ensure(std::max<size_t>(nRec, 1));  L0.sumAlbedo.ensure(std::max<size_t>(nRec, 1)); }
+    const int nParts = (int)lanes.size();
+    for (int part = 0; part < nParts; ++part) {
+        enqueuePart(c, cfg, job, lanes[part], part, nParts, L0);
+        if (part > 0) CUDA_OK(cudaEventRecord(c->lanes[lanes[part]].done, c->lanes[lanes[part]].stream));   // the finalize passes wait for it
+    }
+}
+static void enqueueWavefront(b200pt_ctx* c, LaunchParams& params, const b200pt_config& cfg, int laneIdx, FrameJob& job) {
+    enqueueWavefront(c, params, cfg, std::vector<int>(1, laneIdx), job);
 }
 
 // The finalize passes of an enqueued wavefront: frames fold into the accumulation / frame / AOV buffers in submission order, whatever lane they ran on.
@@ -247,6 +274,7 @@ static void enqueueFinalize(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& j
     Lane& L = c->lanes[job.lane];
     cudaStream_t s = L.stream;
     if (c->lastLane >= 0 && c->lastLane != job.lane) CUDA_OK(cudaStreamWaitEvent(s, c->lanes[c->lastLane].done, 0));
+    for (int k : job.extraLanes) CUDA_OK(cudaStreamWaitEvent(s, c->lanes[k].done, 0));      // the other parts of a split frame
     StageTimer T{c, (cfg.profile & 1) != 0};
     cudaEvent_t a = nullptr, b = nullptr;
     T.begin(ST_ACCUM, a, b);
@@ -258,7 +286,7 @@ static void enqueueFinalize(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& j
     T.end(job.totalEnd);
     CUDA_OK(cudaGetLastError());
     CUDA_OK(cudaEventRecord(L.done, s));
-    c->lastLane = job.lane;  c->countersLane = job.lane;  L.busy = job.lane > 0;
+    c->lastLane = job.lane;  c->countersLane = job.lane;  c->countersExtra = job.extraLanes;  L.busy = job.lane > 0;
     c->profiled = cfg.profile & 3;
     c->last = b200pt_counters{};
     c->last.kernel_launches = job.launches;  c->last.n_trace_closest_launches = job.nClosest;  c->last.n_trace_any_launches = 0;
@@ -284,7 +312,14 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
     if (!sync || nLanes == 1) {                                                  // asynchronous submission, or strictly one frame at a time
         sp.drop();  sp.havePrev = false;
         FrameJob job;
-        enqueueWavefront(c, *params, cfg, nextLane(), job);
+        // one frame at a time, split into interleaved band sets on lanes 1..nSplit: the drain phase of every persistent launch and the thin late bounces
+        // of one part are filled by the other parts' kernels, which is what frames in flight buy for a caller that can run frames ahead
+        const int nSplit = (nLanes == 1 && !(cfg.profile & 3)) ? std::min(std::max(cfg.intra_frame_split, 1), B200PT_MAX_FRAMES_IN_FLIGHT) : 1;
+        if (nSplit > 1) {
+            std::vector<int> lanes;
+            for (int k = 1; k <= nSplit; ++k) lanes.push_back(k);
+            enqueueWavefront(c, *params, cfg, lanes, job);
+        } else enqueueWavefront(c, *params, cfg, nextLane(), job);
         enqueueFinalize(c, cfg, job);
         if (sync) { CUDA_OK(cudaStreamSynchronize(c->lanes[job.lane].stream));  collectCounters(c); }   // CUDA_SYNC_CHECK, SimplePathtracer.cpp:214
         return;
@@ -342,7 +377,7 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
         }
     } else sp.ahead.clear();
     CUDA_OK(cudaStreamSynchronize(c->lanes[myLane].stream));                      // CUDA_SYNC_CHECK, SimplePathtracer.cpp:214 - this frame only
-    c->last = mine;  c->countersLane = myLane;  c->countersPending = true;
+    c->last = mine;  c->countersLane = myLane;  c->countersExtra.clear();  c->countersPending = true;
     collectCounters(c);
 }
 
@@ -407,7 +442,7 @@ int b200pt_render_whitted(b200pt_ctx* c, const b200pt_whitted_params* wp, uint32
     const size_t n = (size_t)c->W * c->H;
     if (n >= ((size_t)1 << 31)) throw std::runtime_error("b200pt_render_whitted: frame too large");
     Lane& L = c->lanes[0];
-    ensurePool(L, n, false, false);
+    ensurePool(L, n, false);
     WhittedParams P;
     P.W = c->W;  P.H = c->H;
     P.position = make_float3(wp->position[0], wp->position[1], wp->position[2]);
@@ -424,9 +459,9 @@ int b200pt_render_whitted(b200pt_ctx* c, const b200pt_whitted_params* wp, uint32
     unsigned* c0 = Q.counters;
     unsigned* c1 = Q.counters + QC_STRIDE;
     launchWhittedRaygen(P, Q, pool, c0, s);
-    launchTrace(S, Q.rayO[0], Q.rayD[0], Q.hit, c0 + QC_RAYS, Q.shO, Q.shD, c0 + QC_SHADOWS /* 0 */, c0 + QC_HEAD, 0.f, 0.f, 1e20f, 0, pool, nullptr, s);
-    launchWhittedShade(P, S, pool, Q, c1 + QC_SHADOWS, s);
-    launchTrace(S, Q.rayO[0], Q.rayD[0], Q.hit, c1 + 3 /* always 0 */, Q.shO, Q.shD, c1 + QC_SHADOWS, c1 + QC_HEAD, 1e-3f, 1e-3f, 1.f - 1e-3f, 0, pool, nullptr, s);
+    launchTrace(S, Q, 0, 1, c0, 0.f, 0.f, 1e20f, 0, 0, pool, nullptr, s);                       // closest hits -> hit queue (c0[QC_HITS]); no shadow rays yet
+    launchWhittedShade(P, S, pool, Q, c0 + QC_HITS, c1 + QC_SHADOWS, s);
+    launchTrace(S, Q, 0, 0, c1, 1e-3f, 1e-3f, 1.f - 1e-3f, 0, 0, pool, nullptr, s);             // shadow rays only
     launchWhittedFinish(P, pool, deviceColorBuffer ? deviceColorBuffer : (uint32_t*)c->frameBuf.p, s);
     CUDA_OK(cudaGetLastError());
     CUDA_OK(cudaStreamSynchronize(s));

@@ -1,11 +1,12 @@
 // b200pt — shared declarations of the CUDA implementation (sm_100a).
 // Data layout in HBM:
-//   BvhNode   32 B  {lo.xyz, link | hi.xyz, aux}; siblings adjacent and 64-byte aligned (one 4x128-bit fetch per step)
+//   BvhNode   32 B  binary record: two quantised child boxes + two links (build, refit, parity hooks)
+//   BvhNode4  64 B  the 4-wide node traceKernel walks (two 256-bit loads per step)
 //   TriRecord 48 B  {v0.xyz,e1.x | e1.yz,e2.xy | e2.z, gid, mesh, -}  in BVH (Morton) order — the "Woop-sized" record;
 //                   untransformed edges so the device test is bit-identical to the oracle's and so the shading
 //                   normal cross(e1,e2) (sv4/deviceProgram.cu:598-605) needs no second gather
-//   queues    32 B ray {o.xyz, slot | d.xyz, -}, 16 B hit {t,u,v,triSlot}
-//   path state SoA indexed by sample slot.
+//   queues    32 B ray {o.xyz, slot | d.xyz, -}, 48 B hit {o, slot | d, t | u, v, triSlot}, 48 B shadow ray {P, slot | wi, target | contribution}
+//   path state: one 32-byte PathState per sample slot + three float4 accumulators.
 #pragma once
 #include <cuda_runtime.h>
 #include <cstdint>
@@ -16,7 +17,8 @@
 #include "../../include/b200pt.h"
 #include "../../include/ref_api/LaunchParams.h"
 
-#define B200PT_NUM_SMS 148
+// SM count of the current device (cudaDevAttrMultiProcessorCount, cached per device; 148 on B200): sizes every persistent grid
+int numSMs();
 
 // One 32-byte record per INNER node, holding both children: their boxes quantised (conservatively, 2 cells of padding) to a
 // 16-bit grid over the scene AABB, and their links.  link >= 0: record index of the child's own node; < 0: leaf code.
@@ -96,27 +98,39 @@ struct FrameParams {               // shared by every pass of a frame
     float4* accum;  uint32_t* frame;  float4* normal;  float4* albedo;  float4* color;
 };
 
-struct PathPool {                  // SoA path state, indexed by sample slot
-    uint2*  rng;                   // Random {seed1, seed2}
-    float4* thr;                   // throughput.xyz, rayEta
-    int*    state;                 // depth | flags<<8
+// Per-path state, one 32-byte record (= one DRAM sector) per sample slot: shadeKernel reads and rewrites it as a whole.
+struct PathState {
+    unsigned rng1, rng2;           // Random {seed1, seed2}
+    float    thrX, thrY, thrZ;     // pathThroughput
+    float    eta;                  // rayEta
+    int      state;                // depth | flags << 8
+    float    bsdfPdf;              // only with mis_on_miss: pdf of the BSDF sample that produced the current segment
+};
+static_assert(sizeof(PathState) == 32, "PathState must be one 32-byte sector");
+
+struct PathPool {                  // path state indexed by sample slot
+    PathState* st;
     float4* direct;                // radiance added at depth 0
     float4* indirect;              // radiance added at depth >= 1, in bounce order
     float4* alpha;                 // prd.alpha
-    float4* pending;               // NEE contribution awaiting its shadow ray
-    float*  bsdfPdf;               // only with mis_on_miss: pdf of the BSDF sample that produced the current segment
     float4* aovNormal;             // only with write_aovs
     float4* aovAlbedo;
 };
 
+// Wavefront queues of one frame in flight.
+//   extension rays  rayO {o.xyz, slot} rayD {d.xyz, -}                       double-buffered, written by raygen / shade, read by trace
+//   hits            hitA {o.xyz, slot} hitB {d.xyz, t} hitC {u, v, triSlot, -}   written by traceKernel, densely packed, for the rays that HIT something: a ray
+//                   that leaves the scene retires inside traceKernel (__miss__radiance only sets DONE, sv4/deviceProgram.cu:251-280), so every
+//                   lane of a shade warp has a surface to shade (with mis_on_miss the misses are queued too, triSlot = -1)
+//   shadow rays     shO {P.xyz, slot} shD {wi.xyz, target} shP {T * lightSample, -}: the NEE contribution travels with its occlusion ray
 struct Queues {
-    float4* rayO[2];  float4* rayD[2];      // double-buffered extension-ray queue
-    float4* hit;                             // closest-hit results, same order as the current ray queue
-    float4* shO;  float4* shD;              // shadow-ray queue
+    float4* rayO[2];  float4* rayD[2];
+    float4* hitA;  float4* hitB;  float4* hitC;
+    float4* shO;  float4* shD;  float4* shP;
     unsigned* counters;                      // per trace launch d: counters[QC_STRIDE*d + QC_*]
 };
-// trace launch d of a frame handles the extension rays of bounce d and the shadow rays emitted by shade pass d-1
-enum { QC_RAYS = 0, QC_SHADOWS = 1, QC_HEAD = 2, QC_STRIDE = 4, QC_MAX_LAUNCHES = 208 };
+// trace launch d of a frame handles the extension rays of bounce d and the shadow rays emitted by shade pass d-1; it produces the hit queue shade pass d reads
+enum { QC_RAYS = 0, QC_SHADOWS = 1, QC_HEAD = 2, QC_HITS = 3, QC_STRIDE = 4, QC_MAX_LAUNCHES = 208 };
 
 struct TraceStats { unsigned long long nodes, tris, rays; };
 
@@ -144,16 +158,16 @@ void bvhRefit(const float3* d_vertices, const uint3* d_indices, const unsigned* 
               BvhBuildResult& io, float* refitMs);
 
 // trace.cu  (compiled with FMA contraction; the triangle test itself uses explicit _rn intrinsics)
-void launchTrace(const SceneDev& scene, const float4* rayO, const float4* rayD, float4* hit, const unsigned* countC,
-                 const float4* shO, const float4* shD, const unsigned* countS, unsigned* head, float tmin, float tminShadow, float tmax, int cullBack,
-                 const PathPool& pool, TraceStats* stats /* [0] closest, [1] any; nullptr = no counting */, cudaStream_t stream);
+// ctr = the QC_* counter block of this launch; cur = which extension-ray buffer it reads; closest = 0: shadow rays only (the frame's last launch)
+void launchTrace(const SceneDev& scene, const Queues& Q, int cur, int closest, unsigned* ctr, float tmin, float tminShadow, float tmax, int cullBack,
+                 int emitMisses, const PathPool& pool, TraceStats* stats /* [0] closest, [1] any; nullptr = no counting */, cudaStream_t stream);
 void launchTraceRaysDebug(const SceneDev& scene, const float4* rayO, const float4* rayD, unsigned n, float tmin, float tmax,
                           int anyHit, int cullBack, float4* hitOut, cudaStream_t stream);
 
 // shade.cu  (compiled with -fmad=false: basic fp32 arithmetic bit-identical to the IEEE host oracle)
 void launchRaygen(const FrameParams& F, const PassParams& P, int k0, int k1, const PathPool& pool, const Queues& Q,
                   cudaStream_t stream);
-void launchShade(const FrameParams& F, const SceneDev& scene, const PathPool& pool, const Queues& Q, int cur, int depth,
+void launchShade(const FrameParams& F, const SceneDev& scene, const PathPool& pool, const Queues& Q, int cur, int launch,
                  cudaStream_t stream);
 void launchGather(const FrameParams& F, const PassParams& P, int k0, int k1, const PathPool& pool, float4* sumRad,
                   float4* sumAlpha, float4* sumNormal, float4* sumAlbedo, cudaStream_t stream);
@@ -162,7 +176,7 @@ void launchFinalize(const FrameParams& F, const PassParams& P, const float4* sum
 void launchResolveSum(const FrameParams& F, int nPasses, cudaStream_t stream);
 struct WhittedParams { int W, H;  float3 position, direction, horizontal, vertical, lightPos; };
 void launchWhittedRaygen(const WhittedParams& P, const Queues& Q, const PathPool& pool, unsigned* counters, cudaStream_t stream);
-void launchWhittedShade(const WhittedParams& P, const SceneDev& scene, const PathPool& pool, const Queues& Q, unsigned* shadowCounter, cudaStream_t stream);
+void launchWhittedShade(const WhittedParams& P, const SceneDev& scene, const PathPool& pool, const Queues& Q, const unsigned* hitCounter, unsigned* shadowCounter, cudaStream_t stream);
 void launchWhittedFinish(const WhittedParams& P, const PathPool& pool, uint32_t* colorBuffer, cudaStream_t stream);
 size_t probeGuideSize(int H);
 void launchProbeGuide(const float* cdfX, const float* cdfY, int W, int H, int* guide, cudaStream_t stream);

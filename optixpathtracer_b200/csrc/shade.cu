@@ -17,17 +17,35 @@
 #define SHADE_MIN_BLOCKS 7          // CTAs per SM for shadeKernel (72 registers); measured per frame: 6: 1.55 ms, 7: 1.44, 8: 1.47, 9: 1.52, 10: 1.56, 12: 1.69
 #endif
 
-DEV void enqueueRay(bool want, float4 o, float4 d, float4* qo, float4* qd, unsigned* counter) {
+// warp-aggregated append: one atomicAdd per warp, entries of a warp contiguous and in lane order
+DEV unsigned enqueueSlot(bool want, unsigned* counter) {
     const unsigned mask = __ballot_sync(0xffffffffu, want);
-    if (!mask) return;
+    if (!mask) return 0u;
     const unsigned lane = threadIdx.x & 31;
     unsigned base = 0;
     if (lane == (unsigned)(__ffs(mask) - 1)) base = atomicAdd(counter, (unsigned)__popc(mask));
     base = __shfl_sync(0xffffffffu, base, __ffs(mask) - 1);
-    if (want) {
-        const unsigned q = base + __popc(mask & ((1u << lane) - 1u));
-        qo[q] = o;  qd[q] = d;
-    }
+    return base + __popc(mask & ((1u << lane) - 1u));
+}
+DEV void enqueueRay(bool want, float4 o, float4 d, float4* qo, float4* qd, unsigned* counter) {
+    const unsigned q = enqueueSlot(want, counter);
+    if (want) { qo[q] = o;  qd[q] = d; }
+}
+DEV void enqueueShadow(bool want, float4 o, float4 d, float4 p, const Queues& Q, unsigned* counter) {
+    const unsigned q = enqueueSlot(want, counter);
+    if (want) { Q.shO[q] = o;  Q.shD[q] = d;  Q.shP[q] = p; }
+}
+
+// the 32-byte path record as one 256-bit access (sm_100: LDG.E.256 / STG.E.256)
+DEV PathState ldState(const PathState* p) {
+    PathState s;
+    asm volatile("ld.global.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(s.rng1), "=r"(s.rng2), "=f"(s.thrX), "=f"(s.thrY), "=f"(s.thrZ), "=f"(s.eta), "=r"(s.state), "=f"(s.bsdfPdf) : "l"(p) : "memory");
+    return s;
+}
+DEV void stState(PathState* p, const PathState& s) {
+    asm volatile("st.global.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 :: "l"(p), "r"(s.rng1), "r"(s.rng2), "f"(s.thrX), "f"(s.thrY), "f"(s.thrZ), "f"(s.eta), "r"(s.state), "f"(s.bsdfPdf) : "memory");
 }
 
 // launch-index bookkeeping shared by raygen / gather / finalize ------------------------------------------------
@@ -81,9 +99,9 @@ raygenKernel(FrameParams F, PassParams P, int k0, int k1, PathPool pool, Queues 
                 unsigned seed = lcgSkip(L.seed0, 2 * (int)k);
                 Rng r;  r.seed(seed);                                             // prd.rand = Random(seed), :445
                 const float3 dir = primaryDir(F, L, seed);
-                pool.rng[slot] = make_uint2(r.s1, r.s2);
-                pool.thr[slot] = make_float4(1.f, 1.f, 1.f, 1.f);                  // throughput 1, rayEta 1 (:447-448)
-                pool.state[slot] = 0;
+                PathState st;                                                     // throughput 1, rayEta 1 (:447-448), depth 0, no flags
+                st.rng1 = r.s1;  st.rng2 = r.s2;  st.thrX = st.thrY = st.thrZ = 1.f;  st.eta = 1.f;  st.state = 0;  st.bsdfPdf = 0.f;
+                stState(pool.st + slot, st);
                 pool.direct[slot] = make_float4(0, 0, 0, 0);
                 pool.indirect[slot] = make_float4(0, 0, 0, 0);
                 pool.alpha[slot] = make_float4(0, 0, 0, 0);
@@ -119,9 +137,11 @@ DEV float3 sampleTexture(const SceneDev& S, const MeshInfo* M, float s, float t)
     return f3(out[0], out[1], out[2]);
 }
 
+// One thread per entry of the hit queue trace launch `launch` produced (every entry is a surface hit; with mis_on_miss the rays
+// that left the scene are queued too, triSlot < 0).
 __global__ void __launch_bounds__(SHADE_BLOCK, SHADE_MIN_BLOCKS)
 shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int launch) {
-    const unsigned count = Q.counters[QC_STRIDE * launch + QC_RAYS];
+    const unsigned count = Q.counters[QC_STRIDE * launch + QC_HITS];
     const int nxt = cur ^ 1;
     unsigned* nextCounter = Q.counters + QC_STRIDE * (launch + 1) + QC_RAYS;
     unsigned* shadowCounter = Q.counters + QC_STRIDE * (launch + 1) + QC_SHADOWS;
@@ -129,24 +149,23 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
     for (unsigned base = blockIdx.x * blockDim.x; base < count; base += stride) {
         const unsigned i = base + threadIdx.x;
         bool wantRay = false, wantShadow = false;
-        float4 ro = make_float4(0, 0, 0, 0), rd = ro, so = ro, sd = ro;
+        float4 po = make_float4(0, 0, 0, 0), rd = po, sd = po, sp = po;     // po = {P, slot}: origin record of both the continuation and the shadow ray
         if (i < count) {
-            const float4 o4 = Q.rayO[cur][i], d4 = Q.rayD[cur][i], h = Q.hit[i];
+            const float4 o4 = Q.hitA[i], d4 = Q.hitB[i], h = Q.hitC[i];      // {o, slot} {d, t} {u, v, triSlot, -}
             const unsigned slot = (unsigned)__float_as_int(o4.w);
-            const int triSlot = __float_as_int(h.w);
-            int st = pool.state[slot];
-            int depth = st & 0xff, flags = st >> 8;
+            const int triSlot = __float_as_int(h.z);
+            PathState st = ldState(pool.st + slot);
+            int depth = st.state & 0xff, flags = st.state >> 8;
             const int segDepth = depth;                                           // prd.depth while this segment is shaded
             const float3 org = f3(o4.x, o4.y, o4.z), dir = f3(d4.x, d4.y, d4.z);
             if (triSlot < 0) {
-                flags |= PF_DONE;                                                 // __miss__radiance, :251-280
+                flags |= PF_DONE;                                                 // __miss__radiance, :251-280 (queued only with mis_on_miss)
                 if (F.misOnMiss && (flags & PF_SECONDARY)) {                      // opt-in extension (:257-267), same rule as oracle/render_core.h
                     const float skyPdf = probePdf(F.probe, dir);
-                    const float bp = pool.bsdfPdf[slot];
+                    const float bp = st.bsdfPdf;
                     const float weight = 0.5f * bp / (0.5f * bp + 0.5f * skyPdf);
                     const float4 sky = probeEval(F.probe, probeDirToUV(dir));
-                    const float4 thr4 = pool.thr[slot];
-                    const float3 add = weight * f3(sky.x, sky.y, sky.z) * f3(thr4.x, thr4.y, thr4.z);
+                    const float3 add = weight * f3(sky.x, sky.y, sky.z) * f3(st.thrX, st.thrY, st.thrZ);
                     float4 acc = pool.indirect[slot];
                     acc.x += add.x;  acc.y += add.y;  acc.z += add.z;
                     pool.indirect[slot] = acc;
@@ -157,11 +176,7 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                 // The probe sample of this vertex (SampleLights, :301-384) depends only on the path's RNG state: start its chain of
                 // dependent table lookups now, while the triangle / mesh / material loads above are still in flight.  The RNG state
                 // is committed further down, only where the reference really draws the sample.
-                const uint2 rs = pool.rng[slot];
-#if SHADE_HOIST_THR
-                const float4 thr4 = pool.thr[slot];                               // issued with the other slot gathers, used far below
-#endif
-                Rng rng;  rng.s1 = rs.x;  rng.s2 = rs.y;
+                Rng rng;  rng.s1 = st.rng1;  rng.s2 = st.rng2;
                 float3 wi, skyColor;  float skyPdf;
                 probeSample(F.probe, F.probeGuide, wi, skyColor, skyPdf, rng);
                 const float3 e1 = f3(ta.w, tb.x, tb.y), e2 = f3(tb.z, tb.w, tc.x);
@@ -171,30 +186,28 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                 const float3 N0 = normalize3(cross3(e1, e2));                     // :603
                 const float3 wo = -dir;
                 const float3 N = N0 * copysignf(1.0f, dot3(wo, N0));              // faceforward, :605
-                const float3 Pp = org + h.x * dir;                                // :609
+                const float3 Pp = org + d4.w * dir;                               // :609
                 const bool catcher = (mat.flags & MATERIAL_FLAG_SHADOW_CATCHER) != 0;
-                if (catcher && (flags & PF_SECONDARY)) {                          // pass-through, :617-622
+                if (catcher && (flags & PF_SECONDARY)) {                          // pass-through, :617-622 (--depth there, ++depth in the raygen loop: depth stays)
                     wantRay = true;
-                    ro = make_float4(Pp.x, Pp.y, Pp.z, o4.w);  rd = d4;
+                    po = make_float4(Pp.x, Pp.y, Pp.z, o4.w);  rd = make_float4(d4.x, d4.y, d4.z, 0.f);
                 } else {
+                    po = make_float4(Pp.x, Pp.y, Pp.z, o4.w);
                     float3 albedo = mat.color;                                    // :625-641
                     if (M->textureID >= 0 && M->hasTexcoord) {
                         const unsigned* ip = reinterpret_cast<const unsigned*>(S.indices + gid);
                         const uint3 id = make_uint3(__ldg(ip), __ldg(ip + 1), __ldg(ip + 2));
                         const float2 t0 = __ldg(S.texcoords + M->firstVertex + id.x), t1 = __ldg(S.texcoords + M->firstVertex + id.y),
                                      t2 = __ldg(S.texcoords + M->firstVertex + id.z);
-                        const float w0 = 1.f - h.y - h.z;
-                        albedo = sampleTexture(S, M, w0 * t0.x + h.y * t1.x + h.z * t2.x, w0 * t0.y + h.y * t1.y + h.z * t2.y);
+                        const float w0 = 1.f - h.x - h.y;
+                        albedo = sampleTexture(S, M, w0 * t0.x + h.x * t1.x + h.y * t2.x, w0 * t0.y + h.x * t1.y + h.y * t2.y);
                     }
                     if (depth == 0 && F.writeAovs) {
                         pool.aovNormal[slot] = make_float4(N.x, N.y, N.z, 0.f);
                         pool.aovAlbedo[slot] = make_float4(albedo.x, albedo.y, albedo.z, 0.f);
                     }
-#if !SHADE_HOIST_THR
-                    const float4 thr4 = pool.thr[slot];
-#endif
-                    float3 T = f3(thr4.x, thr4.y, thr4.z);
-                    float rayEta = thr4.w;
+                    float3 T = f3(st.thrX, st.thrY, st.thrZ);
+                    float rayEta = st.eta;
                     const float outEta = rayEta == 1.0f ? (mat.eta == 0.0f ? 2.0f / (1.0f - sqrtf(0.08f * mat.specular)) - 1.0f : mat.eta) : 1.0f;   // :644-654
                     const bool last = depth >= F.maxDepth;                        // its radiance is dropped at :495
                     // prd.alpha = 1 at every non-catcher hit (:660).  Once it is 1 nothing can change it again (only a PRIMARY catcher hit emits an
@@ -239,7 +252,9 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                             flags |= PF_DONE;
                         } else {
                             if (pdf <= 0.0f) {
-                                flags |= PF_DONE;  valid = false;                 // :679-682: this segment's radiance is dropped
+                                // :679-682: the raygen loop breaks before it adds this segment's prd.radiance (:495-507), so the NEE term is dropped;
+                                // prd.alpha of a catcher hit was already updated by SampleShadow (:663-664) and survives
+                                flags |= PF_DONE;  valid = valid && catcher;
                             } else {
                                 if (!(flags & PF_SECONDARY)) {                    // primary-only emission, :667-669
                                     float4 dacc = pool.direct[slot];
@@ -257,30 +272,30 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                                     if (!(r < p)) rrKill = true;
                                     else T = T / p;
                                 }
-                                pool.thr[slot] = make_float4(T.x, T.y, T.z, rayEta);
-                                pool.rng[slot] = make_uint2(rng.s1, rng.s2);
-                                if (F.misOnMiss) pool.bsdfPdf[slot] = pdf;
+                                st.thrX = T.x;  st.thrY = T.y;  st.thrZ = T.z;  st.eta = rayEta;
+                                st.rng1 = rng.s1;  st.rng2 = rng.s2;
+                                st.bsdfPdf = pdf;
                                 const int nd = depth + 1;
                                 if (rrKill || (nd >= F.maxDepth && (flags & PF_ALPHA_ONE) && !F.misOnMiss)) flags |= PF_DONE;   // roulette, or the next segment could only be dropped
-                                else { wantRay = true;  ro = make_float4(Pp.x, Pp.y, Pp.z, o4.w);  rd = make_float4(bsdfDir.x, bsdfDir.y, bsdfDir.z, 0.f); }
+                                else { wantRay = true;  rd = make_float4(bsdfDir.x, bsdfDir.y, bsdfDir.z, 0.f); }
                                 depth = nd;
                             }
                         }
                         if (valid) {
                             // target: 0 = directLight (:502-504), 1 = indirectLight, 2 = alpha if OCCLUDED (SampleShadow, :663-664)
                             wantShadow = true;
-                            pool.pending[slot] = make_float4(pend.x, pend.y, pend.z, 0.f);
                             const int target = catcher ? 2 : (segDepth == 0 ? 0 : 1);
-                            so = make_float4(Pp.x, Pp.y, Pp.z, o4.w);
                             sd = make_float4(wi.x, wi.y, wi.z, __int_as_float(target));
+                            sp = make_float4(pend.x, pend.y, pend.z, 0.f);
                         }
                     }
                 }
             }
-            pool.state[slot] = (depth & 0xff) | (flags << 8);
+            st.state = (depth & 0xff) | (flags << 8);
+            stState(pool.st + slot, st);
         }
-        enqueueRay(wantRay, ro, rd, Q.rayO[nxt], Q.rayD[nxt], nextCounter);
-        enqueueRay(wantShadow, so, sd, Q.shO, Q.shD, shadowCounter);
+        enqueueRay(wantRay, po, rd, Q.rayO[nxt], Q.rayD[nxt], nextCounter);
+        enqueueShadow(wantShadow, po, sd, sp, Q, shadowCounter);
     }
 }
 
@@ -494,13 +509,13 @@ void launchProbeCdf(const float4* data, int W, int H, float* pdfX, float* cdfX, 
 
 // ---- launchers ---------------------------------------------------------------------------------------------
 static inline unsigned gridFor(unsigned n) { return (n + SHADE_BLOCK - 1) / SHADE_BLOCK; }
-static const unsigned kPersistentGrid = B200PT_NUM_SMS * SHADE_MIN_BLOCKS;
+static inline unsigned persistentGrid() { return (unsigned)numSMs() * SHADE_MIN_BLOCKS; }
 
 void launchRaygen(const FrameParams& F, const PassParams& P, int k0, int k1, const PathPool& pool, const Queues& Q, cudaStream_t s) {
-    raygenKernel<<<kPersistentGrid, SHADE_BLOCK, 0, s>>>(F, P, k0, k1, pool, Q);
+    raygenKernel<<<persistentGrid(), SHADE_BLOCK, 0, s>>>(F, P, k0, k1, pool, Q);
 }
 void launchShade(const FrameParams& F, const SceneDev& scene, const PathPool& pool, const Queues& Q, int cur, int depth, cudaStream_t s) {
-    shadeKernel<<<kPersistentGrid, SHADE_BLOCK, 0, s>>>(F, scene, pool, Q, cur, depth);
+    shadeKernel<<<persistentGrid(), SHADE_BLOCK, 0, s>>>(F, scene, pool, Q, cur, depth);
 }
 void launchGather(const FrameParams& F, const PassParams& P, int k0, int k1, const PathPool& pool, float4* sumRad, float4* sumAlpha,
                   float4* sumNormal, float4* sumAlbedo, cudaStream_t s) {
@@ -537,55 +552,57 @@ __global__ void whittedRaygenKernel(WhittedParams P, float4* __restrict__ rayO, 
     const float3 dir = normalize3(P.direction + (sx - 0.5f) * P.horizontal + (sy - 0.5f) * P.vertical);    // :217-219
     rayO[i] = make_float4(P.position.x, P.position.y, P.position.z, __int_as_float((int)i));
     rayD[i] = make_float4(dir.x, dir.y, dir.z, 0.f);
-    pool.direct[i] = make_float4(0.f, 0.f, 0.f, 0.f);               // lightVisibility (:145): the shadow trace adds `pending` = 1 when unoccluded
-    pool.pending[i] = make_float4(1.f, 1.f, 1.f, 0.f);
+    pool.direct[i] = make_float4(0.f, 0.f, 0.f, 0.f);               // lightVisibility (:145): the shadow trace adds the ray's contribution (1) when unoccluded
+    PathState st;                                                   // __miss__radiance (:172-175) until a hit says otherwise: eta < 0 marks "no surface"
+    st.rng1 = st.rng2 = 0u;  st.thrX = st.thrY = st.thrZ = 0.f;  st.eta = -1.0f;  st.state = 0;  st.bsdfPdf = 0.f;
+    stState(pool.st + i, st);
 }
-// __closesthit__radiance up to the shadow trace (:66-165); parks diffuseColor and cosDN in pool.thr for the finish kernel
+// __closesthit__radiance up to the shadow trace (:66-165); parks diffuseColor and cosDN in the pixel's path record for the finish kernel
 __global__ void __launch_bounds__(SHADE_BLOCK)
-whittedShadeKernel(WhittedParams P, SceneDev S, PathPool pool, Queues Q, unsigned* shadowCounter) {
-    const unsigned n = (unsigned)P.W * (unsigned)P.H;
+whittedShadeKernel(WhittedParams P, SceneDev S, PathPool pool, Queues Q, const unsigned* hitCounter, unsigned* shadowCounter) {
+    const unsigned n = *hitCounter;
     const unsigned stride = gridDim.x * blockDim.x;
     for (unsigned base = blockIdx.x * blockDim.x; base < n; base += stride) {
-        const unsigned i = base + threadIdx.x;
+        const unsigned k = base + threadIdx.x;
         bool wantShadow = false;
         float4 so = make_float4(0, 0, 0, 0), sd = so;
-        if (i < n) {
-            const float4 d4 = Q.rayD[0][i], h = Q.hit[i];
-            const int triSlot = __float_as_int(h.w);
-            if (triSlot < 0) pool.thr[i] = make_float4(0.f, 0.f, 0.f, -1.0f);                            // __miss__radiance (:172-175)
-            else {
-                const float4 tc = __ldg(S.tris + 3 * (size_t)triSlot + 2);
-                const unsigned gid = (unsigned)__float_as_int(tc.y);
-                const MeshInfo* M = S.meshes + __float_as_int(tc.z);
-                const unsigned* ip = reinterpret_cast<const unsigned*>(S.indices + gid);
-                const uint3 id = make_uint3(__ldg(ip), __ldg(ip + 1), __ldg(ip + 2));
-                const float u = h.y, v = h.z, w0 = 1.f - u - v;
-                const float3 A = S.vertices[M->firstVertex + id.x], B = S.vertices[M->firstVertex + id.y], C = S.vertices[M->firstVertex + id.z];
-                float3 Ng = cross3(B - A, C - A);                                                       // :85
-                float3 Ns = M->hasNormal ? (w0 * S.normals[M->firstVertex + id.x] + u * S.normals[M->firstVertex + id.y]
-                                            + v * S.normals[M->firstVertex + id.z]) : Ng;               // :86-90
-                const float3 rayDir = f3(d4.x, d4.y, d4.z);
-                if (dot3(rayDir, Ng) > 0.f) Ng = -Ng;                                                   // :97-102
-                Ng = normalize3(Ng);
-                if (dot3(Ng, Ns) < 0.f) Ns = Ns - 2.f * dot3(Ng, Ns) * Ng;
-                Ns = normalize3(Ns);
-                float3 diffuse = M->material.color;                                                     // sbtData.color (:108)
-                if (M->textureID >= 0 && M->hasTexcoord) {                                              // :109-116
-                    const float2 t0 = __ldg(S.texcoords + M->firstVertex + id.x), t1 = __ldg(S.texcoords + M->firstVertex + id.y),
-                                 t2 = __ldg(S.texcoords + M->firstVertex + id.z);
-                    diffuse = diffuse * sampleTexture(S, M, w0 * t0.x + u * t1.x + v * t2.x, w0 * t0.y + u * t1.y + v * t2.y);
-                }
-                const float3 surfPos = w0 * A + u * B + v * C;                                          // :121-124
-                const float3 lightDir = P.lightPos - surfPos;                                           // :125-126
-                const float cosDN = 0.1f + .8f * fabsf(dot3(rayDir, Ns));                               // :158-160
-                pool.thr[i] = make_float4(diffuse.x, diffuse.y, diffuse.z, cosDN);
-                const float3 o = surfPos + 1e-3f * Ng;                                                  // :134
-                wantShadow = true;
-                so = make_float4(o.x, o.y, o.z, __int_as_float((int)i));
-                sd = make_float4(lightDir.x, lightDir.y, lightDir.z, __int_as_float(0));                // target 0: pool.direct
+        if (k < n) {
+            const float4 o4 = Q.hitA[k], d4 = Q.hitB[k], h = Q.hitC[k];
+            const unsigned i = (unsigned)__float_as_int(o4.w);                                         // pixel = path slot
+            const int triSlot = __float_as_int(h.z);
+            const float4 tc = __ldg(S.tris + 3 * (size_t)triSlot + 2);
+            const unsigned gid = (unsigned)__float_as_int(tc.y);
+            const MeshInfo* M = S.meshes + __float_as_int(tc.z);
+            const unsigned* ip = reinterpret_cast<const unsigned*>(S.indices + gid);
+            const uint3 id = make_uint3(__ldg(ip), __ldg(ip + 1), __ldg(ip + 2));
+            const float u = h.x, v = h.y, w0 = 1.f - u - v;
+            const float3 A = S.vertices[M->firstVertex + id.x], B = S.vertices[M->firstVertex + id.y], C = S.vertices[M->firstVertex + id.z];
+            float3 Ng = cross3(B - A, C - A);                                                       // :85
+            float3 Ns = M->hasNormal ? (w0 * S.normals[M->firstVertex + id.x] + u * S.normals[M->firstVertex + id.y]
+                                        + v * S.normals[M->firstVertex + id.z]) : Ng;               // :86-90
+            const float3 rayDir = f3(d4.x, d4.y, d4.z);
+            if (dot3(rayDir, Ng) > 0.f) Ng = -Ng;                                                   // :97-102
+            Ng = normalize3(Ng);
+            if (dot3(Ng, Ns) < 0.f) Ns = Ns - 2.f * dot3(Ng, Ns) * Ng;
+            Ns = normalize3(Ns);
+            float3 diffuse = M->material.color;                                                     // sbtData.color (:108)
+            if (M->textureID >= 0 && M->hasTexcoord) {                                              // :109-116
+                const float2 t0 = __ldg(S.texcoords + M->firstVertex + id.x), t1 = __ldg(S.texcoords + M->firstVertex + id.y),
+                             t2 = __ldg(S.texcoords + M->firstVertex + id.z);
+                diffuse = diffuse * sampleTexture(S, M, w0 * t0.x + u * t1.x + v * t2.x, w0 * t0.y + u * t1.y + v * t2.y);
             }
+            const float3 surfPos = w0 * A + u * B + v * C;                                          // :121-124
+            const float3 lightDir = P.lightPos - surfPos;                                           // :125-126
+            const float cosDN = 0.1f + .8f * fabsf(dot3(rayDir, Ns));                               // :158-160
+            PathState st;
+            st.rng1 = st.rng2 = 0u;  st.thrX = diffuse.x;  st.thrY = diffuse.y;  st.thrZ = diffuse.z;  st.eta = cosDN;  st.state = 0;  st.bsdfPdf = 0.f;
+            stState(pool.st + i, st);
+            const float3 o = surfPos + 1e-3f * Ng;                                                  // :134
+            wantShadow = true;
+            so = make_float4(o.x, o.y, o.z, __int_as_float((int)i));
+            sd = make_float4(lightDir.x, lightDir.y, lightDir.z, __int_as_float(0));                // target 0: pool.direct
         }
-        enqueueRay(wantShadow, so, sd, Q.shO, Q.shD, shadowCounter);
+        enqueueShadow(wantShadow, so, sd, make_float4(1.f, 1.f, 1.f, 0.f), Q, shadowCounter);
     }
 }
 // the rest of __closesthit__radiance (:162-163) and the raygen epilogue (:232-242)
@@ -593,12 +610,12 @@ __global__ void whittedFinishKernel(WhittedParams P, PathPool pool, uint32_t* __
     const unsigned n = (unsigned)P.W * (unsigned)P.H;
     const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const float4 t = pool.thr[i];
+    const PathState t = ldState(pool.st + i);
     float3 prd = f3(0.f);
-    if (t.w >= 0.f) {
+    if (t.eta >= 0.f) {
         const float4 vis4 = pool.direct[i];
         const float3 vis = f3(vis4.x, vis4.y, vis4.z);
-        prd = (f3(.1f) + (f3(.2f) + .8f * vis) * t.w) * f3(t.x, t.y, t.z);
+        prd = (f3(.1f) + (f3(.2f) + .8f * vis) * t.eta) * f3(t.thrX, t.thrY, t.thrZ);
     }
     const int r = (int)(255.99f * prd.x), g = (int)(255.99f * prd.y), b = (int)(255.99f * prd.z);
     colorBuffer[i] = 0xff000000u | ((unsigned)r << 0) | ((unsigned)g << 8) | ((unsigned)b << 16);
@@ -607,8 +624,8 @@ void launchWhittedRaygen(const WhittedParams& P, const Queues& Q, const PathPool
     const unsigned n = (unsigned)P.W * (unsigned)P.H;
     whittedRaygenKernel<<<gridFor(n), SHADE_BLOCK, 0, s>>>(P, Q.rayO[0], Q.rayD[0], pool, counters);
 }
-void launchWhittedShade(const WhittedParams& P, const SceneDev& scene, const PathPool& pool, const Queues& Q, unsigned* shadowCounter, cudaStream_t s) {
-    whittedShadeKernel<<<kPersistentGrid, SHADE_BLOCK, 0, s>>>(P, scene, pool, Q, shadowCounter);
+void launchWhittedShade(const WhittedParams& P, const SceneDev& scene, const PathPool& pool, const Queues& Q, const unsigned* hitCounter, unsigned* shadowCounter, cudaStream_t s) {
+    whittedShadeKernel<<<persistentGrid(), SHADE_BLOCK, 0, s>>>(P, scene, pool, Q, hitCounter, shadowCounter);
 }
 void launchWhittedFinish(const WhittedParams& P, const PathPool& pool, uint32_t* colorBuffer, cudaStream_t s) {
     const unsigned n = (unsigned)P.W * (unsigned)P.H;

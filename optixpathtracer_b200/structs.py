@@ -127,7 +127,7 @@ class Config(C.Structure):
         ("accumulate", C.c_int), ("inner_radius", C.c_int), ("outer_radius", C.c_int),
         ("launch_w", C.c_int), ("launch_h", C.c_int), ("write_aovs", C.c_int), ("increment_subframe", C.c_int),
         ("accum_mode", C.c_int), ("russian_roulette", C.c_int), ("tile_rank", C.c_int), ("tile_count", C.c_int),
-        ("profile", C.c_int), ("mis_on_miss", C.c_int), ("shadow_tmin", C.c_float), ("frames_in_flight", C.c_int), ("reserved", C.c_int * 1),
+        ("profile", C.c_int), ("mis_on_miss", C.c_int), ("shadow_tmin", C.c_float), ("frames_in_flight", C.c_int), ("intra_frame_split", C.c_int),
     ]
 
 

@@ -77,7 +77,9 @@ def test_bvh_structure(sponza_small):
         rec, plo, phi = stack.pop()
         for k in range(2):
             lo, hi = boxes(rec, k)
-            assert np.all(lo >= plo - 1e-9) or True          # parents are quantised independently: containment is checked via triangles
+            # parents and children are quantised independently (floor/ceil + 2 cells of padding each), so a child box may stick out of
+            # its parent's by a few cells at most; exact containment is checked via the triangles below
+            assert np.all(lo >= plo - 6.0 / gs) and np.all(hi <= phi + 6.0 / gs)
             l = int(link[rec, k])
             if l < 0:
                 c = -(l + 1)
@@ -323,7 +325,8 @@ def test_render_is_deterministic_and_progressive(sponza_small):
         r.render()
     assert r.launchParams.frame.subframe_index == 4
     b = r.downloadAccum()
-    assert np.isfinite(b).all() and b[..., :3].max() <= 10.0 + 1e-3 or True
+    # sub-frame 0 is stored unclamped, every later one is clamped to 10 before the lerp (sv4/deviceProgram.cu:545-552)
+    assert np.isfinite(b).all() and b[..., :3].max() <= max(10.0, float(a[..., :3].max())) + 1e-3
     r.close()
 
 
