@@ -178,6 +178,20 @@ int b200pt_trace_primary(b200pt_ctx* ctx, const struct LaunchParams* params, con
 int b200pt_trace_rays(b200pt_ctx* ctx, const float* origin_xyz, const float* dir_xyz, size_t n,
                       float tmin, float tmax, int any_hit, int shadow_mode,
                       int32_t* prim, int32_t* mesh, float* t, float* u, float* v);
+/* Device-level known-answer hooks for the shading library, on caller-supplied inputs (n items each; float3 arrays are n*3 floats):
+ * BasisFromVector(N) (sv4/maths.h:94-108); BSDFSample with a fresh Random(seeds[i]) (sv4/Disney.cuh:197-315: direction, pdf, lobe type and the
+ * generator's state afterwards - the number of draws is data dependent); BSDFEval / BSDFPdf for the given L (:318-427, :152-193).
+ * These run the very functions shadeKernel inlines, so a lobe-selection or pdf bug shows up here item by item instead of hiding in an image. */
+int b200pt_debug_bsdf(b200pt_ctx* ctx, size_t n, const struct Material* materials, const float* etaI, const float* etaO,
+                      const float* N_xyz, const float* view_xyz, const float* L_xyz, const float* albedo_rgb, const uint32_t* seeds,
+                      float* basisU_xyz, float* basisV_xyz, float* sampleL_xyz, float* samplePdf, int32_t* sampleType, uint32_t* sampleRng_2,
+                      float* evalF_rgb, float* evalPdf);
+/* ProbeSample with a fresh Random(seeds[i]) (sv4/Probe.cuh:138-169) on the probe in *params (b200pt_set_probe*): use_guide != 0 searches the
+ * CDFs through the guide tables (what render() does), 0 with the reference's plain LowerBound (:119-136) - both must return the same texel;
+ * and ProbeDirToUV / ProbeEval / ProbePdf (:38-46, :61-67, :69-93) of m given directions. */
+int b200pt_debug_probe(b200pt_ctx* ctx, const struct LaunchParams* params, int use_guide, size_t n, const uint32_t* seeds,
+                       float* sampleDir_xyz, float* sampleColor_rgb, float* samplePdf,
+                       size_t m, const float* dirs_xyz, float* uv, float* evalColor_rgb, float* evalPdf);
 /* Integer BVH-build stages, bit-exact against a host reference: 63-bit Morton code (21 bits/axis) per
  * global triangle (input order) and the stable radix-sort permutation.  scene_bounds = 6 floats (lo xyz, hi xyz). */
 int b200pt_debug_morton(b200pt_ctx* ctx, uint64_t* codes, uint32_t* sorted_order, float* scene_bounds);

@@ -15,7 +15,7 @@ SYMBOLS = [
     "b200pt_render_whitted", "b200pt_render_async", "b200pt_synchronize", "b200pt_join", "b200pt_download_pixels", "b200pt_download_pixels_async", "b200pt_download_accum",
     "b200pt_upload_accum", "b200pt_download_aov", "b200pt_device_buffers", "b200pt_resolve_sum", "b200pt_clear_accum",
     "b200pt_tonemap_sqrt", "b200pt_tonemap_sqrt_host", "b200pt_trace_primary", "b200pt_trace_rays",
-    "b200pt_debug_morton", "b200pt_bvh_info_get", "b200pt_download_bvh", "b200pt_download_bvh4", "b200pt_get_counters",
+    "b200pt_debug_bsdf", "b200pt_debug_probe", "b200pt_debug_morton", "b200pt_bvh_info_get", "b200pt_download_bvh", "b200pt_download_bvh4", "b200pt_get_counters",
     "computeFinalPixelColors",
 ]
 
@@ -69,6 +69,8 @@ def lib():
     L.b200pt_trace_primary.argtypes = [vp, C.POINTER(LaunchParams), C.POINTER(Config), vp, vp, vp, vp, vp]
     L.b200pt_trace_rays.argtypes = [vp, vp, vp, C.c_size_t, f32, f32, i32, i32, vp, vp, vp, vp, vp]
     L.b200pt_debug_morton.argtypes = [vp, vp, vp, vp]
+    L.b200pt_debug_bsdf.argtypes = [vp, C.c_size_t] + [vp] * 16
+    L.b200pt_debug_probe.argtypes = [vp, C.POINTER(LaunchParams), i32, C.c_size_t, vp, vp, vp, vp, C.c_size_t, vp, vp, vp, vp]
     L.b200pt_bvh_info_get.argtypes = [vp, C.POINTER(BvhInfo)]
     L.b200pt_download_bvh.argtypes = [vp, vp, C.c_size_t, vp, C.c_size_t]
     L.b200pt_get_counters.argtypes = [vp, C.POINTER(Counters)]

@@ -31,7 +31,7 @@ struct Lane {
     cudaStream_t stream = nullptr;
     size_t poolCap = 0;
     DevBuf<PathState> st;  DevBuf<float4> direct, indirect, alpha, aovN, aovA;
-    DevBuf<float4> rayO[2], rayD[2], hitA, hitB, hitC, shO, shD, shP;
+    DevBuf<float4> rayO[2], rayD[2], hit, shO, shD, shP;
     DevBuf<unsigned> counters;          // QC_COUNT queue counters + 8 running totals
     DevBuf<float4> sumRad, sumAlpha, sumNormal, sumAlbedo;
     DevBuf<TraceStats> stats;           // [0] closest, [1] any
@@ -41,7 +41,7 @@ struct Lane {
     void release() {
         st.release();  direct.release();  indirect.release();  alpha.release();  aovN.release();  aovA.release();
         for (int i = 0; i < 2; ++i) { rayO[i].release();  rayD[i].release(); }
-        hitA.release();  hitB.release();  hitC.release();  shO.release();  shD.release();  shP.release();  counters.release();
+        hit.release();  shO.release();  shD.release();  shP.release();  counters.release();
         sumRad.release();  sumAlpha.release();  sumNormal.release();  sumAlbedo.release();  stats.release();
         poolCap = 0;
     }

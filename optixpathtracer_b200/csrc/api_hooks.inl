@@ -168,6 +168,61 @@ int b200pt_trace_rays(b200pt_ctx* c, const float* org, const float* dir, size_t 
     API_END
 }
 
+// Device-level known-answer hooks for the shading library (tests/golden/bsdf.npz, probe.npz): host arrays in, host arrays out.
+int b200pt_debug_bsdf(b200pt_ctx* c, size_t n, const Material* materials, const float* etaI, const float* etaO, const float* N, const float* view,
+                      const float* L, const float* albedo, const uint32_t* seeds, float* basisU, float* basisV, float* sampleL, float* samplePdf,
+                      int32_t* sampleType, uint32_t* sampleRng, float* evalF, float* evalPdf) {
+    if (!c || (n && (!materials || !etaI || !etaO || !N || !view || !L || !albedo || !seeds || !basisU || !basisV || !sampleL || !samplePdf || !sampleType || !sampleRng || !evalF || !evalPdf)))
+        return fail("b200pt_debug_bsdf: null argument");
+    API_BEGIN
+    if (!n) return 0;
+    enterCtx(c);
+    cudaStream_t s = c->stream;
+    DevBuf<Material> dm;  DevBuf<float> dEtaI, dEtaO, dPdf, dEvalPdf;  DevBuf<float3> dN, dView, dL, dAlb, dU, dV, dSL, dF;  DevBuf<unsigned> dSeeds;  DevBuf<int> dType;  DevBuf<uint2> dRng;
+    dm.ensure(n);  dEtaI.ensure(n);  dEtaO.ensure(n);  dPdf.ensure(n);  dEvalPdf.ensure(n);  dN.ensure(n);  dView.ensure(n);  dL.ensure(n);  dAlb.ensure(n);
+    dU.ensure(n);  dV.ensure(n);  dSL.ensure(n);  dF.ensure(n);  dSeeds.ensure(n);  dType.ensure(n);  dRng.ensure(n);
+    auto up = [&](void* d, const void* h, size_t bytes) { CUDA_OK(cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, s)); };
+    auto down = [&](void* h, const void* d, size_t bytes) { CUDA_OK(cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, s)); };
+    up(dm.p, materials, n * sizeof(Material));  up(dEtaI.p, etaI, 4 * n);  up(dEtaO.p, etaO, 4 * n);  up(dN.p, N, 12 * n);  up(dView.p, view, 12 * n);
+    up(dL.p, L, 12 * n);  up(dAlb.p, albedo, 12 * n);  up(dSeeds.p, seeds, 4 * n);
+    launchDebugBsdf((unsigned)n, dm.p, dEtaI.p, dEtaO.p, dN.p, dView.p, dL.p, dAlb.p, dSeeds.p, dU.p, dV.p, dSL.p, dPdf.p, dType.p, dRng.p, dF.p, dEvalPdf.p, s);
+    CUDA_OK(cudaGetLastError());
+    down(basisU, dU.p, 12 * n);  down(basisV, dV.p, 12 * n);  down(sampleL, dSL.p, 12 * n);  down(samplePdf, dPdf.p, 4 * n);  down(sampleType, dType.p, 4 * n);
+    down(sampleRng, dRng.p, 8 * n);  down(evalF, dF.p, 12 * n);  down(evalPdf, dEvalPdf.p, 4 * n);
+    CUDA_OK(cudaStreamSynchronize(s));
+    dm.release();  dEtaI.release();  dEtaO.release();  dPdf.release();  dEvalPdf.release();  dN.release();  dView.release();  dL.release();  dAlb.release();
+    dU.release();  dV.release();  dSL.release();  dF.release();  dSeeds.release();  dType.release();  dRng.release();
+    API_END
+}
+int b200pt_debug_probe(b200pt_ctx* c, const LaunchParams* params, int useGuide, size_t n, const uint32_t* seeds, float* sampleDir, float* sampleColor,
+                       float* samplePdf, size_t m, const float* dirs, float* uv, float* evalColor, float* evalPdf) {
+    if (!c || !params) return fail("b200pt_debug_probe: null argument");
+    if ((n && (!seeds || !sampleDir || !sampleColor || !samplePdf)) || (m && (!dirs || !uv || !evalColor || !evalPdf))) return fail("b200pt_debug_probe: null array");
+    if (!params->probe.data || !params->probe.cdfValuesX) return fail("b200pt_debug_probe: no probe set (call b200pt_set_probe)");
+    API_BEGIN
+    if (!n && !m) return 0;
+    enterCtx(c);
+    cudaStream_t s = c->stream;
+    b200pt_config cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    const FrameParams F = frameOf(*params, cfg, c);                 // resolves the guide tables exactly as render() does
+    if (useGuide && !F.probeGuide) throw std::runtime_error("b200pt_debug_probe: the probe in *params is not the one uploaded by b200pt_set_probe*, no guide tables");
+    DevBuf<unsigned> dSeeds;  DevBuf<float3> dDir, dCol, dDirs, dECol;  DevBuf<float> dPdf, dEPdf;  DevBuf<float2> dUv;
+    dSeeds.ensure(std::max<size_t>(n, 1));  dDir.ensure(std::max<size_t>(n, 1));  dCol.ensure(std::max<size_t>(n, 1));  dPdf.ensure(std::max<size_t>(n, 1));
+    dDirs.ensure(std::max<size_t>(m, 1));  dECol.ensure(std::max<size_t>(m, 1));  dEPdf.ensure(std::max<size_t>(m, 1));  dUv.ensure(std::max<size_t>(m, 1));
+    if (n) CUDA_OK(cudaMemcpyAsync(dSeeds.p, seeds, 4 * n, cudaMemcpyHostToDevice, s));
+    if (m) CUDA_OK(cudaMemcpyAsync(dDirs.p, dirs, 12 * m, cudaMemcpyHostToDevice, s));
+    launchDebugProbe(F.probe, useGuide ? F.probeGuide : nullptr, (unsigned)n, dSeeds.p, dDir.p, dCol.p, dPdf.p, (unsigned)m, dDirs.p, dUv.p, dECol.p, dEPdf.p, s);
+    CUDA_OK(cudaGetLastError());
+    if (n) { CUDA_OK(cudaMemcpyAsync(sampleDir, dDir.p, 12 * n, cudaMemcpyDeviceToHost, s));  CUDA_OK(cudaMemcpyAsync(sampleColor, dCol.p, 12 * n, cudaMemcpyDeviceToHost, s));
+             CUDA_OK(cudaMemcpyAsync(samplePdf, dPdf.p, 4 * n, cudaMemcpyDeviceToHost, s)); }
+    if (m) { CUDA_OK(cudaMemcpyAsync(uv, dUv.p, 8 * m, cudaMemcpyDeviceToHost, s));  CUDA_OK(cudaMemcpyAsync(evalColor, dECol.p, 12 * m, cudaMemcpyDeviceToHost, s));
+             CUDA_OK(cudaMemcpyAsync(evalPdf, dEPdf.p, 4 * m, cudaMemcpyDeviceToHost, s)); }
+    CUDA_OK(cudaStreamSynchronize(s));
+    dSeeds.release();  dDir.release();  dCol.release();  dPdf.release();  dDirs.release();  dECol.release();  dEPdf.release();  dUv.release();
+    API_END
+}
+
 int b200pt_debug_morton(b200pt_ctx* c, uint64_t* codes, uint32_t* order, float* bounds) {
     if (!c || !codes || !order || !bounds) return fail("b200pt_debug_morton: null argument");
     API_BEGIN

@@ -27,7 +27,7 @@ static void ensurePool(Lane& c, size_t slots, bool aovs) {
     if (slots > c.poolCap) {
         c.st.ensure(slots);  c.direct.ensure(slots);  c.indirect.ensure(slots);  c.alpha.ensure(slots);
         for (int i = 0; i < 2; ++i) { c.rayO[i].ensure(slots);  c.rayD[i].ensure(slots); }
-        c.hitA.ensure(slots);  c.hitB.ensure(slots);  c.hitC.ensure(slots);  c.shO.ensure(slots);  c.shD.ensure(slots);  c.shP.ensure(slots);
+        c.hit.ensure(slots);  c.shO.ensure(slots);  c.shD.ensure(slots);  c.shP.ensure(slots);
         c.poolCap = slots;
     }
     if (aovs) { c.aovN.ensure(c.poolCap);  c.aovA.ensure(c.poolCap); }
@@ -38,7 +38,7 @@ static PathPool poolOf(Lane& L) { return PathPool{L.st.p, L.direct.p, L.indirect
 static Queues queuesOf(Lane& L) {
     Queues Q;
     for (int i = 0; i < 2; ++i) { Q.rayO[i] = L.rayO[i].p;  Q.rayD[i] = L.rayD[i].p; }
-    Q.hitA = L.hitA.p;  Q.hitB = L.hitB.p;  Q.hitC = L.hitC.p;  Q.shO = L.shO.p;  Q.shD = L.shD.p;  Q.shP = L.shP.p;  Q.counters = L.counters.p;
+    Q.hit = L.hit.p;  Q.shO = L.shO.p;  Q.shD = L.shD.p;  Q.shP = L.shP.p;  Q.counters = L.counters.p;
     return Q;
 }
 // lane k > 0 gets its stream and `done` event on first use
@@ -227,7 +227,7 @@ static void enqueuePart(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& job, 
         // trace launch d: extension rays of bounce d + the shadow rays shade pass d-1 emitted; launch `bounces` only shadows
         for (int d = 0; d <= bounces; ++d) {
             T.begin(d < bounces ? ST_TRACE : ST_TRACE_TAIL, a, b);
-            launchTrace(S, Q, cur, d < bounces ? 1 : 0, Q.counters + QC_STRIDE * d, cfg.tmin, shadowTmin, cfg.tmax, cullBack, cfg.mis_on_miss, pool, count ? L.stats.p : nullptr, s);
+            launchTrace(S, Q, cur, d < bounces ? 1 : 0, Q.counters + QC_STRIDE * d, cfg.tmin, shadowTmin, cfg.tmax, cullBack, pool, count ? L.stats.p : nullptr, s);
             T.end(b);  ++launches;  ++job.nClosest;
             if (d == bounces) break;
             T.begin(ST_SHADE, a, b);
@@ -459,9 +459,9 @@ int b200pt_render_whitted(b200pt_ctx* c, const b200pt_whitted_params* wp, uint32
     unsigned* c0 = Q.counters;
     unsigned* c1 = Q.counters + QC_STRIDE;
     launchWhittedRaygen(P, Q, pool, c0, s);
-    launchTrace(S, Q, 0, 1, c0, 0.f, 0.f, 1e20f, 0, 0, pool, nullptr, s);                       // closest hits -> hit queue (c0[QC_HITS]); no shadow rays yet
-    launchWhittedShade(P, S, pool, Q, c0 + QC_HITS, c1 + QC_SHADOWS, s);
-    launchTrace(S, Q, 0, 0, c1, 1e-3f, 1e-3f, 1.f - 1e-3f, 0, 0, pool, nullptr, s);             // shadow rays only
+    launchTrace(S, Q, 0, 1, c0, 0.f, 0.f, 1e20f, 0, pool, nullptr, s);                          // closest hits; no shadow rays yet
+    launchWhittedShade(P, S, pool, Q, c1 + QC_SHADOWS, s);
+    launchTrace(S, Q, 0, 0, c1, 1e-3f, 1e-3f, 1.f - 1e-3f, 0, pool, nullptr, s);                // shadow rays only
     launchWhittedFinish(P, pool, deviceColorBuffer ? deviceColorBuffer : (uint32_t*)c->frameBuf.p, s);
     CUDA_OK(cudaGetLastError());
     CUDA_OK(cudaStreamSynchronize(s));

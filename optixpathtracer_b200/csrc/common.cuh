@@ -118,19 +118,21 @@ struct PathPool {                  // path state indexed by sample slot
 };
 
 // Wavefront queues of one frame in flight.
-//   extension rays  rayO {o.xyz, slot} rayD {d.xyz, -}                       double-buffered, written by raygen / shade, read by trace
-//   hits            hitA {o.xyz, slot} hitB {d.xyz, t} hitC {u, v, triSlot, -}   written by traceKernel, densely packed, for the rays that HIT something: a ray
-//                   that leaves the scene retires inside traceKernel (__miss__radiance only sets DONE, sv4/deviceProgram.cu:251-280), so every
-//                   lane of a shade warp has a surface to shade (with mis_on_miss the misses are queued too, triSlot = -1)
+//   extension rays  rayO {o.xyz, slot} rayD {d.xyz, -}      double-buffered, written by raygen / shade, read by trace and shade
+//   hits            hit {t, u, v, triSlot}                  written by traceKernel at the ray's own index (triSlot < 0: the ray left the scene)
 //   shadow rays     shO {P.xyz, slot} shD {wi.xyz, target} shP {T * lightSample, -}: the NEE contribution travels with its occlusion ray
+// The order of the extension-ray queue is inherited from bounce to bounce (a ray's successor is appended in the order of its parent), so the
+// 8x4-pixel tiles of raygen keep neighbouring queue entries close in space at every depth; shadeKernel compacts the hits of a queue segment
+// into dense warps WITHOUT reordering them (a ray that leaves the scene needs no shading: __miss__radiance only sets DONE, sv4/deviceProgram.cu:251-280).
 struct Queues {
     float4* rayO[2];  float4* rayD[2];
-    float4* hitA;  float4* hitB;  float4* hitC;
+    float4* hit;
     float4* shO;  float4* shD;  float4* shP;
     unsigned* counters;                      // per trace launch d: counters[QC_STRIDE*d + QC_*]
 };
-// trace launch d of a frame handles the extension rays of bounce d and the shadow rays emitted by shade pass d-1; it produces the hit queue shade pass d reads
-enum { QC_RAYS = 0, QC_SHADOWS = 1, QC_HEAD = 2, QC_HITS = 3, QC_STRIDE = 4, QC_MAX_LAUNCHES = 208 };
+// trace launch d of a frame handles the extension rays of bounce d and the shadow rays emitted by shade pass d-1; QC_HEAD / QC_SHEAD are the
+// work tickets of trace launch d / shade pass d
+enum { QC_RAYS = 0, QC_SHADOWS = 1, QC_HEAD = 2, QC_SHEAD = 3, QC_STRIDE = 4, QC_MAX_LAUNCHES = 208 };
 
 struct TraceStats { unsigned long long nodes, tris, rays; };
 
@@ -160,7 +162,7 @@ void bvhRefit(const float3* d_vertices, const uint3* d_indices, const unsigned* 
 // trace.cu  (compiled with FMA contraction; the triangle test itself uses explicit _rn intrinsics)
 // ctr = the QC_* counter block of this launch; cur = which extension-ray buffer it reads; closest = 0: shadow rays only (the frame's last launch)
 void launchTrace(const SceneDev& scene, const Queues& Q, int cur, int closest, unsigned* ctr, float tmin, float tminShadow, float tmax, int cullBack,
-                 int emitMisses, const PathPool& pool, TraceStats* stats /* [0] closest, [1] any; nullptr = no counting */, cudaStream_t stream);
+                 const PathPool& pool, TraceStats* stats /* [0] closest, [1] any; nullptr = no counting */, cudaStream_t stream);
 void launchTraceRaysDebug(const SceneDev& scene, const float4* rayO, const float4* rayD, unsigned n, float tmin, float tmax,
                           int anyHit, int cullBack, float4* hitOut, cudaStream_t stream);
 
@@ -176,8 +178,13 @@ void launchFinalize(const FrameParams& F, const PassParams& P, const float4* sum
 void launchResolveSum(const FrameParams& F, int nPasses, cudaStream_t stream);
 struct WhittedParams { int W, H;  float3 position, direction, horizontal, vertical, lightPos; };
 void launchWhittedRaygen(const WhittedParams& P, const Queues& Q, const PathPool& pool, unsigned* counters, cudaStream_t stream);
-void launchWhittedShade(const WhittedParams& P, const SceneDev& scene, const PathPool& pool, const Queues& Q, const unsigned* hitCounter, unsigned* shadowCounter, cudaStream_t stream);
+void launchWhittedShade(const WhittedParams& P, const SceneDev& scene, const PathPool& pool, const Queues& Q, unsigned* shadowCounter, cudaStream_t stream);
 void launchWhittedFinish(const WhittedParams& P, const PathPool& pool, uint32_t* colorBuffer, cudaStream_t stream);
+void launchDebugBsdf(unsigned n, const Material* mats, const float* etaI, const float* etaO, const float3* N, const float3* view, const float3* L,
+                     const float3* albedo, const unsigned* seeds, float3* basisU, float3* basisV, float3* sampleL, float* samplePdf, int* sampleType,
+                     uint2* sampleRng, float3* evalF, float* evalPdf, cudaStream_t stream);
+void launchDebugProbe(const Probe& P, const int* guide, unsigned n, const unsigned* seeds, float3* dir, float3* color, float* pdf, unsigned m,
+                      const float3* dirs, float2* uv, float3* evalColor, float* evalPdf, cudaStream_t stream);
 size_t probeGuideSize(int H);
 void launchProbeGuide(const float* cdfX, const float* cdfY, int W, int H, int* guide, cudaStream_t stream);
 void launchProbeCdf(const float4* data, int W, int H, float* pdfX, float* cdfX, float* pdfY, float* cdfY, float* rowTotal, cudaStream_t stream);

@@ -37,15 +37,30 @@ DEV void enqueueShadow(bool want, float4 o, float4 d, float4 p, const Queues& Q,
 }
 
 // the 32-byte path record as one 256-bit access (sm_100: LDG.E.256 / STG.E.256)
+#ifndef SHADE_STATE_PLAIN
+#define SHADE_STATE_PLAIN 0
+#endif
 DEV PathState ldState(const PathState* p) {
     PathState s;
+#if SHADE_STATE_PLAIN
+    const uint4 a = *reinterpret_cast<const uint4*>(p), b = *(reinterpret_cast<const uint4*>(p) + 1);
+    s.rng1 = a.x;  s.rng2 = a.y;  s.thrX = __uint_as_float(a.z);  s.thrY = __uint_as_float(a.w);
+    s.thrZ = __uint_as_float(b.x);  s.eta = __uint_as_float(b.y);  s.state = (int)b.z;  s.bsdfPdf = __uint_as_float(b.w);
+#else
     asm volatile("ld.global.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=r"(s.rng1), "=r"(s.rng2), "=f"(s.thrX), "=f"(s.thrY), "=f"(s.thrZ), "=f"(s.eta), "=r"(s.state), "=f"(s.bsdfPdf) : "l"(p) : "memory");
+#endif
     return s;
 }
 DEV void stState(PathState* p, const PathState& s) {
+#if SHADE_STATE_PLAIN
+    uint4* q = reinterpret_cast<uint4*>(p);
+    q[0] = make_uint4(s.rng1, s.rng2, __float_as_uint(s.thrX), __float_as_uint(s.thrY));
+    q[1] = make_uint4(__float_as_uint(s.thrZ), __float_as_uint(s.eta), (unsigned)s.state, __float_as_uint(s.bsdfPdf));
+#else
     asm volatile("st.global.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
                  :: "l"(p), "r"(s.rng1), "r"(s.rng2), "f"(s.thrX), "f"(s.thrY), "f"(s.thrZ), "f"(s.eta), "r"(s.state), "f"(s.bsdfPdf) : "memory");
+#endif
 }
 
 // launch-index bookkeeping shared by raygen / gather / finalize ------------------------------------------------
@@ -137,29 +152,74 @@ DEV float3 sampleTexture(const SceneDev& S, const MeshInfo* M, float s, float t)
     return f3(out[0], out[1], out[2]);
 }
 
-// One thread per entry of the hit queue trace launch `launch` produced (every entry is a surface hit; with mis_on_miss the rays
-// that left the scene are queued too, triSlot < 0).
+// Shades the hits of trace launch `launch`.
+// SHADE_COMPACT 0 (default): one lane per queue entry in a static grid-stride loop; the lanes of rays that left the scene idle
+// (__miss__radiance only sets DONE, sv4/deviceProgram.cu:251-280; with mis_on_miss they add the environment term).
+// SHADE_COMPACT 1 (measured, not used): warps take tickets of 32 queue entries and squeeze the rays that hit something into dense groups of
+// 32 with ballots, keeping their queue order; leftovers carry over to the next ticket.  27 % fewer warp-level passes through the Disney code,
+// and yet 1.61 ms per frame against 1.41: the kernel is bound by the latency of its dependent loads (ray -> path record -> probe tables ->
+// triangle -> material), not by issue slots, and the ticket + flag + ballot stage in front of every group lengthens exactly that chain.
+// (A dense hit queue written by traceKernel itself in retirement order was measured too: shade 1.35 ms, but the queue order - and with it the
+// spatial coherence the next bounce's rays inherit - is lost, and traceKernel goes from 2.59 to 2.84 ms.  profiles/README.md, r02a-r02c.)
+#ifndef SHADE_COMPACT
+#define SHADE_COMPACT 0
+#endif
 __global__ void __launch_bounds__(SHADE_BLOCK, SHADE_MIN_BLOCKS)
 shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int launch) {
-    const unsigned count = Q.counters[QC_STRIDE * launch + QC_HITS];
+    const unsigned count = Q.counters[QC_STRIDE * launch + QC_RAYS];
     const int nxt = cur ^ 1;
     unsigned* nextCounter = Q.counters + QC_STRIDE * (launch + 1) + QC_RAYS;
     unsigned* shadowCounter = Q.counters + QC_STRIDE * (launch + 1) + QC_SHADOWS;
+    const float4* __restrict__ rayOq = Q.rayO[cur];
+    const float4* __restrict__ rayDq = Q.rayD[cur];
+#if SHADE_COMPACT
+    __shared__ unsigned list[SHADE_BLOCK / 32][64];
+    unsigned* const head = Q.counters + QC_STRIDE * launch + QC_SHEAD;
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5, ltMask = (1u << lane) - 1u;
+    unsigned fill = 0, ticket = 0;
+    bool more = true;
+    if (lane == 0) ticket = atomicAdd(head, 32u);
+    for (;;) {
+        while (fill < 32u && more) {                                          // append the hits of the next ticket's 32 queue entries, in order
+            const unsigned base = __shfl_sync(0xffffffffu, ticket, 0);
+            if (base >= count) { more = false;  break; }
+            const unsigned j = base + lane;
+            const bool take = j < count && (F.misOnMiss || __float_as_int(Q.hit[j].w) >= 0);
+            if (lane == 0) ticket = atomicAdd(head, 32u);                      // the next ticket is in flight while this group is shaded
+            const unsigned m = __ballot_sync(0xffffffffu, take);
+            if (take) list[warp][fill + __popc(m & ltMask)] = j;
+            fill += __popc(m);
+        }
+        if (fill == 0u) break;
+        __syncwarp();
+        const unsigned n = min(fill, 32u);
+        const bool mine = lane < n;
+        const unsigned i = mine ? list[warp][lane] : 0u;
+        const unsigned carry = (fill > 32u && lane < fill - 32u) ? list[warp][32u + lane] : 0u;
+        __syncwarp();
+        if (fill > 32u && lane < fill - 32u) list[warp][lane] = carry;
+        fill -= n;
+        __syncwarp();
+        {
+#else
     const unsigned stride = gridDim.x * blockDim.x;
     for (unsigned base = blockIdx.x * blockDim.x; base < count; base += stride) {
+        {
         const unsigned i = base + threadIdx.x;
+        const bool mine = i < count;
+#endif
         bool wantRay = false, wantShadow = false;
         float4 po = make_float4(0, 0, 0, 0), rd = po, sd = po, sp = po;     // po = {P, slot}: origin record of both the continuation and the shadow ray
-        if (i < count) {
-            const float4 o4 = Q.hitA[i], d4 = Q.hitB[i], h = Q.hitC[i];      // {o, slot} {d, t} {u, v, triSlot, -}
+        if (mine) {
+            const float4 o4 = rayOq[i], d4 = rayDq[i], h = Q.hit[i];         // {o, slot} {d, -} {t, u, v, triSlot}
             const unsigned slot = (unsigned)__float_as_int(o4.w);
-            const int triSlot = __float_as_int(h.z);
+            const int triSlot = __float_as_int(h.w);
             PathState st = ldState(pool.st + slot);
             int depth = st.state & 0xff, flags = st.state >> 8;
             const int segDepth = depth;                                           // prd.depth while this segment is shaded
             const float3 org = f3(o4.x, o4.y, o4.z), dir = f3(d4.x, d4.y, d4.z);
             if (triSlot < 0) {
-                flags |= PF_DONE;                                                 // __miss__radiance, :251-280 (queued only with mis_on_miss)
+                flags |= PF_DONE;                                                 // __miss__radiance, :251-280 (shaded only with mis_on_miss)
                 if (F.misOnMiss && (flags & PF_SECONDARY)) {                      // opt-in extension (:257-267), same rule as oracle/render_core.h
                     const float skyPdf = probePdf(F.probe, dir);
                     const float bp = st.bsdfPdf;
@@ -186,7 +246,7 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                 const float3 N0 = normalize3(cross3(e1, e2));                     // :603
                 const float3 wo = -dir;
                 const float3 N = N0 * copysignf(1.0f, dot3(wo, N0));              // faceforward, :605
-                const float3 Pp = org + d4.w * dir;                               // :609
+                const float3 Pp = org + h.x * dir;                                // :609
                 const bool catcher = (mat.flags & MATERIAL_FLAG_SHADOW_CATCHER) != 0;
                 if (catcher && (flags & PF_SECONDARY)) {                          // pass-through, :617-622 (--depth there, ++depth in the raygen loop: depth stays)
                     wantRay = true;
@@ -199,8 +259,8 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                         const uint3 id = make_uint3(__ldg(ip), __ldg(ip + 1), __ldg(ip + 2));
                         const float2 t0 = __ldg(S.texcoords + M->firstVertex + id.x), t1 = __ldg(S.texcoords + M->firstVertex + id.y),
                                      t2 = __ldg(S.texcoords + M->firstVertex + id.z);
-                        const float w0 = 1.f - h.x - h.y;
-                        albedo = sampleTexture(S, M, w0 * t0.x + h.x * t1.x + h.y * t2.x, w0 * t0.y + h.x * t1.y + h.y * t2.y);
+                        const float w0 = 1.f - h.y - h.z;
+                        albedo = sampleTexture(S, M, w0 * t0.x + h.y * t1.x + h.z * t2.x, w0 * t0.y + h.y * t1.y + h.z * t2.y);
                     }
                     if (depth == 0 && F.writeAovs) {
                         pool.aovNormal[slot] = make_float4(N.x, N.y, N.z, 0.f);
@@ -296,6 +356,7 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
         }
         enqueueRay(wantRay, po, rd, Q.rayO[nxt], Q.rayD[nxt], nextCounter);
         enqueueShadow(wantShadow, po, sd, sp, Q, shadowCounter);
+        }
     }
 }
 
@@ -540,6 +601,56 @@ void launchResolvePrimary(const SceneDev& scene, const float4* hit, unsigned n, 
     if (n) resolvePrimaryKernel<<<gridFor(n), SHADE_BLOCK, 0, s>>>(scene, hit, n, rayO, prim, mesh, t, u, v);
 }
 
+// ---- parity hooks: the device shading library on caller-supplied inputs (tests/golden/bsdf.npz, probe.npz) -----------------------
+// One thread per item; the same inlined functions shadeKernel calls, in the reference's call order:
+//   BasisFromVector (maths.h:94-108), BSDFSample with a fresh Random(seed) (Disney.cuh:197-315), BSDFEval / BSDFPdf for a given L (:152-193, :318-427).
+__global__ void debugBsdfKernel(unsigned n, const Material* __restrict__ mats, const float* __restrict__ etaI, const float* __restrict__ etaO,
+                                const float3* __restrict__ N, const float3* __restrict__ view, const float3* __restrict__ L, const float3* __restrict__ albedo,
+                                const unsigned* __restrict__ seeds, float3* basisU, float3* basisV, float3* sampleL, float* samplePdf, int* sampleType,
+                                uint2* sampleRng, float3* evalF, float* evalPdf) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const Material mat = mats[i];
+    float3 u, v;
+    basisFromVector(N[i], u, v);
+    basisU[i] = u;  basisV[i] = v;
+    Rng r;  r.seed(seeds[i]);
+    float3 l = f3(0.f);  float pdf = 0.f;  int type = eReflected;
+    bsdfSample(mat, etaI[i], etaO[i], u, v, N[i], view[i], l, pdf, type, r);
+    sampleL[i] = l;  samplePdf[i] = pdf;  sampleType[i] = type;  sampleRng[i] = make_uint2(r.s1, r.s2);
+    evalF[i] = bsdfEval(mat, albedo[i], etaI[i], etaO[i], N[i], view[i], L[i]);
+    evalPdf[i] = bsdfPdf(mat, etaI[i], etaO[i], N[i], view[i], L[i]);
+}
+// ProbeSample with a fresh Random(seed) (Probe.cuh:138-169; guide != nullptr: through the guide tables, as shadeKernel does), and
+// ProbeDirToUV / ProbeEval / ProbePdf of given directions (:38-46, :61-67, :69-93)
+__global__ void debugProbeKernel(Probe P, const int* __restrict__ guide, unsigned n, const unsigned* __restrict__ seeds, float3* dir, float3* color,
+                                 float* pdf, unsigned m, const float3* __restrict__ dirs, float2* uv, float3* evalColor, float* evalPdf) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        Rng r;  r.seed(seeds[i]);
+        float3 d, c;  float q;
+        probeSample(P, guide, d, c, q, r);
+        dir[i] = d;  color[i] = c;  pdf[i] = q;
+    }
+    if (i < m) {
+        const float2 q = probeDirToUV(dirs[i]);
+        uv[i] = q;
+        const float4 c = probeEval(P, q);
+        evalColor[i] = f3(c.x, c.y, c.z);
+        evalPdf[i] = probePdf(P, dirs[i]);
+    }
+}
+void launchDebugBsdf(unsigned n, const Material* mats, const float* etaI, const float* etaO, const float3* N, const float3* view, const float3* L,
+                     const float3* albedo, const unsigned* seeds, float3* basisU, float3* basisV, float3* sampleL, float* samplePdf, int* sampleType,
+                     uint2* sampleRng, float3* evalF, float* evalPdf, cudaStream_t s) {
+    if (n) debugBsdfKernel<<<(n + 127) / 128, 128, 0, s>>>(n, mats, etaI, etaO, N, view, L, albedo, seeds, basisU, basisV, sampleL, samplePdf, sampleType, sampleRng, evalF, evalPdf);
+}
+void launchDebugProbe(const Probe& P, const int* guide, unsigned n, const unsigned* seeds, float3* dir, float3* color, float* pdf, unsigned m,
+                      const float3* dirs, float2* uv, float3* evalColor, float* evalPdf, cudaStream_t s) {
+    const unsigned k = n > m ? n : m;
+    if (k) debugProbeKernel<<<(k + 127) / 128, 128, 0, s>>>(P, guide, n, seeds, dir, color, pdf, m, dirs, uv, evalColor, evalPdf);
+}
+
 // ---- Whitted-style integrator (04HelloRaytracing/deviceProgram.cu:66-243) on the same trace kernels ---------------------------
 // raygen (:196-243): one ray through each pixel centre.  Pixel i is ray i and pool slot i.
 __global__ void whittedRaygenKernel(WhittedParams P, float4* __restrict__ rayO, float4* __restrict__ rayD, PathPool pool, unsigned* counters) {
@@ -559,48 +670,49 @@ __global__ void whittedRaygenKernel(WhittedParams P, float4* __restrict__ rayO, 
 }
 // __closesthit__radiance up to the shadow trace (:66-165); parks diffuseColor and cosDN in the pixel's path record for the finish kernel
 __global__ void __launch_bounds__(SHADE_BLOCK)
-whittedShadeKernel(WhittedParams P, SceneDev S, PathPool pool, Queues Q, const unsigned* hitCounter, unsigned* shadowCounter) {
-    const unsigned n = *hitCounter;
+whittedShadeKernel(WhittedParams P, SceneDev S, PathPool pool, Queues Q, unsigned* shadowCounter) {
+    const unsigned n = (unsigned)P.W * (unsigned)P.H;
     const unsigned stride = gridDim.x * blockDim.x;
     for (unsigned base = blockIdx.x * blockDim.x; base < n; base += stride) {
-        const unsigned k = base + threadIdx.x;
+        const unsigned i = base + threadIdx.x;                                                     // ray i = pixel i = path slot i
         bool wantShadow = false;
         float4 so = make_float4(0, 0, 0, 0), sd = so;
-        if (k < n) {
-            const float4 o4 = Q.hitA[k], d4 = Q.hitB[k], h = Q.hitC[k];
-            const unsigned i = (unsigned)__float_as_int(o4.w);                                         // pixel = path slot
-            const int triSlot = __float_as_int(h.z);
-            const float4 tc = __ldg(S.tris + 3 * (size_t)triSlot + 2);
-            const unsigned gid = (unsigned)__float_as_int(tc.y);
-            const MeshInfo* M = S.meshes + __float_as_int(tc.z);
-            const unsigned* ip = reinterpret_cast<const unsigned*>(S.indices + gid);
-            const uint3 id = make_uint3(__ldg(ip), __ldg(ip + 1), __ldg(ip + 2));
-            const float u = h.x, v = h.y, w0 = 1.f - u - v;
-            const float3 A = S.vertices[M->firstVertex + id.x], B = S.vertices[M->firstVertex + id.y], C = S.vertices[M->firstVertex + id.z];
-            float3 Ng = cross3(B - A, C - A);                                                       // :85
-            float3 Ns = M->hasNormal ? (w0 * S.normals[M->firstVertex + id.x] + u * S.normals[M->firstVertex + id.y]
-                                        + v * S.normals[M->firstVertex + id.z]) : Ng;               // :86-90
-            const float3 rayDir = f3(d4.x, d4.y, d4.z);
-            if (dot3(rayDir, Ng) > 0.f) Ng = -Ng;                                                   // :97-102
-            Ng = normalize3(Ng);
-            if (dot3(Ng, Ns) < 0.f) Ns = Ns - 2.f * dot3(Ng, Ns) * Ng;
-            Ns = normalize3(Ns);
-            float3 diffuse = M->material.color;                                                     // sbtData.color (:108)
-            if (M->textureID >= 0 && M->hasTexcoord) {                                              // :109-116
-                const float2 t0 = __ldg(S.texcoords + M->firstVertex + id.x), t1 = __ldg(S.texcoords + M->firstVertex + id.y),
-                             t2 = __ldg(S.texcoords + M->firstVertex + id.z);
-                diffuse = diffuse * sampleTexture(S, M, w0 * t0.x + u * t1.x + v * t2.x, w0 * t0.y + u * t1.y + v * t2.y);
+        if (i < n) {
+            const float4 d4 = Q.rayD[0][i], h = Q.hit[i];
+            const int triSlot = __float_as_int(h.w);
+            if (triSlot >= 0) {                                                                     // a miss keeps the record whittedRaygen wrote
+                const float4 tc = __ldg(S.tris + 3 * (size_t)triSlot + 2);
+                const unsigned gid = (unsigned)__float_as_int(tc.y);
+                const MeshInfo* M = S.meshes + __float_as_int(tc.z);
+                const unsigned* ip = reinterpret_cast<const unsigned*>(S.indices + gid);
+                const uint3 id = make_uint3(__ldg(ip), __ldg(ip + 1), __ldg(ip + 2));
+                const float u = h.y, v = h.z, w0 = 1.f - u - v;
+                const float3 A = S.vertices[M->firstVertex + id.x], B = S.vertices[M->firstVertex + id.y], C = S.vertices[M->firstVertex + id.z];
+                float3 Ng = cross3(B - A, C - A);                                                       // :85
+                float3 Ns = M->hasNormal ? (w0 * S.normals[M->firstVertex + id.x] + u * S.normals[M->firstVertex + id.y]
+                                            + v * S.normals[M->firstVertex + id.z]) : Ng;               // :86-90
+                const float3 rayDir = f3(d4.x, d4.y, d4.z);
+                if (dot3(rayDir, Ng) > 0.f) Ng = -Ng;                                                   // :97-102
+                Ng = normalize3(Ng);
+                if (dot3(Ng, Ns) < 0.f) Ns = Ns - 2.f * dot3(Ng, Ns) * Ng;
+                Ns = normalize3(Ns);
+                float3 diffuse = M->material.color;                                                     // sbtData.color (:108)
+                if (M->textureID >= 0 && M->hasTexcoord) {                                              // :109-116
+                    const float2 t0 = __ldg(S.texcoords + M->firstVertex + id.x), t1 = __ldg(S.texcoords + M->firstVertex + id.y),
+                                 t2 = __ldg(S.texcoords + M->firstVertex + id.z);
+                    diffuse = diffuse * sampleTexture(S, M, w0 * t0.x + u * t1.x + v * t2.x, w0 * t0.y + u * t1.y + v * t2.y);
+                }
+                const float3 surfPos = w0 * A + u * B + v * C;                                          // :121-124
+                const float3 lightDir = P.lightPos - surfPos;                                           // :125-126
+                const float cosDN = 0.1f + .8f * fabsf(dot3(rayDir, Ns));                               // :158-160
+                PathState st;
+                st.rng1 = st.rng2 = 0u;  st.thrX = diffuse.x;  st.thrY = diffuse.y;  st.thrZ = diffuse.z;  st.eta = cosDN;  st.state = 0;  st.bsdfPdf = 0.f;
+                stState(pool.st + i, st);
+                const float3 o = surfPos + 1e-3f * Ng;                                                  // :134
+                wantShadow = true;
+                so = make_float4(o.x, o.y, o.z, __int_as_float((int)i));
+                sd = make_float4(lightDir.x, lightDir.y, lightDir.z, __int_as_float(0));                // target 0: pool.direct
             }
-            const float3 surfPos = w0 * A + u * B + v * C;                                          // :121-124
-            const float3 lightDir = P.lightPos - surfPos;                                           // :125-126
-            const float cosDN = 0.1f + .8f * fabsf(dot3(rayDir, Ns));                               // :158-160
-            PathState st;
-            st.rng1 = st.rng2 = 0u;  st.thrX = diffuse.x;  st.thrY = diffuse.y;  st.thrZ = diffuse.z;  st.eta = cosDN;  st.state = 0;  st.bsdfPdf = 0.f;
-            stState(pool.st + i, st);
-            const float3 o = surfPos + 1e-3f * Ng;                                                  // :134
-            wantShadow = true;
-            so = make_float4(o.x, o.y, o.z, __int_as_float((int)i));
-            sd = make_float4(lightDir.x, lightDir.y, lightDir.z, __int_as_float(0));                // target 0: pool.direct
         }
         enqueueShadow(wantShadow, so, sd, make_float4(1.f, 1.f, 1.f, 0.f), Q, shadowCounter);
     }
@@ -624,8 +736,8 @@ void launchWhittedRaygen(const WhittedParams& P, const Queues& Q, const PathPool
     const unsigned n = (unsigned)P.W * (unsigned)P.H;
     whittedRaygenKernel<<<gridFor(n), SHADE_BLOCK, 0, s>>>(P, Q.rayO[0], Q.rayD[0], pool, counters);
 }
-void launchWhittedShade(const WhittedParams& P, const SceneDev& scene, const PathPool& pool, const Queues& Q, const unsigned* hitCounter, unsigned* shadowCounter, cudaStream_t s) {
-    whittedShadeKernel<<<persistentGrid(), SHADE_BLOCK, 0, s>>>(P, scene, pool, Q, hitCounter, shadowCounter);
+void launchWhittedShade(const WhittedParams& P, const SceneDev& scene, const PathPool& pool, const Queues& Q, unsigned* shadowCounter, cudaStream_t s) {
+    whittedShadeKernel<<<persistentGrid(), SHADE_BLOCK, 0, s>>>(P, scene, pool, Q, shadowCounter);
 }
 void launchWhittedFinish(const WhittedParams& P, const PathPool& pool, uint32_t* colorBuffer, cudaStream_t s) {
     const unsigned n = (unsigned)P.W * (unsigned)P.H;

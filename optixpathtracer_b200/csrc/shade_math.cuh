@@ -303,8 +303,12 @@ DEV int lowerBound(const float* __restrict__ a, int lower, int upper, float valu
 // for value in [k/G, (k+1)/G) the answer lies in [guide[k], guide[k+1]] and a search of that short range with the SAME comparison
 // returns the SAME index as the reference's search of the whole array (each CDF is non-decreasing) — in ~3 dependent loads
 // instead of log2(n) ~ 10-11.  G is a power of two, so k/G and value*G are exact.
+#ifndef B200PT_GUIDE_Y
 #define B200PT_GUIDE_Y 1024
+#endif
+#ifndef B200PT_GUIDE_X
 #define B200PT_GUIDE_X 256
+#endif
 DEV int guidedLowerBound(const float* __restrict__ a, int base, const int* __restrict__ guide, int G, float value) {
     const int k = min(G - 1, max(0, (int)(value * (float)G)));
     const int lo = __ldg(guide + k), hi = __ldg(guide + k + 1);

@@ -1,6 +1,5 @@
 // b200pt — BVH traversal kernels (replace the closed optixTrace of sv4/deviceProgram.cu:207,232).
-//   RADIANCE rays  — closest hit in (tmin,tmax), ties -> lowest global triangle id; rays that hit are appended, densely packed, to the
-//                    hit queue shadeKernel reads; rays that leave the scene retire here (__miss__radiance only sets DONE, sv4/deviceProgram.cu:251-280)
+//   RADIANCE rays  — closest hit in (tmin,tmax), ties -> lowest global triangle id; the result {t,u,v,triSlot} is written at the ray's own queue index
 //   OCCLUSION rays — any hit (optionally only triangles front-facing the ray), early out;
 //                    visible rays add the NEE contribution that travels with them to the path's radiance accumulator
 // Both kinds are traced by the same launch of traceKernel (one launch per bounce).
@@ -264,7 +263,7 @@ __device__ __forceinline__ void cpAsync16(void* smemDst, const void* gmemSrc) {
 __device__ __forceinline__ void cpAsyncCommit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cpAsyncWaitAll() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
-// One launch traces BOTH queues of a bounce: the extension rays (closest hit -> one 48-byte record in the hit queue) and the
+// One launch traces BOTH queues of a bounce: the extension rays (closest hit -> hit[i] = {t,u,v,triSlot}) and the
 // shadow rays the previous shade pass emitted (any hit; rayO.w = path slot, rayD.w = target: 0 direct, 1 indirect,
 // 2 alpha-when-occluded, see shade.cu).  Work is handed out in chunks of 32 rays by one ticket counter; chunk ids
 // below ceil(countC/32) are extension rays, the rest shadow rays, so the short any-hit rays fill the tail of the
@@ -272,9 +271,9 @@ __device__ __forceinline__ void cpAsyncWaitAll() { asm volatile("cp.async.wait_a
 // while the warp is still traversing the current one.
 template <bool COUNT>
 __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_BLOCKS_PER_SM)
-traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restrict__ rayD, float4* __restrict__ hitA, float4* __restrict__ hitB,
-            float4* __restrict__ hitC, const float4* __restrict__ shO, const float4* __restrict__ shD, const float4* __restrict__ shP,
-            unsigned* ctr, int closest, int emitMisses, float tminC, float tminS, float tmax, int cullBack, PathPool pool,
+traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restrict__ rayD, float4* __restrict__ hit,
+            const float4* __restrict__ shO, const float4* __restrict__ shD, const float4* __restrict__ shP,
+            unsigned* ctr, int closest, float tminC, float tminS, float tmax, int cullBack, PathPool pool,
             TraceStats* stats, int refillThreshold, int leafThreshold, int nodeMin) {
     __shared__ float4 stageO[TRACE_WARPS][2][32], stageD[TRACE_WARPS][2][32];
     const unsigned countC = closest ? ctr[QC_RAYS] : 0u, countS = ctr[QC_SHADOWS];
@@ -292,7 +291,6 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
 
     // per-lane ray state
     bool active = false, isAny = false;
-    bool pendingOut = false;               // a finished radiance ray whose hit record has not been written yet (the lane is idle meanwhile)
     float tmin = tminC;                    // per lane: occlusion rays have their own tmin (0.01 in every variant, also where radiance rays use 0.001)
     unsigned rayIdx = 0;
     float3 o = make_float3(0, 0, 0), d = o;
@@ -326,22 +324,6 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
         // ---------------------------------------------------------------- refill idle lanes (warp-synchronous)
         unsigned idle = __ballot_sync(FULL, !active);
         if (idle == FULL || ((int)__popc(idle) >= refillThreshold && !(pf == 3 && stageNext >= stageEnd))) {
-            // Finished radiance rays keep their hit in registers until the warp refills (>= refillThreshold lanes are idle by then): the
-            // records of all of them go to the hit queue behind ONE atomicAdd, densely packed.
-            const unsigned outMask = __ballot_sync(FULL, pendingOut);
-            if (outMask) {
-                const int leader = __ffs(outMask) - 1;
-                unsigned base = 0;
-                if ((int)lane == leader) base = atomicAdd(ctr + QC_HITS, (unsigned)__popc(outMask));
-                base = __shfl_sync(FULL, base, leader);
-                if (pendingOut) {
-                    const unsigned q = base + __popc(outMask & ltMask);
-                    hitA[q] = make_float4(o.x, o.y, o.z, wO);
-                    hitB[q] = make_float4(d.x, d.y, d.z, best.t);
-                    hitC[q] = make_float4(best.u, best.v, __int_as_float(best.slot), 0.f);
-                    pendingOut = false;
-                }
-            }
 #pragma unroll 1
             for (int round = 0; round < 2 && idle; ++round) {
                 if (stageNext >= stageEnd) {                      // current chunk used up: switch to the prefetched one
@@ -487,8 +469,7 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
             if (!isAny) {
                 // best.u/best.v hold the undivided U, V of the winning triangle: same quotients as dividing at hit time
                 const bool got = best.slot >= 0;
-                best.u = got ? __fdiv_rn(best.u, bestDet) : 0.f;  best.v = got ? __fdiv_rn(best.v, bestDet) : 0.f;
-                pendingOut = got || emitMisses != 0;           // written at the warp's next refill (see above); a miss needs nothing more
+                hit[rayIdx] = make_float4(best.t, got ? __fdiv_rn(best.u, bestDet) : 0.f, got ? __fdiv_rn(best.v, bestDet) : 0.f, __int_as_float(best.slot));
             } else {
                 // prd.radiance += pathThroughput * lightSample (sv4/deviceProgram.cu:659) resolved here.  Target 2 = alpha
                 // when OCCLUDED (shadow catcher, :663-664).  Single writer per slot per launch => deterministic.
@@ -555,10 +536,10 @@ static int leafThreshold() {
 }
 
 void launchTrace(const SceneDev& scene, const Queues& Q, int cur, int closest, unsigned* ctr, float tmin, float tminShadow, float tmax, int cullBack,
-                 int emitMisses, const PathPool& pool, TraceStats* stats, cudaStream_t stream) {
+                 const PathPool& pool, TraceStats* stats, cudaStream_t stream) {
     const dim3 grid((unsigned)numSMs() * TRACE_BLOCKS_PER_SM), block(TRACE_BLOCK);
-    if (stats) traceKernel<true><<<grid, block, 0, stream>>>(scene, Q.rayO[cur], Q.rayD[cur], Q.hitA, Q.hitB, Q.hitC, Q.shO, Q.shD, Q.shP, ctr, closest, emitMisses, tmin, tminShadow, tmax, cullBack, pool, stats, refillThreshold(), leafThreshold(), nodeMinThreshold());
-    else traceKernel<false><<<grid, block, 0, stream>>>(scene, Q.rayO[cur], Q.rayD[cur], Q.hitA, Q.hitB, Q.hitC, Q.shO, Q.shD, Q.shP, ctr, closest, emitMisses, tmin, tminShadow, tmax, cullBack, pool, nullptr, refillThreshold(), leafThreshold(), nodeMinThreshold());
+    if (stats) traceKernel<true><<<grid, block, 0, stream>>>(scene, Q.rayO[cur], Q.rayD[cur], Q.hit, Q.shO, Q.shD, Q.shP, ctr, closest, tmin, tminShadow, tmax, cullBack, pool, stats, refillThreshold(), leafThreshold(), nodeMinThreshold());
+    else traceKernel<false><<<grid, block, 0, stream>>>(scene, Q.rayO[cur], Q.rayD[cur], Q.hit, Q.shO, Q.shD, Q.shP, ctr, closest, tmin, tminShadow, tmax, cullBack, pool, nullptr, refillThreshold(), leafThreshold(), nodeMinThreshold());
 }
 
 void launchTraceRaysDebug(const SceneDev& scene, const float4* rayO, const float4* rayD, unsigned n, float tmin, float tmax,

@@ -245,6 +245,33 @@ class SampleRenderer:
                                              _ptr(prim), _ptr(mesh), _ptr(t), _ptr(u), _ptr(v)))
         return prim, mesh, t, u, v
 
+    def debugBsdf(self, materials, etaI, etaO, N, view, L, albedo, seeds):
+        """Device-level KAT hook: BasisFromVector, BSDFSample (fresh Random(seed)), BSDFEval, BSDFPdf on the given inputs."""
+        from .structs import Material
+        n = len(materials)
+        mats = (Material * n)(*materials)
+        f32 = lambda a: np.ascontiguousarray(a, np.float32)
+        etaI, etaO, N, view, L, albedo = map(f32, (etaI, etaO, N, view, L, albedo))
+        seeds = np.ascontiguousarray(seeds, np.uint32)
+        out = dict(basisU=np.empty((n, 3), np.float32), basisV=np.empty((n, 3), np.float32), sampleL=np.empty((n, 3), np.float32),
+                   samplePdf=np.empty(n, np.float32), sampleType=np.empty(n, np.int32), sampleRng=np.empty((n, 2), np.uint32),
+                   evalF=np.empty((n, 3), np.float32), evalPdf=np.empty(n, np.float32))
+        _lib.check(self._L.b200pt_debug_bsdf(self._h, n, C.cast(mats, C.c_void_p), _ptr(etaI), _ptr(etaO), _ptr(N), _ptr(view), _ptr(L), _ptr(albedo),
+                                             _ptr(seeds), *[_ptr(out[k]) for k in ("basisU", "basisV", "sampleL", "samplePdf", "sampleType", "sampleRng", "evalF", "evalPdf")]))
+        return out
+
+    def debugProbe(self, seeds, dirs, use_guide=True):
+        """Device-level KAT hook on the current probe: ProbeSample (fresh Random(seed)) and ProbeDirToUV / ProbeEval / ProbePdf of `dirs`."""
+        seeds = np.ascontiguousarray(seeds, np.uint32)
+        dirs = np.ascontiguousarray(dirs, np.float32)
+        n, m = len(seeds), len(dirs)
+        out = dict(sampleDir=np.empty((n, 3), np.float32), sampleColor=np.empty((n, 3), np.float32), samplePdf=np.empty(n, np.float32),
+                   uv=np.empty((m, 2), np.float32), evalColor=np.empty((m, 3), np.float32), evalPdf=np.empty(m, np.float32))
+        _lib.check(self._L.b200pt_debug_probe(self._h, C.byref(self.launchParams), int(bool(use_guide)), n, _ptr(seeds), _ptr(out["sampleDir"]),
+                                              _ptr(out["sampleColor"]), _ptr(out["samplePdf"]), m, _ptr(dirs), _ptr(out["uv"]), _ptr(out["evalColor"]),
+                                              _ptr(out["evalPdf"])))
+        return out
+
     def debugMorton(self):
         n = self.model.num_triangles()
         codes, order, bounds = np.empty(n, np.uint64), np.empty(n, np.uint32), np.empty(6, np.float32)
