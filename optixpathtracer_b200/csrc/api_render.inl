@@ -157,7 +157,8 @@ static FrameParams frameOf(const LaunchParams& P, const b200pt_config& cfg, cons
 struct Chunk { int pass, k0, k1;  unsigned slotBase; };
 
 // A shadow-catcher pass-through (sv4/deviceProgram.cu:617-622) re-traces a segment without consuming depth, so a path that crosses catcher
-// geometry k times needs max_depth + 1 + k trace launches; the wavefront allows this many crossings per path (launches on empty queues cost ~2 us).
+// geometry k times needs max_depth + 1 + k trace launches; the wavefront allows max(8, max_depth + 1) crossings per path - one per segment plus the
+// primary ray's, the case of a single catcher plane - (launches on empty queues cost ~2 us each); a path that crosses more often is cut off there.
 #define B200PT_CATCHER_EXTRA_LAUNCHES 8
 
 // Enqueues one wavefront (raygen, the bounce loop, counters, per-launch-index sums) of `job` on lane `laneIdx`: the whole frame (nParts = 1)
@@ -212,7 +213,7 @@ static void enqueuePart(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& job, 
     if (count) CUDA_OK(cudaMemsetAsync(L.stats.p, 0, 2 * sizeof(TraceStats), s));
     T.begin(ST_TOTAL, ta, job.totalEnd);
     // the dropped last segment is traced only if alpha can still change (a catcher in the scene) or the miss carries radiance (mis_on_miss)
-    const int bounces = cfg.max_depth + ((c->hasCatcher || cfg.max_depth == 0) ? 1 : 0) + (c->hasCatcher ? B200PT_CATCHER_EXTRA_LAUNCHES : 0);
+    const int bounces = cfg.max_depth + ((c->hasCatcher || cfg.max_depth == 0) ? 1 : 0) + (c->hasCatcher ? std::max(B200PT_CATCHER_EXTRA_LAUNCHES, cfg.max_depth + 1) : 0);
     const int cullBack = cfg.shadow_mode == B200PT_SHADOW_CULL_BACK;
     const float shadowTmin = cfg.shadow_tmin > 0.f ? cfg.shadow_tmin : cfg.tmin;
     for (auto& group : groups) {
@@ -301,7 +302,7 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
     if (!c->built) throw std::runtime_error("b200pt_render: b200pt_build_accel has not been called");
     if (!params->probe.data || !params->probe.cdfValuesX) throw std::runtime_error("b200pt_render: no probe set (call b200pt_set_probe)");
     if (!params->frame.accum_buffer || !params->frame.frame_buffer) throw std::runtime_error("b200pt_render: frame buffers not allocated (call b200pt_resize)");
-    if (cfg.max_depth < 0 || cfg.max_depth > QC_MAX_LAUNCHES - 8) throw std::runtime_error("b200pt_render: max_depth out of range");
+    if (cfg.max_depth < 0 || cfg.max_depth > (c->hasCatcher ? (QC_MAX_LAUNCHES - 12) / 2 : QC_MAX_LAUNCHES - 8)) throw std::runtime_error("b200pt_render: max_depth out of range");
     c->countersPending = false;                                                  // totals of an un-synchronised previous frame are dropped
 
     // Lanes: instrumented frames run on lane 0 (the primary stream); everything else rotates over cfg.frames_in_flight lanes.  With one lane

@@ -4,7 +4,7 @@ accumulated radiance within fp32 libm noise of the oracle (tolerances stated per
 import numpy as np
 import pytest
 
-from conftest import golden
+from conftest import golden, materials_from_bytes, probe_from_golden
 from optixpathtracer_b200 import SampleRenderer, host_params, loadColor, preset, preset_camera, scenes
 from optixpathtracer_b200.probe import ProbeData, analytic_sky
 from optixpathtracer_b200.renderer import computeFinalPixelColors
@@ -197,6 +197,128 @@ def test_empty_and_single_triangle_scene():
     r = SampleRenderer(one)
     prim, mesh, t, u, v = r.traceRays(o, d, 0.01, 1e16)
     assert np.all(prim == 0) and np.allclose(t, 2.0)
+    r.close()
+
+
+# ------------------------------------------------------------------------------------------------ shading library, item by item
+def ulp_diff(a, b):
+    """Distance in units in the last place between two float32 arrays (same sign assumed where it matters; +0 == -0)."""
+    a, b = np.ascontiguousarray(a, np.float32), np.ascontiguousarray(b, np.float32)
+    ia, ib = a.view(np.int32).astype(np.int64), b.view(np.int32).astype(np.int64)
+    ia = np.where(ia < 0, -(ia & 0x7fffffff), ia)
+    ib = np.where(ib < 0, -(ib & 0x7fffffff), ib)
+    return np.abs(ia - ib)
+
+
+def test_device_bsdf_kat():
+    """The CUDA shading library on the reference-minted fixture (tests/golden/bsdf.npz, from the reference's own Disney.cuh / maths.h host-compiled):
+    BasisFromVector bit-equal (double 1.0/sqrt kept); BSDFSample lobe type and the generator's state afterwards EQUAL (data-dependent draw count);
+    direction and pdf bit-equal on the refraction branch (no sinf/cosf); elsewhere the direction is a sum of three basis vectors weighted by
+    products of sinf/cosf (CUDA's differ from glibc's by <= 2 ulp each): <= 8 ulp of its largest component (measured: 90 % of the directions
+    bit-equal, worst 4.7 ulp) and the pdf of that direction <= 32 ulp (measured 12); BSDFEval / BSDFPdf of a GIVEN direction: bit-equal
+    (logf in GTR1 happens to agree on the fixture).  sv4/Disney.cuh:152-427."""
+    g = golden("bsdf")
+    mats = materials_from_bytes(g["materials"])
+    r = SampleRenderer(scenes.cornell())
+    out = r.debugBsdf(mats, g["etaI"], g["etaO"], g["N"], g["view"], g["L"], g["albedo"], g["seeds"])
+    r.close()
+    assert np.array_equal(out["basisU"].view(np.uint32), g["basisU"].view(np.uint32))
+    assert np.array_equal(out["basisV"].view(np.uint32), g["basisV"].view(np.uint32))
+    assert np.array_equal(out["sampleType"], g["sampleType"])
+    assert np.array_equal(out["sampleRng"], g["sampleRng"])
+    ok = g["samplePdf"] > 0                                             # the direction is unspecified when pdf == 0 (total internal reflection)
+    assert np.array_equal(out["samplePdf"] > 0, ok)
+    spec = ok & (g["sampleType"] == 2)                                  # eSpecular: Refract(), no trigonometry
+    assert spec.sum() > 5
+    assert np.array_equal(out["sampleL"][spec].view(np.uint32), g["sampleL"][spec].view(np.uint32))
+    assert np.array_equal(out["samplePdf"][spec].view(np.uint32), g["samplePdf"][spec].view(np.uint32))
+    scale = np.abs(g["sampleL"][ok]).max(axis=1, keepdims=True)         # ulp of the direction's largest component
+    derr = np.abs(out["sampleL"][ok] - g["sampleL"][ok]) / (scale * 2.0 ** -23)
+    assert derr.max() <= 8.0, derr.max()
+    assert (derr.max(axis=1) == 0).mean() > 0.8
+    assert ulp_diff(out["samplePdf"][ok], g["samplePdf"][ok]).max() <= 32
+    assert ulp_diff(out["evalPdf"], g["evalPdf"]).max() <= 1
+    assert np.array_equal(np.isfinite(out["evalF"]), np.isfinite(g["evalF"]))
+    fin = np.isfinite(g["evalF"]).all(axis=1)
+    fscale = np.maximum(np.abs(g["evalF"][fin]).max(axis=1, keepdims=True), 1e-30)
+    ferr = np.abs(out["evalF"][fin] - g["evalF"][fin]) / (fscale * 2.0 ** -23)
+    assert ferr.max() <= 1.0, ferr.max()
+
+
+@pytest.mark.parametrize("use_guide", [True, False])
+def test_device_probe_kat(use_guide):
+    """ProbeSample / ProbeDirToUV / ProbeEval / ProbePdf on the device against tests/golden/probe.npz (sv4/Probe.cuh:38-169): the CDF search must
+    land on the SAME texel with and without the guide tables (colour bit-equal: it is a table entry), direction / pdf / uv within 4 ulp
+    (sinf, cosf, acosf, atan2f)."""
+    g = golden("probe")
+    probe = probe_from_golden(g)
+    r = make_renderer(scenes.cornell(), probe, (16, 16), preset_camera("cornell"), preset("sv4_uniform"))
+    out = r.debugProbe(g["seeds"], g["dirs"], use_guide=use_guide)
+    r.close()
+    assert np.array_equal(out["sampleColor"].view(np.uint32), g["sampleColor"].view(np.uint32))
+    assert np.array_equal(out["evalColor"].view(np.uint32), g["evalColor"].view(np.uint32))
+    derr = np.abs(out["sampleDir"] - g["sampleDir"]) / 2.0 ** -23       # unit vectors (measured: 1 ulp)
+    assert derr.max() <= 4.0, derr.max()
+    assert ulp_diff(out["samplePdf"], g["samplePdf"]).max() <= 8        # measured 2
+    assert np.abs(out["uv"] - g["uv"]).max() <= 4 * 2.0 ** -24          # measured 2 * 2^-24
+    assert ulp_diff(out["evalPdf"], g["evalPdf"]).max() <= 16           # measured 5 (sinf of acosf)
+
+
+def test_device_probe_kat_large_probe_guided_equals_plain(port):
+    """2048 x 1024 analytic sky (the bench probe): 100 k ProbeSample draws through the guide tables and through the reference's plain LowerBound
+    return the same texel, direction and pdf bit for bit, and both equal the oracle's choice of texel."""
+    probe = analytic_sky(2048, 1024)
+    r = make_renderer(scenes.cornell(), probe, (16, 16), preset_camera("cornell"), preset("sv4_uniform"))
+    seeds = np.random.default_rng(17).integers(0, 2 ** 32, 100000, dtype=np.uint64).astype(np.uint32)
+    dirs = np.zeros((0, 3), np.float32)
+    a, b = r.debugProbe(seeds, dirs, use_guide=True), r.debugProbe(seeds, dirs, use_guide=False)
+    r.close()
+    for k in ("sampleDir", "sampleColor", "samplePdf"):
+        assert np.array_equal(a[k].view(np.uint32), b[k].view(np.uint32)), k
+    d, c, p = port.probe_sample(probe, seeds)
+    assert np.array_equal(a["sampleColor"].view(np.uint32), c.view(np.uint32))
+
+
+def _catcher_scene():
+    """A shadow-catcher ground plane (MATERIAL_FLAG_SHADOW_CATCHER) at y = 0 under two boxes, with an ordinary floor at y = -1 BELOW it: secondary
+    rays cross the catcher on the way down and again on the way up (pass-through, sv4/deviceProgram.cu:617-622), primary rays that see the
+    catcher collect the shadow term in alpha (:663-664)."""
+    from optixpathtracer_b200 import Material, Model, addBox
+    from optixpathtracer_b200.scenes import _mesh
+    from optixpathtracer_b200.structs import MATERIAL_FLAG_SHADOW_CATCHER
+    m = Model()
+    addBox(m, Material.orig_defaults(color=(0.8, 0.3, 0.2)), (-0.6, 0.5, 0.0), (0.4, 0.5, 0.4))
+    addBox(m, Material(color=(0.2, 0.5, 0.9), emission=(0, 0, 0)), (0.7, 0.35, 0.3), (0.35, 0.35, 0.35))
+    catcher = Material.orig_defaults(color=(0.7, 0.7, 0.7))
+    catcher.flags = MATERIAL_FLAG_SHADOW_CATCHER
+    m.meshes.append(_mesh([[-4, 0, -4], [4, 0, -4], [4, 0, 4], [-4, 0, 4]], [[0, 2, 1], [0, 3, 2]], catcher))
+    m.meshes.append(_mesh([[-6, -1, -6], [6, -1, -6], [6, -1, 6], [-6, -1, 6]], [[0, 2, 1], [0, 3, 2]], Material.orig_defaults(color=(0.5, 0.6, 0.4))))
+    return m
+
+
+@pytest.mark.parametrize("pname,spl", [("sv4_uniform", 4), ("orig", 2)])
+def test_shadow_catcher_against_oracle(port, pname, spl):
+    """Shadow-catcher materials: pass-throughs do not consume depth, so paths that cross the catcher need more trace launches than
+    max_depth + 1; the alpha shadow term survives a BSDFSample with pdf <= 0.  Accumulation buffer and pixel alpha against the oracle."""
+    from optixpathtracer_b200 import Camera
+    model = _catcher_scene()
+    probe = analytic_sky(128, 64)
+    cfg = preset(pname, uniform_spl=spl)
+    cam = Camera(eye=(0.0, 2.2, 4.5), lookat=(0.0, 0.3, 0.0), up=(0, 1, 0), fovY=40.0)
+    W, H = 128, 96
+    r = make_renderer(model, probe, (W, H), cam, cfg)
+    r.launchParams.samples_per_launch = spl
+    r.render()
+    got = r.downloadAccum()
+    cnt = r.counters()
+    sc = port.scene(model, probe, brute_force=True)
+    p = host_params(W, H, cam, samples_per_launch=spl)
+    want, wframe, ocnt, _ = sc.render(p, cfg, np.zeros((H, W, 4), np.float32))
+    assert cnt.samples == ocnt["samples"]
+    assert rel_mismatch(got[..., :3], want[..., :3], 2e-4) < 1e-2
+    assert float(np.sqrt(np.mean((np.clip(got[..., :3], 0, 10) - np.clip(want[..., :3], 0, 10)) ** 2))) < 2e-2
+    # every radiance segment the reference traces and keeps is traced here too: pass-throughs included
+    assert cnt.radiance_rays > 0.6 * ocnt["radiance_rays"]
     r.close()
 
 
