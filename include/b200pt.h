@@ -164,6 +164,31 @@ int b200pt_device_buffers(b200pt_ctx* ctx, void** accum_f4, void** frame_rgba8, 
 int b200pt_resolve_sum(b200pt_ctx* ctx, const struct LaunchParams* params, const b200pt_config* cfg, int n_passes);
 int b200pt_clear_accum(b200pt_ctx* ctx);
 
+/* ---- multi-GPU: one context per rank (one process or one thread per GPU), the scene replicated, ONE collective per frame partition --------
+ * The reference has no multi-GPU path (sv4/main.cpp:289-290: "for nvlink configuration ... currently no support"; the SDK's buffer modes are
+ * sutil/CUDAOutputBuffer.h:45-51).  These entry points are what a maintainer's multi-GPU driver binds: the collectives are NCCL's, issued by
+ * the library on the context's primary stream behind every frame in flight; libnccl.so.2 is opened at run time (no link-time dependency).
+ *   sample split  rank r renders sub-frames r, r+N, ... with cfg.accum_mode = B200PT_ACCUM_SUM, then b200pt_reduce_sum
+ *   tile split    rank r renders with cfg.tile_rank = r, cfg.tile_count = N (uniform schedules), then b200pt_gather_bands                      */
+#define B200PT_UNIQUE_ID_BYTES 128
+/* ncclGetUniqueId on the calling rank; the host distributes the 128 bytes to the other ranks with its own plumbing (MPI, torch.distributed, a file). */
+int b200pt_comm_unique_id(void* id_out_128);
+/* ncclCommInitRank (collective over all ranks).  From here on the accumulation buffer lives in ncclMemAlloc'd memory registered with the
+ * communicator - an existing one is moved (contents kept) and params->frame.accum_buffer, if it pointed at it, is rewritten (params may be NULL). */
+int b200pt_comm_init(b200pt_ctx* ctx, int n_ranks, int rank, const void* id_128, struct LaunchParams* params);
+int b200pt_comm_destroy(b200pt_ctx* ctx);
+/* n_ranks, rank, NCCL version code, accum_registered: bit 0 = ncclMemAlloc'd, bit 1 = ncclCommRegister'ed.  Any pointer may be NULL. */
+int b200pt_comm_info(b200pt_ctx* ctx, int* n_ranks, int* rank, int* nccl_version, int* accum_registered);
+/* Sample split epilogue: fp32 SUM ncclReduce of params->frame.accum_buffer onto `root`, followed there by sum / n_passes and the display
+ * transform into frame_buffer.  keep_local = 0: in place, root's accumulation buffer ends up holding the mean (b200pt_resolve_sum; end of a
+ * job).  keep_local = 1: progressive display - every rank keeps its partial sum, root receives the total into a buffer of its own and only
+ * refreshes frame_buffer, so the ranks go on accumulating and reduce again later (n_passes = passes summed so far over all ranks).
+ * Enqueued on the primary stream; b200pt_synchronize or a download waits for it. */
+int b200pt_reduce_sum(b200pt_ctx* ctx, const struct LaunchParams* params, const b200pt_config* cfg, int root, int n_passes, int keep_local);
+/* Tile split epilogue: the 32-row bands each rank rendered (band % n_ranks == rank) are sent to `root`, which receives them in place.
+ * what: bit 0 = RGBA8 frame buffer, bit 1 = float4 accumulation buffer.  One grouped ncclSend / ncclRecv batch on the primary stream. */
+int b200pt_gather_bands(b200pt_ctx* ctx, const struct LaunchParams* params, int root, int what);
+
 /* computeFinalPixelColors (sv4/toneMap.cu:41-70, toneMap.h:4): sqrt-gamma float4 -> RGBA8, device pointers. */
 int b200pt_tonemap_sqrt(int width, int height, const void* d_float4_in, void* d_rgba8_out, void* stream);
 /* Host-buffer convenience around the same kernel (H2D + kernel + D2H). */

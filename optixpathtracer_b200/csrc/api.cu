@@ -66,8 +66,11 @@ struct Speculation {
     void drop() { ahead.clear();  havePrediction = false;  hits = 0; }
 };
 
+struct MultiState;                    // api_multi.inl: NCCL communicator + registrations of one rank
 struct b200pt_ctx {
     int device = 0;
+    MultiState* multi = nullptr;
+    bool accumFromNccl = false;       // accumBuf.p came from ncclMemAlloc (freed with ncclMemFree)
     cudaStream_t stream = nullptr;
     bool stale = false;           // vertices updated since the last build/refit
     float refitMs = 0.f;
@@ -93,6 +96,10 @@ struct b200pt_ctx {
     bool countersPending = false;  int profiled = 0;
     std::vector<cudaEvent_t> evPool;  std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> evUsed;  size_t evNext = 0;
 };
+
+static void freeAccum(b200pt_ctx* c);                 // api_multi.inl
+static void allocAccum(b200pt_ctx* c, size_t n);
+static void destroyMulti(b200pt_ctx* c);
 
 // Orders the primary stream after every frame in flight on the other lanes (no host synchronisation): what the entry points that touch
 // shared state (frame buffers, scene, probe, counters) do first, and what b200pt_join exposes to callers that time or copy on that stream.
@@ -174,7 +181,8 @@ void b200pt_destroy(b200pt_ctx* c) {
     for (int k = 0; k < B200PT_MAX_LANES; ++k) if (c->lanes[k].stream) cudaStreamSynchronize(c->lanes[k].stream);
     bvhFree(c->bvh);
     c->dVertices.release();  c->dNormals.release();  c->dTexcoords.release();  c->dIndices.release();  c->dTriMesh.release();  c->dMeshes.release();  c->dTexels.release();
-    c->frameBuf.release();  c->accumBuf.release();  c->normalBuf.release();  c->albedoBuf.release();  c->colorBuf.release();
+    freeAccum(c);  destroyMulti(c);
+    c->frameBuf.release();  c->normalBuf.release();  c->albedoBuf.release();  c->colorBuf.release();
     c->probeData.release();  c->probePdfX.release();  c->probeCdfX.release();  c->probePdfY.release();  c->probeCdfY.release();  c->probeGuide.release();  c->probeRowTotal.release();
     for (int k = 0; k < B200PT_MAX_LANES; ++k) {
         Lane& L = c->lanes[k];
@@ -296,3 +304,4 @@ static SceneDev sceneOf(b200pt_ctx* c) {
 
 #include "api_render.inl"
 #include "api_hooks.inl"
+#include "api_multi.inl"

@@ -392,8 +392,10 @@ int b200pt_resize(b200pt_ctx* c, int w, int h, LaunchParams* params) {
     enterCtxMutating(c);
     CUDA_OK(cudaStreamSynchronize(c->stream));
     const size_t n = (size_t)w * h;
-    c->frameBuf.release();  c->accumBuf.release();  c->normalBuf.release();  c->albedoBuf.release();  c->colorBuf.release();
-    c->frameBuf.ensure(n);  c->accumBuf.ensure(n);  c->normalBuf.ensure(n);  c->albedoBuf.ensure(n);  c->colorBuf.ensure(n);
+    freeAccum(c);
+    c->frameBuf.release();  c->normalBuf.release();  c->albedoBuf.release();  c->colorBuf.release();
+    c->frameBuf.ensure(n);  c->normalBuf.ensure(n);  c->albedoBuf.ensure(n);  c->colorBuf.ensure(n);
+    allocAccum(c, n);                                                            // ncclMemAlloc + registration once a communicator exists (api_multi.inl)
     // The reference's CUDABuffer::resize leaves the new buffers uninitialised; a render() that keeps accumulating across a resize (subframe_index > 0)
     // would then average against whatever the allocator handed out.  Zeroed here, so that sequence is at least deterministic.
     CUDA_OK(cudaMemsetAsync(c->frameBuf.p, 0, sizeof(uint32_t) * n, c->stream));  CUDA_OK(cudaMemsetAsync(c->accumBuf.p, 0, sizeof(float4) * n, c->stream));

@@ -176,6 +176,7 @@ void launchGather(const FrameParams& F, const PassParams& P, int k0, int k1, con
 void launchFinalize(const FrameParams& F, const PassParams& P, const float4* sumRad, const float4* sumAlpha,
                     const float4* sumNormal, const float4* sumAlbedo, cudaStream_t stream);
 void launchResolveSum(const FrameParams& F, int nPasses, cudaStream_t stream);
+void launchResolveTotal(const FrameParams& F, const float4* total, int nPasses, cudaStream_t stream);
 struct WhittedParams { int W, H;  float3 position, direction, horizontal, vertical, lightPos; };
 void launchWhittedRaygen(const WhittedParams& P, const Queues& Q, const PathPool& pool, unsigned* counters, cudaStream_t stream);
 void launchWhittedShade(const WhittedParams& P, const SceneDev& scene, const PathPool& pool, const Queues& Q, unsigned* shadowCounter, cudaStream_t stream);

@@ -463,6 +463,16 @@ __global__ void resolveSumKernel(FrameParams F, int nPasses) {
     F.frame[i] = displayColor(F, mean);
 }
 
+// the same from a separate buffer of totals, refreshing only the frame buffer (progressive display of a sample split: the accumulation
+// buffer keeps this rank's partial sum)
+__global__ void resolveTotalKernel(FrameParams F, const float4* __restrict__ total, int nPasses) {
+    const unsigned n = (unsigned)F.W * (unsigned)F.H;
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 s = total[i];
+    F.frame[i] = displayColor(F, f3(s.x, s.y, s.z) / (float)nPasses);
+}
+
 // computeFinalPixelColorsKernel, sv4/toneMap.cu:41-58.  20 B/pixel streaming; one thread per pixel, 1-D
 // (the reference's 32x32 tiling buys nothing for a pure stream).
 __global__ void tonemapSqrtKernel(uint32_t* __restrict__ out, const float4* __restrict__ in, unsigned n) {
@@ -588,6 +598,9 @@ void launchFinalize(const FrameParams& F, const PassParams& P, const float4* sum
 }
 void launchResolveSum(const FrameParams& F, int nPasses, cudaStream_t s) {
     resolveSumKernel<<<gridFor((unsigned)F.W * F.H), SHADE_BLOCK, 0, s>>>(F, nPasses);
+}
+void launchResolveTotal(const FrameParams& F, const float4* total, int nPasses, cudaStream_t s) {
+    resolveTotalKernel<<<gridFor((unsigned)F.W * F.H), SHADE_BLOCK, 0, s>>>(F, total, nPasses);
 }
 void launchTonemapSqrt(int w, int h, const float4* in, uint32_t* out, cudaStream_t s) {
     const unsigned n = (unsigned)w * (unsigned)h;

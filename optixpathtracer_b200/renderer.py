@@ -210,6 +210,38 @@ class SampleRenderer:
         cfg = config or self.config
         _lib.check(self._L.b200pt_resolve_sum(self._h, C.byref(self.launchParams), C.byref(cfg), int(n_passes)))
 
+    # ---- multi-GPU below Python: NCCL collectives issued by the library (include/b200pt.h) ----------
+    @staticmethod
+    def commUniqueId():
+        """ncclGetUniqueId -> 128 bytes (numpy uint8) for rank 0 to hand to the other ranks."""
+        L = _lib.lib()
+        buf = np.zeros(128, np.uint8)
+        _lib.check(L.b200pt_comm_unique_id(_ptr(buf)))
+        return buf
+
+    def commInit(self, n_ranks, rank, unique_id):
+        uid = np.ascontiguousarray(unique_id, np.uint8)
+        assert uid.size == 128
+        _lib.check(self._L.b200pt_comm_init(self._h, int(n_ranks), int(rank), _ptr(uid), C.byref(self.launchParams)))
+
+    def commDestroy(self):
+        _lib.check(self._L.b200pt_comm_destroy(self._h))
+
+    def commInfo(self):
+        n, r, v, reg = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        _lib.check(self._L.b200pt_comm_info(self._h, C.byref(n), C.byref(r), C.byref(v), C.byref(reg)))
+        return dict(n_ranks=n.value, rank=r.value, nccl_version=v.value, accum_nccl_alloc=bool(reg.value & 1), accum_registered=bool(reg.value & 2))
+
+    def reduceSum(self, n_passes, root=0, config=None, keep_local=False):
+        """Sample split: fp32 SUM reduce of the accumulation buffer onto `root` + resolve there (asynchronous on the primary stream).
+        keep_local: progressive display - the ranks keep their partial sums, root only refreshes its frame buffer."""
+        cfg = config or self.config
+        _lib.check(self._L.b200pt_reduce_sum(self._h, C.byref(self.launchParams), C.byref(cfg), int(root), int(n_passes), int(bool(keep_local))))
+
+    def gatherBands(self, root=0, frame=True, accum=False):
+        """Tile split: this rank's 32-row bands go to `root` (asynchronous on the primary stream)."""
+        _lib.check(self._L.b200pt_gather_bands(self._h, C.byref(self.launchParams), int(root), (1 if frame else 0) | (2 if accum else 0)))
+
     def deviceBuffers(self):
         a, f, s = C.c_void_p(), C.c_void_p(), C.c_void_p()
         _lib.check(self._L.b200pt_device_buffers(self._h, C.byref(a), C.byref(f), C.byref(s)))

@@ -791,6 +791,60 @@ def test_refit_and_rebuild_after_vertex_update(port):
     r.close()
 
 
+def test_async_download_after_join_is_ordered(sponza_small):
+    """render_async, then an entry point that joins the lanes (b200pt_join / counters), THEN b200pt_download_pixels_async: the copy
+    is new work on the frame's lane, and b200pt_synchronize must wait for it ('valid after b200pt_synchronize')."""
+    import torch
+    probe = analytic_sky(128, 64)
+    cfg = preset("orig", uniform_spl=1)
+    cfg.frames_in_flight = 3
+    r = make_renderer(sponza_small, probe, (640, 360), preset_camera("sponza"), cfg)
+    host = torch.zeros((360, 640), dtype=torch.int32).pin_memory().numpy().view(np.uint32)
+    for k in range(5):
+        r.launchParams.frame.subframe_index = k
+        r.render(sync=False)
+        r.join()                                         # clears the lanes' busy flags
+        host[:] = 0
+        r.downloadPixelsAsync(host)
+        r.synchronize()
+        assert np.array_equal(host, r.downloadPixels()), k
+        assert (host >> 24 == 255).all()
+    r.close()
+
+
+def test_speculative_wavefront_dropped_before_refit(port):
+    """a blocking render() that has speculative next sub-frames in flight, then a camera move (mis-prediction: the wavefronts are
+    abandoned but keep running), then IMMEDIATELY update_vertices + refit + render: the mutating entry points must drain every lane first.
+    The frame after the refit equals the frame of a renderer that never speculated."""
+    import copy
+    base = scenes.sponza_class(30000)
+    probe = analytic_sky(128, 64)
+    cam, cam2 = preset_camera("sponza"), preset_camera("sponza")
+    cam2.eye = (cam2.eye[0] + 3.0, cam2.eye[1], cam2.eye[2])
+    moved = [np.asarray(m.vertex, np.float32) + np.float32(7.5) for m in base.meshes]
+
+    def run(in_flight):
+        cfg = preset("orig", uniform_spl=1)
+        cfg.frames_in_flight = in_flight
+        r = make_renderer(copy.deepcopy(base), probe, (320, 180), cam, cfg)
+        for k in range(6):                               # progressive accumulation: from the third call on the next sub-frames are speculated
+            r.launchParams.frame.subframe_index = k
+            r.render()
+        r.setCamera(cam2)                                # wrong guess for the speculative wavefronts: abandoned, still running
+        r.launchParams.frame.subframe_index = 0
+        r.render()
+        for k, v in enumerate(moved):                    # scene changes right behind it
+            r.updateVertices(k, v)
+        r.refitAccel()
+        r.launchParams.frame.subframe_index = 1
+        r.render()
+        out = r.downloadAccum().copy()
+        r.close()
+        return out
+
+    assert np.array_equal(run(1), run(3))
+
+
 def check_bvh_boxes_contain_triangles(r, model):
     """Every leaf's triangles lie inside the (dequantised) child box that refers to them, and child boxes nest in their parents'."""
     info = r.bvhInfo()

@@ -14,6 +14,6 @@ flags="-gencode arch=compute_100a,code=sm_100a -std=c++17 -O3 -lineinfo -Xcompil
   nvcc $flags -fmad=${SHADE_FMAD:-false} -c shade.cu -o "$out/shade.o" &
   nvcc $flags -c api.cu -o "$out/api.o" &
   wait )
-nvcc -gencode arch=compute_100a,code=sm_100a -shared -o "$root/build/variants/libb200pt_$name.so" "$out"/*.o -lcudart
+nvcc -gencode arch=compute_100a,code=sm_100a -shared -o "$root/build/variants/libb200pt_$name.so" "$out"/*.o -lcudart -ldl
 rm -rf "$out"
 echo "built build/variants/libb200pt_$name.so"
