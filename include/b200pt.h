@@ -176,7 +176,8 @@ int b200pt_comm_unique_id(void* id_out_128);
 /* ncclCommInitRank (collective over all ranks).  From here on the accumulation buffer lives in ncclMemAlloc'd memory registered with the
  * communicator - an existing one is moved (contents kept) and params->frame.accum_buffer, if it pointed at it, is rewritten (params may be NULL). */
 int b200pt_comm_init(b200pt_ctx* ctx, int n_ranks, int rank, const void* id_128, struct LaunchParams* params);
-int b200pt_comm_destroy(b200pt_ctx* ctx);
+/* Drops the communicator; the accumulation buffer moves back to a plain allocation (contents kept) and params->frame.accum_buffer follows it. */
+int b200pt_comm_destroy(b200pt_ctx* ctx, struct LaunchParams* params);
 /* n_ranks, rank, NCCL version code, accum_registered: bit 0 = ncclMemAlloc'd, bit 1 = ncclCommRegister'ed.  Any pointer may be NULL. */
 int b200pt_comm_info(b200pt_ctx* ctx, int* n_ranks, int* rank, int* nccl_version, int* accum_registered);
 /* Sample split epilogue: fp32 SUM ncclReduce of params->frame.accum_buffer onto `root`, followed there by sum / n_passes and the display

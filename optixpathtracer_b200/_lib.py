@@ -67,7 +67,7 @@ def lib():
     L.b200pt_clear_accum.argtypes = [vp]
     L.b200pt_comm_unique_id.argtypes = [vp]
     L.b200pt_comm_init.argtypes = [vp, i32, i32, vp, C.POINTER(LaunchParams)]
-    L.b200pt_comm_destroy.argtypes = [vp]
+    L.b200pt_comm_destroy.argtypes = [vp, C.POINTER(LaunchParams)]
     L.b200pt_comm_info.argtypes = [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]
     L.b200pt_reduce_sum.argtypes = [vp, C.POINTER(LaunchParams), C.POINTER(Config), i32, i32, i32]
     L.b200pt_gather_bands.argtypes = [vp, C.POINTER(LaunchParams), i32, i32]

@@ -94,6 +94,20 @@ static void destroyMulti(b200pt_ctx* c) {
     c->multi = nullptr;
 }
 
+// drops the communicator; an accumulation buffer that lives in NCCL-allocated memory goes back to a plain allocation, contents kept
+static void leaveComm(b200pt_ctx* c) {
+    if (!c->multi) return;
+    if (c->accumFromNccl && c->accumBuf.p) {
+        const size_t n = c->accumBuf.n;
+        std::vector<float4> keep(n);
+        CUDA_OK(cudaMemcpy(keep.data(), c->accumBuf.p, n * sizeof(float4), cudaMemcpyDeviceToHost));
+        freeAccum(c);                                                          // deregisters + ncclMemFree while the communicator still exists
+        destroyMulti(c);
+        c->accumBuf.ensure(n);
+        CUDA_OK(cudaMemcpy(c->accumBuf.p, keep.data(), n * sizeof(float4), cudaMemcpyHostToDevice));
+    } else destroyMulti(c);                                                    // (deregisters what it registered)
+}
+
 extern "C" {
 
 int b200pt_comm_unique_id(void* id128) {
@@ -112,7 +126,8 @@ int b200pt_comm_init(b200pt_ctx* c, int nranks, int rank, const void* id128, Lau
     API_BEGIN
     enterCtxMutating(c);
     CUDA_OK(cudaStreamSynchronize(c->stream));
-    if (c->multi) { const bool had = c->accumBuf.p != nullptr;  if (had) freeAccum(c);  destroyMulti(c); }
+    const bool callerPointsAtOurs = params && c->accumBuf.p && params->frame.accum_buffer == c->accumBuf.p;
+    leaveComm(c);                                                              // re-initialisation: drop the old communicator first (the buffer's contents survive)
     ncclUniqueId id;
     memcpy(&id, id128, sizeof(id));
     MultiState* m = new MultiState();
@@ -124,7 +139,6 @@ int b200pt_comm_init(b200pt_ctx* c, int nranks, int rank, const void* id128, Lau
         const size_t n = (size_t)c->W * c->H;
         std::vector<float4> keep(n);
         CUDA_OK(cudaMemcpy(keep.data(), c->accumBuf.p, n * sizeof(float4), cudaMemcpyDeviceToHost));
-        const bool callerPointsAtOurs = params && params->frame.accum_buffer == c->accumBuf.p;
         allocAccum(c, n);
         CUDA_OK(cudaMemcpy(c->accumBuf.p, keep.data(), n * sizeof(float4), cudaMemcpyHostToDevice));
         if (callerPointsAtOurs) params->frame.accum_buffer = c->accumBuf.p;
@@ -132,20 +146,14 @@ int b200pt_comm_init(b200pt_ctx* c, int nranks, int rank, const void* id128, Lau
     API_END
 }
 
-int b200pt_comm_destroy(b200pt_ctx* c) {
+int b200pt_comm_destroy(b200pt_ctx* c, LaunchParams* params) {
     if (!c) return fail("b200pt_comm_destroy: null context");
     API_BEGIN
     enterCtxMutating(c);
     CUDA_OK(cudaStreamSynchronize(c->stream));
-    if (c->multi && c->accumFromNccl) {                                        // back to a plain allocation (contents kept)
-        const size_t n = c->accumBuf.n;
-        std::vector<float4> keep(n);
-        CUDA_OK(cudaMemcpy(keep.data(), c->accumBuf.p, n * sizeof(float4), cudaMemcpyDeviceToHost));
-        freeAccum(c);
-        destroyMulti(c);
-        c->accumBuf.ensure(n);
-        CUDA_OK(cudaMemcpy(c->accumBuf.p, keep.data(), n * sizeof(float4), cudaMemcpyHostToDevice));
-    } else destroyMulti(c);
+    const bool callerPointsAtOurs = params && c->accumBuf.p && params->frame.accum_buffer == c->accumBuf.p;
+    leaveComm(c);
+    if (callerPointsAtOurs) params->frame.accum_buffer = c->accumBuf.p;       // the buffer moved back to a plain allocation
     API_END
 }
 

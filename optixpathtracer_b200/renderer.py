@@ -225,7 +225,7 @@ class SampleRenderer:
         _lib.check(self._L.b200pt_comm_init(self._h, int(n_ranks), int(rank), _ptr(uid), C.byref(self.launchParams)))
 
     def commDestroy(self):
-        _lib.check(self._L.b200pt_comm_destroy(self._h))
+        _lib.check(self._L.b200pt_comm_destroy(self._h, C.byref(self.launchParams)))
 
     def commInfo(self):
         n, r, v, reg = C.c_int(), C.c_int(), C.c_int(), C.c_int()

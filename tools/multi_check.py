@@ -72,6 +72,22 @@ def main():
         print(f"sample split over {world} ranks: max rel err of the mean {err:.2e}, pixels off by > 1/255: {(d8 > 1).mean():.2e}, comm {info} -> {'OK' if s_ok else 'FAIL'}", flush=True)
         ok &= s_ok
         one.close()
+    # re-initialise the communicator on a live context (the accumulation buffer moves, contents kept), then drop it: the context must
+    # keep rendering into a valid buffer that launchParams follows
+    before = r.downloadAccum().copy()
+    r.commInit(world, rank, share_unique_id(rank))
+    same_after_reinit = np.array_equal(before.view(np.uint32), r.downloadAccum().view(np.uint32))
+    r.commDestroy()
+    same_after_destroy = np.array_equal(before.view(np.uint32), r.downloadAccum().view(np.uint32))
+    r.config.accum_mode = 0
+    r.launchParams.frame.subframe_index = 0
+    r.render()
+    alive = bool(np.isfinite(r.downloadAccum()).all()) and r.commInfo()["n_ranks"] == 1
+    c_ok = same_after_reinit and same_after_destroy and alive
+    print(f"rank {rank}: comm re-init keeps the buffer: {same_after_reinit}, comm destroy keeps it: {same_after_destroy}, renders afterwards: {alive}", flush=True)
+    flag = torch.tensor([1 if c_ok else 0], device="cuda")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    ok &= bool(int(flag.item()))
     r.close()
 
     # ---- tile split
