@@ -115,6 +115,18 @@ int b200pt_set_probe(b200pt_ctx* ctx, int width, int height, const float* data_r
                      const float* pdfX, const float* cdfX, const float* pdfY, const float* cdfY,
                      const float* offset_xyz, struct LaunchParams* params /* probe pointers written */);
 
+/* ProbeData::BuildCDF on the device WITHOUT any allocation.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernels and the same
+ * bits as b200pt_set_probe_image; the only scratch they need (one float per probe row) lives in a file-scope `static __device__` array of
+ * B200PT_NOALLOC_MAX_ROWS floats (64 KiB, held by every GPU that loads the library until the process exits).  The caller passes DEVICE pointers:
+ * width*height float4 texels in; pdfX, cdfX (width*height floats each) and pdfY, cdfY (height floats each) out.  The launches go to `stream`
+ * (NULL = the context's primary stream) and are not waited for.  Calls no cudaMalloc / cudaFree / allocating library routine; the first call on a
+ * device resolves the array's address (cudaGetSymbolAddress) - make one call before starting a graph capture.  height > B200PT_NOALLOC_MAX_ROWS
+ * is rejected with an error.  Every call on a GPU shares the array: calls that overlap on the GPU race on it, serialise them (one stream). */
+#define B200PT_NOALLOC_MAX_ROWS 16384
+int b200pt_build_cdf_noalloc(b200pt_ctx* ctx, int width, int height, const void* d_data_rgba_f32,
+                             void* d_pdfX, void* d_cdfX, void* d_pdfY, void* d_cdfY, void* stream);
+
 /* ---- second integrator on the same traversal kernels: 04HelloRaytracing (deviceProgram.cu:66-243) -----
  * One primary ray per pixel centre (tmin 0, tmax 1e20), interpolated shading normal (geometric normal when the mesh has none),
  * diffuse colour x texture, one shadow ray to a point light (origin + 1e-3 Ng, unnormalised direction, t in (1e-3, 1 - 1e-3),

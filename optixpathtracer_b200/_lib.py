@@ -15,7 +15,7 @@ SYMBOLS = [
     "b200pt_render_whitted", "b200pt_render_async", "b200pt_synchronize", "b200pt_join", "b200pt_download_pixels", "b200pt_download_pixels_async", "b200pt_download_accum",
     "b200pt_upload_accum", "b200pt_download_aov", "b200pt_device_buffers", "b200pt_resolve_sum", "b200pt_clear_accum",
     "b200pt_comm_unique_id", "b200pt_comm_init", "b200pt_comm_destroy", "b200pt_comm_info", "b200pt_reduce_sum", "b200pt_gather_bands",
-    "b200pt_tonemap_sqrt", "b200pt_tonemap_sqrt_host", "b200pt_trace_primary", "b200pt_trace_rays",
+    "b200pt_build_cdf_noalloc", "b200pt_tonemap_sqrt", "b200pt_tonemap_sqrt_host", "b200pt_trace_primary", "b200pt_trace_rays",
     "b200pt_debug_bsdf", "b200pt_debug_probe", "b200pt_debug_morton", "b200pt_bvh_info_get", "b200pt_download_bvh", "b200pt_download_bvh4", "b200pt_get_counters",
     "computeFinalPixelColors",
 ]
@@ -65,6 +65,7 @@ def lib():
     L.b200pt_device_buffers.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
     L.b200pt_resolve_sum.argtypes = [vp, C.POINTER(LaunchParams), C.POINTER(Config), i32]
     L.b200pt_clear_accum.argtypes = [vp]
+    L.b200pt_build_cdf_noalloc.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, vp]
     L.b200pt_comm_unique_id.argtypes = [vp]
     L.b200pt_comm_init.argtypes = [vp, i32, i32, vp, C.POINTER(LaunchParams)]
     L.b200pt_comm_destroy.argtypes = [vp, C.POINTER(LaunchParams)]

@@ -73,6 +73,21 @@ int b200pt_resolve_sum(b200pt_ctx* c, const LaunchParams* params, const b200pt_c
     API_END
 }
 
+// BuildCDF on caller-owned device buffers with the kernels' scratch in a static __device__ array (shade.cu): no allocation anywhere on this path.
+int b200pt_build_cdf_noalloc(b200pt_ctx* c, int w, int h, const void* data, void* pdfX, void* cdfX, void* pdfY, void* cdfY, void* stream) {
+    if (!c) return fail("b200pt_build_cdf_noalloc: null context");
+    if (w <= 0 || h <= 0 || !data || !pdfX || !cdfX || !pdfY || !cdfY) return fail("Probe Data is not valid");
+    if (h > B200PT_NOALLOC_MAX_ROWS)
+        return fail("b200pt_build_cdf_noalloc: height " + std::to_string(h) + " exceeds the static scratch (B200PT_NOALLOC_MAX_ROWS = " +
+                    std::to_string(B200PT_NOALLOC_MAX_ROWS) + " rows); use b200pt_set_probe_image");
+    if ((long long)w * h >= (1ll << 31)) return fail("b200pt_build_cdf_noalloc: probe too large");
+    API_BEGIN
+    CUDA_OK(cudaSetDevice(c->device));
+    launchProbeCdfNoAlloc((const float4*)data, w, h, (float*)pdfX, (float*)cdfX, (float*)pdfY, (float*)cdfY, stream ? (cudaStream_t)stream : c->stream);
+    CUDA_OK(cudaPeekAtLastError());
+    API_END
+}
+
 int b200pt_tonemap_sqrt(int w, int h, const void* in, void* out, void* stream) {
     if (w < 0 || h < 0 || ((size_t)w * h && (!in || !out))) return fail("b200pt_tonemap_sqrt: bad argument");
     API_BEGIN

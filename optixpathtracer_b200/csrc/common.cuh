@@ -189,6 +189,7 @@ void launchDebugProbe(const Probe& P, const int* guide, unsigned n, const unsign
 size_t probeGuideSize(int H);
 void launchProbeGuide(const float* cdfX, const float* cdfY, int W, int H, int* guide, cudaStream_t stream);
 void launchProbeCdf(const float4* data, int W, int H, float* pdfX, float* cdfX, float* pdfY, float* cdfY, float* rowTotal, cudaStream_t stream);
+void launchProbeCdfNoAlloc(const float4* data, int W, int H, float* pdfX, float* cdfX, float* pdfY, float* cdfY, cudaStream_t stream);   // scratch: static __device__ array in shade.cu
 void launchTonemapSqrt(int w, int h, const float4* in, uint32_t* out, cudaStream_t stream);
 void launchPrimaryRays(const FrameParams& F, const PassParams& P, float4* rayO, float4* rayD, cudaStream_t stream);
 void launchResolvePrimary(const SceneDev& scene, const float4* hit, unsigned n, const float4* rayO, int32_t* prim, int32_t* mesh,

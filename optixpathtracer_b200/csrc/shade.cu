@@ -578,6 +578,35 @@ void launchProbeCdf(const float4* data, int W, int H, float* pdfX, float* cdfX, 
     probeColCdfKernel<<<1, 32, 0, s>>>(rowTotal, H, pdfY, cdfY);
 }
 
+// ---- the same BuildCDF without any allocation (b200pt_build_cdf_noalloc, no reference counterpart) ----
+// The only scratch of the two kernels above is the per-row total (H floats).  Here it lives in a file-scope device array of a fixed maximum
+// size, so callers that must not allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc) can build the tables:
+//   * every GPU that loads the library holds these B200PT_NOALLOC_MAX_ROWS * 4 bytes = 64 KiB until the process exits;
+//   * the array is shared by every call on that GPU and keeps the last call's contents.  Nothing has to start at zero: probeRowCdfKernel writes
+//     rowTotal[0, H) in full before probeColCdfKernel (next on the same stream) reads exactly that range, stale entries beyond H are never read;
+//   * two calls that overlap on the GPU (different streams, or different contexts on one device) race on the array: serialise them.
+// In host code `g_noallocRowTotal` is only a host-side stand-in for the symbol, NOT a device address; the device address is resolved with
+// cudaGetSymbolAddress once per device, with that device current, and that pointer is what the kernels get.
+static __device__ __align__(256) float g_noallocRowTotal[B200PT_NOALLOC_MAX_ROWS];
+
+static float* noallocRowTotalAddress() {                     // the current device's copy of the array
+    static float* cache[64];                                 // one slot per device ordinal; 0 = not resolved yet
+    int dev = 0;
+    CUDA_OK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) throw std::runtime_error("b200pt_build_cdf_noalloc: device ordinal out of range");
+    if (!cache[dev]) {
+        float* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noallocRowTotal);
+        if (e != cudaSuccess || !p) throw std::runtime_error(std::string("b200pt_build_cdf_noalloc: cudaGetSymbolAddress failed: ") + cudaGetErrorString(e));
+        cache[dev] = p;
+    }
+    return cache[dev];
+}
+void launchProbeCdfNoAlloc(const float4* data, int W, int H, float* pdfX, float* cdfX, float* pdfY, float* cdfY, cudaStream_t s) {
+    if (H > B200PT_NOALLOC_MAX_ROWS) throw std::runtime_error("b200pt_build_cdf_noalloc: height exceeds B200PT_NOALLOC_MAX_ROWS");
+    launchProbeCdf(data, W, H, pdfX, cdfX, pdfY, cdfY, noallocRowTotalAddress(), s);
+}
+
 // ---- launchers ---------------------------------------------------------------------------------------------
 static inline unsigned gridFor(unsigned n) { return (n + SHADE_BLOCK - 1) / SHADE_BLOCK; }
 static inline unsigned persistentGrid() { return (unsigned)numSMs() * SHADE_MIN_BLOCKS; }

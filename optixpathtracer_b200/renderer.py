@@ -157,6 +157,12 @@ class SampleRenderer:
         _lib.check(self._L.b200pt_set_probe_image(self._h, data.shape[1], data.shape[0], _ptr(data), _ptr(off),
                                                   C.byref(self.launchParams)))
 
+    def buildCdfNoAlloc(self, width, height, d_data, d_pdfX, d_cdfX, d_pdfY, d_cdfY, stream=None):
+        """BuildCDF on caller-owned DEVICE buffers (integer addresses) without any allocation (b200pt_build_cdf_noalloc): height <=
+        structs.NOALLOC_MAX_ROWS; asynchronous on `stream` (None = the renderer's primary stream)."""
+        _lib.check(self._L.b200pt_build_cdf_noalloc(self._h, int(width), int(height), C.c_void_p(d_data), C.c_void_p(d_pdfX), C.c_void_p(d_cdfX),
+                                                    C.c_void_p(d_pdfY), C.c_void_p(d_cdfY), C.c_void_p(stream) if stream else None))
+
     def downloadProbe(self):
         """(pdfX, cdfX, pdfY, cdfY) of the current probe, read back from the device."""
         w, h = self.launchParams.probe.width, self.launchParams.probe.height

@@ -72,6 +72,7 @@ class Material(C.Structure):
 
 
 MATERIAL_FLAG_SHADOW_CATCHER = 1
+NOALLOC_MAX_ROWS = 16384          # B200PT_NOALLOC_MAX_ROWS, include/b200pt.h
 
 
 class Probe(C.Structure):
