@@ -78,6 +78,7 @@ static void collectCounters(b200pt_ctx* c) {
         CUDA_OK(cudaMemcpy(st, L.stats.p, sizeof(st), cudaMemcpyDeviceToHost));
         c->last.nodes_fetched = st[0].nodes;  c->last.tris_fetched = st[0].tris;
         c->last.nodes_fetched_shadow = st[1].nodes;  c->last.tris_fetched_shadow = st[1].tris;
+        c->last.closest_hits = st[0].hits;  c->last.occluded_shadow_rays = st[1].hits;
     }
     if (c->profiled & 1) {
         float acc[6] = {0, 0, 0, 0, 0, 0};

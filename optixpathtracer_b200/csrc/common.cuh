@@ -134,7 +134,7 @@ struct Queues {
 // work tickets of trace launch d / shade pass d
 enum { QC_RAYS = 0, QC_SHADOWS = 1, QC_HEAD = 2, QC_SHEAD = 3, QC_STRIDE = 4, QC_MAX_LAUNCHES = 208 };
 
-struct TraceStats { unsigned long long nodes, tris, rays; };
+struct TraceStats { unsigned long long nodes, tris, rays, hits; };      // hits: closest-hit rays that found a surface ([0]) / occluded shadow rays ([1])
 
 #define CUDA_OK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
     throw std::runtime_error(std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)

@@ -36,6 +36,45 @@ DEV void enqueueShadow(bool want, float4 o, float4 d, float4 p, const Queues& Q,
     if (want) { Q.shO[q] = o;  Q.shD[q] = d;  Q.shP[q] = p; }
 }
 
+// Block-level append with the block's rays grouped by direction octant (SHADE_SORT_OCTANT): the up-to-SHADE_BLOCK continuation rays of one
+// grid-stride step leave neighbouring surface points; grouped by the sign octant of their direction, the 32 consecutive queue entries a trace
+// warp takes as one chunk also agree on the order in which they visit a node's children.  Deterministic (warp-major order inside an octant);
+// a path's result does not depend on its position in the queue, so images are unchanged bit for bit.  Must be reached by every thread of the block.
+#ifndef SHADE_SORT_OCTANT
+#define SHADE_SORT_OCTANT 0
+#endif
+DEV void enqueueRayByOctant(bool want, float4 o, float4 d, float4* qo, float4* qd, unsigned* counter) {
+    __shared__ unsigned warpCount[SHADE_BLOCK / 32][8];
+    __shared__ unsigned binBase[8];
+    __shared__ unsigned blockBase;
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned key = want ? ((d.x < 0.f ? 1u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 4u : 0u)) : 8u;
+    if (lane < 8) warpCount[warp][lane] = 0;
+    __syncwarp();
+    const unsigned peers = __match_any_sync(0xffffffffu, key);
+    const unsigned rank = __popc(peers & ((1u << lane) - 1u));
+    if (want && rank == 0) warpCount[warp][key] = __popc(peers);
+    __syncthreads();
+    if (threadIdx.x < 8) {                                      // thread b: bin b's offset inside the block's batch needs every bin's total
+        unsigned tot[8];
+#pragma unroll
+        for (int b = 0; b < 8; ++b) { tot[b] = 0;  for (int w = 0; w < SHADE_BLOCK / 32; ++w) tot[b] += warpCount[w][b]; }
+        unsigned run = 0, mine = 0;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) { if (b == (int)threadIdx.x) mine = run;  run += tot[b]; }
+        binBase[threadIdx.x] = mine;
+        if (threadIdx.x == 0) blockBase = run ? atomicAdd(counter, run) : 0u;
+    }
+    __syncthreads();
+    if (want) {
+        unsigned before = 0;
+        for (unsigned w = 0; w < warp; ++w) before += warpCount[w][key];
+        const unsigned q = blockBase + binBase[key] + before + rank;
+        qo[q] = o;  qd[q] = d;
+    }
+    __syncthreads();                                            // the tables are rewritten by the next step
+}
+
 // the 32-byte path record as one 256-bit access (sm_100: LDG.E.256 / STG.E.256)
 #ifndef SHADE_STATE_PLAIN
 #define SHADE_STATE_PLAIN 0
@@ -354,7 +393,11 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
             st.state = (depth & 0xff) | (flags << 8);
             stState(pool.st + slot, st);
         }
+#if SHADE_SORT_OCTANT && !SHADE_COMPACT
+        enqueueRayByOctant(wantRay, po, rd, Q.rayO[nxt], Q.rayD[nxt], nextCounter);
+#else
         enqueueRay(wantRay, po, rd, Q.rayO[nxt], Q.rayD[nxt], nextCounter);
+#endif
         enqueueShadow(wantShadow, po, sd, sp, Q, shadowCounter);
         }
     }

@@ -235,16 +235,18 @@ __device__ __forceinline__ bool traverse(const SceneDev& S, const float3 o, cons
     return best.slot >= 0;
 }
 
-__device__ __forceinline__ void flushStats(TraceStats* stats, unsigned nNodes, unsigned nTris, unsigned nRays) {
+__device__ __forceinline__ void flushStats(TraceStats* stats, unsigned nNodes, unsigned nTris, unsigned nRays, unsigned nHits) {
     for (int off = 16; off; off >>= 1) {
         nNodes += __shfl_xor_sync(FULL, nNodes, off);
         nTris += __shfl_xor_sync(FULL, nTris, off);
         nRays += __shfl_xor_sync(FULL, nRays, off);
+        nHits += __shfl_xor_sync(FULL, nHits, off);
     }
     if ((threadIdx.x & 31) == 0) {
         atomicAdd(&stats->nodes, (unsigned long long)nNodes);
         atomicAdd(&stats->tris, (unsigned long long)nTris);
         atomicAdd(&stats->rays, (unsigned long long)nRays);
+        atomicAdd(&stats->hits, (unsigned long long)nHits);
     }
 }
 
@@ -282,7 +284,7 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned ltMask = (1u << lane) - 1u;
     const int rootLink = S.rootLink4;
-    unsigned nNodes[2] = {0, 0}, nTris[2] = {0, 0}, nRays[2] = {0, 0}, myNodes = 0, myTris = 0;
+    unsigned nNodes[2] = {0, 0}, nTris[2] = {0, 0}, nRays[2] = {0, 0}, nHits[2] = {0, 0}, myNodes = 0, myTris = 0;
 
     // warp-uniform staging state: rays [stageNext, stageEnd) of the current chunk are still unassigned
     unsigned stageNext = 0, stageEnd = 0, stageFirst = 0;  int stageAny = 0, buf = 0;
@@ -488,11 +490,11 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
                     *acc = r;
                 }
             }
-            if (COUNT) { nNodes[isAny] += myNodes;  nTris[isAny] += myTris; }
+            if (COUNT) { nNodes[isAny] += myNodes;  nTris[isAny] += myTris;  nHits[isAny] += isAny ? (occluded ? 1u : 0u) : (best.slot >= 0 ? 1u : 0u); }
             active = false;
         }
     }
-    if (COUNT) { flushStats(stats, nNodes[0], nTris[0], nRays[0]);  flushStats(stats + 1, nNodes[1], nTris[1], nRays[1]); }
+    if (COUNT) { flushStats(stats, nNodes[0], nTris[0], nRays[0], nHits[0]);  flushStats(stats + 1, nNodes[1], nTris[1], nRays[1], nHits[1]); }
 }
 
 __global__ void traceRaysDebugKernel(SceneDev S, const float4* rayO, const float4* rayD, unsigned n, float tmin, float tmax,
