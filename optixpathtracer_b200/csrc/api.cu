@@ -5,6 +5,7 @@
 #include <deque>
 #include <cstring>
 #include <cstdlib>
+#include <nvtx3/nvToolsExt.h>
 
 static thread_local std::string g_lastError;
 static int fail(const std::string& msg) { g_lastError = msg;  return -1; }
@@ -179,6 +180,14 @@ void b200pt_destroy(b200pt_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     for (int k = 0; k < B200PT_MAX_LANES; ++k) if (c->lanes[k].stream) cudaStreamSynchronize(c->lanes[k].stream);
+#ifdef B200PT_CHECKED
+    {   // the checked build's verdict for everything this process ran on the device so far
+        unsigned nt = 0, ft = 0, ns = 0, fs = 0;
+        checkedReportTrace(&nt, &ft);  checkedReportShade(&ns, &fs);
+        fprintf(stderr, "B200PT_CHECKED: trace.cu %u violations (first code %u), shade.cu %u violations (first code %u), last CUDA error: %s\n", nt, ft, ns, fs,
+                cudaGetErrorString(cudaGetLastError()));
+    }
+#endif
     bvhFree(c->bvh);
     c->dVertices.release();  c->dNormals.release();  c->dTexcoords.release();  c->dIndices.release();  c->dTriMesh.release();  c->dMeshes.release();  c->dTexels.release();
     freeAccum(c);  destroyMulti(c);
@@ -299,6 +308,7 @@ static SceneDev sceneOf(b200pt_ctx* c) {
     S.tris = c->bvh.tris;  S.meshes = c->dMeshes.p;  S.indices = c->dIndices.p;
     S.vertices = c->dVertices.p;  S.normals = c->dNormals.p;
     S.texcoords = c->dTexcoords.p;  S.texels = c->dTexels.p;  S.nTris = c->bvh.nTris;  S.nNodes = c->bvh.nNodes;
+    S.nNodes4 = c->bvh.nNodes4;  S.nMeshes = (unsigned)c->hMeshes.size();  S.nTexels = (unsigned)c->hTexels.size();  S.nVertices = (unsigned)c->hVertices.size();
     return S;
 }
 

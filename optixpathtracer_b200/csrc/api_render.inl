@@ -34,11 +34,11 @@ static void ensurePool(Lane& c, size_t slots, bool aovs) {
     c.counters.ensure(QC_STRIDE * QC_MAX_LAUNCHES + 8);                      // per-launch queue counters, then 8 frame totals
     c.stats.ensure(2);
 }
-static PathPool poolOf(Lane& L) { return PathPool{L.st.p, L.direct.p, L.indirect.p, L.alpha.p, L.aovN.p, L.aovA.p}; }
+static PathPool poolOf(Lane& L) { return PathPool{(unsigned)L.poolCap, L.st.p, L.direct.p, L.indirect.p, L.alpha.p, L.aovN.p, L.aovA.p}; }
 static Queues queuesOf(Lane& L) {
     Queues Q;
     for (int i = 0; i < 2; ++i) { Q.rayO[i] = L.rayO[i].p;  Q.rayD[i] = L.rayD[i].p; }
-    Q.hit = L.hit.p;  Q.shO = L.shO.p;  Q.shD = L.shD.p;  Q.shP = L.shP.p;  Q.counters = L.counters.p;
+    Q.hit = L.hit.p;  Q.shO = L.shO.p;  Q.shD = L.shD.p;  Q.shP = L.shP.p;  Q.counters = L.counters.p;  Q.cap = (unsigned)L.poolCap;
     return Q;
 }
 // lane k > 0 gets its stream and `done` event on first use
@@ -49,16 +49,23 @@ static Lane& laneOf(b200pt_ctx* c, int k) {
     return L;
 }
 
-struct StageTimer {          // CUDA-event pairs per stage, resolved after the frame (profile=1 only)
+// NVTX ranges (SURVEY §5 tracing row): one per render() call and one per stage of a wavefront, around the host-side submission of that stage's
+// launches - what a timeline tool (Nsight Systems) needs to attribute the kernels of overlapping frames.  Header-only nvtx3: a no-op costing a few
+// nanoseconds per call when no tool is attached.
+static const char* const kStageName[] = {"b200pt raygen", "b200pt trace", "b200pt trace (shadow tail)", "b200pt shade", "b200pt accumulate", "b200pt frame"};
+struct NvtxRange { explicit NvtxRange(const char* name) { nvtxRangePushA(name); }  ~NvtxRange() { nvtxRangePop(); } };
+
+struct StageTimer {          // NVTX range per stage; CUDA-event pairs per stage, resolved after the frame (profile=1 only)
     b200pt_ctx* c;  bool on;
     void begin(int stage, cudaEvent_t& a, cudaEvent_t& b) {
+        if (stage != 5 /* ST_TOTAL: spans two functions, see render() */) nvtxRangePushA(kStageName[stage]);
         if (!on) return;
         while (c->evPool.size() < c->evNext + 2) { cudaEvent_t e;  CUDA_OK(cudaEventCreate(&e));  c->evPool.push_back(e); }
         a = c->evPool[c->evNext++];  b = c->evPool[c->evNext++];
         c->evUsed.push_back({stage, {a, b}});
         CUDA_OK(cudaEventRecord(a, c->stream));
     }
-    void end(cudaEvent_t b) { if (on) CUDA_OK(cudaEventRecord(b, c->stream)); }
+    void end(cudaEvent_t b, bool stageRange = true) { if (on) CUDA_OK(cudaEventRecord(b, c->stream));  if (stageRange) nvtxRangePop(); }
 };
 enum { ST_RAYGEN = 0, ST_TRACE, ST_TRACE_TAIL, ST_SHADE, ST_ACCUM, ST_TOTAL };
 
@@ -285,7 +292,7 @@ static void enqueueFinalize(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& j
         launchFinalize(job.F, p.P, L.sumRad.p, L.sumAlpha.p, L.sumNormal.p, L.sumAlbedo.p, s);  ++job.launches;
     }
     T.end(b);
-    T.end(job.totalEnd);
+    T.end(job.totalEnd, false);
     CUDA_OK(cudaGetLastError());
     CUDA_OK(cudaEventRecord(L.done, s));
     c->lastLane = job.lane;  c->countersLane = job.lane;  c->countersExtra = job.extraLanes;  L.busy = job.lane > 0;
@@ -299,6 +306,7 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
     if (!c || !params || !cfgp) throw std::runtime_error("b200pt_render: null argument");
     if (params->frame.size.x == 0) return;                                       // SimplePathtracer.cpp:81
     const b200pt_config cfg = *cfgp;
+    NvtxRange frameRange(sync ? "b200pt_render" : "b200pt_render_async");
     CUDA_OK(cudaSetDevice(c->device));
     if (!c->built) throw std::runtime_error("b200pt_render: b200pt_build_accel has not been called");
     if (!params->probe.data || !params->probe.cdfValuesX) throw std::runtime_error("b200pt_render: no probe set (call b200pt_set_probe)");

@@ -70,6 +70,7 @@ struct SceneDev {                  // everything the kernels need about the scen
     const float3* normals;         // global, per vertex (zeros where a mesh has none)
     const uint32_t* texels;        // RGBA8 pool
     unsigned nTris, nNodes;
+    unsigned nNodes4, nMeshes, nTexels, nVertices;   // array sizes (B200PT_CHECKED builds bounds-check against them)
 };
 
 struct PassParams {                // one optixLaunch of the reference = one pass of the wavefront
@@ -109,6 +110,7 @@ struct PathState {
 static_assert(sizeof(PathState) == 32, "PathState must be one 32-byte sector");
 
 struct PathPool {                  // path state indexed by sample slot
+    unsigned cap;                  // slots allocated (= capacity of every ray queue)
     PathState* st;
     float4* direct;                // radiance added at depth 0
     float4* indirect;              // radiance added at depth >= 1, in bounce order
@@ -129,10 +131,26 @@ struct Queues {
     float4* hit;
     float4* shO;  float4* shD;  float4* shP;
     unsigned* counters;                      // per trace launch d: counters[QC_STRIDE*d + QC_*]
+    unsigned cap;                            // entries allocated per queue
 };
 // trace launch d of a frame handles the extension rays of bounce d and the shadow rays emitted by shade pass d-1; QC_HEAD / QC_SHEAD are the
 // work tickets of trace launch d / shade pass d
 enum { QC_RAYS = 0, QC_SHADOWS = 1, QC_HEAD = 2, QC_SHEAD = 3, QC_STRIDE = 4, QC_MAX_LAUNCHES = 208 };
+
+// ---- B200PT_CHECKED builds (tools/build_variant.sh checked -DB200PT_CHECKED): compute-sanitizer is closed on the GPU pool, so the kernels carry
+// their own bounds checks: every index into a queue, the path pool, the traversal stack, the node / triangle / mesh / texel arrays goes through
+// CHK(condition, code); a violation is counted (per .cu file, first code kept), the access is skipped or redirected to element 0, and
+// b200pt_destroy prints the totals.  In normal builds CHK(c, k) is the constant `true` and costs nothing.
+#ifdef B200PT_CHECKED
+#define CHK_DECL static __device__ unsigned g_chkCount, g_chkFirst; \
+    static __device__ __noinline__ void chkFail(unsigned code) { if (atomicAdd(&g_chkCount, 1u) == 0u) g_chkFirst = code; }
+#define CHK(cond, code) ((cond) ? true : (chkFail(code), false))
+#else
+#define CHK_DECL
+#define CHK(cond, code) true
+#endif
+void checkedReportTrace(unsigned* count, unsigned* first);   // trace.cu / shade.cu: this file's violation count (0, 0 in normal builds)
+void checkedReportShade(unsigned* count, unsigned* first);
 
 struct TraceStats { unsigned long long nodes, tris, rays, hits; };      // hits: closest-hit rays that found a surface ([0]) / occluded shadow rays ([1])
 

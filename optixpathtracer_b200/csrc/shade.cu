@@ -6,6 +6,7 @@
 //   tonemapSqrtKernel  computeFinalPixelColorsKernel, sv4/toneMap.cu:41-58
 // All HBM-streaming / gather bound; compiled with -fmad=false (see shade_math.cuh).
 #include "shade_math.cuh"
+CHK_DECL          // B200PT_CHECKED builds: violation counter of this file (codes 20-39)
 
 #ifndef SHADE_HOIST_THR
 #define SHADE_HOIST_THR 1
@@ -27,13 +28,13 @@ DEV unsigned enqueueSlot(bool want, unsigned* counter) {
     base = __shfl_sync(0xffffffffu, base, __ffs(mask) - 1);
     return base + __popc(mask & ((1u << lane) - 1u));
 }
-DEV void enqueueRay(bool want, float4 o, float4 d, float4* qo, float4* qd, unsigned* counter) {
+DEV void enqueueRay(bool want, float4 o, float4 d, float4* qo, float4* qd, unsigned* counter, unsigned cap) {
     const unsigned q = enqueueSlot(want, counter);
-    if (want) { qo[q] = o;  qd[q] = d; }
+    if (want && CHK(q < cap, 20)) { qo[q] = o;  qd[q] = d; }
 }
 DEV void enqueueShadow(bool want, float4 o, float4 d, float4 p, const Queues& Q, unsigned* counter) {
     const unsigned q = enqueueSlot(want, counter);
-    if (want) { Q.shO[q] = o;  Q.shD[q] = d;  Q.shP[q] = p; }
+    if (want && CHK(q < Q.cap, 21)) { Q.shO[q] = o;  Q.shD[q] = d;  Q.shP[q] = p; }
 }
 
 // Block-level append with the block's rays grouped by direction octant (SHADE_SORT_OCTANT): the up-to-SHADE_BLOCK continuation rays of one
@@ -43,7 +44,7 @@ DEV void enqueueShadow(bool want, float4 o, float4 d, float4 p, const Queues& Q,
 #ifndef SHADE_SORT_OCTANT
 #define SHADE_SORT_OCTANT 0
 #endif
-DEV void enqueueRayByOctant(bool want, float4 o, float4 d, float4* qo, float4* qd, unsigned* counter) {
+DEV void enqueueRayByOctant(bool want, float4 o, float4 d, float4* qo, float4* qd, unsigned* counter, unsigned cap) {
     __shared__ unsigned warpCount[SHADE_BLOCK / 32][8];
     __shared__ unsigned binBase[8];
     __shared__ unsigned blockBase;
@@ -70,7 +71,7 @@ DEV void enqueueRayByOctant(bool want, float4 o, float4 d, float4* qo, float4* q
         unsigned before = 0;
         for (unsigned w = 0; w < warp; ++w) before += warpCount[w][key];
         const unsigned q = blockBase + binBase[key] + before + rank;
-        qo[q] = o;  qd[q] = d;
+        if (CHK(q < cap, 20)) { qo[q] = o;  qd[q] = d; }
     }
     __syncthreads();                                            // the tables are rewritten by the next step
 }
@@ -148,7 +149,7 @@ raygenKernel(FrameParams F, PassParams P, int k0, int k1, PathPool pool, Queues 
         if (t < total && lx < (unsigned)P.launchW && ly < (unsigned)P.launchH) {
             const unsigned li = ly * (unsigned)P.launchW + lx, k = (unsigned)k0 + t % kc;
             const LaunchIdx L = decodeLaunch(F, P, li);
-            if (L.live) {
+            if (L.live && CHK(P.slotBase + li * kc + (k - (unsigned)k0) < pool.cap, 22)) {
                 const unsigned slot = P.slotBase + li * kc + (k - (unsigned)k0);       // chunk-local slot
                 unsigned seed = lcgSkip(L.seed0, 2 * (int)k);
                 Rng r;  r.seed(seed);                                             // prd.rand = Random(seed), :445
@@ -165,7 +166,7 @@ raygenKernel(FrameParams F, PassParams P, int k0, int k1, PathPool pool, Queues 
                 want = true;
             }
         }
-        enqueueRay(want, o4, d4, Q.rayO[0], Q.rayD[0], Q.counters + QC_RAYS);
+        enqueueRay(want, o4, d4, Q.rayO[0], Q.rayD[0], Q.counters + QC_RAYS, Q.cap);
     }
 }
 
@@ -178,6 +179,7 @@ DEV float3 sampleTexture(const SceneDev& S, const MeshInfo* M, float s, float t)
     int i0 = (int)fx, j0 = (int)fy, i1 = i0 + 1, j1 = j0 + 1;
     // wrap: x is in [-0.5, W - 0.5], so i0 is in [-1, W - 1] and i1 in [0, W] (same for j): one conditional add replaces the modulo
     i0 += i0 < 0 ? W : 0;  i1 -= i1 >= W ? W : 0;  j0 += j0 < 0 ? H : 0;  j1 -= j1 >= H ? H : 0;
+    if (!CHK((size_t)M->texOffset + (size_t)max(j0, j1) * W + max(i0, i1) < S.nTexels && min(i0, j0) >= 0, 26)) return f3(0.f);
     const uint32_t* px = S.texels + M->texOffset;
     const uint32_t p00 = __ldg(px + (size_t)j0 * W + i0), p10 = __ldg(px + (size_t)j0 * W + i1);
     const uint32_t p01 = __ldg(px + (size_t)j1 * W + i0), p11 = __ldg(px + (size_t)j1 * W + i1);
@@ -249,7 +251,7 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
 #endif
         bool wantRay = false, wantShadow = false;
         float4 po = make_float4(0, 0, 0, 0), rd = po, sd = po, sp = po;     // po = {P, slot}: origin record of both the continuation and the shadow ray
-        if (mine) {
+        if (mine && CHK(i < Q.cap && (unsigned)__float_as_int(rayOq[i].w) < pool.cap && __float_as_int(Q.hit[i].w) < (int)S.nTris, 23)) {
             const float4 o4 = rayOq[i], d4 = rayDq[i], h = Q.hit[i];         // {o, slot} {d, -} {t, u, v, triSlot}
             const unsigned slot = (unsigned)__float_as_int(o4.w);
             const int triSlot = __float_as_int(h.w);
@@ -280,7 +282,7 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                 probeSample(F.probe, F.probeGuide, wi, skyColor, skyPdf, rng);
                 const float3 e1 = f3(ta.w, tb.x, tb.y), e2 = f3(tb.z, tb.w, tc.x);
                 const unsigned gid = (unsigned)__float_as_int(tc.y);
-                const MeshInfo* M = S.meshes + __float_as_int(tc.z);
+                const MeshInfo* M = S.meshes + (CHK((unsigned)__float_as_int(tc.z) < S.nMeshes && gid < S.nTris, 24) ? __float_as_int(tc.z) : 0);
                 const Material& mat = M->material;
                 const float3 N0 = normalize3(cross3(e1, e2));                     // :603
                 const float3 wo = -dir;
@@ -296,8 +298,10 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                     if (M->textureID >= 0 && M->hasTexcoord) {
                         const unsigned* ip = reinterpret_cast<const unsigned*>(S.indices + gid);
                         const uint3 id = make_uint3(__ldg(ip), __ldg(ip + 1), __ldg(ip + 2));
-                        const float2 t0 = __ldg(S.texcoords + M->firstVertex + id.x), t1 = __ldg(S.texcoords + M->firstVertex + id.y),
-                                     t2 = __ldg(S.texcoords + M->firstVertex + id.z);
+                        const bool tcOk = CHK(M->firstVertex + max(id.x, max(id.y, id.z)) < S.nVertices, 25);      // (a violation reads vertex 0 instead)
+                        const unsigned fv = tcOk ? M->firstVertex : 0u;
+                        const float2 t0 = __ldg(S.texcoords + fv + (tcOk ? id.x : 0u)), t1 = __ldg(S.texcoords + fv + (tcOk ? id.y : 0u)),
+                                     t2 = __ldg(S.texcoords + fv + (tcOk ? id.z : 0u));
                         const float w0 = 1.f - h.y - h.z;
                         albedo = sampleTexture(S, M, w0 * t0.x + h.y * t1.x + h.z * t2.x, w0 * t0.y + h.y * t1.y + h.z * t2.y);
                     }
@@ -394,9 +398,9 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
             stState(pool.st + slot, st);
         }
 #if SHADE_SORT_OCTANT && !SHADE_COMPACT
-        enqueueRayByOctant(wantRay, po, rd, Q.rayO[nxt], Q.rayD[nxt], nextCounter);
+        enqueueRayByOctant(wantRay, po, rd, Q.rayO[nxt], Q.rayD[nxt], nextCounter, Q.cap);
 #else
-        enqueueRay(wantRay, po, rd, Q.rayO[nxt], Q.rayD[nxt], nextCounter);
+        enqueueRay(wantRay, po, rd, Q.rayO[nxt], Q.rayD[nxt], nextCounter, Q.cap);
 #endif
         enqueueShadow(wantShadow, po, sd, sp, Q, shadowCounter);
         }
@@ -421,6 +425,7 @@ gatherKernel(FrameParams F, PassParams P, int k0, int k1, PathPool pool, float4*
     }
     for (int k = k0; k < k1; ++k) {
         const unsigned slot = P.slotBase + li * (unsigned)(k1 - k0) + (unsigned)(k - k0);
+        if (!CHK(slot < pool.cap, 27)) break;
         const float4 d = pool.direct[slot], i = pool.indirect[slot], a = pool.alpha[slot];
         result = result + (f3(d.x, d.y, d.z) + f3(i.x, i.y, i.z));
         alpha = alpha + f3(a.x, a.y, a.z);
@@ -471,6 +476,7 @@ finalizeKernel(FrameParams F, PassParams P, const float4* sumRad, const float4* 
             unsigned iy = L.ly * P.factorY + (unsigned)j + P.offY;
             ix = min(ix, (unsigned)(F.W - 1));  iy = min(iy, (unsigned)(F.H - 1));      // :534
             const unsigned image_index = iy * (unsigned)F.W + ix;
+            if (!CHK(image_index < (unsigned)F.W * (unsigned)F.H, 28)) continue;
             float3 acc = fresh;
             if (F.accumMode == B200PT_ACCUM_SUM) {
                 const float3 c = P.subframe > 0 ? clamp3(acc, 0.0f, 10.0f) : acc;
@@ -648,6 +654,13 @@ static float* noallocRowTotalAddress() {                     // the current devi
 void launchProbeCdfNoAlloc(const float4* data, int W, int H, float* pdfX, float* cdfX, float* pdfY, float* cdfY, cudaStream_t s) {
     if (H > B200PT_NOALLOC_MAX_ROWS) throw std::runtime_error("b200pt_build_cdf_noalloc: height exceeds B200PT_NOALLOC_MAX_ROWS");
     launchProbeCdf(data, W, H, pdfX, cdfX, pdfY, cdfY, noallocRowTotalAddress(), s);
+}
+
+void checkedReportShade(unsigned* count, unsigned* first) {
+    *count = 0;  *first = 0;
+#ifdef B200PT_CHECKED
+    cudaMemcpyFromSymbol(count, g_chkCount, sizeof(unsigned));  cudaMemcpyFromSymbol(first, g_chkFirst, sizeof(unsigned));
+#endif
 }
 
 // ---- launchers ---------------------------------------------------------------------------------------------

@@ -16,6 +16,7 @@
 // The ray/triangle test is the exact fp32 operation sequence of oracle/scene_core.h (no FMA contraction,
 // enforced with __f*_rn intrinsics), which makes the chosen triangle and (t,u,v) BVH-independent.
 #include "common.cuh"
+CHK_DECL          // B200PT_CHECKED builds: violation counter of this file (codes 10-19)
 
 #ifndef TRACE_BLOCK
 #define TRACE_BLOCK 128
@@ -175,7 +176,7 @@ struct Best { float t, u, v; int slot; unsigned gid; };
 // branch around the LDL (2.85 against 2.76 ms per frame); entry distances stored beside the links and stale entries culled on pop (node visits
 // per ray 14.8 -> 14.0, but 3.28 ms: the second array doubles the stack's L1 traffic).
 #define STACK_DECL_ int stack[B200PT_STACK];  int sp = 0;
-#define PUSH_IF_(x, c) { if (c) stack[sp++] = (x); }
+#define PUSH_IF_(x, c) { if ((c) && CHK(sp < B200PT_STACK, 11)) stack[sp++] = (x); }
 #define POP_IF_(dst, c) { if (c) dst = sp ? stack[--sp] : EMPTY; }
 #define POP_(dst) POP_IF_(dst, true)
 
@@ -184,7 +185,7 @@ struct Best { float t, u, v; int slot; unsigned gid; };
 #define CEX_(ta, la, tb, lb) { const bool s_ = tb < ta;  const float tt_ = s_ ? tb : ta;  const int ll_ = s_ ? lb : la;  tb = s_ ? ta : tb;  lb = s_ ? la : lb;  ta = tt_;  la = ll_; }
 #define NODE_STEP4()                                                                             \
     {                                                                                            \
-        const uint4* np_ = S.nodes4 + 4 * (size_t)cur;                                           \
+        const uint4* np_ = S.nodes4 + 4 * (size_t)(CHK((unsigned)cur < S.nNodes4, 12) ? cur : 0);   \
         const Node8 A_ = ldgNode(np_), B_ = ldgNode(np_ + 2);                                    \
         float t0_, t1_, t2_, t3_;                                                                \
         const bool h0_ = boxTest(A_.w[0], A_.w[1], A_.w[2], g, tmin, best.t, t0_);               \
@@ -217,7 +218,7 @@ __device__ __forceinline__ bool traverse(const SceneDev& S, const float3 o, cons
             unsigned first, count;
             leafDecode(cur, first, count);
             for (unsigned k = 0; k < count; ++k) {
-                const float4* tp = S.tris + 3 * (size_t)(first + k);
+                const float4* tp = S.tris + 3 * (size_t)(CHK(first + k < S.nTris, 13) ? first + k : 0u);
                 const float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
                 if (COUNT) nTris += 1;
                 TriHit h;
@@ -354,7 +355,8 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
                 const unsigned r = __popc(idle & ltMask);
                 if (!active && r < avail) {
                     const unsigned j = stageNext + r;
-                    const float4 o4 = stageO[warp][buf][j - stageFirst], d4 = stageD[warp][buf][j - stageFirst];
+                    const unsigned sj_ = CHK(j - stageFirst < 32u, 15) ? j - stageFirst : 0u;
+                    const float4 o4 = stageO[warp][buf][sj_], d4 = stageD[warp][buf][sj_];
                     o = make_float3(o4.x, o4.y, o4.z);  d = make_float3(d4.x, d4.y, d4.z);  wO = o4.w;  wD = d4.w;
                     g = makeGridRay(S, o, d);
                     rayIdx = j;  active = true;  isAny = stageAny != 0;  tmin = isAny ? tminS : tminC;
@@ -415,7 +417,7 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
 #else
                     const unsigned slot_ = k < cntA ? firstA + k : firstB + (k - cntA);
 #endif
-                    const float4* tp = S.tris + 3 * (size_t)slot_;
+                    const float4* tp = S.tris + 3 * (size_t)(CHK(slot_ < S.nTris, 13) ? slot_ : 0u);
                     const float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
                     if (COUNT) myTris += 1;
                     float det, U, V, Tn;
@@ -442,7 +444,7 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
                 leafDecode(leaf, first, cnt);
                 const bool cull = isAny && cullBack != 0;
                 for (unsigned k = 0; k < cnt; ++k) {
-                    const float4* tp = S.tris + 3 * (size_t)(first + k);
+                    const float4* tp = S.tris + 3 * (size_t)(CHK(first + k < S.nTris, 13) ? first + k : 0u);
                     const float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
                     if (COUNT) myTris += 1;
                     float det, U, V, Tn;
@@ -471,12 +473,12 @@ traceKernel(SceneDev S, const float4* __restrict__ rayO, const float4* __restric
             if (!isAny) {
                 // best.u/best.v hold the undivided U, V of the winning triangle: same quotients as dividing at hit time
                 const bool got = best.slot >= 0;
-                hit[rayIdx] = make_float4(best.t, got ? __fdiv_rn(best.u, bestDet) : 0.f, got ? __fdiv_rn(best.v, bestDet) : 0.f, __int_as_float(best.slot));
+                if (CHK(rayIdx < countC && rayIdx < pool.cap, 10)) hit[rayIdx] = make_float4(best.t, got ? __fdiv_rn(best.u, bestDet) : 0.f, got ? __fdiv_rn(best.v, bestDet) : 0.f, __int_as_float(best.slot));
             } else {
                 // prd.radiance += pathThroughput * lightSample (sv4/deviceProgram.cu:659) resolved here.  Target 2 = alpha
                 // when OCCLUDED (shadow catcher, :663-664).  Single writer per slot per launch => deterministic.
                 const int target = __float_as_int(wD);
-                if (occluded == (target == 2)) {
+                if (occluded == (target == 2) && CHK(rayIdx < countS && (unsigned)__float_as_int(wO) < pool.cap && (unsigned)target <= 2u, 14)) {
                     const unsigned slot = (unsigned)__float_as_int(wO);
                     float4* acc = (target == 0 ? pool.direct : (target == 1 ? pool.indirect : pool.alpha)) + slot;
 #if TRACE_STREAM_BYPASS_L1
@@ -511,6 +513,13 @@ __global__ void traceRaysDebugKernel(SceneDev S, const float4* rayO, const float
         traverse<false, false>(S, make_float3(o4.x, o4.y, o4.z), make_float3(d4.x, d4.y, d4.z), tmin, tmax, false, b, a, c);
         hitOut[i] = make_float4(b.t, b.u, b.v, __int_as_float(b.slot));
     }
+}
+
+void checkedReportTrace(unsigned* count, unsigned* first) {
+    *count = 0;  *first = 0;
+#ifdef B200PT_CHECKED
+    cudaMemcpyFromSymbol(count, g_chkCount, sizeof(unsigned));  cudaMemcpyFromSymbol(first, g_chkFirst, sizeof(unsigned));
+#endif
 }
 
 static int refillThreshold() {
