@@ -723,7 +723,8 @@ def run_b200(a):
                               "+ 32 B x continuation rays + 48 B x shadow rays, / the CUDA-event time of the frame's shade launches; the material records and probe guide "
                               "tables are cache-resident, so DRAM traffic (traffic, dram_frac) is below the algorithmic figure"}
         # (3) gather + finalize: 48 B per sample (direct, indirect, alpha) in, 2 x 32 B per launch index through the per-launch-index sums, 36 B per pixel (accum r/w + RGBA8)
-        acc_bytes = 48.0 * rays["samples"] / max(1, a.steps) + (64 + 36) * n_px
+        aov = 1 if cfg.write_aovs else 0                                            # the `orig` preset also writes the normal / albedo / colour AOVs (orig/deviceProgram.cu:472-474)
+        acc_bytes = (48.0 + 32.0 * aov) * rays["samples"] / max(1, a.steps) + (64 + 36 + aov * (64 + 48)) * n_px
         g_ncu, g_fr = ncu_of("gatherKernel")
         f_ncu, f_fr = ncu_of("finalizeKernel")
         acc_gbs = acc_bytes / (st["accumulate"] * 1e-3) / 1e9
@@ -732,8 +733,9 @@ def run_b200(a):
                     "dram_frac_gather": g_fr["dram_frac"], "dram_frac_finalize": f_fr["dram_frac"], "ncu_gather": g_ncu, "ncu_finalize": f_ncu, "traffic_source": src,
                     "algorithmic_bytes_per_step": acc_bytes, "ms_per_step": st["accumulate"],
                     "note": "48 B per sample read by gatherKernel + 32 B written / 32 B read per launch index (per-launch-index sums) + 36 B per pixel in finalizeKernel "
-                            "(16 B accumulation read, 16 B written, 4 B RGBA8), / the CUDA-event time of the two launches (tens of microseconds each: launch ramp and tail are a "
-                            "visible share of a kernel this short)"}
+                            "(16 B accumulation read, 16 B written, 4 B RGBA8); with AOVs (preset orig) + 32 B per sample, + 64 B per launch index, + 48 B per pixel; / the "
+                            "CUDA-event time of the two launches (tens of microseconds each: launch ramp and tail are a visible share of a kernel this short); "
+                            "dram_frac_* = measured DRAM bytes / duration / HBM peak of each kernel under ncu"}
         parallelism = "single GPU" if world == 1 else (f"sample split over {world} GPUs (rank r renders sub-frames r, r+N, ...), one NCCL fp32 reduce of the SUM buffer "
                                                         "+ resolve on rank 0 inside the timed region (b200pt_reduce_sum)")
         e2e_note = (f"setCamera + render() (blocking) + downloadPixels() into pinned host memory every step, the reference's call sequence; cfg.frames_in_flight = {a.in_flight}: while "

@@ -16,6 +16,7 @@
 #include <memory>
 #include <random>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../include/ref_api/SimplePathtracer.h"
@@ -105,9 +106,86 @@ static void dumpModel(const Model* m, const char* path) {    // flat binary for 
     fclose(f);
 }
 
+// --ranks N: the multi-GPU driver below Python.  One host thread and one SampleRenderer per GPU in this process, the scene replicated, the frame
+// partitioned by samples (--split sample: rank r renders sub-frames r, r+N, ..., ONE fp32 SUM reduce + resolve on rank 0) or by 32-row bands
+// (--split tile: every frame gathered to rank 0).  The collectives are the library's (b200pt_reduce_sum / b200pt_gather_bands over NCCL); the
+// 128-byte NCCL id is shared through this process' memory.  Prints the checksum of rank 0's final image, comparable with a single-GPU run.
+static int multiMain(const Model* model, const ProbeData& probe, const sutil::Camera& camera, const std::string& preset, int W, int H, int frames, int spl,
+                     int ranks, bool tileSplit, const std::string& out) {
+    unsigned char uid[B200PT_UNIQUE_ID_BYTES];
+    SampleRenderer::commUniqueId(uid);
+    std::vector<std::string> errors(ranks);
+    std::vector<uint32_t> px((size_t)W * H);
+    std::vector<double> seconds(ranks, 0.0);
+    unsigned long long samples0 = 0;
+    auto worker = [&](int rank) {
+        try {
+            SampleRenderer sample(model, rank, preset.c_str());
+            sample.setCamera(camera);
+            sample.resize(int2{W, H});
+            sample.setProbe(probe);
+            sample.launchParams.samples_per_launch = spl;
+            sample.commInit(ranks, rank, uid);
+            sample.config.frames_in_flight = tileSplit ? 1 : 3;
+            if (tileSplit) { sample.config.tile_rank = rank;  sample.config.tile_count = ranks; }
+            else sample.config.accum_mode = B200PT_ACCUM_SUM;
+            sample.clearAccum();
+            sample.synchronize();
+            const auto t0 = std::chrono::steady_clock::now();
+            if (tileSplit) {
+                for (int f = 0; f < frames; ++f) {                                  // every rank renders its bands of the SAME sub-frame
+                    sample.launchParams.frame.subframe_index = f;
+                    sample.setCamera(camera);
+                    sample.renderAsync();
+                    sample.gatherBands(0, true, true);
+                    sample.synchronize();
+                }
+            } else {
+                const int total = (frames / ranks) * ranks;
+                for (int f = rank; f < total; f += ranks) {                         // rank r renders sub-frames r, r+N, ...
+                    sample.launchParams.frame.subframe_index = f;
+                    sample.setCamera(camera);
+                    sample.renderAsync();
+                }
+                sample.reduceSum(total, 0, false);
+                sample.synchronize();
+            }
+            seconds[rank] = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+            if (rank == 0) { sample.downloadPixels(px.data());  samples0 = sample.counters().samples; }
+            sample.commDestroy();
+        } catch (const std::exception& e) { errors[rank] = e.what(); }
+    };
+    std::vector<std::thread> threads;
+    for (int r = 0; r < ranks; ++r) threads.emplace_back(worker, r);
+    for (auto& t : threads) t.join();
+    for (int r = 0; r < ranks; ++r) if (!errors[r].empty()) { fprintf(stderr, "rank %d: %s\n", r, errors[r].c_str());  return 1; }
+    double slowest = 0.0;
+    for (double s : seconds) slowest = std::max(slowest, s);
+    const int done = tileSplit ? frames : (frames / ranks) * ranks;
+    printf("%d ranks, %s split: %d frames in %.3f s (slowest rank): %.2f frames/s, %.1f Msamples/s\n", ranks, tileSplit ? "tile" : "sample", done, slowest,
+           done / slowest, (double)W * H * spl * done / slowest / 1e6);
+    (void)samples0;
+    unsigned long long sum = 0;
+    for (uint32_t p : px) sum += p & 0xffffffu;
+    printf("pixel checksum %llu\n", sum);
+    if (!out.empty()) {
+        std::vector<unsigned char> rgb((size_t)W * H * 3);
+        for (int y = 0; y < H; ++y)
+            for (int x = 0; x < W; ++x) {
+                const uint32_t p = px[(size_t)(H - 1 - y) * W + x];
+                unsigned char* q = &rgb[((size_t)y * W + x) * 3];
+                q[0] = (unsigned char)p;  q[1] = (unsigned char)(p >> 8);  q[2] = (unsigned char)(p >> 16);
+            }
+        writePNG(out, W, H, rgb);
+    }
+    return 0;
+}
+
 int main(int argc, char** argv) {
     std::string obj, preset = "sv4_fov", cam = "cornell", out, log, dump, hdr, dumpProbe;
-    int W = 1280, H = 720, frames = 16, boxes = 64, spl = 1, inFlight = 1;
+    int W = 1280, H = 720, frames = 16, boxes = 64, spl = 1, inFlight = 1, ranks = 1;
+    std::string split = "sample";
+    bool splitGiven = false;
     float3 sky{1.f, 1.f, 1.f};
     bool noRender = false, gpuCdf = false, whitted = false, async = false;
     for (int i = 1; i < argc; ++i) {
@@ -120,6 +198,8 @@ int main(int argc, char** argv) {
         else if (a == "--size") { if (sscanf(next(), "%dx%d", &W, &H) != 2) { fprintf(stderr, "--size WxH\n");  return 2; } }
         else if (a == "--frames") frames = atoi(next());
         else if (a == "--spl") spl = atoi(next());
+        else if (a == "--ranks") ranks = atoi(next());             // one thread + one renderer per GPU, collectives in the library (multiMain)
+        else if (a == "--split") { split = next();  splitGiven = true; }   // sample | tile (given explicitly, also runs with --ranks 1: a one-rank communicator)
         else if (a == "--in-flight") inFlight = atoi(next());      // b200pt_config.frames_in_flight: render() starts the predicted next sub-frames before it blocks
         else if (a == "--async") async = true;                     // with --in-flight N: submit frames through renderAsync() and synchronize once at the end
         else if (a == "--sky") { if (sscanf(next(), "%f,%f,%f", &sky.x, &sky.y, &sky.z) != 3) { fprintf(stderr, "--sky r,g,b\n");  return 2; } }
@@ -152,6 +232,13 @@ int main(int argc, char** argv) {
         }
         if (noRender) return 0;
         sutil::Camera camera = cameraPreset(cam);                                                           // :213-217
+        if (ranks > 1 || splitGiven) {
+            if (split != "sample" && split != "tile") throw std::runtime_error("--split sample|tile");
+            if (gpuCdf || !probe.valid) throw std::runtime_error("--ranks needs a host-built probe (no --gpu-cdf)");
+            const int rc = multiMain(model.get(), probe, camera, preset, W, H, frames, spl, ranks, split == "tile", out);
+            delete[] probe.data;  delete[] probe.pdfValuesX;  delete[] probe.cdfValuesX;  delete[] probe.pdfValuesY;  delete[] probe.cdfValuesY;
+            return rc;
+        }
         SampleRenderer sample(model.get(), 0, preset.c_str());                                              // :252
         sample.setCamera(camera);                                                                           // :253 (before resize, like the reference)
         sample.resize(int2{W, H});                                                                          // :256-262

@@ -115,6 +115,16 @@ public:
                                     {lightPos.x, lightPos.y, lightPos.z}};
         if (b200pt_render_whitted(ctx, &wp, nullptr) != 0) fail();
     }
+    // Multi-GPU (no reference counterpart: sv4/main.cpp:289-290 "for nvlink configuration ... currently no support"): one SampleRenderer per GPU
+    // (one host thread or process each), the scene replicated, ONE collective per frame partition, issued by the library (NCCL) on `stream`.
+    //   sample split: config.accum_mode = B200PT_ACCUM_SUM, rank r renders sub-frames r, r+N, ..., then reduceSum(passes) -> image on `root`
+    //   tile split  : config.tile_rank = r, config.tile_count = N (uniform schedules), render the SAME sub-frame, then gatherBands() -> image on `root`
+    static void commUniqueId(unsigned char id[B200PT_UNIQUE_ID_BYTES]) { if (b200pt_comm_unique_id(id) != 0) fail(); }
+    void commInit(int nRanks, int rank, const unsigned char id[B200PT_UNIQUE_ID_BYTES]) { if (b200pt_comm_init(ctx, nRanks, rank, id, &launchParams) != 0) fail(); }
+    void commDestroy() { if (b200pt_comm_destroy(ctx, &launchParams) != 0) fail(); }
+    void reduceSum(int nPasses, int root = 0, bool keepLocal = false) { if (b200pt_reduce_sum(ctx, &launchParams, &config, root, nPasses, keepLocal ? 1 : 0) != 0) fail(); }
+    void gatherBands(int root = 0, bool frame = true, bool accum = false) { if (b200pt_gather_bands(ctx, &launchParams, root, (frame ? 1 : 0) | (accum ? 2 : 0)) != 0) fail(); }
+    void clearAccum() { if (b200pt_clear_accum(ctx) != 0) fail(); }
     // animated geometry: new positions for mesh `meshID` (same count), then refit (topology kept) or a full rebuild
     void updateVertices(int meshID, const std::vector<float3>& vertex) {
         if (b200pt_update_vertices(ctx, meshID, reinterpret_cast<const float*>(vertex.data()), vertex.size()) != 0) fail();

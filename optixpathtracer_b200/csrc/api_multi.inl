@@ -23,28 +23,28 @@ struct NcclApi {
     ncclResult_t (*GroupStart)() = nullptr;
     ncclResult_t (*GroupEnd)() = nullptr;
 };
-static NcclApi& ncclApi() {
-    static NcclApi a;
-    static bool tried = false;
-    if (!tried) {
-        tried = true;
-        const char* names[] = {"libnccl.so.2", "libnccl.so"};
-        for (const char* n : names) { a.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);  if (a.lib) break; }
-        if (a.lib) {
-            bool ok = true;
-            auto sym = [&](const char* name, bool required) -> void* { void* p = dlsym(a.lib, name);  if (!p && required) ok = false;  return p; };
+static NcclApi loadNcclApi() {
+    NcclApi a;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char* n : names) { a.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);  if (a.lib) break; }
+    if (a.lib) {
+        bool ok = true;
+        auto sym = [&](const char* name, bool required) -> void* { void* p = dlsym(a.lib, name);  if (!p && required) ok = false;  return p; };
 #define B200PT_NCCL_SYM(field, name, req) a.field = reinterpret_cast<decltype(a.field)>(sym(name, req))
-            B200PT_NCCL_SYM(GetVersion, "ncclGetVersion", true);  B200PT_NCCL_SYM(GetUniqueId, "ncclGetUniqueId", true);
-            B200PT_NCCL_SYM(CommInitRank, "ncclCommInitRank", true);  B200PT_NCCL_SYM(CommDestroy, "ncclCommDestroy", true);
-            B200PT_NCCL_SYM(GetErrorString, "ncclGetErrorString", true);  B200PT_NCCL_SYM(Reduce, "ncclReduce", true);
-            B200PT_NCCL_SYM(Send, "ncclSend", true);  B200PT_NCCL_SYM(Recv, "ncclRecv", true);
-            B200PT_NCCL_SYM(GroupStart, "ncclGroupStart", true);  B200PT_NCCL_SYM(GroupEnd, "ncclGroupEnd", true);
-            B200PT_NCCL_SYM(MemAlloc, "ncclMemAlloc", false);  B200PT_NCCL_SYM(MemFree, "ncclMemFree", false);           // NCCL >= 2.19
-            B200PT_NCCL_SYM(CommRegister, "ncclCommRegister", false);  B200PT_NCCL_SYM(CommDeregister, "ncclCommDeregister", false);
+        B200PT_NCCL_SYM(GetVersion, "ncclGetVersion", true);  B200PT_NCCL_SYM(GetUniqueId, "ncclGetUniqueId", true);
+        B200PT_NCCL_SYM(CommInitRank, "ncclCommInitRank", true);  B200PT_NCCL_SYM(CommDestroy, "ncclCommDestroy", true);
+        B200PT_NCCL_SYM(GetErrorString, "ncclGetErrorString", true);  B200PT_NCCL_SYM(Reduce, "ncclReduce", true);
+        B200PT_NCCL_SYM(Send, "ncclSend", true);  B200PT_NCCL_SYM(Recv, "ncclRecv", true);
+        B200PT_NCCL_SYM(GroupStart, "ncclGroupStart", true);  B200PT_NCCL_SYM(GroupEnd, "ncclGroupEnd", true);
+        B200PT_NCCL_SYM(MemAlloc, "ncclMemAlloc", false);  B200PT_NCCL_SYM(MemFree, "ncclMemFree", false);           // NCCL >= 2.19
+        B200PT_NCCL_SYM(CommRegister, "ncclCommRegister", false);  B200PT_NCCL_SYM(CommDeregister, "ncclCommDeregister", false);
 #undef B200PT_NCCL_SYM
-            if (!ok) { dlclose(a.lib);  a.lib = nullptr; }
-        }
+        if (!ok) { dlclose(a.lib);  a.lib = nullptr; }
     }
+    return a;
+}
+static NcclApi& ncclApi() {
+    static NcclApi a = loadNcclApi();                          // initialised once, thread-safe (one host thread per GPU may call in concurrently)
     if (!a.lib) throw std::runtime_error("libnccl.so.2 could not be loaded (multi-GPU entry points need NCCL on the library path)");
     return a;
 }

@@ -415,8 +415,8 @@ void bvhBuild(const float3* d_vertices, const uint3* d_indices, const unsigned* 
     }
     out.tris = dalloc<float4>(3 * (size_t)nTris);
     out.finalGid = dalloc<unsigned>(nTris);
-    static bool attrSet = false;
-    if (!attrSet) { CUDA_OK(cudaFuncSetAttribute(sahJobKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SahShared)));  attrSet = true; }
+    // per device (a host with one thread per GPU builds on several devices in one process): cheap, so set on every build
+    CUDA_OK(cudaFuncSetAttribute(sahJobKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SahShared)));
     const unsigned nFlag = nTris + 1, nTiles = (nFlag + SCAN_TILE - 1) / SCAN_TILE;
     unsigned* flagNext = dalloc<unsigned>(nFlag);  unsigned* rankA = dalloc<unsigned>(nFlag);  unsigned* rankB = dalloc<unsigned>(nFlag);
     unsigned* tileSum = dalloc<unsigned>(nTiles);  unsigned* tileOff = dalloc<unsigned>(nTiles);

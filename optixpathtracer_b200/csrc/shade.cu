@@ -205,6 +205,9 @@ DEV float3 sampleTexture(const SceneDev& S, const MeshInfo* M, float s, float t)
 #ifndef SHADE_COMPACT
 #define SHADE_COMPACT 0
 #endif
+#ifndef SHADE_SMEM_CDFY
+#define SHADE_SMEM_CDFY 0         // rows of cdfValuesY staged in shared memory per CTA (0 = off)
+#endif
 __global__ void __launch_bounds__(SHADE_BLOCK, SHADE_MIN_BLOCKS)
 shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int launch) {
     const unsigned count = Q.counters[QC_STRIDE * launch + QC_RAYS];
@@ -213,6 +216,22 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
     unsigned* shadowCounter = Q.counters + QC_STRIDE * (launch + 1) + QC_SHADOWS;
     const float4* __restrict__ rayOq = Q.rayO[cur];
     const float4* __restrict__ rayDq = Q.rayD[cur];
+#if SHADE_SMEM_CDFY
+    // ProbeSample's row search from shared memory: cdfValuesY (H floats) and its guide table, staged once per CTA when the probe has <= SHADE_SMEM_CDFY rows
+    __shared__ float sCdfYBuf[SHADE_SMEM_CDFY];
+    __shared__ int sGuideYBuf[B200PT_GUIDE_Y + 1];
+    const bool stageY = F.probeGuide != nullptr && F.probe.height <= SHADE_SMEM_CDFY;
+    if (stageY) {
+        for (int k = threadIdx.x; k < F.probe.height; k += SHADE_BLOCK) sCdfYBuf[k] = __ldg(F.probe.cdfValuesY + k);
+        for (int k = threadIdx.x; k <= B200PT_GUIDE_Y; k += SHADE_BLOCK) sGuideYBuf[k] = __ldg(F.probeGuide + k);
+    }
+    __syncthreads();
+    const float* const sCdfY = stageY ? sCdfYBuf : nullptr;
+    const int* const sGuideY = stageY ? sGuideYBuf : nullptr;
+#else
+    const float* const sCdfY = nullptr;
+    const int* const sGuideY = nullptr;
+#endif
 #if SHADE_COMPACT
     __shared__ unsigned list[SHADE_BLOCK / 32][64];
     unsigned* const head = Q.counters + QC_STRIDE * launch + QC_SHEAD;
@@ -279,7 +298,7 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                 // is committed further down, only where the reference really draws the sample.
                 Rng rng;  rng.s1 = st.rng1;  rng.s2 = st.rng2;
                 float3 wi, skyColor;  float skyPdf;
-                probeSample(F.probe, F.probeGuide, wi, skyColor, skyPdf, rng);
+                probeSample(F.probe, F.probeGuide, wi, skyColor, skyPdf, rng, sCdfY, sGuideY);
                 const float3 e1 = f3(ta.w, tb.x, tb.y), e2 = f3(tb.z, tb.w, tc.x);
                 const unsigned gid = (unsigned)__float_as_int(tc.y);
                 const MeshInfo* M = S.meshes + (CHK((unsigned)__float_as_int(tc.z) < S.nMeshes && gid < S.nTris, 24) ? __float_as_int(tc.z) : 0);

@@ -314,11 +314,26 @@ DEV int guidedLowerBound(const float* __restrict__ a, int base, const int* __res
     const int lo = __ldg(guide + k), hi = __ldg(guide + k + 1);
     return lowerBound(a, base + lo, base + hi, value) - base;
 }
-DEV void probeSample(const Probe& P, const int* __restrict__ guide, float3& dir, float3& color, float& pdf, Rng& rand) {   // :138-169
+// the same search on copies of cdfValuesY and its guide table in shared memory (shadeKernel stages them per CTA when they fit): same data, same
+// comparisons, same index - the row search then costs shared-memory latency instead of ~4 dependent L1/L2 round trips
+DEV int lowerBoundShared(const float* a, int lower, int upper, float value) {
+    while (lower < upper) {
+        const int mid = lower + (upper - lower) / 2;
+        if (a[mid] < value) lower = mid + 1;
+        else upper = mid;
+    }
+    return lower;
+}
+DEV void probeSample(const Probe& P, const int* __restrict__ guide, float3& dir, float3& color, float& pdf, Rng& rand,
+                     const float* sCdfY = nullptr, const int* sGuideY = nullptr) {   // :138-169
     float r1, r2;
     sample2D(rand, r1, r2);
     int row, col;
-    if (guide) {
+    if (guide && sCdfY) {
+        const int k = min(B200PT_GUIDE_Y - 1, max(0, (int)(r1 * (float)B200PT_GUIDE_Y)));
+        row = lowerBoundShared(sCdfY, sGuideY[k], sGuideY[k + 1], r1);
+        col = guidedLowerBound(P.cdfValuesX, row * P.width, guide + (B200PT_GUIDE_Y + 1) + (size_t)row * (B200PT_GUIDE_X + 1), B200PT_GUIDE_X, r2);
+    } else if (guide) {
         row = guidedLowerBound(P.cdfValuesY, 0, guide, B200PT_GUIDE_Y, r1);
         col = guidedLowerBound(P.cdfValuesX, row * P.width, guide + (B200PT_GUIDE_Y + 1) + (size_t)row * (B200PT_GUIDE_X + 1), B200PT_GUIDE_X, r2);
     } else {

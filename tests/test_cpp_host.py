@@ -130,6 +130,29 @@ def test_cpp_frames_in_flight_give_the_same_image(exe, tmp_path):
     assert imgs[0] == imgs[1] == imgs[2] and len(imgs[0]) > 96 * 64 * 3
 
 
+@pytest.mark.gpu
+def test_cpp_multi_gpu_driver_one_rank(exe, tmp_path):
+    """The multi-GPU driver below Python (host/headless_main.cpp multiMain: one thread + one SampleRenderer per GPU, b200pt_comm_init, the library's
+    NCCL collectives) on the ranks this box has: one.  A tile split over one rank + gather is the plain sequence bit for bit; a sample split's
+    resolved SUM equals the running mean to the last RGBA8 step (fp32 summation order).  tools/multi_check.py and bench.py --gpus N cover N > 1."""
+    import re
+    scenes.cornell("disney", directory=str(tmp_path))
+    obj = os.path.join(str(tmp_path), "cornell.obj")
+    base = [exe, "--obj", obj, "--preset", "sv3_uniform", "--size", "96x64", "--frames", "6", "--camera", "cornell", "--sky", "1,1,1"]
+
+    def checksum(extra):
+        p = subprocess.run(base + extra, capture_output=True, text=True)
+        assert p.returncode == 0, p.stderr
+        return int(re.search(r"pixel checksum (\d+)", p.stdout).group(1)), p.stdout
+
+    plain, _ = checksum([])
+    tile, out = checksum(["--ranks", "1", "--split", "tile"])
+    assert "1 ranks, tile split" in out and tile == plain
+    samp, out = checksum(["--ranks", "1", "--split", "sample"])
+    # the checksum sums the packed 24-bit pixels: one RGBA8 step of a blue channel moves it by 65536, so a few pixels off by one step stay below 1e-3
+    assert "1 ranks, sample split" in out and abs(samp - plain) <= 1e-3 * plain
+
+
 # ---- Radiance .hdr readers (loadProbe, sv4/main.cpp:154-165) against the reference's own stb_image (tests/golden/hdr.npz) ----
 HDR_CASES = ["rle", "flat", "narrow", "wide_rle"]
 

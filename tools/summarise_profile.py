@@ -13,7 +13,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 G, P = os.path.join(ROOT, "gpurun_out"), os.path.join(ROOT, "profiles")
-COLS = ["Kernel Name", "Grid Size", "Block Size", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "lts__t_bytes.sum",
+COLS = ["Kernel Name", "Grid Size", "Block Size", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "lts__t_sectors.sum",
         "launch__registers_per_thread", "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__thread_inst_executed_per_inst_executed.ratio",
         "sm__throughput.avg.pct_of_peak_sustained_elapsed", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "lts__t_sector_hit_rate.pct",
         "l1tex__t_sector_hit_rate.pct", "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum",
@@ -53,7 +53,7 @@ def per_kernel(cols, out, hbm_peak):
         dur = avg("gpu__time_duration.sum")
         rd, wr = avg("dram__bytes_read.sum"), avg("dram__bytes_write.sum")
         dram = (rd or 0) + (wr or 0) if rd is not None or wr is not None else None
-        res[name] = {"launches_captured": len(rs), "duration_us": dur, "dram_bytes_per_launch": dram, "lts_bytes_per_launch": avg("lts__t_bytes.sum"),
+        res[name] = {"launches_captured": len(rs), "duration_us": dur, "dram_bytes_per_launch": dram, "lts_bytes_per_launch": (32.0 * avg("lts__t_sectors.sum")) if avg("lts__t_sectors.sum") is not None else None,
                      "dram_frac_of_peak": (dram / (dur * 1e-6) / 1e9 / hbm_peak) if dram is not None and dur else None,
                      "ipc_per_sm": avg("sm__inst_issued.avg.per_cycle_active"),
                      "active_threads_per_warp_inst": avg("smsp__thread_inst_executed_per_inst_executed.ratio"),
@@ -77,7 +77,7 @@ def main():
         csv.writer(f).writerows(out)
     kernels = per_kernel(cols, out, hbm_peak)
     tj = {"source": f"profiles/{tag}_frame_ncu_full_summary.csv (ncu --set full --clock-control none: every traceKernel / shadeKernel / gatherKernel / finalizeKernel "
-                    "launch of one frame of the bench workload; per-kernel averages; dram = dram__bytes_read.sum + dram__bytes_write.sum, l2 = lts__t_bytes.sum)",
+                    "launch of one frame of the bench workload; per-kernel averages; dram = dram__bytes_read.sum + dram__bytes_write.sum, l2 = 32 B x lts__t_sectors.sum)",
           "hbm_peak_gbs": hbm_peak, "kernels": kernels}
     if c5tag:
         c5cols, c5out = raw_rows(os.path.join(G, f"prof_{c5tag}.ncu-rep"))
