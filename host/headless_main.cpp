@@ -162,9 +162,8 @@ static int multiMain(const Model* model, const ProbeData& probe, const sutil::Ca
     double slowest = 0.0;
     for (double s : seconds) slowest = std::max(slowest, s);
     const int done = tileSplit ? frames : (frames / ranks) * ranks;
-    printf("%d ranks, %s split: %d frames in %.3f s (slowest rank): %.2f frames/s, %.1f Msamples/s\n", ranks, tileSplit ? "tile" : "sample", done, slowest,
-           done / slowest, (double)W * H * spl * done / slowest / 1e6);
-    (void)samples0;
+    printf("%d ranks, %s split: %d frames in %.3f s (slowest rank, first-use set-up included): %.2f frames/s; rank 0's last frame: %llu samples\n", ranks,
+           tileSplit ? "tile" : "sample", done, slowest, done / slowest, samples0);
     unsigned long long sum = 0;
     for (uint32_t p : px) sum += p & 0xffffffu;
     printf("pixel checksum %llu\n", sum);
