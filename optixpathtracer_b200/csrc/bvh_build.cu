@@ -499,15 +499,15 @@ __global__ void collapse4Kernel(const BvhNode* __restrict__ n2, BvhNode4* __rest
     const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= *countIn) return;
     const int2 it = frontIn[i];
-    unsigned q[4][3];
-    int link[4];
+    unsigned q[B200PT_WIDE][3];
+    int link[B200PT_WIDE];
     {
         const BvhNode a = n2[it.x];
         for (int k = 0; k < 3; ++k) { q[0][k] = a.q[k];  q[1][k] = a.q[3 + k]; }
         link[0] = a.link[0];  link[1] = a.link[1];
     }
     int n = 2;
-    for (int iter = 0; iter < 2; ++iter) {
+    for (int iter = 0; iter < B200PT_WIDE - 2; ++iter) {
         int best = -1;
         float bestA = -1.f;
         for (int c = 0; c < n; ++c)
@@ -524,12 +524,13 @@ __global__ void collapse4Kernel(const BvhNode* __restrict__ n2, BvhNode4* __rest
             frontOut[pos] = make_int2(link[c], (int)idx);
             link[c] = (int)idx;
         }
-    for (int c = n; c < 4; ++c) { q[c][0] = q[c][1] = q[c][2] = 0x0000ffffu;  link[c] = B200PT_LINK_EMPTY; }
-    uint4* dst = reinterpret_cast<uint4*>(n4) + 4 * (size_t)it.y;
-    dst[0] = make_uint4(q[0][0], q[0][1], q[0][2], q[1][0]);
-    dst[1] = make_uint4(q[1][1], q[1][2], q[2][0], q[2][1]);
-    dst[2] = make_uint4(q[2][2], q[3][0], q[3][1], q[3][2]);
-    dst[3] = make_uint4((unsigned)link[0], (unsigned)link[1], (unsigned)link[2], (unsigned)link[3]);
+    for (int c = n; c < B200PT_WIDE; ++c) { q[c][0] = q[c][1] = q[c][2] = 0x0000ffffu;  link[c] = B200PT_LINK_EMPTY; }
+    unsigned w[4 * B200PT_WIDE];                                  // record: 3 words per child, then the links
+#pragma unroll
+    for (int c = 0; c < B200PT_WIDE; ++c) { w[3 * c] = q[c][0];  w[3 * c + 1] = q[c][1];  w[3 * c + 2] = q[c][2];  w[3 * B200PT_WIDE + c] = (unsigned)link[c]; }
+    uint4* dst = reinterpret_cast<uint4*>(n4) + B200PT_WIDE * (size_t)it.y;
+#pragma unroll
+    for (int k = 0; k < B200PT_WIDE; ++k) dst[k] = make_uint4(w[4 * k], w[4 * k + 1], w[4 * k + 2], w[4 * k + 3]);
 }
 // (re)derives io.nodes4 from io.nodes; io.nodes4 is allocated on first use (as many nodes as binary records at most)
 float bvhCollapse4(cudaStream_t s, BvhBuildResult& io) {
@@ -557,7 +558,7 @@ float bvhCollapse4(cudaStream_t s, BvhBuildResult& io) {
     CUDA_OK(cudaMemcpy(&io.nNodes4, ctr + 2, sizeof(unsigned), cudaMemcpyDeviceToHost));
     io.rootLink4 = 0;  io.maxDepth4 = depth;
     cudaFree(front[0]);  cudaFree(front[1]);  cudaFree(ctr);
-    if (3 * io.maxDepth4 + 4 > B200PT_STACK) throw std::runtime_error("4-wide BVH deeper than the traversal stack");
+    if ((B200PT_WIDE - 1) * io.maxDepth4 + B200PT_WIDE > B200PT_STACK) throw std::runtime_error("wide BVH deeper than the traversal stack");
     return std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
 }
 

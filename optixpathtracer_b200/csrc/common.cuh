@@ -27,8 +27,12 @@ struct BvhNode { unsigned q[6]; int link[2]; };
 static_assert(sizeof(BvhNode) == 32, "BvhNode must be 32 bytes");
 // The tree the traversal kernels read: the binary tree above collapsed to 4 children per node (64 bytes = two 256-bit loads).
 // Child c: q[3c..3c+2] in the BvhNode word layout, link[c].  Unused slots: inverted box (lo 65535, hi 0: never hit), link EMPTY.
-struct BvhNode4 { unsigned q[12]; int link[4]; };
-static_assert(sizeof(BvhNode4) == 64, "BvhNode4 must be 64 bytes");
+// B200PT_WIDE = children per node of that tree: 4 (default, 64 B = two 256-bit loads) or 8 (tuning builds, 128 B = four: measured slower, profiles/README.md r02f).
+#ifndef B200PT_WIDE
+#define B200PT_WIDE 4
+#endif
+struct BvhNode4 { unsigned q[3 * B200PT_WIDE]; int link[B200PT_WIDE]; };
+static_assert(sizeof(BvhNode4) == 16 * B200PT_WIDE, "wide node = 16 bytes per child");
 #define B200PT_LINK_EMPTY 0x7fffffff
 #define B200PT_GRID_ORIGIN 2.0      // grid coordinate of the scene AABB's low corner ...
 #define B200PT_GRID_SPAN 65531.0    // ... and the span of the scene AABB in cells: padded boxes stay inside [0, 65535]

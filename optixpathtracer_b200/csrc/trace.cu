@@ -183,6 +183,7 @@ struct Best { float t, u, v; int slot; unsigned gid; };
 // One step through a 4-wide node (two 256-bit loads): test the four child boxes, order the hit ones by entry distance with a
 // 5-exchange sorting network, continue with the nearest and push the others, farthest first.
 #define CEX_(ta, la, tb, lb) { const bool s_ = tb < ta;  const float tt_ = s_ ? tb : ta;  const int ll_ = s_ ? lb : la;  tb = s_ ? ta : tb;  lb = s_ ? la : lb;  ta = tt_;  la = ll_; }
+#if B200PT_WIDE == 4
 #define NODE_STEP4()                                                                             \
     {                                                                                            \
         const uint4* np_ = S.nodes4 + 4 * (size_t)(CHK((unsigned)cur < S.nNodes4, 12) ? cur : 0);   \
@@ -201,6 +202,32 @@ struct Best { float t, u, v; int slot; unsigned gid; };
         PUSH_IF_(l3_, t3_ < inf_)  PUSH_IF_(l2_, t2_ < inf_)  PUSH_IF_(l1_, t1_ < inf_)             \
         { const bool any_ = t0_ < inf_;  cur = any_ ? l0_ : cur;  POP_IF_(cur, !any_) }                 \
     }
+#else
+// The 8-wide variant (tuning builds, -DB200PT_WIDE=8): four 256-bit loads, eight box tests; the nearest hit child is visited next (a chain of seven
+// compare-exchanges leaves it in slot 0), the other hit children are pushed in slot order.
+#define NODE_STEP4()                                                                             \
+    {                                                                                            \
+        const uint4* np_ = S.nodes4 + 8 * (size_t)(CHK((unsigned)cur < S.nNodes4, 12) ? cur : 0);   \
+        const Node8 A_ = ldgNode(np_), B_ = ldgNode(np_ + 2), C_ = ldgNode(np_ + 4), D_ = ldgNode(np_ + 6);   \
+        const float inf_ = __int_as_float(0x7f800000);                                           \
+        float t0_, t1_, t2_, t3_, t4_, t5_, t6_, t7_;                                            \
+        t0_ = boxTest(A_.w[0], A_.w[1], A_.w[2], g, tmin, best.t, t0_) ? t0_ : inf_;             \
+        t1_ = boxTest(A_.w[3], A_.w[4], A_.w[5], g, tmin, best.t, t1_) ? t1_ : inf_;             \
+        t2_ = boxTest(A_.w[6], A_.w[7], B_.w[0], g, tmin, best.t, t2_) ? t2_ : inf_;             \
+        t3_ = boxTest(B_.w[1], B_.w[2], B_.w[3], g, tmin, best.t, t3_) ? t3_ : inf_;             \
+        t4_ = boxTest(B_.w[4], B_.w[5], B_.w[6], g, tmin, best.t, t4_) ? t4_ : inf_;             \
+        t5_ = boxTest(B_.w[7], C_.w[0], C_.w[1], g, tmin, best.t, t5_) ? t5_ : inf_;             \
+        t6_ = boxTest(C_.w[2], C_.w[3], C_.w[4], g, tmin, best.t, t6_) ? t6_ : inf_;             \
+        t7_ = boxTest(C_.w[5], C_.w[6], C_.w[7], g, tmin, best.t, t7_) ? t7_ : inf_;             \
+        int l0_ = (int)D_.w[0], l1_ = (int)D_.w[1], l2_ = (int)D_.w[2], l3_ = (int)D_.w[3];      \
+        int l4_ = (int)D_.w[4], l5_ = (int)D_.w[5], l6_ = (int)D_.w[6], l7_ = (int)D_.w[7];      \
+        CEX_(t0_, l0_, t1_, l1_)  CEX_(t0_, l0_, t2_, l2_)  CEX_(t0_, l0_, t3_, l3_)  CEX_(t0_, l0_, t4_, l4_)   \
+        CEX_(t0_, l0_, t5_, l5_)  CEX_(t0_, l0_, t6_, l6_)  CEX_(t0_, l0_, t7_, l7_)             \
+        PUSH_IF_(l7_, t7_ < inf_)  PUSH_IF_(l6_, t6_ < inf_)  PUSH_IF_(l5_, t5_ < inf_)  PUSH_IF_(l4_, t4_ < inf_)   \
+        PUSH_IF_(l3_, t3_ < inf_)  PUSH_IF_(l2_, t2_ < inf_)  PUSH_IF_(l1_, t1_ < inf_)          \
+        { const bool any_ = t0_ < inf_;  cur = any_ ? l0_ : cur;  POP_IF_(cur, !any_) }                 \
+    }
+#endif
 
 // Reference single-ray traversal (parity hooks only; the production kernels below inline the same steps).
 template <bool ANY, bool COUNT>

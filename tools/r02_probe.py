@@ -60,6 +60,8 @@ def main():
         acc = r.downloadAccum()
         if ref is None:
             ref = acc
+            import hashlib
+            print(f"[{tag}] accumulation buffer sha1 {hashlib.sha1(acc.tobytes()).hexdigest()[:16]} (hits are tree-independent: equal across builds)", flush=True)
         same = np.array_equal(ref.view(np.uint32), acc.view(np.uint32))
         print(f"[{tag}] in flight {n}: {n_samples / ms / 1e3:.1f} Msamples/s, {ms:.3f} ms/frame, accum identical: {same}", flush=True)
 
