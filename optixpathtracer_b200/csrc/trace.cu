@@ -205,6 +205,8 @@ struct Best { float t, u, v; int slot; unsigned gid; };
 #else
 // The 8-wide variant (tuning builds, -DB200PT_WIDE=8): four 256-bit loads, eight box tests; the nearest hit child is visited next (a chain of seven
 // compare-exchanges leaves it in slot 0), the other hit children are pushed in slot order.
+// Measured on B200 (profiles/README.md, r02f): node visits per ray 14.6 -> 10.2, identical hits, trace 2.60 -> 3.07 ms per frame: the kernel is issue-bound and
+// 10.2 x 8 box tests cost more instructions than 14.6 x 4.  Kept as a variant, not the default.
 #define NODE_STEP4()                                                                             \
     {                                                                                            \
         const uint4* np_ = S.nodes4 + 8 * (size_t)(CHK((unsigned)cur < S.nNodes4, 12) ? cur : 0);   \
