@@ -167,8 +167,8 @@ int b200pt_reduce_sum(b200pt_ctx* c, const LaunchParams* params, const b200pt_co
     if (!c->multi || !c->multi->comm) return fail("b200pt_reduce_sum: no communicator (call b200pt_comm_init)");
     if (root < 0 || root >= c->multi->nranks) return fail("b200pt_reduce_sum: root out of range");
     API_BEGIN
-    enterCtxMutating(c);
-    float4* buf = params->frame.accum_buffer;
+    enterCtx(c);                                                               // stream-level join only: the primary stream waits for every frame in flight, the host does not
+    float4* buf = params->frame.accum_buffer;                                  // (speculative wavefronts never touch the accumulation buffer: only finalize passes do)
     const size_t n = (size_t)params->frame.size.x * params->frame.size.y;
     if (!buf || !n) throw std::runtime_error("b200pt_reduce_sum: frame buffers not allocated (call b200pt_resize)");
     float4* dst = buf;
@@ -201,7 +201,7 @@ int b200pt_gather_bands(b200pt_ctx* c, const LaunchParams* params, int root, int
     if (!c->multi || !c->multi->comm) return fail("b200pt_gather_bands: no communicator (call b200pt_comm_init)");
     if (root < 0 || root >= c->multi->nranks) return fail("b200pt_gather_bands: root out of range");
     API_BEGIN
-    enterCtxMutating(c);
+    enterCtx(c);                                                               // stream-level join only (see b200pt_reduce_sum)
     const int W = params->frame.size.x, H = params->frame.size.y, n = c->multi->nranks, me = c->multi->rank;
     uint32_t* frame = (uint32_t*)params->frame.frame_buffer;
     float4* accum = params->frame.accum_buffer;

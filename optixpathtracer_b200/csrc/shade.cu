@@ -684,7 +684,10 @@ void checkedReportShade(unsigned* count, unsigned* first) {
 
 // ---- launchers ---------------------------------------------------------------------------------------------
 static inline unsigned gridFor(unsigned n) { return (n + SHADE_BLOCK - 1) / SHADE_BLOCK; }
-static inline unsigned persistentGrid() { return (unsigned)numSMs() * SHADE_MIN_BLOCKS; }
+static inline unsigned persistentGrid() {
+    static const int ctasPerSM = [] { const char* e = getenv("B200PT_SHADE_CTAS");  const int v = e ? atoi(e) : SHADE_MIN_BLOCKS;  return v < 1 ? 1 : (v > 16 ? 16 : v); }();   // tuning knob (see launchTrace)
+    return (unsigned)numSMs() * ctasPerSM;
+}
 
 void launchRaygen(const FrameParams& F, const PassParams& P, int k0, int k1, const PathPool& pool, const Queues& Q, cudaStream_t s) {
     raygenKernel<<<persistentGrid(), SHADE_BLOCK, 0, s>>>(F, P, k0, k1, pool, Q);

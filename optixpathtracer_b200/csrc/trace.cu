@@ -577,7 +577,8 @@ static int leafThreshold() {
 
 void launchTrace(const SceneDev& scene, const Queues& Q, int cur, int closest, unsigned* ctr, float tmin, float tminShadow, float tmax, int cullBack,
                  const PathPool& pool, TraceStats* stats, cudaStream_t stream) {
-    const dim3 grid((unsigned)numSMs() * TRACE_BLOCKS_PER_SM), block(TRACE_BLOCK);
+    static const int ctasPerSM = [] { const char* e = getenv("B200PT_TRACE_CTAS");  const int v = e ? atoi(e) : TRACE_BLOCKS_PER_SM;  return v < 1 ? 1 : (v > TRACE_BLOCKS_PER_SM ? TRACE_BLOCKS_PER_SM : v); }();   // tuning knob: fewer persistent CTAs per SM leave room for a concurrent shadeKernel of another frame
+    const dim3 grid((unsigned)numSMs() * ctasPerSM), block(TRACE_BLOCK);
     if (stats) traceKernel<true><<<grid, block, 0, stream>>>(scene, Q.rayO[cur], Q.rayD[cur], Q.hit, Q.shO, Q.shD, Q.shP, ctr, closest, tmin, tminShadow, tmax, cullBack, pool, stats, refillThreshold(), leafThreshold(), nodeMinThreshold());
     else traceKernel<false><<<grid, block, 0, stream>>>(scene, Q.rayO[cur], Q.rayD[cur], Q.hit, Q.shO, Q.shD, Q.shP, ctr, closest, tmin, tminShadow, tmax, cullBack, pool, nullptr, refillThreshold(), leafThreshold(), nodeMinThreshold());
 }
