@@ -845,6 +845,94 @@ def test_speculative_wavefront_dropped_before_refit(port):
     assert np.array_equal(run(1), run(3))
 
 
+@pytest.mark.parametrize("pname", ["orig", "sv4_fov"])
+def test_intra_frame_split_is_bit_identical(sponza_small, pname):
+    """cfg.intra_frame_split = 2..4 (one frame at a time, run as concurrent sets of 32-row bands on separate lanes): accumulation buffer, pixels, AOVs and the
+    frame's counters equal the unsplit frame's, also across accumulating sub-frames and for the foveated three-pass schedule."""
+    probe = analytic_sky(128, 64)
+    cam = preset_camera("sponza")
+
+    def run(split):
+        cfg = preset(pname)
+        if pname == "orig":
+            cfg.uniform_spl = 2
+        cfg.frames_in_flight, cfg.intra_frame_split = 1, split
+        r = make_renderer(sponza_small, probe, (200, 150), cam, cfg)
+        if pname == "sv4_fov":
+            r.launchParams.frame.c.x, r.launchParams.frame.c.y = 100, 75
+            r.config.inner_radius, r.config.outer_radius = 20, 50
+        cnts = []
+        for k in range(3):
+            if pname == "orig":
+                r.launchParams.frame.subframe_index = k
+            r.render()
+            c = r.counters()
+            cnts.append((c.samples, c.radiance_rays, c.shadow_rays))
+        out = (r.downloadAccum().copy(), r.downloadPixels().copy(), r.downloadAOV("normal").copy() if pname == "orig" else None, cnts)
+        r.close()
+        return out
+
+    want = run(0)
+    for split in (2, 3, 4):
+        got = run(split)
+        assert np.array_equal(got[0].view(np.uint32), want[0].view(np.uint32)) and np.array_equal(got[1], want[1]), split
+        assert got[3] == want[3], split
+        if pname == "orig":
+            assert np.array_equal(got[2], want[2])
+
+
+def test_collectives_on_a_one_rank_communicator(sponza_small):
+    """The library-side NCCL path on the ranks the test box has (one): b200pt_comm_init moves the accumulation buffer into ncclMemAlloc'd memory with its
+    contents and launchParams follows it; b200pt_reduce_sum (in place) equals b200pt_resolve_sum; keep_local leaves the partial sum untouched and only
+    refreshes the frame buffer; b200pt_gather_bands is a no-op; b200pt_comm_destroy keeps the buffer.  N > 1: tools/multi_check.py, bench.py --gpus N."""
+    from optixpathtracer_b200.structs import ACCUM_SUM
+    probe = analytic_sky(128, 64)
+    cam = preset_camera("sponza")
+
+    def fresh():
+        cfg = preset("orig", uniform_spl=1)
+        cfg.accumulate, cfg.accum_mode, cfg.frames_in_flight = 1, ACCUM_SUM, 3
+        r = make_renderer(sponza_small, probe, (160, 96), cam, cfg)
+        r.clearAccum()
+        for k in range(4):
+            r.launchParams.frame.subframe_index = k
+            r.render(sync=False)
+        r.synchronize()
+        return r
+
+    a = fresh()
+    sums = a.downloadAccum().copy()
+    a.resolveSum(4)
+    want_acc, want_px = a.downloadAccum().copy(), a.downloadPixels().copy()
+    a.close()
+
+    b = fresh()
+    before_ptr = b.launchParams.frame.accum_buffer
+    b.commInit(1, 0, SampleRenderer.commUniqueId())
+    info = b.commInfo()
+    assert info["n_ranks"] == 1 and info["rank"] == 0 and info["nccl_version"] >= 21900
+    if info["accum_nccl_alloc"]:
+        assert b.launchParams.frame.accum_buffer != before_ptr                      # the buffer moved and launchParams followed it
+    assert np.array_equal(b.downloadAccum().view(np.uint32), sums.view(np.uint32))  # ... with its contents
+    b.reduceSum(4, root=0, keep_local=True)                                         # progressive display: sums stay, frame refreshed
+    b.synchronize()
+    assert np.array_equal(b.downloadAccum().view(np.uint32), sums.view(np.uint32))
+    assert np.array_equal(b.downloadPixels(), want_px)
+    b.gatherBands(root=0, frame=True, accum=True)                                   # one rank owns every band
+    b.reduceSum(4, root=0)                                                          # end of job: in place, accum = mean
+    b.synchronize()
+    assert np.array_equal(b.downloadAccum().view(np.uint32), want_acc.view(np.uint32)) and np.array_equal(b.downloadPixels(), want_px)
+    b.commDestroy()
+    assert b.commInfo()["n_ranks"] == 1 and not b.commInfo()["accum_nccl_alloc"]
+    assert np.array_equal(b.downloadAccum().view(np.uint32), want_acc.view(np.uint32))
+    with pytest.raises(RuntimeError):
+        b.reduceSum(4)                                                              # no communicator any more
+    b.launchParams.frame.subframe_index = 0
+    b.render()                                                                      # still renders into a valid buffer
+    assert np.isfinite(b.downloadAccum()).all()
+    b.close()
+
+
 def check_bvh_boxes_contain_triangles(r, model):
     """Every leaf's triangles lie inside the (dequantised) child box that refers to them, and child boxes nest in their parents'."""
     info = r.bvhInfo()
