@@ -177,13 +177,16 @@ DEV float3 ggxReflect(const Material& mat, float3 U, float3 V, float3 N, float3 
 DEV void bsdfSampleDir(const Material& mat, float etaI, float etaO, float3 U, float3 V, float3 N, float3 view,
                        float3& light, float& pdf, int& type, bool& needPdf, Rng& rand) {
     needPdf = false;
+    // The GGX half-vector reflection is reached from two branches (transmission lobe after the Fresnel test, :209-228; specular lobe, :281-305).  Both only
+    // set `ggx` and share ONE copy of ggxReflect below: lanes of a warp that took different branches then run it together instead of one copy after the
+    // other.  The random numbers are drawn inside the branches, in the reference's order.
+    bool ggx = false;
+    float r1 = 0.f, r2 = 0.f;
     if (rand.randf() < mat.transmission) {
         const float F = fresnelDielectric(dot3(N, view), etaI, etaO);
         if (rand.randf() < F) {
-            float r1, r2;
             sample2D(rand, r1, r2);
-            type = eReflected;
-            light = ggxReflect(mat, U, V, N, view, r1, r2);
+            ggx = true;
         } else {
             const float eta = etaI / etaO;
             if (refractDir(view, N, eta, light)) { type = eSpecular;  pdf = (1.0f - F) * mat.transmission;  return; }
@@ -191,7 +194,6 @@ DEV void bsdfSampleDir(const Material& mat, float etaI, float etaO, float3 U, fl
             return;
         }
     } else {
-        float r1, r2;
         sample2D(rand, r1, r2);
         if (rand.randf() < 0.5f) {
             if (rand.randf() < mat.subsurface) {
@@ -203,11 +205,9 @@ DEV void bsdfSampleDir(const Material& mat, float etaI, float etaO, float3 U, fl
                 light = U * d.x + V * d.y + N * d.z;
                 type = eReflected;
             }
-        } else {
-            light = ggxReflect(mat, U, V, N, view, r1, r2);
-            type = eReflected;
-        }
+        } else ggx = true;
     }
+    if (ggx) { light = ggxReflect(mat, U, V, N, view, r1, r2);  type = eReflected; }
     needPdf = true;
 }
 DEV void bsdfSample(const Material& mat, float etaI, float etaO, float3 U, float3 V, float3 N, float3 view,
