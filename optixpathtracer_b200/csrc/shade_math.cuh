@@ -226,21 +226,27 @@ DEV float3 bsdfEval(const Material& mat, float3 albedo, float etaI, float etaO, 
     const float3 Ctint = Cdlum > 0.0f ? Cdlin / Cdlum : f3(1.0f);
     const float3 Cspec0 = lerp3((float)((double)mat.specular * .08) * lerp3(f3(1.0f), Ctint, mat.specularTint), Cdlin, mat.metallic);
     float3 bsdf = f3(0.0f), brdf = f3(0.0f);
+    // Above the surface both lobes need the same GTR2 and Smith terms (same arguments), and most materials run both lobes (the reference's default has
+    // transmission 0.4): computed once here.  `above` is the reference's else-branch of `NDotL <= 0` (so a NaN goes where it goes there).
+    const bool above = !(NDotL <= 0.0f);
+    float a = 0.0f, Ds = 0.0f, Gs = 0.0f;
+    if (above) {
+        a = fmaxf(0.001f, mat.roughness);
+        Ds = GTR2(NDotH, a);
+        Gs = smithGGX(NDotV, a) * smithGGX(NDotL, a);
+    }
     if (mat.transmission > 0.0f) {
-        if (NDotL <= 0.0f) {
-            const float F = fresnelDielectric(NDotV, etaI, etaO);
+        // one copy of Fr for the two sides: below the surface it is evaluated at N.V (:332-336), above at L.H (:338-345)
+        const float F = fresnelDielectric(above ? LDotH : NDotV, etaI, etaO);
+        if (!above) {
             bsdf = f3(mat.transmission * (1.0f - F) / fabsf(NDotL) * (1.0f - mat.metallic));
         } else {
-            const float a = fmaxf(0.001f, mat.roughness);
-            const float Ds = GTR2(NDotH, a);
-            const float FH = fresnelDielectric(LDotH, etaI, etaO);
-            const float3 Fs = lerp3(Cspec0, f3(1.0f), FH);
-            const float Gs = smithGGX(NDotV, a) * smithGGX(NDotL, a);
+            const float3 Fs = lerp3(Cspec0, f3(1.0f), F);
             bsdf = Gs * Fs * Ds;
         }
     }
     if (mat.transmission < 1.0f) {
-        if (NDotL <= 0.0f) {
+        if (!above) {
             if (mat.subsurface > 0.0f) {
                 const float3 s = f3(sqrtf(mat.color.x), sqrtf(mat.color.y), sqrtf(mat.color.z));
                 const float FL = schlickFresnel(fabsf(NDotL)), FV = schlickFresnel(NDotV);
@@ -248,11 +254,8 @@ DEV float3 bsdfEval(const Material& mat, float3 albedo, float etaI, float etaO, 
                 brdf = kInvPi * s * mat.subsurface * Fd * (1.0f - mat.metallic);
             }
         } else {
-            const float a = fmaxf(0.001f, mat.roughness);
-            const float Ds = GTR2(NDotH, a);
             const float FH = schlickFresnel(LDotH);
             const float3 Fs = lerp3(Cspec0, f3(1.f), FH);
-            const float Gs = smithGGX(NDotV, a) * smithGGX(NDotL, a);
             const float FL = schlickFresnel(NDotL), FV = schlickFresnel(NDotV);
             const float Fd90 = (float)(0.5 + (double)(2.0f * LDotH * LDotH * mat.roughness));
             const float Fd = lerpf(1.0f, Fd90, FL) * lerpf(1.0f, Fd90, FV);
