@@ -340,11 +340,14 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                     } else {
                         // The continuation direction is drawn first (the RNG order is the reference's: the probe sample was drawn above,
                         // DisneySample comes next, and nothing in between consumes random numbers) ...
+                        // Fr(N.wo) and the two index ratios are the same in DisneySample, DisneyPdf and DisneyEval of this vertex: once
+                        const EtaPair etaPair = makeEtaPair(rayEta, outEta);
+                        const float FNV = fresnelDielectric(dot3(N, wo), etaPair);
                         float3 bsdfDir = f3(0.f);  float pdf = 0.0f;  int type = 0;  bool dirNeedsPdf = false;
                         if (!last) {
                             float3 u, v;
                             basisFromVector(N, u, v);                             // :671-677
-                            bsdfSampleDir(mat, rayEta, outEta, u, v, N, wo, bsdfDir, pdf, type, dirNeedsPdf, rng);
+                            bsdfSampleDir(mat, rayEta, outEta, FNV, u, v, N, wo, bsdfDir, pdf, type, dirNeedsPdf, rng);
                         }
                         // ... so that DisneyPdf / DisneyEval of the two directions of this vertex — k = 0: the NEE direction wi (SampleLights,
                         // :301-384), k = 1: the drawn direction (:683-695) — run through ONE rolled copy of the code.
@@ -353,12 +356,12 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                         for (int k = 0; k < 2; ++k) {
                             const float3 L = k ? bsdfDir : wi;
                             float p = pdf;
-                            if (k == 0 || dirNeedsPdf) p = bsdfPdf(mat, rayEta, outEta, N, wo, L);
+                            if (k == 0 || dirNeedsPdf) p = bsdfPdf(mat, FNV, N, wo, L);
                             bool ev;
                             if (k == 0) ev = p > 0.0f && 0.5f * skyPdf / (0.5f * p + 0.5f * skyPdf) > 0.0f;
                             else ev = !last && p > 0.0f;
                             float3 f = f3(0.f);
-                            if (ev) f = bsdfEval(mat, albedo, rayEta, outEta, N, wo, L);
+                            if (ev) f = bsdfEval(mat, albedo, etaPair, FNV, N, wo, L);
                             if (k == 0) { bp = p;  fNee = f;  evalNee = ev; }
                             else { pdf = p;  fDir = f; }
                         }

@@ -132,22 +132,29 @@ SHADE_NI_GGX_ATTR float smithGGX(float NDotv, float alphaG) {
     const float a = alphaG * alphaG, b = NDotv * NDotv;
     return 1.0f / (NDotv + sqrtf(a + b - a * b));
 }
-SHADE_NI_FRESNEL_ATTR float fresnelDielectric(float VDotN, float etaI, float etaT) {                 // Fr, :81-98
-    const float sinT2 = sqrf(etaI / etaT) * (1.0f - VDotN * VDotN);
+// Fr (:81-98).  Both media of a vertex are fixed while it is shaded, so the two divisions that involve only the indices are done ONCE per vertex
+// (EtaPair) instead of in every one of the up to five Fr evaluations: the same operands, so the same bits.
+struct EtaPair { float sq, inv; };                               // sqr(etaI / etaT), etaT / etaI
+DEV EtaPair makeEtaPair(float etaI, float etaT) { EtaPair e;  e.sq = sqrf(etaI / etaT);  e.inv = etaT / etaI;  return e; }
+SHADE_NI_FRESNEL_ATTR float fresnelDielectric(float VDotN, const EtaPair e) {
+    const float sinT2 = e.sq * (1.0f - VDotN * VDotN);
     if (sinT2 > 1.0f) return 1.0f;
     const float LDotN = sqrtf(1.0f - sinT2);
-    const float eta = etaT / etaI;
+    const float eta = e.inv;
     const float r1 = (VDotN - eta * LDotN) / (VDotN + eta * LDotN);
     const float r2 = (LDotN - eta * VDotN) / (LDotN + eta * VDotN);
     return 0.5f * (sqrf(r1) + sqrf(r2));
 }
+DEV float fresnelDielectric(float VDotN, float etaI, float etaT) { return fresnelDielectric(VDotN, makeEtaPair(etaI, etaT)); }
 
-DEV float bsdfPdf(const Material& mat, float etaI, float etaO, float3 n, float3 V, float3 L) {   // :152-193
+// FNV = Fr(n.V, etaI, etaO): needed by BSDFSample's transmission branch and by BSDFPdf of every direction above the surface - the same value each time,
+// so shadeKernel computes it once per vertex and passes it in
+DEV float bsdfPdf(const Material& mat, float FNV, float3 n, float3 V, float3 L) {   // :152-193
     if (dot3(L, n) <= 0.0f) {
         const float brdfPdf = kInv2Pi * mat.subsurface * 0.5f;
         return lerpf(brdfPdf, 0.0f, mat.transmission);
     }
-    const float F = fresnelDielectric(dot3(n, V), etaI, etaO);
+    const float F = FNV;
     const float a = fmaxf(0.001f, mat.roughness);
     const float3 half = safeNormalize(L + V);
     const float cosThetaHalf = fabsf(dot3(half, n));
@@ -174,7 +181,7 @@ DEV float3 ggxReflect(const Material& mat, float3 U, float3 V, float3 N, float3 
 // The direction-drawing half of DisneySample (:197-315).  needPdf = the reference goes on to `pdf = DisneyPdf(...)` for the drawn
 // direction (every branch but the two refraction returns, which set pdf themselves); shadeKernel evaluates that pdf in the same
 // rolled loop as the NEE direction's, so the kernel holds ONE copy of bsdfPdf/bsdfEval instead of two (instruction-cache footprint).
-DEV void bsdfSampleDir(const Material& mat, float etaI, float etaO, float3 U, float3 V, float3 N, float3 view,
+DEV void bsdfSampleDir(const Material& mat, float etaI, float etaO, float FNV, float3 U, float3 V, float3 N, float3 view,
                        float3& light, float& pdf, int& type, bool& needPdf, Rng& rand) {
     needPdf = false;
     // The GGX half-vector reflection is reached from two branches (transmission lobe after the Fresnel test, :209-228; specular lobe, :281-305).  Both only
@@ -183,7 +190,7 @@ DEV void bsdfSampleDir(const Material& mat, float etaI, float etaO, float3 U, fl
     bool ggx = false;
     float r1 = 0.f, r2 = 0.f;
     if (rand.randf() < mat.transmission) {
-        const float F = fresnelDielectric(dot3(N, view), etaI, etaO);
+        const float F = FNV;
         if (rand.randf() < F) {
             sample2D(rand, r1, r2);
             ggx = true;
@@ -213,11 +220,12 @@ DEV void bsdfSampleDir(const Material& mat, float etaI, float etaO, float3 U, fl
 DEV void bsdfSample(const Material& mat, float etaI, float etaO, float3 U, float3 V, float3 N, float3 view,
                     float3& light, float& pdf, int& type, Rng& rand) {            // :197-315
     bool needPdf;
-    bsdfSampleDir(mat, etaI, etaO, U, V, N, view, light, pdf, type, needPdf, rand);
-    if (needPdf) pdf = bsdfPdf(mat, etaI, etaO, N, view, light);
+    const float FNV = fresnelDielectric(dot3(N, view), etaI, etaO);
+    bsdfSampleDir(mat, etaI, etaO, FNV, U, V, N, view, light, pdf, type, needPdf, rand);
+    if (needPdf) pdf = bsdfPdf(mat, FNV, N, view, light);
 }
 
-DEV float3 bsdfEval(const Material& mat, float3 albedo, float etaI, float etaO, float3 N, float3 V, float3 L) {   // :318-427
+DEV float3 bsdfEval(const Material& mat, float3 albedo, const EtaPair eta, float FNV, float3 N, float3 V, float3 L) {   // :318-427
     const float NDotL = dot3(N, L), NDotV = dot3(N, V);
     const float3 H = normalize3(L + V);
     const float NDotH = dot3(N, H), LDotH = dot3(L, H);
@@ -237,7 +245,7 @@ DEV float3 bsdfEval(const Material& mat, float3 albedo, float etaI, float etaO, 
     }
     if (mat.transmission > 0.0f) {
         // one copy of Fr for the two sides: below the surface it is evaluated at N.V (:332-336), above at L.H (:338-345)
-        const float F = fresnelDielectric(above ? LDotH : NDotV, etaI, etaO);
+        const float F = above ? fresnelDielectric(LDotH, eta) : FNV;               // below: Fr(N.V), the per-vertex value
         if (!above) {
             bsdf = f3(mat.transmission * (1.0f - F) / fabsf(NDotL) * (1.0f - mat.metallic));
         } else {
@@ -266,6 +274,11 @@ DEV float3 bsdfEval(const Material& mat, float3 albedo, float etaI, float etaO, 
         }
     }
     return lerp3(brdf, bsdf, mat.transmission);
+}
+
+DEV float bsdfPdf(const Material& mat, float etaI, float etaO, float3 n, float3 V, float3 L) { return bsdfPdf(mat, fresnelDielectric(dot3(n, V), etaI, etaO), n, V, L); }
+DEV float3 bsdfEval(const Material& mat, float3 albedo, float etaI, float etaO, float3 N, float3 V, float3 L) {
+    return bsdfEval(mat, albedo, makeEtaPair(etaI, etaO), fresnelDielectric(dot3(N, V), etaI, etaO), N, V, L);
 }
 
 // ---- environment probe: sv4/Probe.cuh ----------------------------------------------------------------
