@@ -360,10 +360,11 @@ DEV void probeSample(const Probe& P, const int* __restrict__ guide, float3& dir,
     color = f3(c.x, c.y, c.z);
     pdf = __ldg(P.pdfValuesX + row * P.width + col) * __ldg(P.pdfValuesY + row);
     const float u = col / (float)P.width, v = row / (float)P.height;
-    const float sinTheta = sinf(v * kPi);
+    const float theta = v * kPi, phi = u * 2.0f * kPi;                      // ProbeUVToDir's angles (:48-58)
+    const float sinTheta = sinf(theta);                                     // the pdf's sin(theta) (:160) and ProbeUVToDir's are the same value: once
     if (sinTheta == 0.0f) pdf = 0.0f;
     else pdf *= (float)(P.width * P.height) / (2.0f * kPi * kPi * sinTheta);
-    dir = probeUVToDir(u, v);
+    dir = f3(-sinTheta * cosf(phi), cosf(theta), -sinTheta * sinf(phi));
 }
 
 // ---- display transform: cuda/helpers.h:35-62, sv4/deviceProgram.cu:124-129 ---------------------------
