@@ -267,10 +267,17 @@ DEV float3 bsdfEval(const Material& mat, float3 albedo, const EtaPair eta, float
             const float FL = schlickFresnel(NDotL), FV = schlickFresnel(NDotV);
             const float Fd90 = (float)(0.5 + (double)(2.0f * LDotH * LDotH * mat.roughness));
             const float Fd = lerpf(1.0f, Fd90, FL) * lerpf(1.0f, Fd90, FV);
-            const float Dr = GTR1(NDotH, lerpf(.1f, .001f, mat.clearcoatGloss));
-            const float Fc = lerpf(.04f, 1.0f, FH);
-            const float Gr = smithGGX(NDotL, .25f) * smithGGX(NDotV, .25f);
-            brdf = kInvPi * Fd * Cdlin * (1.0f - mat.metallic) * (1.0f - mat.subsurface) + Gs * Fs * Ds + f3(mat.clearcoat * Gr * Fc * Dr);
+            // Clearcoat lobe (:411-417).  With clearcoat == 0 - every material the reference constructs (Material.h:13-38) - the term is exactly +0: Gr, Fc
+            // and Dr are finite and positive for N.L > 0 (each Smith denominator is >= 0.25; GTR1's t lies in [a^2, 1], a <= 0.1), and x + (+0) == x, so the
+            // logf, the three divisions and the two square roots are skipped without changing a bit of the result.
+            float3 coat = f3(0.0f);
+            if (mat.clearcoat != 0.0f) {
+                const float Dr = GTR1(NDotH, lerpf(.1f, .001f, mat.clearcoatGloss));
+                const float Fc = lerpf(.04f, 1.0f, FH);
+                const float Gr = smithGGX(NDotL, .25f) * smithGGX(NDotV, .25f);
+                coat = f3(mat.clearcoat * Gr * Fc * Dr);
+            }
+            brdf = kInvPi * Fd * Cdlin * (1.0f - mat.metallic) * (1.0f - mat.subsurface) + Gs * Fs * Ds + coat;
         }
     }
     return lerp3(brdf, bsdf, mat.transmission);
