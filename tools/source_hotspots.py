@@ -6,7 +6,7 @@ import csv
 import sys
 
 
-KEY = 2
+KEY = int(__import__("os").environ.get("HOT_KEY", 2))
 
 
 def main():
