@@ -311,9 +311,66 @@ def _tile_split_section(a, torch, dist, world, rank, local, r, cam, stream):
         identical = bool(np.array_equal(got_px, r.downloadPixels()) and np.array_equal(got_acc.view(np.uint32), r.downloadAccum().view(np.uint32)))
     if world > 1:
         dist.barrier()
+    one_sided = None
+    if world > 1:
+        # The same frames with the one-sided exchange (b200pt_peer_*): rank 0 exports its frame buffer, the other ranks map it (CUDA IPC; the 192-byte
+        # handle travels over torch.distributed) and their finalize passes write their bands straight into it over NVLink; rank 0 acquires /
+        # downloads / releases.  No collective and no staging copy in the frame.
+        cfg.tile_rank, cfg.tile_count = rank, world
+        h = torch.from_numpy(r.peerExport(0, world).copy()).cuda() if rank == 0 else torch.zeros(192, dtype=torch.uint8, device="cuda")
+        dist.broadcast(h, src=0)
+        if rank != 0:
+            r.peerAttach(h.cpu().numpy(), rank, world)
+
+        def one_p2p(i, download):
+            r.launchParams.frame.subframe_index = i
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            dist.barrier()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            e0.record(stream)
+            r.render(sync=False)
+            if rank == 0:
+                r.peerAcquire()
+            else:
+                r.join()
+            e1.record(stream)
+            if download and rank == 0:
+                r.downloadPixels(host_px)
+            else:
+                r.synchronize()
+            wall = time.perf_counter() - t0
+            if rank == 0:
+                r.peerRelease()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1), wall * 1e3
+
+        r.clearAccum()
+        for i in range(3):
+            one_p2p(i, True)
+        p_dev = _max_over_ranks(torch, dist, world, sum(one_p2p(i, False)[0] for i in range(frames)) / frames)
+        p_wall = _max_over_ranks(torch, dist, world, sum(one_p2p(i, True)[1] for i in range(frames)) / frames)
+        r.clearAccum()
+        one_p2p(0, True)
+        same = None
+        if rank == 0:
+            got_px = r.downloadPixels().copy()
+            cfg.tile_rank, cfg.tile_count = 0, 1
+            r.clearAccum()
+            r.launchParams.frame.subframe_index = 0
+            r.render()
+            same = bool(np.array_equal(got_px, r.downloadPixels()))
+        st = r.peerStatus()
+        bad = _max_over_ranks(torch, dist, world, float(st["state"]))
+        dist.barrier()
+        r.peerDetach()
+        one_sided = {"frame_ms": p_dev, "frames_per_s": 1e3 / p_dev, "with_download_ms": p_wall, "bit_identical_to_single_gpu": same, "timeouts": int(bad),
+                     "note": "the same frames with b200pt_peer_export / attach / acquire / release instead of the gather: every other rank's finalizeKernel "
+                             "stores its bands straight into rank 0's frame buffer over NVLink (CUDA IPC mapping), a release-store publishes the frame's "
+                             "epoch, rank 0's stream waits on the epochs with a one-CTA kernel; no NCCL call and no staging copy inside the frame"}
     cfg.accum_mode, cfg.tile_rank, cfg.tile_count, cfg.frames_in_flight, cfg.intra_frame_split, cfg.profile = keep
     return {"frame_ms": dev_ms, "frames_per_s": 1e3 / dev_ms, "value": a.width * a.height * a.spl / dev_ms / 1e3, "unit": "Msamples/s",
-            "with_download_ms": wall_ms, "scaling": "strong", "n_gpus": world, "bit_identical_to_single_gpu": identical,
+            "with_download_ms": wall_ms, "scaling": "strong", "n_gpus": world, "bit_identical_to_single_gpu": identical, "one_sided": one_sided,
             "gather_bytes_to_root": int(4 * a.width * a.height * (world - 1) / world) if world > 1 else 0,
             "note": f"one {a.width}x{a.height} frame per step, 32-row bands interleaved over {world} rank(s) (band b on rank b % N), "
                     "b200pt_render_async + b200pt_gather_bands (RGBA8 bands to rank 0, grouped ncclSend/ncclRecv on the primary stream), CUDA events "

@@ -8,11 +8,13 @@
 //                   [--camera sponza|lost_empire|san_miguel|cornell] [--sky r,g,b] [--out image.ppm|image.png] [--log fps.tsv]
 //                   [--hdr probe.hdr] [--gpu-cdf] [--whitted] [--dump-model file.bin] [--dump-probe file.bin] [--no-render]
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <future>
 #include <memory>
 #include <random>
 #include <string>
@@ -108,38 +110,60 @@ static void dumpModel(const Model* m, const char* path) {    // flat binary for 
 
 // --ranks N: the multi-GPU driver below Python.  One host thread and one SampleRenderer per GPU in this process, the scene replicated, the frame
 // partitioned by samples (--split sample: rank r renders sub-frames r, r+N, ..., ONE fp32 SUM reduce + resolve on rank 0) or by 32-row bands
-// (--split tile: every frame gathered to rank 0).  The collectives are the library's (b200pt_reduce_sum / b200pt_gather_bands over NCCL); the
+// (--split tile: every frame gathered to rank 0; --split peer: the same partition, the other ranks' finalize passes write into rank 0's frame buffer).  The collectives are the library's (b200pt_reduce_sum / b200pt_gather_bands over NCCL); the
 // 128-byte NCCL id is shared through this process' memory.  Prints the checksum of rank 0's final image, comparable with a single-GPU run.
 static int multiMain(const Model* model, const ProbeData& probe, const sutil::Camera& camera, const std::string& preset, int W, int H, int frames, int spl,
-                     int ranks, bool tileSplit, const std::string& out) {
+                     int ranks, int mode /* 0 sample, 1 tile (gather), 2 tile, one-sided over peer memory */, int devices, const std::string& out) {
+    const bool tileSplit = mode != 0, oneSided = mode == 2;
     unsigned char uid[B200PT_UNIQUE_ID_BYTES];
-    SampleRenderer::commUniqueId(uid);
+    if (!oneSided) SampleRenderer::commUniqueId(uid);
+    unsigned char peerHandle[B200PT_PEER_HANDLE_BYTES];
+    std::promise<void> exported;                                   // rank 0 fulfils it once peerHandle is valid
+    std::shared_future<void> exportedF = exported.get_future().share();
     std::vector<std::string> errors(ranks);
     std::vector<uint32_t> px((size_t)W * H);
     std::vector<double> seconds(ranks, 0.0);
     unsigned long long samples0 = 0;
+    std::atomic<int> ready{0};
+    std::atomic<bool> failed{false};
     auto worker = [&](int rank) {
         try {
-            SampleRenderer sample(model, rank, preset.c_str());
+            SampleRenderer sample(model, devices > 0 ? rank % devices : rank, preset.c_str());   // --devices 1: every rank on GPU 0 (one-sided split only: NCCL wants one GPU per rank)
             sample.setCamera(camera);
             sample.resize(int2{W, H});
             sample.setProbe(probe);
             sample.launchParams.samples_per_launch = spl;
-            sample.commInit(ranks, rank, uid);
+            if (!oneSided) sample.commInit(ranks, rank, uid);
+            else if (ranks > 1) {
+                // one throw-away frame first: every kernel of a frame is loaded (CUDA loads kernels lazily, and a load synchronises the context - with
+                // ranks sharing one GPU that must not happen while another rank's stream is already waiting for this rank's bands)
+                sample.config.tile_rank = rank;  sample.config.tile_count = ranks;
+                sample.render();
+                if (rank == 0) {
+                    try { sample.peerExport(0, ranks, peerHandle);  exported.set_value(); }
+                    catch (...) { exported.set_exception(std::current_exception());  throw; }
+                } else { exportedF.get();  sample.peerAttach(peerHandle, rank, ranks); }
+            }
             sample.config.frames_in_flight = tileSplit ? 1 : 3;
             if (tileSplit) { sample.config.tile_rank = rank;  sample.config.tile_count = ranks; }
             else sample.config.accum_mode = B200PT_ACCUM_SUM;
             sample.clearAccum();
             sample.synchronize();
+            // every rank has finished its set-up before any rank starts a frame: set-up calls synchronise the whole device (cudaFree, copies on the
+            // legacy stream), which ranks sharing one GPU (--devices) must not do while another rank's stream already waits for their bands
+            ready.fetch_add(1);
+            while (ready.load() < ranks && !failed.load()) std::this_thread::yield();
             const auto t0 = std::chrono::steady_clock::now();
             if (tileSplit) {
                 for (int f = 0; f < frames; ++f) {                                  // every rank renders its bands of the SAME sub-frame
                     sample.launchParams.frame.subframe_index = f;
                     sample.setCamera(camera);
                     sample.renderAsync();
-                    sample.gatherBands(0, true, true);
-                    sample.synchronize();
+                    if (!oneSided) { sample.gatherBands(0, true, true);  sample.synchronize(); }
+                    else if (rank == 0 && ranks > 1) { sample.peerAcquire();  sample.downloadPixels(px.data());  sample.peerRelease(); }
                 }
+                sample.synchronize();
+                if (oneSided && ranks > 1 && sample.peerState() != 0) throw std::runtime_error("one-sided tile split: a wait timed out (b200pt_peer_status)");
             } else {
                 const int total = (frames / ranks) * ranks;
                 for (int f = rank; f < total; f += ranks) {                         // rank r renders sub-frames r, r+N, ...
@@ -152,8 +176,8 @@ static int multiMain(const Model* model, const ProbeData& probe, const sutil::Ca
             }
             seconds[rank] = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
             if (rank == 0) { sample.downloadPixels(px.data());  samples0 = sample.counters().samples; }
-            sample.commDestroy();
-        } catch (const std::exception& e) { errors[rank] = e.what(); }
+            if (!oneSided) sample.commDestroy();
+        } catch (const std::exception& e) { errors[rank] = e.what();  failed.store(true); }
     };
     std::vector<std::thread> threads;
     for (int r = 0; r < ranks; ++r) threads.emplace_back(worker, r);
@@ -163,7 +187,7 @@ static int multiMain(const Model* model, const ProbeData& probe, const sutil::Ca
     for (double s : seconds) slowest = std::max(slowest, s);
     const int done = tileSplit ? frames : (frames / ranks) * ranks;
     printf("%d ranks, %s split: %d frames in %.3f s (slowest rank, first-use set-up included): %.2f frames/s; rank 0's last frame: %llu samples\n", ranks,
-           tileSplit ? "tile" : "sample", done, slowest, done / slowest, samples0);
+           oneSided ? "tile (one-sided)" : tileSplit ? "tile" : "sample", done, slowest, done / slowest, samples0);
     unsigned long long sum = 0;
     for (uint32_t p : px) sum += p & 0xffffffu;
     printf("pixel checksum %llu\n", sum);
@@ -185,6 +209,7 @@ int main(int argc, char** argv) {
     int W = 1280, H = 720, frames = 16, boxes = 64, spl = 1, inFlight = 1, ranks = 1;
     std::string split = "sample";
     bool splitGiven = false;
+    int devices = 0;
     float3 sky{1.f, 1.f, 1.f};
     bool noRender = false, gpuCdf = false, whitted = false, async = false;
     for (int i = 1; i < argc; ++i) {
@@ -198,7 +223,8 @@ int main(int argc, char** argv) {
         else if (a == "--frames") frames = atoi(next());
         else if (a == "--spl") spl = atoi(next());
         else if (a == "--ranks") ranks = atoi(next());             // one thread + one renderer per GPU, collectives in the library (multiMain)
-        else if (a == "--split") { split = next();  splitGiven = true; }   // sample | tile (given explicitly, also runs with --ranks 1: a one-rank communicator)
+        else if (a == "--devices") devices = atoi(next());        // ranks share `devices` GPUs (rank % devices); default: one GPU per rank
+        else if (a == "--split") { split = next();  splitGiven = true; }   // sample | tile | peer (given explicitly, also runs with --ranks 1: a one-rank communicator)
         else if (a == "--in-flight") inFlight = atoi(next());      // b200pt_config.frames_in_flight: render() starts the predicted next sub-frames before it blocks
         else if (a == "--async") async = true;                     // with --in-flight N: submit frames through renderAsync() and synchronize once at the end
         else if (a == "--sky") { if (sscanf(next(), "%f,%f,%f", &sky.x, &sky.y, &sky.z) != 3) { fprintf(stderr, "--sky r,g,b\n");  return 2; } }
@@ -232,9 +258,9 @@ int main(int argc, char** argv) {
         if (noRender) return 0;
         sutil::Camera camera = cameraPreset(cam);                                                           // :213-217
         if (ranks > 1 || splitGiven) {
-            if (split != "sample" && split != "tile") throw std::runtime_error("--split sample|tile");
+            if (split != "sample" && split != "tile" && split != "peer") throw std::runtime_error("--split sample|tile|peer");
             if (gpuCdf || !probe.valid) throw std::runtime_error("--ranks needs a host-built probe (no --gpu-cdf)");
-            const int rc = multiMain(model.get(), probe, camera, preset, W, H, frames, spl, ranks, split == "tile", out);
+            const int rc = multiMain(model.get(), probe, camera, preset, W, H, frames, spl, ranks, split == "tile" ? 1 : split == "peer" ? 2 : 0, devices, out);
             delete[] probe.data;  delete[] probe.pdfValuesX;  delete[] probe.cdfValuesX;  delete[] probe.pdfValuesY;  delete[] probe.cdfValuesY;
             return rc;
         }

@@ -202,6 +202,29 @@ int b200pt_reduce_sum(b200pt_ctx* ctx, const struct LaunchParams* params, const 
  * what: bit 0 = RGBA8 frame buffer, bit 1 = float4 accumulation buffer.  One grouped ncclSend / ncclRecv batch on the primary stream. */
 int b200pt_gather_bands(b200pt_ctx* ctx, const struct LaunchParams* params, int root, int what);
 
+/* ---- one-sided tile split over NVLink peer memory: the exchange done by the producing kernel, no collective ---------------------------------
+ * No reference counterpart (same note as above).  Root exports its RGBA8 frame buffer once; the other ranks map it (CUDA IPC between processes,
+ * peer access inside one process) and from then on every frame they render with cfg.tile_count > 1 (and not ACCUM_SUM) writes its 32-row bands
+ * from the finalize pass straight into root's frame buffer, followed by a release-store of the frame's epoch into root's flag block.
+ *   root, once:         b200pt_peer_export(ctx, params, root_rank, n_ranks, handle)  -> hand the 192 bytes to every other rank
+ *   other ranks, once:  b200pt_peer_attach(ctx, handle, rank, n_ranks)
+ *   every frame:        all ranks b200pt_render[_async] with cfg.tile_rank / tile_count;
+ *                       root: b200pt_peer_acquire (primary stream waits until every rank's bands of this frame have landed), consume the frame
+ *                       (b200pt_download_pixels...), b200pt_peer_release (the ranks' next finalize pass waits for it: no frame is overwritten early)
+ * Nothing synchronises with the host.  A wait that sees no progress for B200PT_PEER_TIMEOUT_MS (environment, default 5000) gives up and records
+ * its code (b200pt_peer_status: 0 = fine, 1 + r = root timed out waiting for rank r, 1000 + 64 = a rank timed out waiting for root's release).
+ * The accumulation buffer of a band stays on the rank that renders it (progressive accumulation needs no exchange); a resize drops the export /
+ * the mapping (export and attach again).  Pixels are byte-identical to b200pt_gather_bands' and to a single-GPU frame. */
+#define B200PT_PEER_HANDLE_BYTES 192
+int b200pt_peer_export(b200pt_ctx* ctx, const struct LaunchParams* params, int rank, int n_ranks, void* handle_192);
+int b200pt_peer_attach(b200pt_ctx* ctx, const void* handle_192, int rank, int n_ranks);
+int b200pt_peer_detach(b200pt_ctx* ctx);
+int b200pt_peer_acquire(b200pt_ctx* ctx);
+int b200pt_peer_release(b200pt_ctx* ctx);
+/* state: see above; attached_rank: this context's rank in a partition it attached to (-1: none); epoch: frames acquired (root) / put (others).
+ * Waits for the context's streams.  Any pointer may be NULL. */
+int b200pt_peer_status(b200pt_ctx* ctx, int* state, int* attached_rank, unsigned* epoch);
+
 /* computeFinalPixelColors (sv4/toneMap.cu:41-70, toneMap.h:4): sqrt-gamma float4 -> RGBA8, device pointers. */
 int b200pt_tonemap_sqrt(int width, int height, const void* d_float4_in, void* d_rgba8_out, void* stream);
 /* Host-buffer convenience around the same kernel (H2D + kernel + D2H). */

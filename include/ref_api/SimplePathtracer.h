@@ -124,6 +124,15 @@ public:
     void commDestroy() { if (b200pt_comm_destroy(ctx, &launchParams) != 0) fail(); }
     void reduceSum(int nPasses, int root = 0, bool keepLocal = false) { if (b200pt_reduce_sum(ctx, &launchParams, &config, root, nPasses, keepLocal ? 1 : 0) != 0) fail(); }
     void gatherBands(int root = 0, bool frame = true, bool accum = false) { if (b200pt_gather_bands(ctx, &launchParams, root, (frame ? 1 : 0) | (accum ? 2 : 0)) != 0) fail(); }
+    //   one-sided tile split: no communicator - root peerExport()s its frame buffer once and hands the 192 bytes to the other ranks, which peerAttach();
+    //   from then on their finalize pass stores their bands straight into root's frame over NVLink.  Per frame on root: render, peerAcquire(),
+    //   consume the frame (downloadPixels), peerRelease()
+    void peerExport(int rank, int nRanks, unsigned char handle[B200PT_PEER_HANDLE_BYTES]) { if (b200pt_peer_export(ctx, &launchParams, rank, nRanks, handle) != 0) fail(); }
+    void peerAttach(const unsigned char handle[B200PT_PEER_HANDLE_BYTES], int rank, int nRanks) { if (b200pt_peer_attach(ctx, handle, rank, nRanks) != 0) fail(); }
+    void peerDetach() { if (b200pt_peer_detach(ctx) != 0) fail(); }
+    void peerAcquire() { if (b200pt_peer_acquire(ctx) != 0) fail(); }
+    void peerRelease() { if (b200pt_peer_release(ctx) != 0) fail(); }
+    int peerState() { int st = 0;  if (b200pt_peer_status(ctx, &st, nullptr, nullptr) != 0) fail();  return st; }
     void clearAccum() { if (b200pt_clear_accum(ctx) != 0) fail(); }
     // animated geometry: new positions for mesh `meshID` (same count), then refit (topology kept) or a full rebuild
     void updateVertices(int meshID, const std::vector<float3>& vertex) {

@@ -15,6 +15,7 @@ SYMBOLS = [
     "b200pt_render_whitted", "b200pt_render_async", "b200pt_synchronize", "b200pt_join", "b200pt_download_pixels", "b200pt_download_pixels_async", "b200pt_download_accum",
     "b200pt_upload_accum", "b200pt_download_aov", "b200pt_device_buffers", "b200pt_resolve_sum", "b200pt_clear_accum",
     "b200pt_comm_unique_id", "b200pt_comm_init", "b200pt_comm_destroy", "b200pt_comm_info", "b200pt_reduce_sum", "b200pt_gather_bands",
+    "b200pt_peer_export", "b200pt_peer_attach", "b200pt_peer_detach", "b200pt_peer_acquire", "b200pt_peer_release", "b200pt_peer_status",
     "b200pt_build_cdf_noalloc", "b200pt_tonemap_sqrt", "b200pt_tonemap_sqrt_host", "b200pt_trace_primary", "b200pt_trace_rays",
     "b200pt_debug_bsdf", "b200pt_debug_probe", "b200pt_debug_morton", "b200pt_bvh_info_get", "b200pt_download_bvh", "b200pt_download_bvh4", "b200pt_get_counters",
     "computeFinalPixelColors",
@@ -72,6 +73,12 @@ def lib():
     L.b200pt_comm_info.argtypes = [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]
     L.b200pt_reduce_sum.argtypes = [vp, C.POINTER(LaunchParams), C.POINTER(Config), i32, i32, i32]
     L.b200pt_gather_bands.argtypes = [vp, C.POINTER(LaunchParams), i32, i32]
+    L.b200pt_peer_export.argtypes = [vp, C.POINTER(LaunchParams), i32, i32, vp]
+    L.b200pt_peer_attach.argtypes = [vp, vp, i32, i32]
+    L.b200pt_peer_detach.argtypes = [vp]
+    L.b200pt_peer_acquire.argtypes = [vp]
+    L.b200pt_peer_release.argtypes = [vp]
+    L.b200pt_peer_status.argtypes = [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(C.c_uint)]
     L.b200pt_tonemap_sqrt.argtypes = [i32, i32, vp, vp, vp]
     L.b200pt_tonemap_sqrt_host.argtypes = [vp, i32, i32, vp, vp]
     L.b200pt_trace_primary.argtypes = [vp, C.POINTER(LaunchParams), C.POINTER(Config), vp, vp, vp, vp, vp]

@@ -68,9 +68,20 @@ struct Speculation {
 };
 
 struct MultiState;                    // api_multi.inl: NCCL communicator + registrations of one rank
+// One-sided tile split (api_peer.inl): what a context knows about an exported frame (root) or about its mapping of root's frame (the other ranks)
+struct PeerState {
+    unsigned* flags = nullptr;            // exporter: [r] = last frame epoch rank r has put, [PEER_ACK] = last epoch root has consumed (its own device memory)
+    bool exported = false;  unsigned acquired = 0, released = 0;
+    uint32_t* remoteFrame = nullptr;  unsigned* remoteFlags = nullptr;    // attached side: root's frame buffer and flag block, mapped over NVLink
+    bool viaIpc = false;  int rank = -1, nranks = 0, W = 0, H = 0;  unsigned put = 0;
+    unsigned* err = nullptr;              // device word: 0 = fine, else the code of the wait that timed out
+    unsigned long long timeoutNs = 5000000000ull;
+};
+
 struct b200pt_ctx {
     int device = 0;
     MultiState* multi = nullptr;
+    PeerState* peer = nullptr;
     bool accumFromNccl = false;       // accumBuf.p came from ncclMemAlloc (freed with ncclMemFree)
     cudaStream_t stream = nullptr;
     bool stale = false;           // vertices updated since the last build/refit
@@ -101,6 +112,9 @@ struct b200pt_ctx {
 static void freeAccum(b200pt_ctx* c);                 // api_multi.inl
 static void allocAccum(b200pt_ctx* c, size_t n);
 static void destroyMulti(b200pt_ctx* c);
+static void destroyPeer(b200pt_ctx* c);               // api_peer.inl
+static bool peerPutBegin(b200pt_ctx* c, const b200pt_config& cfg, FrameParams& F, cudaStream_t s);
+static void peerPutEnd(b200pt_ctx* c, cudaStream_t s);
 
 // Orders the primary stream after every frame in flight on the other lanes (no host synchronisation): what the entry points that touch
 // shared state (frame buffers, scene, probe, counters) do first, and what b200pt_join exposes to callers that time or copy on that stream.
@@ -190,6 +204,7 @@ void b200pt_destroy(b200pt_ctx* c) {
 #endif
     bvhFree(c->bvh);
     c->dVertices.release();  c->dNormals.release();  c->dTexcoords.release();  c->dIndices.release();  c->dTriMesh.release();  c->dMeshes.release();  c->dTexels.release();
+    destroyPeer(c);
     freeAccum(c);  destroyMulti(c);
     c->frameBuf.release();  c->normalBuf.release();  c->albedoBuf.release();  c->colorBuf.release();
     c->probeData.release();  c->probePdfX.release();  c->probeCdfX.release();  c->probePdfY.release();  c->probeCdfY.release();  c->probeGuide.release();  c->probeRowTotal.release();
@@ -315,3 +330,4 @@ static SceneDev sceneOf(b200pt_ctx* c) {
 #include "api_render.inl"
 #include "api_hooks.inl"
 #include "api_multi.inl"
+#include "api_peer.inl"

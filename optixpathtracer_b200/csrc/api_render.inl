@@ -287,10 +287,15 @@ static void enqueueFinalize(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& j
     StageTimer T{c, (cfg.profile & 1) != 0};
     cudaEvent_t a = nullptr, b = nullptr;
     T.begin(ST_ACCUM, a, b);
+    // one-sided tile split (api_peer.inl): this rank's bands of the RGBA8 frame are written by finalizeKernel straight into root's frame buffer over
+    // NVLink, once root has consumed the previous frame; a one-thread kernel behind the passes tells root that they have landed
+    FrameParams F = job.F;
+    const bool put = peerPutBegin(c, cfg, F, s);
     for (auto& p : job.passes) {                                                 // pass order = the reference's launch order (overwrite semantics)
         if (!p.nLaunch) continue;
-        launchFinalize(job.F, p.P, L.sumRad.p, L.sumAlpha.p, L.sumNormal.p, L.sumAlbedo.p, s);  ++job.launches;
+        launchFinalize(F, p.P, L.sumRad.p, L.sumAlpha.p, L.sumNormal.p, L.sumAlbedo.p, s);  ++job.launches;
     }
+    if (put) peerPutEnd(c, s);
     T.end(b);
     T.end(job.totalEnd, false);
     CUDA_OK(cudaGetLastError());
@@ -401,6 +406,7 @@ int b200pt_resize(b200pt_ctx* c, int w, int h, LaunchParams* params) {
     enterCtxMutating(c);
     CUDA_OK(cudaStreamSynchronize(c->stream));
     const size_t n = (size_t)w * h;
+    destroyPeer(c);                                                              // an exported / mapped frame does not survive a resize: export and attach again
     freeAccum(c);
     c->frameBuf.release();  c->normalBuf.release();  c->albedoBuf.release();  c->colorBuf.release();
     c->frameBuf.ensure(n);  c->normalBuf.ensure(n);  c->albedoBuf.ensure(n);  c->colorBuf.ensure(n);

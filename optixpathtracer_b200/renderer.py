@@ -248,6 +248,38 @@ class SampleRenderer:
         """Tile split: this rank's 32-row bands go to `root` (asynchronous on the primary stream)."""
         _lib.check(self._L.b200pt_gather_bands(self._h, C.byref(self.launchParams), int(root), (1 if frame else 0) | (2 if accum else 0)))
 
+    # ---- one-sided tile split over NVLink peer memory (b200pt_peer_*): the finalize pass of every other rank writes its bands into root's frame
+    PEER_HANDLE_BYTES = 192
+
+    def peerExport(self, rank, n_ranks):
+        """Root, once: exports the RGBA8 frame buffer; returns the 192-byte handle (numpy uint8) every other rank passes to peerAttach."""
+        h = np.zeros(self.PEER_HANDLE_BYTES, np.uint8)
+        _lib.check(self._L.b200pt_peer_export(self._h, C.byref(self.launchParams), int(rank), int(n_ranks), h.ctypes.data))
+        return h
+
+    def peerAttach(self, handle, rank, n_ranks):
+        """Other ranks, once: maps root's frame; from now on tile-split frames (cfg.tile_count > 1) are written there by finalizeKernel."""
+        h = np.ascontiguousarray(handle, np.uint8)
+        if h.size != self.PEER_HANDLE_BYTES:
+            raise ValueError("peerAttach: the handle must be the 192 bytes peerExport returned")
+        _lib.check(self._L.b200pt_peer_attach(self._h, h.ctypes.data, int(rank), int(n_ranks)))
+
+    def peerDetach(self):
+        _lib.check(self._L.b200pt_peer_detach(self._h))
+
+    def peerAcquire(self):
+        """Root, every frame: the primary stream waits until every rank's bands of the next frame have landed (no host synchronisation)."""
+        _lib.check(self._L.b200pt_peer_acquire(self._h))
+
+    def peerRelease(self):
+        """Root, every frame, after the frame has been consumed on the primary stream: the ranks may write the next frame."""
+        _lib.check(self._L.b200pt_peer_release(self._h))
+
+    def peerStatus(self):
+        st, r, e = C.c_int(), C.c_int(), C.c_uint()
+        _lib.check(self._L.b200pt_peer_status(self._h, C.byref(st), C.byref(r), C.byref(e)))
+        return dict(state=st.value, attached_rank=r.value, epoch=e.value)
+
     def deviceBuffers(self):
         a, f, s = C.c_void_p(), C.c_void_p(), C.c_void_p()
         _lib.check(self._L.b200pt_device_buffers(self._h, C.byref(a), C.byref(f), C.byref(s)))

@@ -151,6 +151,9 @@ def test_cpp_multi_gpu_driver_one_rank(exe, tmp_path):
     samp, out = checksum(["--ranks", "1", "--split", "sample"])
     # the checksum sums the packed 24-bit pixels: one RGBA8 step of a blue channel moves it by 65536, so a few pixels off by one step stay below 1e-3
     assert "1 ranks, sample split" in out and abs(samp - plain) <= 1e-3 * plain
+    # one-sided tile split: two rank threads sharing this box's one GPU (no NCCL in this mode), rank 1's finalize pass writes into rank 0's frame
+    peer, out = checksum(["--ranks", "2", "--split", "peer", "--devices", "1"])
+    assert "2 ranks, tile (one-sided) split" in out and peer == plain
 
 
 # ---- Radiance .hdr readers (loadProbe, sv4/main.cpp:154-165) against the reference's own stb_image (tests/golden/hdr.npz) ----

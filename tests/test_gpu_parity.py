@@ -960,3 +960,70 @@ def check_bvh_boxes_contain_triangles(r, model):
         inner = ~leaf
         ch = links[inner, k]
         assert np.all(np.minimum(blo[ch, 0], blo[ch, 1]) >= blo[inner][:, k] - 4) and np.all(np.maximum(bhi[ch, 0], bhi[ch, 1]) <= bhi[inner][:, k] + 4)
+
+
+def test_one_sided_tile_split_two_contexts_one_device(sponza_small):
+    """b200pt_peer_*: context B (tile_rank 1 of 2) attaches to the frame context A (tile_rank 0) exported and its finalize pass writes its bands
+    straight into A's frame buffer; A acquires, downloads, releases.  Three progressive frames with frames in flight: every acquired frame equals
+    the unsplit single-context frame byte for byte, and nothing times out.  (Same-process path: raw pointers; two processes / two GPUs go through
+    CUDA IPC - tools/multi_check.py, bench.py --gpus N.)"""
+    probe = analytic_sky(64, 32)
+    size, cam = (96, 100), preset_camera("sponza")
+    full = make_renderer(sponza_small, probe, size, cam, preset("sv3_uniform", uniform_spl=2))
+    want = []
+    for i in range(3):
+        full.launchParams.frame.subframe_index = i
+        full.render()
+        want.append(full.downloadPixels().copy())
+    full.close()
+    ctx = []
+    for rank in range(2):
+        cfg = preset("sv3_uniform", uniform_spl=2, tile_rank=rank, tile_count=2)
+        cfg.frames_in_flight = 3
+        r = make_renderer(sponza_small, probe, size, cam, cfg)
+        r.clearAccum()
+        ctx.append(r)
+    a, b = ctx
+    with pytest.raises(Exception, match="nothing exported"):
+        a.peerAcquire()
+    handle = a.peerExport(0, 2)
+    with pytest.raises(Exception, match="root does not attach"):
+        a.peerAttach(handle, 1, 2)
+    with pytest.raises(Exception, match="not a handle"):
+        b.peerAttach(np.zeros(192, np.uint8), 1, 2)
+    b.peerAttach(handle, 1, 2)
+    with pytest.raises(Exception, match="no acquired frame"):
+        a.peerRelease()
+    for i in range(3):
+        for r in ctx:
+            r.launchParams.frame.subframe_index = i
+        b.render(sync=False)                                   # B runs ahead; its frame i + 1 must not land before A released frame i
+        a.render(sync=False)
+        a.peerAcquire()
+        got = a.downloadPixels().copy()
+        a.peerRelease()
+        assert np.array_equal(got, want[i]), f"frame {i}"
+    assert a.peerStatus() == dict(state=0, attached_rank=-1, epoch=3)
+    assert b.peerStatus() == dict(state=0, attached_rank=1, epoch=3)
+    # B's own frame buffer was not written (its bands went to A), and after a detach it is again
+    assert not b.downloadPixels().any()
+    b.peerDetach()
+    b.launchParams.frame.subframe_index = 3
+    b.render()
+    assert b.downloadPixels().any()
+    for r in ctx:
+        r.close()
+
+
+def test_one_sided_tile_split_times_out_instead_of_hanging(sponza_small, monkeypatch):
+    """A root that acquires a frame nobody puts gives up after B200PT_PEER_TIMEOUT_MS and reports which rank it waited for."""
+    monkeypatch.setenv("B200PT_PEER_TIMEOUT_MS", "100")
+    probe = analytic_sky(64, 32)
+    cfg = preset("sv3_uniform", uniform_spl=1, tile_rank=0, tile_count=3)
+    a = make_renderer(sponza_small, probe, (64, 64), preset_camera("sponza"), cfg)
+    a.peerExport(0, 3)
+    a.render(sync=False)
+    a.peerAcquire()
+    st = a.peerStatus()
+    assert st["state"] in (2, 3) and st["epoch"] == 1                  # 1 + r for r = 1 or 2, whichever gave up first
+    a.close()

@@ -4,7 +4,8 @@
   * sample split: rank r renders sub-frames r, r+N, ... in ACCUM_SUM mode, b200pt_reduce_sum onto rank 0 -> equals the single-GPU running mean of
     the same sub-frames up to fp32 summation order, and the tone-mapped frame to 1/255;
   * tile split: rank r renders bands b % N == r of ONE sub-frame, b200pt_gather_bands -> frame and accumulation buffer on rank 0 bit-identical to
-    the single-GPU frame.
+    the single-GPU frame;
+  * one-sided tile split (b200pt_peer_*): the same partition with the other ranks' finalize passes writing into rank 0's frame over NVLink.
 torch.distributed only carries the 128-byte NCCL unique id (and the final verdict); the collectives are the library's own."""
 import os
 import sys
@@ -115,6 +116,43 @@ def main():
         print(f"tile split over {world} ranks: gathered frame + accumulation buffer bit-identical to one GPU: {t_ok}", flush=True)
         ok &= bool(t_ok)
         one.close()
+    dist.barrier()
+
+    # ---- tile split, one-sided: no communicator at all - rank 0 exports its frame, the others map it (CUDA IPC) and their finalize passes write
+    # their bands into it; four progressive frames with the ranks running ahead of rank 0's acquire / download / release
+    r.commDestroy()
+    r.config.frames_in_flight = 3
+    r.clearAccum()
+    h = torch.from_numpy(r.peerExport(0, world).copy()).cuda() if rank == 0 else torch.zeros(192, dtype=torch.uint8, device="cuda")
+    dist.broadcast(h, src=0)
+    if rank != 0:
+        r.peerAttach(h.cpu().numpy(), rank, world)
+    frames = []
+    for f in range(4):
+        r.launchParams.frame.subframe_index = f
+        r.render(sync=False)
+        if rank == 0:
+            r.peerAcquire()
+            frames.append(r.downloadPixels().copy())
+            r.peerRelease()
+    st = r.peerStatus()
+    if rank == 0:
+        one = SampleRenderer(model, device=local, config=preset("sv3_uniform", uniform_spl=2))
+        one.resize((W, H))
+        one.setCamera(cam)
+        one.setProbe(probe)
+        p_ok = True
+        for f in range(4):
+            one.launchParams.frame.subframe_index = f
+            one.render()
+            p_ok &= bool(np.array_equal(frames[f], one.downloadPixels()))
+        print(f"one-sided tile split over {world} ranks: 4 progressive frames byte-identical to one GPU: {p_ok}, status {st}", flush=True)
+        ok &= p_ok
+        one.close()
+    flag = torch.tensor([1 if st["state"] == 0 else 0], device="cuda")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    ok &= bool(int(flag.item()))
+    dist.barrier()
     r.close()
     v = torch.tensor([1 if ok else 0], device="cuda")
     dist.broadcast(v, src=0)
