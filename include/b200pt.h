@@ -214,7 +214,9 @@ int b200pt_gather_bands(b200pt_ctx* ctx, const struct LaunchParams* params, int 
  * Nothing synchronises with the host.  A wait that sees no progress for B200PT_PEER_TIMEOUT_MS (environment, default 5000) gives up and records
  * its code (b200pt_peer_status: 0 = fine, 1 + r = root timed out waiting for rank r, 1000 + 64 = a rank timed out waiting for root's release).
  * The accumulation buffer of a band stays on the rank that renders it (progressive accumulation needs no exchange); a resize drops the export /
- * the mapping (export and attach again).  Pixels are byte-identical to b200pt_gather_bands' and to a single-GPU frame. */
+ * the mapping (export and attach again).  Pixels are byte-identical to b200pt_gather_bands' and to a single-GPU frame.
+ * Ranks that share ONE GPU inside ONE process (tests): CUDA loads kernels lazily and a load synchronises the context, so every such rank must have
+ * rendered a frame and attached before any of them starts waiting; ranks on different GPUs or in different processes need no such care. */
 #define B200PT_PEER_HANDLE_BYTES 192
 int b200pt_peer_export(b200pt_ctx* ctx, const struct LaunchParams* params, int rank, int n_ranks, void* handle_192);
 int b200pt_peer_attach(b200pt_ctx* ctx, const void* handle_192, int rank, int n_ranks);
