@@ -210,6 +210,9 @@ def _peaks():
         return 7700.0, "B200_PROFILING.md fallback (nominal HBM3e ~7.7 TB/s); MEASURED_PEAKS.json absent"
 
 
+MULTI_E2E_SPECULATE = os.environ.get("B200PT_MULTI_E2E", "spec") == "spec"
+
+
 def _share_unique_id(torch, dist, rank):
     """The 128-byte NCCL id of the library's own communicator travels over torch.distributed (plumbing only)."""
     from optixpathtracer_b200 import SampleRenderer
@@ -585,7 +588,7 @@ def run_b200(a):
     # ---- e2e: the reference-facing call sequence with HOST buffers, every step, one frame at a time.  The same a.steps frames as the timed
     # region, so their ray / sample / launch counters (read after each step, outside the clock) are the timed region's.
     #   N = 1: setCamera + render() (blocking) + downloadPixels() - the reference's sequence (sv4/main.cpp:328-335 + SimplePathtracer.cpp:279-283).
-    #   N > 1: the sample split END TO END: every rank setCamera + render, then the fp32 reduce of the SUM buffers onto rank 0 with the resolve there
+    #   N > 1: the sample split END TO END: every rank setCamera + render (blocking, predicted next sub-frames in flight as at N = 1), then the fp32 reduce of the SUM buffers onto rank 0 with the resolve there
     #          (b200pt_reduce_sum, keep_local: the ranks keep their partial sums and go on accumulating - progressive display) and downloadPixels()
     #          of the combined image on rank 0, all inside the clock; the collective keeps the ranks in lockstep.
     cfg.profile = 0
@@ -598,7 +601,10 @@ def run_b200(a):
             r.render()                                                          # blocking, as the reference's render()
             r.downloadPixels(host_px)                                           # D2H W*H RGBA8
         else:
-            r.render(sync=False)
+            if MULTI_E2E_SPECULATE:
+                r.render()                                                      # blocking, with the predicted next sub-frames in flight on the other lanes
+            else:
+                r.render(sync=False)
             r.reduceSum((i + 1) * world, root=0, keep_local=True)
             if rank == 0:
                 r.downloadPixels(host_px)
@@ -643,6 +649,9 @@ def run_b200(a):
         e2e_moving_s = e2e_loop(e2e_serial_steps, False, moving=True)
         cfg.intra_frame_split = 0
         # ... then the same blocking calls with the library allowed to start the predicted next sub-frame while it blocks (frames_in_flight > 1)
+        cfg.frames_in_flight = a.in_flight
+        e2e_s = e2e_loop(a.steps, True)
+    elif MULTI_E2E_SPECULATE:
         cfg.frames_in_flight = a.in_flight
         e2e_s = e2e_loop(a.steps, True)
     else:
@@ -801,9 +810,11 @@ def run_b200(a):
                     "accumulation this config is; a wrong guess is dropped, pixels are bit-identical either way); one_at_a_time_value = the same calls with frames_in_flight = 1; "
                     "moving_camera_value = the camera moves every step, so nothing can be rendered ahead (frames_in_flight = 1, intra_frame_split = 2): the figure for interactive "
                     f"use; scene/BVH upload is one-off in the ctor ({ctor_s:.2f} s incl. LBVH build {float(info.build_ms):.2f} ms)") if world == 1 else (
-                    f"the sample split end to end, every step, on {world} ranks: setCamera + b200pt_render_async on every rank, b200pt_reduce_sum (fp32 SUM of the {16 * n_px / 1e6:.1f} MB "
+                    f"the sample split end to end, every step, on {world} ranks: setCamera + render() on every rank, b200pt_reduce_sum (fp32 SUM of the {16 * n_px / 1e6:.1f} MB "
                     "accumulation buffers onto rank 0 + resolve there, keep_local: the ranks keep accumulating) and downloadPixels() of the combined image on rank 0, all inside the "
-                    "wall clock (max over ranks); one frame at a time per rank (frames_in_flight = 1, intra_frame_split = 2)")
+                    "wall clock (max over ranks); " + (f"render() is the blocking call with cfg.frames_in_flight = {a.in_flight}, as at N = 1: while a rank reduces and rank 0 downloads, "
+                    "the library already runs the predicted next sub-frames of that rank (index stride = the rank count); B200PT_MULTI_E2E=serial gives the figure with strictly "
+                    "one frame at a time per rank" if MULTI_E2E_SPECULATE else "one frame at a time per rank (b200pt_render_async, frames_in_flight = 1, intra_frame_split = 2)"))
         line = {
             "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",

@@ -1027,3 +1027,34 @@ def test_one_sided_tile_split_times_out_instead_of_hanging(sponza_small, monkeyp
     st = a.peerStatus()
     assert st["state"] in (2, 3) and st["epoch"] == 1                  # 1 + r for r = 1 or 2, whichever gave up first
     a.close()
+
+
+def test_sum_mode_blocking_render_with_speculation_is_bit_identical(sponza_small):
+    """One rank of a sample split as bench.py's N > 1 end-to-end loop drives it: ACCUM_SUM, sub-frames striding by the rank count, BLOCKING render() with
+    frames in flight (the predicted next sub-frames run while the caller reduces / downloads).  The SUM buffer after every call and the resolved image equal
+    those of strictly one-at-a-time calls bit for bit."""
+    from optixpathtracer_b200.structs import ACCUM_SUM
+    probe, cam = analytic_sky(128, 64), preset_camera("sponza")
+
+    def run(in_flight):
+        cfg = preset("orig", uniform_spl=1)
+        cfg.accumulate, cfg.accum_mode, cfg.frames_in_flight = 1, ACCUM_SUM, in_flight
+        r = make_renderer(sponza_small, probe, (160, 96), cam, cfg)
+        r.clearAccum()
+        out = []
+        for k in range(8):
+            r.setCamera(cam)
+            r.launchParams.frame.subframe_index = 1 + 2 * k               # rank 1 of 2
+            r.render()
+            out.append(r.downloadAccum().copy())
+        r.resolveSum(8)
+        out.append(r.downloadAccum().copy())
+        px = r.downloadPixels().copy()
+        r.close()
+        return out, px
+
+    want, want_px = run(1)
+    got, got_px = run(3)
+    for k, (a, b) in enumerate(zip(got, want)):
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32)), f"call {k}"
+    assert np.array_equal(got_px, want_px)
