@@ -320,10 +320,26 @@ def _tile_split_section(a, torch, dist, world, rank, local, r, cam, stream):
         # handle travels over torch.distributed) and their finalize passes write their bands straight into it over NVLink; rank 0 acquires /
         # downloads / releases.  No collective and no staging copy in the frame.
         cfg.tile_rank, cfg.tile_count = rank, world
-        h = torch.from_numpy(r.peerExport(0, world).copy()).cuda() if rank == 0 else torch.zeros(192, dtype=torch.uint8, device="cuda")
+        why = ""
+        h = torch.zeros(192, dtype=torch.uint8, device="cuda")
+        try:
+            if rank == 0:
+                h = torch.from_numpy(r.peerExport(0, world).copy()).cuda()
+        except Exception as e:                                                   # (every rank still takes part in the broadcast and the vote below)
+            why = str(e)
         dist.broadcast(h, src=0)
-        if rank != 0:
-            r.peerAttach(h.cpu().numpy(), rank, world)
+        try:
+            if rank != 0:
+                r.peerAttach(h.cpu().numpy(), rank, world)
+        except Exception as e:
+            why = str(e)
+        mapped = torch.tensor([0 if why else 1], device="cuda")
+        dist.all_reduce(mapped, op=dist.ReduceOp.MIN)
+    if world > 1 and int(mapped.item()) == 0:
+        # e.g. CUDA IPC closed between the ranks' containers: the gather above is the tile split's figure then
+        r.peerDetach()
+        one_sided = {"unavailable": why or "another rank could not map rank 0's frame buffer (b200pt_peer_attach)"}
+    elif world > 1:
 
         def one_p2p(i, download):
             r.launchParams.frame.subframe_index = i
@@ -727,9 +743,20 @@ def run_b200(a):
 
     peak, peak_src = _peaks()
     l2_peak = _measure_l2_peak(torch) if rank == 0 else 0.0
-    tile = None if a.no_tile_split else _tile_split_section(a, torch, dist, world, rank, local, r, cam, stream)
+
+    def side_object(fn, *args):
+        """The additional objects must not cost the contract line: on one GPU a failure inside one of them is reported in its place.  (On several
+        ranks an exception is left to torchrun - a rank that skipped a collective would leave the others waiting.)"""
+        if world > 1:
+            return fn(*args)
+        try:
+            return fn(*args)
+        except Exception as e:                                                   # noqa: BLE001
+            return {"error": f"{type(e).__name__}: {e}"}
+
+    tile = None if a.no_tile_split else side_object(_tile_split_section, a, torch, dist, world, rank, local, r, cam, stream)
     r.close()
-    c5 = None if a.no_c5 else _c5_section(a, torch, dist, world, rank, local, peak)
+    c5 = None if a.no_c5 else side_object(_c5_section, a, torch, dist, world, rank, local, peak)
 
     if rank == 0:
         tj = _ncu_summary()
