@@ -18,6 +18,7 @@
 #include "../../include/ref_api/LaunchParams.h"
 
 // SM count of the current device (cudaDevAttrMultiProcessorCount, cached per device; 148 on B200): sizes every persistent grid
+#define B200PT_SMEM_CARVEOUT 28       // percent of the SM's shared memory asked for by traceKernel / shadeKernel (-> the 64 KB configuration; trace.cu launchTrace)
 int numSMs();
 
 // One 32-byte record per INNER node, holding both children: their boxes quantised (conservatively, 2 cells of padding) to a

@@ -6,6 +6,7 @@
 //   tonemapSqrtKernel  computeFinalPixelColorsKernel, sv4/toneMap.cu:41-58
 // All HBM-streaming / gather bound; compiled with -fmad=false (see shade_math.cuh).
 #include "shade_math.cuh"
+#include <atomic>
 CHK_DECL          // B200PT_CHECKED builds: violation counter of this file (codes 20-39)
 
 #ifndef SHADE_HOIST_THR
@@ -723,6 +724,15 @@ void launchRaygen(const FrameParams& F, const PassParams& P, int k0, int k1, con
     raygenKernel<<<persistentGrid(), SHADE_BLOCK, 0, s>>>(F, P, k0, k1, pool, Q);
 }
 void launchShade(const FrameParams& F, const SceneDev& scene, const PathPool& pool, const Queues& Q, int cur, int depth, cudaStream_t s) {
+    // the same shared-memory carve-out as traceKernel (see launchTrace: kernels of frames in flight share an SM only with equal configurations); the
+    // kernel's own time does not depend on it (1.143-1.151 ms per frame from 0 to 28 %)
+    static const int carveout = [] { const char* e = getenv("B200PT_SHADE_CARVEOUT");  return e ? atoi(e) : B200PT_SMEM_CARVEOUT; }();
+    static std::atomic<unsigned long long> carved{0ull};
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < 64 && !(carved.load() >> dev & 1ull)) {
+        cudaFuncSetAttribute(shadeKernel, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
+        carved.fetch_or(1ull << dev);
+    }
     shadeKernel<<<persistentGrid(), SHADE_BLOCK, 0, s>>>(F, scene, pool, Q, cur, depth);
 }
 void launchGather(const FrameParams& F, const PassParams& P, int k0, int k1, const PathPool& pool, float4* sumRad, float4* sumAlpha,

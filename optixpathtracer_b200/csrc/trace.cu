@@ -16,6 +16,7 @@
 // The ray/triangle test is the exact fp32 operation sequence of oracle/scene_core.h (no FMA contraction,
 // enforced with __f*_rn intrinsics), which makes the chosen triangle and (t,u,v) BVH-independent.
 #include "common.cuh"
+#include <atomic>
 CHK_DECL          // B200PT_CHECKED builds: violation counter of this file (codes 10-19)
 
 #ifndef TRACE_BLOCK
@@ -579,6 +580,18 @@ void launchTrace(const SceneDev& scene, const Queues& Q, int cur, int closest, u
                  const PathPool& pool, TraceStats* stats, cudaStream_t stream) {
     static const int ctasPerSM = [] { const char* e = getenv("B200PT_TRACE_CTAS");  const int v = e ? atoi(e) : TRACE_BLOCKS_PER_SM;  return v < 1 ? 1 : (v > TRACE_BLOCKS_PER_SM ? TRACE_BLOCKS_PER_SM : v); }();   // tuning knob: fewer persistent CTAs per SM leave room for a concurrent shadeKernel of another frame
     const dim3 grid((unsigned)numSMs() * ctasPerSM), block(TRACE_BLOCK);
+    // Shared-memory carve-out: 7 CTAs x (8 KB of ray staging + 1 KB reserved) fit the 64 KB configuration, which leaves the most L1 for the tree and the
+    // stacks.  Left to itself the driver picks a larger carve-out here; measured on B200 (trace ms per frame): default 2.601, 25-30 % (= 64 KB) 2.558,
+    // 50 % 2.611, 100 % 2.738.  shadeKernel asks for the same configuration (shade.cu): kernels with different carve-outs do not share an SM, and with
+    // frames in flight they should (shade at 0 % or 10 %: 596 Msamples/s in flight instead of 603).  Set once per device (B200PT_TRACE_CARVEOUT overrides).
+    static const int carveout = [] { const char* e = getenv("B200PT_TRACE_CARVEOUT");  return e ? atoi(e) : B200PT_SMEM_CARVEOUT; }();
+    static std::atomic<unsigned long long> carved{0ull};
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < 64 && !(carved.load() >> dev & 1ull)) {
+        cudaFuncSetAttribute(traceKernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
+        cudaFuncSetAttribute(traceKernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
+        carved.fetch_or(1ull << dev);
+    }
     if (stats) traceKernel<true><<<grid, block, 0, stream>>>(scene, Q.rayO[cur], Q.rayD[cur], Q.hit, Q.shO, Q.shD, Q.shP, ctr, closest, tmin, tminShadow, tmax, cullBack, pool, stats, refillThreshold(), leafThreshold(), nodeMinThreshold());
     else traceKernel<false><<<grid, block, 0, stream>>>(scene, Q.rayO[cur], Q.rayD[cur], Q.hit, Q.shO, Q.shD, Q.shP, ctr, closest, tmin, tminShadow, tmax, cullBack, pool, nullptr, refillThreshold(), leafThreshold(), nodeMinThreshold());
 }
