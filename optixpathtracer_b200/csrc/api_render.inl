@@ -210,6 +210,15 @@ static void enqueuePart(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& job, 
 
     PathPool pool = poolOf(L);
     Queues Q = queuesOf(L);
+    // One group whose chunks are whole passes, one part: the per-launch-index records are not needed - the finalize passes read the pool (which nothing
+    // reuses before them: a lane's next wavefront is enqueued behind its finalize passes).  B200PT_FUSE_GATHER=0 keeps the separate gather pass (A/B).
+    static const bool fuseAllowed = [] { const char* e = getenv("B200PT_FUSE_GATHER");  return !e || atoi(e) != 0; }();
+    bool fuse = fuseAllowed && nParts == 1 && groups.size() == 1;
+    for (auto& ch : groups[0]) fuse = fuse && ch.k0 == 0 && ch.k1 == passes[ch.pass].P.spl;
+    if (fuse) {
+        job.fused = true;  job.pool = pool;
+        for (auto& ch : groups[0]) passes[ch.pass].P.slotBase = ch.slotBase;
+    }
 
     const bool prof = (cfg.profile & 1) != 0, count = (cfg.profile & 2) != 0;   // 1: stage events, 2: traversal counters
     if (prof) { c->evUsed.clear();  c->evNext = 0; }
@@ -245,6 +254,7 @@ static void enqueuePart(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& job, 
             cur ^= 1;
         }
         tallyCountersKernel<<<1, 32, 0, s>>>(Q.counters, bounces + 1, totals);  ++launches;
+        if (fuse) continue;
         T.begin(ST_ACCUM, a, b);
         for (auto& ch : group) {
             PassParams P = passes[ch.pass].P;  P.slotBase = ch.slotBase;
@@ -293,7 +303,7 @@ static void enqueueFinalize(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& j
     const bool put = peerPutBegin(c, cfg, F, s);
     for (auto& p : job.passes) {                                                 // pass order = the reference's launch order (overwrite semantics)
         if (!p.nLaunch) continue;
-        launchFinalize(F, p.P, L.sumRad.p, L.sumAlpha.p, L.sumNormal.p, L.sumAlbedo.p, s);  ++job.launches;
+        launchFinalize(F, p.P, L.sumRad.p, L.sumAlpha.p, L.sumNormal.p, L.sumAlbedo.p, job.fused ? &job.pool : nullptr, s);  ++job.launches;
     }
     if (put) peerPutEnd(c, s);
     T.end(b);

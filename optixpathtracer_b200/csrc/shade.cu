@@ -457,6 +457,22 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
     }
 }
 
+// samples k0..k1-1 of launch index li added to the running sums, in sample order (result += direct + indirect, :516-517)
+DEV void gatherSamples(const FrameParams& F, const PassParams& P, int k0, int k1, const PathPool& pool, unsigned li,
+                       float3& result, float3& alpha, float3& normal, float3& albedo) {
+    for (int k = k0; k < k1; ++k) {
+        const unsigned slot = P.slotBase + li * (unsigned)(k1 - k0) + (unsigned)(k - k0);
+        if (!CHK(slot < pool.cap, 27)) break;
+        const float4 d = pool.direct[slot], i = pool.indirect[slot], a = pool.alpha[slot];
+        result = result + (f3(d.x, d.y, d.z) + f3(i.x, i.y, i.z));
+        alpha = alpha + f3(a.x, a.y, a.z);
+        if (F.writeAovs) {
+            const float4 nn = pool.aovNormal[slot], aa = pool.aovAlbedo[slot];
+            normal = normal + f3(nn.x, nn.y, nn.z);  albedo = albedo + f3(aa.x, aa.y, aa.z);
+        }
+    }
+}
+
 // Per-launch-index sums over the samples of one chunk, in sample order (result += direct+indirect, :516-517).
 __global__ void __launch_bounds__(SHADE_BLOCK)
 gatherKernel(FrameParams F, PassParams P, int k0, int k1, PathPool pool, float4* sumRad, float4* sumAlpha,
@@ -473,17 +489,7 @@ gatherKernel(FrameParams F, PassParams P, int k0, int k1, PathPool pool, float4*
         result = f3(r.x, r.y, r.z);  alpha = f3(a.x, a.y, a.z);
         if (F.writeAovs) { const float4 nn = sumNormal[rec], aa = sumAlbedo[rec];  normal = f3(nn.x, nn.y, nn.z);  albedo = f3(aa.x, aa.y, aa.z); }
     }
-    for (int k = k0; k < k1; ++k) {
-        const unsigned slot = P.slotBase + li * (unsigned)(k1 - k0) + (unsigned)(k - k0);
-        if (!CHK(slot < pool.cap, 27)) break;
-        const float4 d = pool.direct[slot], i = pool.indirect[slot], a = pool.alpha[slot];
-        result = result + (f3(d.x, d.y, d.z) + f3(i.x, i.y, i.z));
-        alpha = alpha + f3(a.x, a.y, a.z);
-        if (F.writeAovs) {
-            const float4 nn = pool.aovNormal[slot], aa = pool.aovAlbedo[slot];
-            normal = normal + f3(nn.x, nn.y, nn.z);  albedo = albedo + f3(aa.x, aa.y, aa.z);
-        }
-    }
+    gatherSamples(F, P, k0, k1, pool, li, result, alpha, normal, albedo);
     sumRad[rec] = make_float4(result.x, result.y, result.z, 0.f);
     sumAlpha[rec] = make_float4(alpha.x, alpha.y, alpha.z, 0.f);
     if (F.writeAovs) { sumNormal[rec] = make_float4(normal.x, normal.y, normal.z, 0.f);  sumAlbedo[rec] = make_float4(albedo.x, albedo.y, albedo.z, 0.f); }
@@ -497,7 +503,7 @@ DEV uint32_t displayColor(const FrameParams& F, float3 accum) {
 // Accumulation + display transform + fillSize^2 block replication (:521-587).  36 B/pixel streaming.
 __global__ void __launch_bounds__(SHADE_BLOCK)
 finalizeKernel(FrameParams F, PassParams P, const float4* sumRad, const float4* sumAlpha, const float4* sumNormal,
-               const float4* sumAlbedo) {
+               const float4* sumAlbedo, PathPool pool, int fused) {
     const unsigned n = (unsigned)P.launchW * (unsigned)P.launchH;
     const unsigned li = blockIdx.x * blockDim.x + threadIdx.x;
     if (li >= n) return;
@@ -510,14 +516,17 @@ finalizeKernel(FrameParams F, PassParams P, const float4* sumRad, const float4* 
     const float3 lastDir = primaryDir(F, L, seed);
     const float4 bp4 = probeEval(F.probe, probeDirToUV(lastDir));
     const float3 backplate = f3(bp4.x, bp4.y, bp4.z);
-    const float4 r4 = sumRad[rec], a4 = sumAlpha[rec];
-    const float3 result = f3(r4.x, r4.y, r4.z);
-    const float3 alpha = f3(a4.x, a4.y, a4.z) / spl;                                  // :523
-    float3 normal = f3(0.f), albedo = f3(0.f);
-    if (F.writeAovs) {
-        const float4 nn = sumNormal[rec], aa = sumAlbedo[rec];
-        normal = f3(nn.x, nn.y, nn.z) / spl;  albedo = f3(aa.x, aa.y, aa.z) / spl;    // :521-522
+    // The per-launch-index sums: read back from gatherKernel's records, or - a frame whose samples sit in ONE chunk of the path pool (fused) - summed here
+    // straight from the pool in the same order, which saves the records' round trip through HBM (64 B written + 64 B read per launch index, 128 with AOVs)
+    float3 result = f3(0.f), alphaSum = f3(0.f), normal = f3(0.f), albedo = f3(0.f);
+    if (fused) gatherSamples(F, P, 0, P.spl, pool, li, result, alphaSum, normal, albedo);
+    else {
+        const float4 r4 = sumRad[rec], a4 = sumAlpha[rec];
+        result = f3(r4.x, r4.y, r4.z);  alphaSum = f3(a4.x, a4.y, a4.z);
+        if (F.writeAovs) { const float4 nn = sumNormal[rec], aa = sumAlbedo[rec];  normal = f3(nn.x, nn.y, nn.z);  albedo = f3(aa.x, aa.y, aa.z); }
     }
+    const float3 alpha = alphaSum / spl;                                              // :523
+    if (F.writeAovs) { normal = normal / spl;  albedo = albedo / spl; }               // :521-522
     const float3 color = (backplate * spl) * (f3(1.0f) - alpha) + result;             // :538
     const float3 fresh = color / spl;                                                 // :540
     for (int i = 0; i < P.fillSize; ++i) {
@@ -740,8 +749,9 @@ void launchGather(const FrameParams& F, const PassParams& P, int k0, int k1, con
     gatherKernel<<<gridFor((unsigned)P.launchW * P.launchH), SHADE_BLOCK, 0, s>>>(F, P, k0, k1, pool, sumRad, sumAlpha, sumNormal, sumAlbedo);
 }
 void launchFinalize(const FrameParams& F, const PassParams& P, const float4* sumRad, const float4* sumAlpha, const float4* sumNormal,
-                    const float4* sumAlbedo, cudaStream_t s) {
-    finalizeKernel<<<gridFor((unsigned)P.launchW * P.launchH), SHADE_BLOCK, 0, s>>>(F, P, sumRad, sumAlpha, sumNormal, sumAlbedo);
+                    const float4* sumAlbedo, const PathPool* fusedPool, cudaStream_t s) {
+    finalizeKernel<<<gridFor((unsigned)P.launchW * P.launchH), SHADE_BLOCK, 0, s>>>(F, P, sumRad, sumAlpha, sumNormal, sumAlbedo,
+                                                                                     fusedPool ? *fusedPool : PathPool{}, fusedPool ? 1 : 0);
 }
 void launchResolveSum(const FrameParams& F, int nPasses, cudaStream_t s) {
     resolveSumKernel<<<gridFor((unsigned)F.W * F.H), SHADE_BLOCK, 0, s>>>(F, nPasses);
