@@ -728,6 +728,7 @@ def run_b200(a):
     nodes = tris = crays = hits = 0
     nodes_s = tris_s = srays = 0
     replay = min(a.steps, 4)
+    fused_finalize = False
     for i in range(replay):
         r.launchParams.frame.subframe_index = frame_index(a.warmup + i)
         r.render()
@@ -739,6 +740,7 @@ def run_b200(a):
         nodes_s += c.nodes_fetched_shadow
         tris_s += c.tris_fetched_shadow
         srays += c.shadow_rays
+        fused_finalize = bool(c.fused_finalize)
     cfg.profile = 0
 
     peak, peak_src = _peaks()
@@ -818,17 +820,19 @@ def run_b200(a):
                               "tables are cache-resident, so DRAM traffic (traffic, dram_frac) is below the algorithmic figure"}
         # (3) gather + finalize: 48 B per sample (direct, indirect, alpha) in, 2 x 32 B per launch index through the per-launch-index sums, 36 B per pixel (accum r/w + RGBA8)
         aov = 1 if cfg.write_aovs else 0                                            # the `orig` preset also writes the normal / albedo / colour AOVs (orig/deviceProgram.cu:472-474)
-        acc_bytes = (48.0 + 32.0 * aov) * rays["samples"] / max(1, a.steps) + (64 + 36 + aov * (64 + 48)) * n_px
+        rec_bytes = 0 if fused_finalize else 64 + aov * 64                         # per-launch-index records of a separate gather pass (written + read back)
+        acc_bytes = (48.0 + 32.0 * aov) * rays["samples"] / max(1, a.steps) + (rec_bytes + 36 + aov * 48) * n_px
         g_ncu, g_fr = ncu_of("gatherKernel")
         f_ncu, f_fr = ncu_of("finalizeKernel")
         acc_gbs = acc_bytes / (st["accumulate"] * 1e-3) / 1e9
-        roof_acc = {"bound": "hbm", "kernel": "gatherKernel + finalizeKernel", "achieved": acc_gbs, "peak": peak, "unit": "GB/s", "frac": acc_gbs / peak,
+        roof_acc = {"bound": "hbm", "kernel": "finalizeKernel (gather fused)" if fused_finalize else "gatherKernel + finalizeKernel", "fused": fused_finalize, "achieved": acc_gbs, "peak": peak, "unit": "GB/s", "frac": acc_gbs / peak,
                     "traffic": (g_fr["traffic"] or 0) + (f_fr["traffic"] or 0) if (g_fr["traffic"] is not None or f_fr["traffic"] is not None) else None,
                     "dram_frac_gather": g_fr["dram_frac"], "dram_frac_finalize": f_fr["dram_frac"], "ncu_gather": g_ncu, "ncu_finalize": f_ncu, "traffic_source": src,
                     "algorithmic_bytes_per_step": acc_bytes, "ms_per_step": st["accumulate"],
-                    "note": "48 B per sample read by gatherKernel + 32 B written / 32 B read per launch index (per-launch-index sums) + 36 B per pixel in finalizeKernel "
-                            "(16 B accumulation read, 16 B written, 4 B RGBA8); with AOVs (preset orig) + 32 B per sample, + 64 B per launch index, + 48 B per pixel; / the "
-                            "CUDA-event time of the two launches (tens of microseconds each: launch ramp and tail are a visible share of a kernel this short); "
+                    "note": "48 B per sample (direct, indirect, alpha) + 36 B per pixel (16 B accumulation read, 16 B written, 4 B RGBA8); with AOVs (preset orig) + 32 B per "
+                            "sample and + 48 B per pixel; a frame whose samples sit in one chunk of the path pool (fused: true) sums the samples inside finalizeKernel, "
+                            "otherwise gatherKernel writes per-launch-index records that finalizeKernel reads back (+ 64 B per launch index, + 64 with AOVs); / the "
+                            "CUDA-event time of the launch(es) (tens of microseconds: launch ramp and tail are a visible share of a kernel this short); "
                             "dram_frac_* = measured DRAM bytes / duration / HBM peak of each kernel under ncu"}
         parallelism = "single GPU" if world == 1 else (f"sample split over {world} GPUs (rank r renders sub-frames r, r+N, ...), one NCCL fp32 reduce of the SUM buffer "
                                                         "+ resolve on rank 0 inside the timed region (b200pt_reduce_sum)")

@@ -289,7 +289,7 @@ typedef struct b200pt_counters {      /* last render()                          
     float    ms_total, ms_raygen, ms_trace_closest, ms_trace_any, ms_shade, ms_accumulate;   /* profile=1 */
     uint32_t kernel_launches;         /* kernels launched by the last render()                          */
     uint32_t n_trace_closest_launches, n_trace_any_launches;
-    uint32_t reserved_;
+    uint32_t fused_finalize;          /* 1: the frame's finalize passes summed the samples straight from the path pool (no gather pass) */
     uint64_t closest_hits;            /* radiance rays that hit a surface = entries shadeKernel shades (profile bit 1)  */
     uint64_t occluded_shadow_rays;    /* (profile bit 1)                                                                */
 } b200pt_counters;

@@ -313,7 +313,7 @@ static void enqueueFinalize(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& j
     c->lastLane = job.lane;  c->countersLane = job.lane;  c->countersExtra = job.extraLanes;  L.busy = job.lane > 0;
     c->profiled = cfg.profile & 3;
     c->last = b200pt_counters{};
-    c->last.kernel_launches = job.launches;  c->last.n_trace_closest_launches = job.nClosest;  c->last.n_trace_any_launches = 0;
+    c->last.kernel_launches = job.launches;  c->last.n_trace_closest_launches = job.nClosest;  c->last.n_trace_any_launches = 0;  c->last.fused_finalize = job.fused ? 1u : 0u;
     c->countersPending = true;
 }
 

@@ -172,7 +172,7 @@ class Counters(C.Structure):
                 ("ms_total", C.c_float), ("ms_raygen", C.c_float), ("ms_trace_closest", C.c_float),
                 ("ms_trace_any", C.c_float), ("ms_shade", C.c_float), ("ms_accumulate", C.c_float),
                 ("kernel_launches", C.c_uint32), ("n_trace_closest_launches", C.c_uint32),
-                ("n_trace_any_launches", C.c_uint32), ("reserved_", C.c_uint32),
+                ("n_trace_any_launches", C.c_uint32), ("fused_finalize", C.c_uint32),
                 ("closest_hits", C.c_uint64), ("occluded_shadow_rays", C.c_uint64)]
 
 
