@@ -53,9 +53,10 @@ struct PassDesc { PassParams P;  size_t nLaunch; };
 // shared accumulation / frame / AOV buffers).
 // `lane` runs the wavefront - or, for a frame split into interleaved band sets (cfg.intra_frame_split), part 0 of it, with the other parts on `extraLanes`;
 // the finalize passes always run on `lane`, whose sumRad/sumAlpha buffers collect the per-launch-index sums of every part.
-// `fused`: every sample of the frame sits in one chunk of `lane`'s pool, so no gather pass ran: the finalize passes sum the samples from `pool` themselves.
+// `fused.n > 0`: every sample of the frame (of each band set) sits in one chunk of its lane's pool, so no gather pass ran: the finalize passes sum the samples from
+// those pools themselves.
 struct FrameJob { int lane = -1;  std::vector<int> extraLanes;  std::vector<PassDesc> passes;  FrameParams F;  unsigned launches = 0, nClosest = 0;  cudaEvent_t totalEnd = nullptr;
-                  bool fused = false;  PathPool pool{}; };
+                  FusedPools fused{}; };
 // Speculative next sub-frame (blocking b200pt_render with cfg.frames_in_flight > 1).  Progressive accumulation calls render() again and again with
 // the same launchParams and the next subframe_index; once a call has been predicted right, render() enqueues the wavefront of the
 // PREDICTED next call(s) on the other lanes before it blocks on the current frame.  The next call either matches the prediction byte for byte

@@ -210,13 +210,14 @@ static void enqueuePart(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& job, 
 
     PathPool pool = poolOf(L);
     Queues Q = queuesOf(L);
-    // One group whose chunks are whole passes, one part: the per-launch-index records are not needed - the finalize passes read the pool (which nothing
+    // One group whose chunks are whole passes: the per-launch-index records are not needed - the finalize passes read the pool(s) (which nothing
     // reuses before them: a lane's next wavefront is enqueued behind its finalize passes).  B200PT_FUSE_GATHER=0 keeps the separate gather pass (A/B).
     static const bool fuseAllowed = [] { const char* e = getenv("B200PT_FUSE_GATHER");  return !e || atoi(e) != 0; }();
-    bool fuse = fuseAllowed && nParts == 1 && groups.size() == 1;
+    // (every band set of a split frame sees the same passes and the same pool limit, so they all decide alike and share the passes' slot bases)
+    bool fuse = fuseAllowed && nParts <= 4 && groups.size() == 1;
     for (auto& ch : groups[0]) fuse = fuse && ch.k0 == 0 && ch.k1 == passes[ch.pass].P.spl;
     if (fuse) {
-        job.fused = true;  job.pool = pool;
+        job.fused.n = nParts;  job.fused.p[part] = pool;
         for (auto& ch : groups[0]) passes[ch.pass].P.slotBase = ch.slotBase;
     }
 
@@ -303,7 +304,7 @@ static void enqueueFinalize(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& j
     const bool put = peerPutBegin(c, cfg, F, s);
     for (auto& p : job.passes) {                                                 // pass order = the reference's launch order (overwrite semantics)
         if (!p.nLaunch) continue;
-        launchFinalize(F, p.P, L.sumRad.p, L.sumAlpha.p, L.sumNormal.p, L.sumAlbedo.p, job.fused ? &job.pool : nullptr, s);  ++job.launches;
+        launchFinalize(F, p.P, L.sumRad.p, L.sumAlpha.p, L.sumNormal.p, L.sumAlbedo.p, job.fused, s);  ++job.launches;
     }
     if (put) peerPutEnd(c, s);
     T.end(b);
@@ -313,7 +314,7 @@ static void enqueueFinalize(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& j
     c->lastLane = job.lane;  c->countersLane = job.lane;  c->countersExtra = job.extraLanes;  L.busy = job.lane > 0;
     c->profiled = cfg.profile & 3;
     c->last = b200pt_counters{};
-    c->last.kernel_launches = job.launches;  c->last.n_trace_closest_launches = job.nClosest;  c->last.n_trace_any_launches = 0;  c->last.fused_finalize = job.fused ? 1u : 0u;
+    c->last.kernel_launches = job.launches;  c->last.n_trace_closest_launches = job.nClosest;  c->last.n_trace_any_launches = 0;  c->last.fused_finalize = job.fused.n > 0 ? 1u : 0u;
     c->countersPending = true;
 }
 

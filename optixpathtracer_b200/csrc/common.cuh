@@ -196,9 +196,11 @@ void launchShade(const FrameParams& F, const SceneDev& scene, const PathPool& po
                  cudaStream_t stream);
 void launchGather(const FrameParams& F, const PassParams& P, int k0, int k1, const PathPool& pool, float4* sumRad,
                   float4* sumAlpha, float4* sumNormal, float4* sumAlbedo, cudaStream_t stream);
+// the pools a fused finalize pass sums the samples from: one per band set of the frame (n = 1: the whole frame; n = 0: not fused, read gatherKernel's records).
+// Band b of a pass belongs to set ((b % (tileCount * n)) - tileRank) / tileCount - the partition enqueuePart gives the sets (api_render.inl).
+struct FusedPools { PathPool p[4];  int n; };
 void launchFinalize(const FrameParams& F, const PassParams& P, const float4* sumRad, const float4* sumAlpha,
-                    const float4* sumNormal, const float4* sumAlbedo, const PathPool* fusedPool /* non-null: sum the samples from the pool (P.slotBase, P.spl) */,
-                    cudaStream_t stream);
+                    const float4* sumNormal, const float4* sumAlbedo, const FusedPools& fused, cudaStream_t stream);
 void launchResolveSum(const FrameParams& F, int nPasses, cudaStream_t stream);
 void launchResolveTotal(const FrameParams& F, const float4* total, int nPasses, cudaStream_t stream);
 struct WhittedParams { int W, H;  float3 position, direction, horizontal, vertical, lightPos; };

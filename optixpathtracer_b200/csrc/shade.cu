@@ -503,7 +503,7 @@ DEV uint32_t displayColor(const FrameParams& F, float3 accum) {
 // Accumulation + display transform + fillSize^2 block replication (:521-587).  36 B/pixel streaming.
 __global__ void __launch_bounds__(SHADE_BLOCK)
 finalizeKernel(FrameParams F, PassParams P, const float4* sumRad, const float4* sumAlpha, const float4* sumNormal,
-               const float4* sumAlbedo, PathPool pool, int fused) {
+               const float4* sumAlbedo, FusedPools fused) {
     const unsigned n = (unsigned)P.launchW * (unsigned)P.launchH;
     const unsigned li = blockIdx.x * blockDim.x + threadIdx.x;
     if (li >= n) return;
@@ -519,7 +519,14 @@ finalizeKernel(FrameParams F, PassParams P, const float4* sumRad, const float4* 
     // The per-launch-index sums: read back from gatherKernel's records, or - a frame whose samples sit in ONE chunk of the path pool (fused) - summed here
     // straight from the pool in the same order, which saves the records' round trip through HBM (64 B written + 64 B read per launch index, 128 with AOVs)
     float3 result = f3(0.f), alphaSum = f3(0.f), normal = f3(0.f), albedo = f3(0.f);
-    if (fused) gatherSamples(F, P, 0, P.spl, pool, li, result, alphaSum, normal, albedo);
+    if (fused.n > 0) {
+        int set = 0;
+        if (fused.n > 1) {                                                            // the band set that rendered this launch row (enqueuePart's partition)
+            const unsigned tc = (unsigned)max(F.tileCount, 1), tr = F.tileCount > 1 ? (unsigned)F.tileRank : 0u;
+            set = (int)((((L.ly / 32u) % (tc * (unsigned)fused.n)) - tr) / tc);
+        }
+        gatherSamples(F, P, 0, P.spl, fused.p[set], li, result, alphaSum, normal, albedo);
+    }
     else {
         const float4 r4 = sumRad[rec], a4 = sumAlpha[rec];
         result = f3(r4.x, r4.y, r4.z);  alphaSum = f3(a4.x, a4.y, a4.z);
@@ -749,9 +756,8 @@ void launchGather(const FrameParams& F, const PassParams& P, int k0, int k1, con
     gatherKernel<<<gridFor((unsigned)P.launchW * P.launchH), SHADE_BLOCK, 0, s>>>(F, P, k0, k1, pool, sumRad, sumAlpha, sumNormal, sumAlbedo);
 }
 void launchFinalize(const FrameParams& F, const PassParams& P, const float4* sumRad, const float4* sumAlpha, const float4* sumNormal,
-                    const float4* sumAlbedo, const PathPool* fusedPool, cudaStream_t s) {
-    finalizeKernel<<<gridFor((unsigned)P.launchW * P.launchH), SHADE_BLOCK, 0, s>>>(F, P, sumRad, sumAlpha, sumNormal, sumAlbedo,
-                                                                                     fusedPool ? *fusedPool : PathPool{}, fusedPool ? 1 : 0);
+                    const float4* sumAlbedo, const FusedPools& fused, cudaStream_t s) {
+    finalizeKernel<<<gridFor((unsigned)P.launchW * P.launchH), SHADE_BLOCK, 0, s>>>(F, P, sumRad, sumAlpha, sumNormal, sumAlbedo, fused);
 }
 void launchResolveSum(const FrameParams& F, int nPasses, cudaStream_t s) {
     resolveSumKernel<<<gridFor((unsigned)F.W * F.H), SHADE_BLOCK, 0, s>>>(F, nPasses);
