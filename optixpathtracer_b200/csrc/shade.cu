@@ -180,8 +180,8 @@ raygenKernel(FrameParams F, PassParams P, int k0, int k1, PathPool pool, Queues 
                 stState(pool.st + slot, st);
                 pool.direct[slot] = make_float4(0, 0, 0, 0);
                 pool.indirect[slot] = make_float4(0, 0, 0, 0);
-                pool.alpha[slot] = make_float4(0, 0, 0, 0);
-                if (F.writeAovs) { pool.aovNormal[slot] = make_float4(0, 0, 0, 0);  pool.aovAlbedo[slot] = make_float4(0, 0, 0, 0); }
+                // prd.alpha and the AOV records are NOT zeroed here: every primary ray passes through shadeKernel's first pass exactly once, which writes them
+                // whatever it finds (a surface: alpha 1 or, on a shadow catcher, 0, and the hit's normal / albedo; a miss: zeros) - 48 B per sample less to write
                 o4 = make_float4(F.eye.x, F.eye.y, F.eye.z, __int_as_float((int)slot));
                 d4 = make_float4(dir.x, dir.y, dir.z, 0.f);
                 want = true;
@@ -303,6 +303,10 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
             const float3 org = f3(o4.x, o4.y, o4.z), dir = f3(d4.x, d4.y, d4.z);
             if (triSlot < 0) {
                 flags |= PF_DONE;                                                 // __miss__radiance, :251-280 (shaded only with mis_on_miss)
+                if (depth == 0) {                                                 // a primary miss: the records raygen leaves to this pass (alpha 0, no AOV features)
+                    pool.alpha[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (F.writeAovs) { pool.aovNormal[slot] = make_float4(0.f, 0.f, 0.f, 0.f);  pool.aovAlbedo[slot] = make_float4(0.f, 0.f, 0.f, 0.f); }
+                }
                 if (F.misOnMiss && (flags & PF_SECONDARY)) {                      // opt-in extension (:257-267), same rule as oracle/render_core.h
                     const float skyPdf = probePdf(F.probe, dir);
                     const float bp = st.bsdfPdf;
@@ -358,6 +362,7 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                     // prd.alpha = 1 at every non-catcher hit (:660).  Once it is 1 nothing can change it again (only a PRIMARY catcher hit emits an
                     // alpha-targeted shadow ray, and that one resolves before this pass), so the 16-byte scattered store happens once per path.
                     if (!catcher && !(flags & PF_ALPHA_ONE)) { pool.alpha[slot] = make_float4(1.f, 1.f, 1.f, 0.f);  flags |= PF_ALPHA_ONE; }
+                    else if (catcher && depth == 0) pool.alpha[slot] = make_float4(0.f, 0.f, 0.f, 0.f);   // a primary catcher hit starts from prd.alpha = 0 (:441; raygen does not write it)
                     if (last && !catcher) {
                         flags |= PF_DONE;
                     } else {
