@@ -446,8 +446,8 @@ shadeKernel(FrameParams F, SceneDev S, PathPool pool, Queues Q, int cur, int lau
                     }
                 }
             }
-            st.state = (depth & 0xff) | (flags << 8);
-            stState(pool.st + slot, st);
+            // the record is read again only by the pass that shades this path's next ray: a path that ends here (miss, depth cap, pdf <= 0, roulette) leaves none
+            if (wantRay) { st.state = (depth & 0xff) | (flags << 8);  stState(pool.st + slot, st); }
         }
 #if SHADE_SORT_OCTANT && !SHADE_COMPACT
         enqueueRayByOctant(wantRay, po, rd, Q.rayO[nxt], Q.rayD[nxt], nextCounter, Q.cap);
