@@ -213,6 +213,11 @@ int b200pt_gather_bands(b200pt_ctx* ctx, const struct LaunchParams* params, int 
  *                       (b200pt_download_pixels...), b200pt_peer_release (the ranks' next finalize pass waits for it: no frame is overwritten early)
  * Nothing synchronises with the host.  A wait that sees no progress for B200PT_PEER_TIMEOUT_MS (environment, default 5000) gives up and records
  * its code (b200pt_peer_status: 0 = fine, 1 + r = root timed out waiting for rank r, 1000 + 64 = a rank timed out waiting for root's release).
+ * Schedules with several passes (the foveated presets: a later pass overwrites pixels of an earlier one) work too: the partition is by 32-row bands of
+ * every pass's launch rows (each rank gets an equal share of fovea, mid ring and periphery), and between two passes every rank publishes "pass k done"
+ * and waits for all the others (the same flag block), so the overwrite order of a single GPU is kept; such a frame is byte-identical to one GPU when it
+ * does not read the accumulation buffer (subframe_index 0 or redraw: the interactive mode), and root (cfg.tile_rank / tile_count = the exported rank /
+ * n_ranks) takes part in the barriers.
  * The accumulation buffer of a band stays on the rank that renders it (progressive accumulation needs no exchange); a resize drops the export /
  * the mapping (export and attach again).  Pixels are byte-identical to b200pt_gather_bands' and to a single-GPU frame.
  * Ranks that share ONE GPU inside ONE process (tests): CUDA loads kernels lazily and a load synchronises the context, so every such rank must have

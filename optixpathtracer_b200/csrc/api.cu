@@ -116,8 +116,9 @@ static void freeAccum(b200pt_ctx* c);                 // api_multi.inl
 static void allocAccum(b200pt_ctx* c, size_t n);
 static void destroyMulti(b200pt_ctx* c);
 static void destroyPeer(b200pt_ctx* c);               // api_peer.inl
-static bool peerPutBegin(b200pt_ctx* c, const b200pt_config& cfg, FrameParams& F, cudaStream_t s);
-static void peerPutEnd(b200pt_ctx* c, cudaStream_t s);
+static int peerPutBegin(b200pt_ctx* c, const b200pt_config& cfg, FrameParams& F, cudaStream_t s);
+static void peerPassBarrier(b200pt_ctx* c, int role, int k, cudaStream_t s);
+static void peerPutEnd(b200pt_ctx* c, int role, cudaStream_t s);
 
 // Orders the primary stream after every frame in flight on the other lanes (no host synchronisation): what the entry points that touch
 // shared state (frame buffers, scene, probe, counters) do first, and what b200pt_join exposes to callers that time or copy on that stream.

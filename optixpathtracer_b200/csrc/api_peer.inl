@@ -73,18 +73,38 @@ static void destroyPeer(b200pt_ctx* c) {
 }
 
 // enqueueFinalize's hooks (api_render.inl) ------------------------------------------------------------------------------------------------
-static bool peerPutBegin(b200pt_ctx* c, const b200pt_config& cfg, FrameParams& F, cudaStream_t s) {
+// Epochs: a rank that has put f frames publishes 8 * f; inside frame f + 1 it publishes 8 * f + k after its k-th finalize pass when the frame has several
+// (the foveated schedule: a later pass overwrites pixels of an earlier one, so no rank may start pass k + 1 before every rank has finished pass k).
+// role: 0 = not part of a one-sided partition for this frame, 1 = attached rank (writes root's frame), 2 = the exporting root (writes its own frame, takes
+// part in the pass barriers).
+static int peerRole(b200pt_ctx* c, const b200pt_config& cfg, const FrameParams& F) {
     PeerState* p = c->peer;
-    if (!p || !p->remoteFrame || cfg.tile_count <= 1 || cfg.accum_mode == B200PT_ACCUM_SUM || F.W != p->W || F.H != p->H) return false;
-    // root must have consumed the frame before this one (epoch `put`) - the first frame passes at once
-    peerWaitKernel<<<1, 32, 0, s>>>(p->remoteFlags, PEER_ACK, 1, -1, p->put, p->timeoutNs, p->err, 1000u);
-    F.frame = p->remoteFrame;
-    return true;
+    if (!p || cfg.tile_count <= 1 || cfg.accum_mode == B200PT_ACCUM_SUM || F.W != p->W || F.H != p->H) return 0;
+    if (p->remoteFrame) return 1;
+    return (p->exported && cfg.tile_count == p->nranks && cfg.tile_rank == p->rank) ? 2 : 0;
 }
-static void peerPutEnd(b200pt_ctx* c, cudaStream_t s) {
+static int peerPutBegin(b200pt_ctx* c, const b200pt_config& cfg, FrameParams& F, cudaStream_t s) {
+    const int role = peerRole(c, cfg, F);
+    PeerState* p = c->peer;
+    if (role == 1) {
+        // root must have consumed the frame before this one (epoch 8 * put) - the first frame passes at once
+        peerWaitKernel<<<1, 32, 0, s>>>(p->remoteFlags, PEER_ACK, 1, -1, 8u * p->put, p->timeoutNs, p->err, 1000u);
+        F.frame = p->remoteFrame;
+    }
+    return role;
+}
+// between two finalize passes of a frame: publish "pass k done", wait until every rank has
+static void peerPassBarrier(b200pt_ctx* c, int role, int k, cudaStream_t s) {
+    PeerState* p = c->peer;
+    unsigned* flags = role == 1 ? p->remoteFlags : p->flags;
+    const unsigned epoch = 8u * p->put + (unsigned)k;
+    peerSignalKernel<<<1, 1, 0, s>>>(flags + p->rank, epoch);
+    peerWaitKernel<<<1, PEER_MAX_RANKS, 0, s>>>(flags, 0, p->nranks, p->rank, epoch, p->timeoutNs, p->err, 2000u);
+}
+static void peerPutEnd(b200pt_ctx* c, int role, cudaStream_t s) {
     PeerState* p = c->peer;
     ++p->put;
-    peerSignalKernel<<<1, 1, 0, s>>>(p->remoteFlags + p->rank, p->put);
+    peerSignalKernel<<<1, 1, 0, s>>>((role == 1 ? p->remoteFlags : p->flags) + p->rank, 8u * p->put);
 }
 
 extern "C" {
@@ -102,7 +122,7 @@ int b200pt_peer_export(b200pt_ctx* c, const LaunchParams* params, int rank, int 
     CUDA_OK(cudaMemset(p->flags, 0, PEER_FLAG_WORDS * sizeof(unsigned)));      // a new export starts a new epoch count: every rank attaches again
     CUDA_OK(cudaMemset(p->err, 0, sizeof(unsigned)));
     peerUnmap(c);                                                              // (a context is either the root of a partition or attached to one)
-    p->exported = true;  p->acquired = 0;  p->released = 0;  p->W = c->W;  p->H = c->H;  p->rank = rank;  p->nranks = nranks;
+    p->exported = true;  p->acquired = 0;  p->released = 0;  p->put = 0;  p->W = c->W;  p->H = c->H;  p->rank = rank;  p->nranks = nranks;
     PeerHandle h;
     memset(&h, 0, sizeof(h));
     h.magic = PEER_MAGIC;  h.device = c->device;  h.pid = (long long)getpid();  h.W = c->W;  h.H = c->H;
@@ -168,7 +188,7 @@ int b200pt_peer_acquire(b200pt_ctx* c) {
     enterCtx(c);                                                               // stream-level join: root's own bands of this frame are behind the primary stream too
     PeerState* p = c->peer;
     ++p->acquired;
-    peerWaitKernel<<<1, PEER_MAX_RANKS, 0, c->stream>>>(p->flags, 0, p->nranks, p->rank, p->acquired, p->timeoutNs, p->err, 1u);
+    peerWaitKernel<<<1, PEER_MAX_RANKS, 0, c->stream>>>(p->flags, 0, p->nranks, p->rank, 8u * p->acquired, p->timeoutNs, p->err, 1u);
     CUDA_OK(cudaGetLastError());
     API_END
 }
@@ -181,7 +201,7 @@ int b200pt_peer_release(b200pt_ctx* c) {
     PeerState* p = c->peer;
     if (p->released == p->acquired) throw std::runtime_error("b200pt_peer_release: no acquired frame to release");
     ++p->released;
-    peerSignalKernel<<<1, 1, 0, c->stream>>>(p->flags + PEER_ACK, p->released);   // behind whatever the caller enqueued on the primary stream since the acquire
+    peerSignalKernel<<<1, 1, 0, c->stream>>>(p->flags + PEER_ACK, 8u * p->released);   // behind whatever the caller enqueued on the primary stream since the acquire
     CUDA_OK(cudaGetLastError());
     API_END
 }

@@ -301,12 +301,17 @@ static void enqueueFinalize(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& j
     // one-sided tile split (api_peer.inl): this rank's bands of the RGBA8 frame are written by finalizeKernel straight into root's frame buffer over
     // NVLink, once root has consumed the previous frame; a one-thread kernel behind the passes tells root that they have landed
     FrameParams F = job.F;
-    const bool put = peerPutBegin(c, cfg, F, s);
+    const int role = peerPutBegin(c, cfg, F, s);
+    int nLive = 0, done = 0;
+    for (auto& p : job.passes) nLive += p.nLaunch ? 1 : 0;
     for (auto& p : job.passes) {                                                 // pass order = the reference's launch order (overwrite semantics)
         if (!p.nLaunch) continue;
         launchFinalize(F, p.P, L.sumRad.p, L.sumAlpha.p, L.sumNormal.p, L.sumAlbedo.p, job.fused, s);  ++job.launches;
+        // several passes (the foveated schedule) written by several ranks into ONE frame: pass k + 1 of any rank may overwrite pass k of another, so every
+        // rank waits here until all of them have finished pass k (epoch flags in root's memory; nothing synchronises with a host)
+        if (role && ++done < nLive) peerPassBarrier(c, role, done, s);
     }
-    if (put) peerPutEnd(c, s);
+    if (role) peerPutEnd(c, role, s);
     T.end(b);
     T.end(job.totalEnd, false);
     CUDA_OK(cudaGetLastError());

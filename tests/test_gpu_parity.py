@@ -1058,3 +1058,43 @@ def test_sum_mode_blocking_render_with_speculation_is_bit_identical(sponza_small
     for k, (a, b) in enumerate(zip(got, want)):
         assert np.array_equal(a.view(np.uint32), b.view(np.uint32)), f"call {k}"
     assert np.array_equal(got_px, want_px)
+
+
+def test_one_sided_tile_split_foveated_pass_barriers(sponza_small):
+    """The sv4 foveated schedule (three passes, a later pass overwrites pixels of an earlier one) split over two contexts that write ONE frame: every rank
+    waits after pass k until all ranks have finished pass k (epoch flags in the exporting context's memory), so the frame root acquires equals the unsplit
+    frame byte for byte.  Gaze moves every frame and subframe_index stays 0 (the interactive mode: the frame does not read the accumulation buffer)."""
+    probe = analytic_sky(128, 64)
+    cam = preset_camera("sponza")
+    W, H = 256, 160
+    gazes = ((128, 80), (100, 70), (150, 90))                 # every ring inside the frame: no border-clamp write races
+
+    def fov(rank, count):
+        cfg = preset("sv4_fov", inner_radius=20, outer_radius=60, tile_rank=rank, tile_count=count)
+        r = make_renderer(sponza_small, probe, (W, H), cam, cfg)
+        r.clearAccum()
+        return r
+
+    def shoot(r, gaze):
+        r.launchParams.frame.c.x, r.launchParams.frame.c.y = gaze
+        r.launchParams.frame.subframe_index = 0
+        r.render(sync=False)
+
+    full = fov(0, 1)
+    want = []
+    for g in gazes:
+        shoot(full, g)
+        want.append(full.downloadPixels().copy())
+    full.close()
+    a, b = fov(0, 2), fov(1, 2)
+    b.peerAttach(a.peerExport(0, 2), 1, 2)
+    for k, g in enumerate(gazes):
+        shoot(b, g)
+        shoot(a, g)
+        a.peerAcquire()
+        got = a.downloadPixels().copy()
+        a.peerRelease()
+        assert np.array_equal(got, want[k]), f"frame {k}: {(got != want[k]).sum()} pixels differ"
+    assert a.peerStatus()["state"] == 0 and b.peerStatus()["state"] == 0
+    a.close()
+    b.close()

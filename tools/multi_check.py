@@ -5,7 +5,8 @@
     the same sub-frames up to fp32 summation order, and the tone-mapped frame to 1/255;
   * tile split: rank r renders bands b % N == r of ONE sub-frame, b200pt_gather_bands -> frame and accumulation buffer on rank 0 bit-identical to
     the single-GPU frame;
-  * one-sided tile split (b200pt_peer_*): the same partition with the other ranks' finalize passes writing into rank 0's frame over NVLink.
+  * one-sided tile split (b200pt_peer_*): the same partition with the other ranks' finalize passes writing into rank 0's frame over NVLink;
+  * the same for the three-pass foveated schedule at 3840x2160 (pass barriers between the ranks), with its frame time against one GPU.
 torch.distributed only carries the 128-byte NCCL unique id (and the final verdict); the collectives are the library's own."""
 import os
 import sys
@@ -148,6 +149,82 @@ def main():
             p_ok &= bool(np.array_equal(frames[f], one.downloadPixels()))
         print(f"one-sided tile split over {world} ranks: 4 progressive frames byte-identical to one GPU: {p_ok}, status {st}", flush=True)
         ok &= p_ok
+        one.close()
+    flag = torch.tensor([1 if st["state"] == 0 else 0], device="cuda")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    ok &= bool(int(flag.item()))
+    dist.barrier()
+    r.close()
+
+    # ---- the foveated schedule (three passes, later passes overwrite earlier ones) split one-sided: pass barriers between the ranks.  3840x2160, the
+    # gaze moves every frame, subframe_index 0 (the reference's interactive mode); byte-identical to one GPU, and timed (device, max over ranks)
+    W4, H4 = 3840, 2160
+    fcfg = preset("sv4_fov")
+    fcfg.tile_rank, fcfg.tile_count = rank, world
+    r = SampleRenderer(model, device=local, config=fcfg)
+    r.resize((W4, H4))
+    r.setCamera(cam)
+    r.setProbe(probe)
+    r.clearAccum()
+    h = torch.from_numpy(r.peerExport(0, world).copy()).cuda() if rank == 0 else torch.zeros(192, dtype=torch.uint8, device="cuda")
+    dist.broadcast(h, src=0)
+    if rank != 0:
+        r.peerAttach(h.cpu().numpy(), rank, world)
+    _, _, sp = r.deviceBuffers()
+    stream = torch.cuda.ExternalStream(sp, device=local)
+    gazes = [(1920 + 37 * k, 1080 + 23 * k) for k in range(20)]
+    got, ms = [], 0.0
+    for k, g in enumerate(gazes):
+        r.launchParams.frame.c.x, r.launchParams.frame.c.y = g
+        r.launchParams.frame.subframe_index = 0
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        r.render(sync=False)
+        if rank == 0:
+            r.peerAcquire()
+        else:
+            r.join()
+        e1.record(stream)
+        r.synchronize()
+        torch.cuda.synchronize()
+        if k >= 4:
+            ms += e0.elapsed_time(e1)
+        if rank == 0:
+            if k < 3:
+                got.append(r.downloadPixels().copy())
+            r.peerRelease()
+    t = torch.tensor([ms / (len(gazes) - 4)], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    st = r.peerStatus()
+    if rank == 0:
+        one = SampleRenderer(model, device=local, config=preset("sv4_fov"))
+        one.resize((W4, H4))
+        one.setCamera(cam)
+        one.setProbe(probe)
+        f_ok, one_ms = True, 0.0
+        _, _, sp1 = one.deviceBuffers()
+        s1 = torch.cuda.ExternalStream(sp1, device=local)
+        for k, g in enumerate(gazes):
+            one.launchParams.frame.c.x, one.launchParams.frame.c.y = g
+            one.launchParams.frame.subframe_index = 0
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(s1)
+            one.render(sync=False)
+            one.join()
+            e1.record(s1)
+            one.synchronize()
+            torch.cuda.synchronize()
+            if k >= 4:
+                one_ms += e0.elapsed_time(e1)
+            if k < 3:
+                f_ok &= bool(np.array_equal(got[k], one.downloadPixels()))
+        one_ms /= len(gazes) - 4
+        print(f"one-sided FOVEATED tile split over {world} ranks (3840x2160, sv4 preset, gaze moves every frame): 3 frames byte-identical to one GPU: {f_ok}; "
+              f"{float(t.item()):.3f} ms per frame against {one_ms:.3f} ms on one GPU ({one_ms / float(t.item()):.2f}x), status {st}", flush=True)
+        ok &= f_ok
         one.close()
     flag = torch.tensor([1 if st["state"] == 0 else 0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
