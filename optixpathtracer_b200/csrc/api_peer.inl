@@ -8,6 +8,8 @@
 // ld.acquire.sys), consumes the frame (download, display), and hands the buffer back with b200pt_peer_release; a rank's next finalize waits for
 // that acknowledgement, so a fast rank never overwrites a frame root is still reading.  No NCCL, no staging copy, no host synchronisation; every spin
 // gives up after a time-out (B200PT_PEER_TIMEOUT_MS, default 5000) and records which wait failed (b200pt_peer_status).
+// Frames with several finalize passes (the foveated schedule: later passes overwrite earlier ones) add a barrier between the passes through the same flags:
+// every rank, root included, publishes "pass k done" and waits for all the others before its pass k + 1 may write.
 // The reference has no counterpart (sv4/main.cpp:289-290); pixels are the same bytes b200pt_gather_bands delivers.
 #include <unistd.h>
 
