@@ -211,8 +211,9 @@ int b200pt_gather_bands(b200pt_ctx* ctx, const struct LaunchParams* params, int 
  *   every frame:        all ranks b200pt_render[_async] with cfg.tile_rank / tile_count;
  *                       root: b200pt_peer_acquire (primary stream waits until every rank's bands of this frame have landed), consume the frame
  *                       (b200pt_download_pixels...), b200pt_peer_release (the ranks' next finalize pass waits for it: no frame is overwritten early)
+ * Epochs count frames: after the export / attach every rank must render the same sequence of tile-split frames (as any frame partition requires).
  * Nothing synchronises with the host.  A wait that sees no progress for B200PT_PEER_TIMEOUT_MS (environment, default 5000) gives up and records
- * its code (b200pt_peer_status: 0 = fine, 1 + r = root timed out waiting for rank r, 1000 + 64 = a rank timed out waiting for root's release).
+ * its code (b200pt_peer_status: 0 = fine, 1 + r = root timed out waiting for rank r, 1000 + 64 = a rank timed out waiting for root's release, 2000 + r = a pass barrier timed out waiting for rank r).
  * Schedules with several passes (the foveated presets: a later pass overwrites pixels of an earlier one) work too: the partition is by 32-row bands of
  * every pass's launch rows (each rank gets an equal share of fovea, mid ring and periphery), and between two passes every rank publishes "pass k done"
  * and waits for all the others (the same flag block), so the overwrite order of a single GPU is kept; such a frame is byte-identical to one GPU when it
