@@ -37,6 +37,7 @@ struct Lane {
     DevBuf<float4> sumRad, sumAlpha, sumNormal, sumAlbedo;
     DevBuf<TraceStats> stats;           // [0] closest, [1] any
     cudaEvent_t done = nullptr;         // recorded after the last kernel of the lane's latest frame
+    cudaEvent_t headStart = nullptr;    // recorded behind pass B200PT_STAGGER of the lane's latest wavefront: the next wavefront (on another lane) starts behind it
     bool busy = false;                  // has work the primary stream has not been ordered after yet
     bool forked = false;                // already ordered after the primary stream's earlier work (since the last join)
     void release() {
@@ -101,6 +102,8 @@ struct b200pt_ctx {
     DevBuf<float> probeData, probePdfX, probeCdfX, probePdfY, probeCdfY, probeRowTotal;  DevBuf<int> probeGuide;  int probeW = 0, probeH = 0;
     // --- wavefront state: one Lane per frame in flight (lane 0 runs on `stream`, the reference's single stream)
     Lane lanes[B200PT_MAX_LANES];
+    int wavePrevLane = -1;              // lane of the most recently enqueued WAVEFRONT (speculative ones included): the next one is staggered behind it
+    bool staggerWaves = false;          // set by the blocking render() around its enqueues: batches submitted with b200pt_render_async are not held back
     int lastLane = -1;                  // lane of the most recently enqueued frame (its `done` event orders the next frame's accumulation)
     int countersLane = 0;               // lane whose device counters `last` will be read from ...
     std::vector<int> countersExtra;     // ... plus the lanes of the other parts of a split frame
@@ -217,6 +220,7 @@ void b200pt_destroy(b200pt_ctx* c) {
         if (L.stream) cudaStreamSynchronize(L.stream);
         L.release();
         if (L.done) cudaEventDestroy(L.done);
+        if (L.headStart) cudaEventDestroy(L.headStart);
         if (k > 0 && L.stream) cudaStreamDestroy(L.stream);
     }
     if (c->forkEv) cudaEventDestroy(c->forkEv);

@@ -234,6 +234,17 @@ static void enqueuePart(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& job, 
     const int bounces = cfg.max_depth + ((c->hasCatcher || cfg.max_depth == 0) ? 1 : 0) + (c->hasCatcher ? std::max(B200PT_CATCHER_EXTRA_LAUNCHES, cfg.max_depth + 1) : 0);
     const int cullBack = cfg.shadow_mode == B200PT_SHADOW_CULL_BACK;
     const float shadowTmin = cfg.shadow_tmin > 0.f ? cfg.shadow_tmin : cfg.tmin;
+    // Frames in flight are kept staggered: this wavefront starts only when the wavefront enqueued just before it (on another lane) has finished its pass
+    // `stagger`.  Left alone, the kernels of concurrent frames are dispatched in launch order, the younger frames catch up with the oldest and all of them finish
+    // together: a blocking caller then waits ~3 frame times for one call in three (9.3 / 0.3 / 0.4 ms at 1080p) and a run that stops pays for the frames it
+    // never asks for.  With the head start the oldest frame stays ahead and the calls return at an even pace (3.2 / 3.9 / 2.8 ms) at 99 % of the throughput
+    // (measured: 2 passes; 3 evens the calls out completely but costs 3 %, holding EVERY pass back costs 1.5-3 %).  Only the blocking render() asks for it
+    // (c->staggerWaves): a batch submitted with b200pt_render_async has nobody waiting for single frames.  B200PT_STAGGER=0: off.
+    static const int stagger = [] { const char* e = getenv("B200PT_STAGGER");  return e ? atoi(e) : 2; }();
+    const bool wholeFrame = nParts == 1 && groups.size() == 1 && laneIdx > 0;
+    if (stagger > 0 && c->staggerWaves && wholeFrame && c->wavePrevLane > 0 && c->wavePrevLane != laneIdx && c->lanes[c->wavePrevLane].headStart)
+        CUDA_OK(cudaStreamWaitEvent(s, c->lanes[c->wavePrevLane].headStart, 0));
+    if (wholeFrame && !L.headStart) CUDA_OK(cudaEventCreateWithFlags(&L.headStart, cudaEventDisableTiming));
     for (auto& group : groups) {
         if (group.empty()) continue;
         T.begin(ST_RAYGEN, a, b);
@@ -248,10 +259,11 @@ static void enqueuePart(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& job, 
             T.begin(d < bounces ? ST_TRACE : ST_TRACE_TAIL, a, b);
             launchTrace(S, Q, cur, d < bounces ? 1 : 0, Q.counters + QC_STRIDE * d, cfg.tmin, shadowTmin, cfg.tmax, cullBack, pool, count ? L.stats.p : nullptr, s);
             T.end(b);  ++launches;  ++job.nClosest;
-            if (d == bounces) break;
+            if (d == bounces) { if (wholeFrame && d <= stagger) CUDA_OK(cudaEventRecord(L.headStart, s));  break; }
             T.begin(ST_SHADE, a, b);
             launchShade(F, S, pool, Q, cur, d, s);
             T.end(b);  ++launches;
+            if (wholeFrame && d == stagger) CUDA_OK(cudaEventRecord(L.headStart, s));
             cur ^= 1;
         }
         tallyCountersKernel<<<1, 32, 0, s>>>(Q.counters, bounces + 1, totals);  ++launches;
@@ -264,6 +276,7 @@ static void enqueuePart(b200pt_ctx* c, const b200pt_config& cfg, FrameJob& job, 
         T.end(b);
     }
     CUDA_OK(cudaGetLastError());
+    if (part == 0) c->wavePrevLane = wholeFrame ? laneIdx : -1;
 }
 
 // Enqueues one frame's wavefront on `lanes` (one lane: the whole frame; several: the frame split into that many band sets).  `params` is mutated
@@ -357,6 +370,7 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
     }
 
     // ---- blocking call with lanes to spare: consume the oldest speculative wavefront if this call is the one that was predicted
+    struct StaggerScope { b200pt_ctx* c;  explicit StaggerScope(b200pt_ctx* c_) : c(c_) { c->staggerWaves = true; }  ~StaggerScope() { c->staggerWaves = false; } } staggerScope(c);
     const unsigned thisIndex = params->frame.subframe_index;
     // "the previous call again, apart from subframe_index" (progressive accumulation) / "... and with exactly the predicted index"
     bool sameButIndex = false;
