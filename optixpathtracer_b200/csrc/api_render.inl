@@ -370,7 +370,10 @@ static void renderImpl(b200pt_ctx* c, LaunchParams* params, const b200pt_config*
     }
 
     // ---- blocking call with lanes to spare: consume the oldest speculative wavefront if this call is the one that was predicted
-    struct StaggerScope { b200pt_ctx* c;  explicit StaggerScope(b200pt_ctx* c_) : c(c_) { c->staggerWaves = true; }  ~StaggerScope() { c->staggerWaves = false; } } staggerScope(c);
+    // (not in ACCUM_SUM mode: a frame of a sample split is a partial sum nobody looks at on its own, and the collective that follows every call competes with
+    // the wavefronts for the GPU - measured on 2 x B200: e2e 1163 without the head start, 1122 with it)
+    struct StaggerScope { b200pt_ctx* c;  StaggerScope(b200pt_ctx* c_, bool on) : c(c_) { c->staggerWaves = on; }  ~StaggerScope() { c->staggerWaves = false; } }
+        staggerScope(c, cfg.accum_mode != B200PT_ACCUM_SUM);
     const unsigned thisIndex = params->frame.subframe_index;
     // "the previous call again, apart from subframe_index" (progressive accumulation) / "... and with exactly the predicted index"
     bool sameButIndex = false;
