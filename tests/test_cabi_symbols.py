@@ -61,3 +61,18 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".inl", ".cpp", ".h")):
                 src = open(os.path.join(dirpath, f), errors="replace").read()
                 assert not re.search(r"^\s*(from|import)\s+oracle|#include\s+[\"<].*oracle/", src, flags=re.M), f
+
+
+def test_header_constants_match_python_twin():
+    """Sizes the Python mirror hard-codes must be the ones include/b200pt.h declares (handle of the one-sided tile split, NCCL id, no-alloc scratch)."""
+    import re
+    from optixpathtracer_b200.renderer import SampleRenderer
+    from optixpathtracer_b200.structs import NOALLOC_MAX_ROWS
+    text = open(os.path.join(ROOT, "include", "b200pt.h")).read()
+
+    def const(name):
+        return int(re.search(rf"#define\s+{name}\s+(\d+)", text).group(1))
+
+    assert const("B200PT_PEER_HANDLE_BYTES") == SampleRenderer.PEER_HANDLE_BYTES == 192
+    assert const("B200PT_UNIQUE_ID_BYTES") == 128
+    assert const("B200PT_NOALLOC_MAX_ROWS") == NOALLOC_MAX_ROWS
